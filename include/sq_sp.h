@@ -1,0 +1,107 @@
+/*
+ * sq_sp.h -- C ABI of the B200 shortest-path library (HP-2).
+ *
+ * Part 1 is the drop-in surface: the ten symbols the reference's `sp` library exports from
+ * projects/bolinas_civic/sp/src/py.cc:6-88 and that projects/bolinas_civic/sp/interface.py:12-67 binds with
+ * ctypes.  Names, argument order, argument meaning and return conventions are the reference's; the
+ * work behind `dijkstra` runs on the GPU (one near-far SSSP tree per CTA, f64).
+ *
+ * Part 2 is additive: batched trees (one tree per origin), device-resident variants that take
+ * plain device pointers (no torch types), weight upload, and tuning knobs.
+ *
+ * All functions are `extern "C"`, take plain pointers and sizes, and never throw across the
+ * boundary.  There is no CPU fallback: every compute entry point returns an error (or aborts with a
+ * message for the reference-shaped calls that have no error channel) when no CUDA device is usable.
+ */
+#ifndef SQ_SP_H_
+#define SQ_SP_H_
+
+#include <stdbool.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct SqGraph Graph;               /* opaque; reference: class Graph, sp/include/graph.h:57 */
+typedef struct SqShortestPath ShortestPath; /* opaque; reference: struct ShortestPath, sp/include/graph.h:20 */
+
+/* ---- Part 1: reference-compatible surface (sp/src/py.cc) ------------------------------------ */
+
+/* py.cc:11-15  toy graph of graph.cc:121-135 (7 vertices, 11 edges). */
+Graph* simplegraph(bool directed);
+/* py.cc:21-25  MatrixMarket reader, graph.cc:55-97 (first data line is the header; nvertices = n+1). */
+Graph* readgraph(char* filename, bool directed);
+/* py.cc:36-41  COO edge list; `nvertices` is the maximum vertex id (graph.cc:141 adds one). */
+Graph* creategraph(int* edge_starts, int* edge_ends, double* edge_wghs, int nedges, int nvertices,
+                   bool directed);
+/* py.cc:46-48  MatrixMarket writer, graph.cc:100-119 (unique (v1,v2) keys in key order). */
+bool writegraph(Graph* graph, char* filename);
+/* py.cc:54-56  one tree from `origin`; destination -1 = all.  The GPU always settles the whole
+ * tree, which is a superset of the reference's early-exit result (graph.cc:196).  Invalid ids give
+ * a tree with no distances (graph.cc:161-163). */
+ShortestPath* dijkstra(Graph* graph, int origin, int destination);
+/* py.cc:63-65  set the weight of edge (vertex1, vertex2).  A missing edge aborts the reference
+ * (std::out_of_range across the C boundary); here it is ignored and counted (sp_last_error). */
+void update_edge(Graph* graph, int vertex1, int vertex2, double weight);
+/* py.cc:69 */
+int origin(ShortestPath* sp);
+/* py.cc:74-77  DBL_MAX when the tree is empty or the vertex is unreachable. */
+double distance(ShortestPath* sp, int destination);
+/* py.cc:80 */
+void clear(ShortestPath* sp);
+/* py.cc:85-87  -1 for the origin and for unreachable vertices.  Out-of-range ids return -1
+ * (the reference throws). */
+int parent(ShortestPath* sp, int destination);
+
+/* ---- Part 2: additive surface ------------------------------------------------------------------ */
+
+/* Graph::remove_edge (graph.cc:40-52) is public C++ in the reference but not exported; exported
+ * here so the reference's own known-answer test (sp/tests/graph_test.cc:47-64, 95-103) can be
+ * replayed through the C ABI.  Removes the edge currently mapped at key (v1,v2) (after the
+ * undirected swap).  Returns 0 on success, -1 if absent. */
+int sp_remove_edge(Graph* graph, int vertex1, int vertex2);
+void sp_free_graph(Graph* graph);
+int sp_nvertices(Graph* graph);
+int sp_nedges(Graph* graph); /* adjacency entries (duplicates included) */
+
+/* One full tree per origin.  Host buffers: dist_out[n][V] (f64, DBL_MAX = unreachable) and
+ * parent_out[n][V] (i32, -1 = none); either may be NULL.  Predecessors follow the canonical rule
+ * parent[v] = min{u : fl(dist[u] + w(u,v)) == dist[v]}.  Returns 0, or a negative error code. */
+int sp_sssp_batch(Graph* graph, const int* origins, int n, double* dist_out, int* parent_out);
+
+/* Same with device pointers (CUDA device memory owned by the caller, e.g. a torch tensor's
+ * data_ptr()); `stream` is a cudaStream_t passed as void* (NULL = default stream).  Asynchronous
+ * with respect to the host.  Either output may be NULL (the tree is then kept in library scratch
+ * only and just timed). */
+int sp_sssp_batch_device(Graph* graph, const int* origins_dev, int n, double* dist_dev,
+                         int* parent_dev, void* stream);
+
+/* Bulk weight refresh, one weight per edge in insertion order (creategraph order); replaces n calls
+ * to update_edge (queue_class.py:463-466 is called once per link every 100 ticks). */
+int sp_set_weights(Graph* graph, const double* weights, int nedges);
+
+/* Push pending host-side edits (update_edge / sp_set_weights / structure) to the device now.
+ * Called implicitly by every compute entry point. */
+int sp_sync(Graph* graph);
+
+/* Tuning knobs for the tree kernel: threads per CTA (128..1024, multiple of 32), CTAs per SM
+ * (0 = fill shared memory), delta = delta_factor x mean finite edge weight (<=0 keeps current),
+ * shared-memory queue slots per queue (0 = default). */
+int sp_set_tuning(Graph* graph, int threads, int ctas_per_sm, double delta_factor, int smem_queue);
+
+/* Statistics of the last batch: [0] trees, [1] rounds, [2] relaxations, [3] bucket transitions,
+ * [4] queue overflows into global scratch.  Filled only when stats were enabled at build time
+ * (SQ_SSSP_STATS); otherwise zeros. */
+int sp_last_stats(Graph* graph, long long* out5);
+
+/* Last error text of the calling thread ("" if none). */
+const char* sp_last_error(void);
+
+/* Number of CUDA kernels this library has launched in this process (for bench gpu_launches). */
+long long sp_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SQ_SP_H_ */

@@ -1,0 +1,58 @@
+"""ctypes loader of the product library.  No fallback: a missing library or GPU is an error."""
+import ctypes as C
+import os
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libsqb200.so")
+_lib = None
+
+
+class B200LibraryError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libsqb200.so (built by spatial_queue_b200.build / __graft_entry__.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B200LibraryError(
+                f"{LIB_PATH} is missing: run `python -m spatial_queue_b200.build` (needs nvcc). "
+                "There is no CPU fallback for the tick or the SSSP path.")
+        L = C.CDLL(LIB_PATH)
+        _declare(L)
+        _lib = L
+    return _lib
+
+
+def _declare(L):
+    vp, ci, cd, cb = C.c_void_p, C.c_int, C.c_double, C.c_bool
+    # ---- sp surface (include/sq_sp.h part 1) ----
+    L.simplegraph.restype = vp; L.simplegraph.argtypes = [cb]
+    L.readgraph.restype = vp; L.readgraph.argtypes = [C.c_char_p, cb]
+    L.creategraph.restype = vp; L.creategraph.argtypes = [vp, vp, vp, ci, ci, cb]
+    L.writegraph.restype = cb; L.writegraph.argtypes = [vp, C.c_char_p]
+    L.dijkstra.restype = vp; L.dijkstra.argtypes = [vp, ci, ci]
+    L.update_edge.restype = None; L.update_edge.argtypes = [vp, ci, ci, cd]
+    L.origin.restype = ci; L.origin.argtypes = [vp]
+    L.distance.restype = cd; L.distance.argtypes = [vp, ci]
+    L.clear.restype = None; L.clear.argtypes = [vp]
+    L.parent.restype = ci; L.parent.argtypes = [vp, ci]
+    # ---- additive ----
+    L.sp_remove_edge.restype = ci; L.sp_remove_edge.argtypes = [vp, ci, ci]
+    L.sp_free_graph.restype = None; L.sp_free_graph.argtypes = [vp]
+    L.sp_nvertices.restype = ci; L.sp_nvertices.argtypes = [vp]
+    L.sp_nedges.restype = ci; L.sp_nedges.argtypes = [vp]
+    L.sp_sssp_batch.restype = ci; L.sp_sssp_batch.argtypes = [vp, vp, ci, vp, vp]
+    L.sp_sssp_batch_device.restype = ci; L.sp_sssp_batch_device.argtypes = [vp, vp, ci, vp, vp, vp]
+    L.sp_set_weights.restype = ci; L.sp_set_weights.argtypes = [vp, vp, ci]
+    L.sp_sync.restype = ci; L.sp_sync.argtypes = [vp]
+    L.sp_set_tuning.restype = ci; L.sp_set_tuning.argtypes = [vp, ci, ci, cd, ci]
+    L.sp_last_stats.restype = ci; L.sp_last_stats.argtypes = [vp, vp]
+    L.sp_last_error.restype = C.c_char_p; L.sp_last_error.argtypes = []
+    L.sp_kernel_launches.restype = C.c_longlong; L.sp_kernel_launches.argtypes = []
+
+
+def check(rc, what="call"):
+    if rc != 0:
+        raise B200LibraryError(f"{what} failed ({rc}): {lib().sp_last_error().decode()}")

@@ -1,0 +1,161 @@
+"""Host-side mirror of the reference's `sp/interface.py` on top of the B200 library.
+
+Same names, argument meaning and return conventions as projects/bolinas_civic/sp/interface.py:15-67
+(`ShortestPath.origin/distance/parent/route/clear`, `Graph.dijkstra/update_edge/writegraph`,
+`simplegraph`, `readgraph`, `from_dataframe`), so `queue_class.py` can bind to it unchanged
+(`from sp import interface` -> `from spatial_queue_b200 import sp_interface as interface`).
+
+Additive: `Graph.sssp_batch` (one tree per origin, host arrays), `Graph.sssp_batch_device` (torch CUDA
+tensors handed over as raw device pointers), `Graph.set_weights`, `Graph.remove_edge`.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import lib, check
+
+DBL_MAX = np.finfo(np.float64).max
+
+
+class ShortestPath:
+    """One shortest-path tree (reference: interface.py:15-32, struct ShortestPath in sp/include/graph.h:20-53)."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    @property
+    def origin(self):
+        return lib().origin(self._h)
+
+    def distance(self, destination):
+        return lib().distance(self._h, int(destination))
+
+    def parent(self, destination):
+        return lib().parent(self._h, int(destination))
+
+    def route(self, destination):
+        """Yield (parent, node) hops from the origin to `destination` (interface.py:26-30).
+
+        The reference recurses once per hop (and dies past ~990 hops); this walks iteratively and is bounded by
+        the vertex count, so a broken predecessor chain cannot loop forever."""
+        origin = self.origin
+        hops = []
+        node = int(destination)
+        limit = 1 << 31
+        while node != origin:
+            par = self.parent(node)
+            if par < 0:
+                raise KeyError(f"vertex {node} has no predecessor towards origin {origin}")
+            hops.append((par, node))
+            node = par
+            limit -= 1
+            if limit <= 0 or len(hops) > 50_000_000:
+                raise RuntimeError("predecessor chain does not terminate")
+        return iter(reversed(hops))
+
+    def clear(self):
+        if self._h:
+            lib().clear(self._h)
+            self._h = None
+
+
+class Graph:
+    """Reference: interface.py:36-42 (class Graph) over sp/src/py.cc."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    # -- reference surface --
+    def dijkstra(self, origin, destination):
+        return ShortestPath(lib().dijkstra(self._h, int(origin), int(destination)))
+
+    def update_edge(self, origin, destination, weight):
+        w = weight.value if isinstance(weight, C.c_double) else float(weight)
+        return lib().update_edge(self._h, int(origin), int(destination), w)
+
+    def writegraph(self, filename):
+        if isinstance(filename, str):
+            filename = filename.encode()
+        return lib().writegraph(self._h, filename)
+
+    # -- additive --
+    @property
+    def nvertices(self):
+        return lib().sp_nvertices(self._h)
+
+    @property
+    def nedges(self):
+        return lib().sp_nedges(self._h)
+
+    def remove_edge(self, v1, v2):
+        check(lib().sp_remove_edge(self._h, int(v1), int(v2)), "remove_edge")
+
+    def set_weights(self, weights):
+        w = np.ascontiguousarray(weights, dtype=np.float64)
+        check(lib().sp_set_weights(self._h, w.ctypes.data, len(w)), "sp_set_weights")
+
+    def set_tuning(self, threads=0, ctas_per_sm=-1, delta_factor=0.0, smem_queue=-1):
+        check(lib().sp_set_tuning(self._h, threads, ctas_per_sm, float(delta_factor), smem_queue), "sp_set_tuning")
+
+    def sync(self):
+        check(lib().sp_sync(self._h), "sp_sync")
+
+    def sssp_batch(self, origins, want_dist=True, want_parent=True):
+        """Full trees for `origins` -> (dist f64[n,V] or None, parent i32[n,V] or None), host arrays."""
+        o = np.ascontiguousarray(origins, dtype=np.int32)
+        V = self.nvertices
+        d = np.empty((len(o), V), dtype=np.float64) if want_dist else None
+        p = np.empty((len(o), V), dtype=np.int32) if want_parent else None
+        check(lib().sp_sssp_batch(self._h, o.ctypes.data, len(o),
+                                  d.ctypes.data if want_dist else None,
+                                  p.ctypes.data if want_parent else None), "sp_sssp_batch")
+        return d, p
+
+    def sssp_batch_device(self, origins_dev, dist_dev=None, parent_dev=None, stream=None):
+        """Device-resident batch.  Arguments are torch CUDA tensors (int32 origins [n]; float64 dist [n,V];
+        int32 parent [n,V]); only their data pointers cross the C ABI.  Asynchronous on `stream`."""
+        n = int(origins_dev.numel())
+        sp = C.c_void_p(stream.cuda_stream) if stream is not None else None
+        if stream is None:
+            import torch
+            sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(lib().sp_sssp_batch_device(self._h, C.c_void_p(origins_dev.data_ptr()), n,
+                                         C.c_void_p(dist_dev.data_ptr()) if dist_dev is not None else None,
+                                         C.c_void_p(parent_dev.data_ptr()) if parent_dev is not None else None,
+                                         sp), "sp_sssp_batch_device")
+
+    def last_stats(self):
+        out = (C.c_longlong * 5)()
+        lib().sp_last_stats(self._h, out)
+        return dict(zip(("trees", "rounds", "relaxations", "transitions", "overflows"), list(out)))
+
+    def free(self):
+        if self._h:
+            lib().sp_free_graph(self._h)
+            self._h = None
+
+
+def simplegraph(directed=True):
+    return Graph(lib().simplegraph(bool(directed)))
+
+
+def readgraph(filename, directed=True):
+    if isinstance(filename, str):
+        filename = filename.encode()
+    return Graph(lib().readgraph(filename, bool(directed)))
+
+
+def from_arrays(starts, ends, weights, max_vertex_id=None, directed=True):
+    s = np.ascontiguousarray(starts, dtype=np.int32)
+    e = np.ascontiguousarray(ends, dtype=np.int32)
+    w = np.ascontiguousarray(weights, dtype=np.float64)
+    if max_vertex_id is None:
+        max_vertex_id = int(max(s.max(), e.max()))
+    return Graph(lib().creategraph(s.ctypes.data, e.ctypes.data, w.ctypes.data, len(s), int(max_vertex_id), bool(directed)))
+
+
+def from_dataframe(edges=None, start_node_col=None, end_node_col=None, weight_col=None, directed=True):
+    """interface.py:59-67: edge count from the frame, vertex count = largest id seen in either column."""
+    return from_arrays(edges[start_node_col].values, edges[end_node_col].values,
+                       np.asarray(edges[weight_col].values, dtype=np.float64),
+                       int(np.max(edges[[start_node_col, end_node_col]].values)), directed)

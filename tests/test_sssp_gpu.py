@@ -1,0 +1,151 @@
+"""GPU parity tests for HP-2: the CUDA tree kernel, called through the C ABI, against the oracle."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import grid_graph
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+DBL_MAX = np.finfo(np.float64).max
+
+
+@pytest.fixture(scope="module")
+def spi():
+    from spatial_queue_b200 import sp_interface
+    return sp_interface
+
+
+def test_known_answers_through_the_abi(spi):
+    # sp/tests/graph_test.cc:31-64 (directed) and :91-103 (undirected), replayed through the C ABI
+    g = spi.simplegraph(True)
+    sp = g.dijkstra(1, 3)
+    assert sp.origin == 1
+    assert sp.distance(3) == pytest.approx(7.2, rel=1e-7)
+    assert [h[1] for h in sp.route(3)] == [2, 4, 3]
+    sp.clear()
+    g.update_edge(1, 3, 3.7)
+    sp = g.dijkstra(1, 3); assert sp.distance(3) == pytest.approx(3.7, rel=1e-7); sp.clear()
+    g = spi.simplegraph(True)
+    g.remove_edge(3, 1)
+    sp = g.dijkstra(1, 3); assert sp.distance(3) == pytest.approx(7.2, rel=1e-7); sp.clear()
+    g.remove_edge(2, 4)
+    sp = g.dijkstra(1, 3); assert sp.distance(3) == pytest.approx(9.1, rel=1e-7); sp.clear()
+    g = spi.simplegraph(False)
+    sp = g.dijkstra(1, 3); assert sp.distance(3) == pytest.approx(5.6, rel=1e-7); sp.clear()
+    g.remove_edge(3, 1)
+    sp = g.dijkstra(1, 3); assert sp.distance(3) == pytest.approx(9.1, rel=1e-7); sp.clear()
+    # bad ids: empty tree, distance() = DBL_MAX (py.cc:74-77)
+    sp = g.dijkstra(99, -1); assert sp.distance(3) == DBL_MAX; sp.clear()
+    # missing edge: ignored, not an abort
+    g.update_edge(5, 1, 1.0)
+
+
+def test_network_mtx_golden(spi):
+    gold = json.load(open(os.path.join(GOLD, "sp_golden.json")))
+    z = np.load(os.path.join(GOLD, "sp_network.npz"))
+    g = spi.from_arrays(z["starts"], z["ends"], z["weights"], max_vertex_id=int(z["header_n"]))
+    assert g.nvertices == gold["network_mtx"]["nvertices"]
+    sp = g.dijkstra(1020, 20)
+    assert sp.distance(20) == 12409.660000000002  # graph_test.cc:127
+    assert float(sp.distance(20)).hex() == gold["one_to_one_1020_20_hex"]
+    sp.clear()
+    origins = [t["origin"] for t in gold["trees"]]
+    d, p = g.sssp_batch(origins)
+    for i, t in enumerate(gold["trees"]):
+        assert hashlib.sha256(d[i].tobytes()).hexdigest() == t["dist_sha256"]
+        assert hashlib.sha256(p[i].tobytes()).hexdigest() == t["canonical_parent_sha256"]
+        assert int((d[i] < 1e300).sum()) == t["reached"]
+
+
+@pytest.mark.parametrize("directed", [True, False])
+@pytest.mark.parametrize("threads,smemq", [(256, 0), (128, 32), (1024, 64)])
+def test_random_graphs_bit_exact(spi, directed, threads, smemq):
+    from oracle import sssp as osssp
+    rng = np.random.default_rng(11 + threads)
+    for trial in range(5):
+        V = int(rng.integers(3, 3000))
+        E = int(rng.integers(1, 6 * V))
+        s = rng.integers(0, V, E).astype(np.int32)
+        e = rng.integers(0, V, E).astype(np.int32)
+        w = np.where(rng.random(E) < 0.05, 1e8, rng.random(E) * 100.0)
+        w = np.where(rng.random(E) < 0.3, np.round(w) + 1.0, w)  # ties, strictly positive
+        og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1, directed=directed)
+        g = spi.from_arrays(s, e, w, max_vertex_id=V - 1, directed=directed)
+        g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
+        origins = np.concatenate([rng.integers(0, V, 7), [-1, V, V + 5]]).astype(np.int32)
+        d, p = g.sssp_batch(origins)
+        do, po = og.sssp_batch(origins)
+        assert d.tobytes() == do.tobytes()
+        assert (p == po).all()
+        g.free()
+
+
+def test_weight_updates_reach_the_device(spi):
+    from oracle import sssp as osssp
+    s, e, w = grid_graph(24, seed=5)
+    g = spi.from_arrays(s, e, w)
+    rng = np.random.default_rng(0)
+    w2 = w.copy()
+    for _ in range(3):
+        idx = rng.choice(len(w), 200, replace=False)
+        w2[idx] = np.where(rng.random(200) < 0.2, 1e8, w[idx] * (1 + 5 * rng.random(200)))
+        for i in idx[:50]:
+            g.update_edge(int(s[i]), int(e[i]), float(w2[i]))
+        if len(idx) > 50:
+            g.set_weights(w2)
+        og = osssp.OracleGraph(s, e, w2)
+        origins = rng.integers(0, 24 * 24, 5).astype(np.int32)
+        d, p = g.sssp_batch(origins)
+        do, po = og.sssp_batch(origins)
+        assert d.tobytes() == do.tobytes() and (p == po).all()
+
+
+def test_grid_batch_and_device_api(spi):
+    import torch
+    from oracle import sssp as osssp
+    n = 64
+    s, e, w = grid_graph(n, seed=1)
+    g = spi.from_arrays(s, e, w)
+    og = osssp.OracleGraph(s, e, w)
+    origins = np.random.default_rng(2).permutation(n * n)[:300].astype(np.int32)
+    o_dev = torch.from_numpy(origins).cuda()
+    d_dev = torch.empty((len(origins), n * n), dtype=torch.float64, device="cuda")
+    p_dev = torch.empty((len(origins), n * n), dtype=torch.int32, device="cuda")
+    g.sssp_batch_device(o_dev, d_dev, p_dev)
+    torch.cuda.synchronize()
+    do, po = og.sssp_batch(origins)
+    assert d_dev.cpu().numpy().tobytes() == do.tobytes()
+    assert (p_dev.cpu().numpy() == po).all()
+
+
+def test_full_size_properties(spi):
+    """BASELINE config 5 size (224x224 grid): fixed-point and tree properties that need no oracle."""
+    n = 224
+    s, e, w = grid_graph(n, seed=1)
+    g = spi.from_arrays(s, e, w)
+    origins = np.array([0, n * n - 1, (n // 2) * n + n // 2, 12345], dtype=np.int32)
+    d, p = g.sssp_batch(origins)
+    for i, o in enumerate(origins):
+        di = d[i]
+        assert di[o] == 0.0 and p[i][o] == -1
+        assert (di < 1e300).all()                       # grid is strongly connected
+        assert (di[e] <= di[s] + w).all()               # no edge can still relax
+        pv = p[i]
+        v = np.arange(n * n)
+        m = v != o
+        # every predecessor is an in-neighbour that attains the distance exactly
+        key = {(int(a), int(b)): float(ww) for a, b, ww in zip(s, e, w)}
+        idx = np.random.default_rng(1).choice(v[m], 2000, replace=False)
+        for vv in idx:
+            u = int(pv[vv])
+            assert di[u] + key[(u, int(vv))] == di[vv]
+        # sum of distances symmetric check: d(o -> x) on the reversed graph equals d(x -> o)
+    # reversed graph trees from x give d(x->o): compare one pair exactly through a second graph
+    gr = spi.from_arrays(e, s, w)
+    dr, _ = gr.sssp_batch(origins[:1])
+    # path costs are summed in opposite orders, so equality is to rounding only
+    assert np.allclose(dr[0][origins[1]], d[1][origins[0]], rtol=1e-12)
