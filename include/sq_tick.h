@@ -1,0 +1,115 @@
+/*
+ * sq_tick.h -- C ABI of the B200 spatial-queue tick (HP-1, SURVEY.md section 8 rows A0-A8, seam B2).
+ *
+ * One call, sq_step(sim, t), replaces what the reference drivers do once per simulated second
+ * (projects/bolinas_civic/run_traffic_simulation.py:111, 52-69):
+ *     for agent in network.agents.values(): agent.load_vehicle(t, ...)          queue_class.py:587-596
+ *     for link  in network.links.values():  link.run_link_model(t, ...)         queue_class.py:445-455
+ *     for node  in {end node of links with a queue}: node.run_node_model(t,...) queue_class.py:226-394
+ * State lives on the GPU between calls (SoA arrays, per-link vehicle rings, per-node turn tables);
+ * the getters below copy it back for the object mirror (spatial_queue_b200/queue_class.py) at
+ * whatever cadence the driver reads it.
+ *
+ * The network description is the flat form of the reference's objects, in the reference's own
+ * iteration orders (spatial_queue_b200/flatten.py).  Indices: real nodes 0..n_nodes-1; links
+ * 0..n_links-1 in network.links order (virtual source links first); agents in network.agents order.
+ *
+ * Randomness: the reference's shuffle / random.choices draws are replaced by the counter-based
+ * contract of spatial_queue_b200/rng.py, keyed on (seed, t, node_key, slot).
+ *
+ * Plain pointers and sizes only; host pointers unless a name ends in _dev.  No CPU fallback.
+ */
+#ifndef SQ_TICK_H_
+#define SQ_TICK_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct SqNetDesc {
+  int32_t n_nodes, n_links, n_agents, reserved0;
+  uint64_t seed;
+  /* ---- links (queue_class.py:396-442) ---- */
+  const int32_t* link_start_node;  /* real node index, -1 for the virtual start of a source link     */
+  const int32_t* link_end_node;
+  const uint8_t* link_is_virtual;  /* link_type == 'v' (queue_class.py:224)                           */
+  const int32_t* link_lanes_floor; /* int(floor(lanes)) (:246, :279)                                  */
+  const double* link_cap_per_s;    /* capacity / 3600 as Python computes it (:454)                    */
+  const double* link_storage_cap;  /* max(18, length * lanes) (:416)                                  */
+  const double* link_fft;          /* free-flow time, s (:54)                                         */
+  const uint8_t* link_closed;      /* status in {closed, burning_closed} (:455)                       */
+  const int32_t* link_reverse;     /* node2link[(end, start)] or -1 (:272)                            */
+  const double* link_capacity;     /* veh/h, for the edge-weight model (:465)                         */
+  const double* link_maxmph;       /* (:411)                                                          */
+  /* ---- nodes (queue_class.py:204-218, 158-176) ---- */
+  const int64_t* node_key;         /* integer node id, RNG key                                        */
+  const uint8_t* node_type;        /* 0 plain, 1 signal, 2 priority (:233-238)                        */
+  const int32_t* node_in_ptr;      /* [n_nodes+1] CSR over incoming_links order                       */
+  const int32_t* node_in_links;
+  const uint8_t* node_in_phase;    /* per in-link: bit0 in phase_1, bit1 in phase_2 (signal nodes)    */
+  const int32_t* node_in_prio;     /* per in-link: rank in the priority list or -1 (priority nodes)   */
+  const int32_t* node_out_ptr;     /* [n_nodes+1] CSR over outgoing_links order                       */
+  const int32_t* node_out_links;
+  const int64_t* node_turn_ptr;    /* [n_nodes+1] offset of the node's indeg x outdeg angle table      */
+  const double* turn_angle;        /* degrees, row = in-link, col = out-link (:169-176)               */
+  /* ---- agents (queue_class.py:478-499) ---- */
+  const int64_t* agent_key;
+  const int32_t* agent_origin;
+  const int32_t* agent_destin;
+  const int32_t* agent_dept;
+  const int32_t* agent_vlen;       /* 8 or 18 (:191)                                                  */
+  const uint8_t* agent_status;     /* 0 unloaded ... (flatten.STATUS_CODES); 3 = shelter_p = inactive */
+  const int64_t* route_ptr;        /* [n_agents+1]                                                    */
+  const int32_t* route_links;      /* link indices from the origin node to the destination           */
+} SqNetDesc;
+
+typedef struct SqSim SqSim;
+
+/* Agent status codes (spatial_queue_b200/flatten.py STATUS_CODES). */
+enum { SQ_UNLOADED = 0, SQ_ENROUTE = 1, SQ_ARRIVE = 2, SQ_SHELTER_P = 3 };
+
+/* Build device state from a network that has not ticked yet.  NULL on failure (sq_last_error). */
+SqSim* sq_create(const SqNetDesc* desc);
+void sq_destroy(SqSim* sim);
+
+/* One simulated second: load + link model + node model for tick t.  Asynchronous; errors detected on
+ * the device (a queued vehicle with no next link away from its destination, queue_class.py:312-314;
+ * a turn that is not in the node's table, :257-262) surface from sq_sync / the getters as SQ_ERR_STATE. */
+int sq_step(SqSim* sim, int32_t t);
+/* n consecutive ticks t0 .. t0+n-1 (replayed as CUDA graphs of tick pairs). */
+int sq_run(SqSim* sim, int32_t t0, int32_t n);
+/* Wait for the device and report any device-side error. */
+int sq_sync(SqSim* sim);
+
+/* Replace the routes of n agents (Agent.get_path + find_next_link, queue_class.py:501-522, 598-608):
+ * ptr[n+1] offsets into links[]; the new route starts at the end node of the agent's current link. */
+int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t* ptr, const int32_t* links);
+/* Link status changes (model/dta_meso_butte.py:77-81, 89-101, 113): closed != 0 zeroes the inflow
+ * capacity in the link model (queue_class.py:455). */
+int sq_set_link_closed(SqSim* sim, int32_t n, const int32_t* link_idx, const uint8_t* closed);
+
+/* ---- state read-back (any pointer may be NULL) ---- */
+int sq_get_link_state(SqSim* sim, int32_t* queue_len, int32_t* run_len, int32_t* total_left, double* inflow_c,
+                      double* outflow_c, double* storage_c);
+/* Vehicles on every link, queue first then run list, in list order: ptr[n_links+1], agents[ptr[n_links]]
+ * (agents must hold n_agents entries). */
+int sq_get_link_vehicles(SqSim* sim, int64_t* ptr, int32_t* agents);
+int sq_get_agent_state(SqSim* sim, uint8_t* status, int32_t* cur_link, int32_t* next_link, int32_t* enter_time,
+                       int32_t* arrive_tick);
+int sq_get_node_state(SqSim* sim, int64_t* node_move);
+/* Edge weights for routing, one per link (queue_class.py:463-466): len(queue)/(capacity+0.1)*3600*25/maxmph + fft
+ * for open real links, else the current weight is left untouched (returned as NaN). */
+int sq_get_link_weights(SqSim* sim, double* weights);
+/* Run counters: [0] ticks, [1] sum over ticks of vehicles on links after the tick (agent-steps),
+ * [2] moves (transfers + arrivals), [3] active nodes, [4] arrivals, [5] kernel launches of this sim. */
+int sq_get_counters(SqSim* sim, int64_t* out6);
+
+const char* sq_last_error(void);
+long long sq_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SQ_TICK_H_ */

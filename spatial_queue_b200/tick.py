@@ -1,0 +1,160 @@
+"""ctypes front-end of the device tick (include/sq_tick.h): FlatNetwork -> SqNetDesc -> SqSim."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+_FIELDS = [
+    ("n_nodes", C.c_int32), ("n_links", C.c_int32), ("n_agents", C.c_int32), ("reserved0", C.c_int32),
+    ("seed", C.c_uint64),
+    ("link_start_node", C.c_void_p), ("link_end_node", C.c_void_p), ("link_is_virtual", C.c_void_p),
+    ("link_lanes_floor", C.c_void_p), ("link_cap_per_s", C.c_void_p), ("link_storage_cap", C.c_void_p),
+    ("link_fft", C.c_void_p), ("link_closed", C.c_void_p), ("link_reverse", C.c_void_p),
+    ("link_capacity", C.c_void_p), ("link_maxmph", C.c_void_p),
+    ("node_key", C.c_void_p), ("node_type", C.c_void_p), ("node_in_ptr", C.c_void_p), ("node_in_links", C.c_void_p),
+    ("node_in_phase", C.c_void_p), ("node_in_prio", C.c_void_p), ("node_out_ptr", C.c_void_p),
+    ("node_out_links", C.c_void_p), ("node_turn_ptr", C.c_void_p), ("turn_angle", C.c_void_p),
+    ("agent_key", C.c_void_p), ("agent_origin", C.c_void_p), ("agent_destin", C.c_void_p), ("agent_dept", C.c_void_p),
+    ("agent_vlen", C.c_void_p), ("agent_status", C.c_void_p), ("route_ptr", C.c_void_p), ("route_links", C.c_void_p),
+]
+_DTYPES = {
+    "link_start_node": np.int32, "link_end_node": np.int32, "link_is_virtual": np.uint8, "link_lanes_floor": np.int32,
+    "link_cap_per_s": np.float64, "link_storage_cap": np.float64, "link_fft": np.float64, "link_closed": np.uint8,
+    "link_reverse": np.int32, "link_capacity": np.float64, "link_maxmph": np.float64, "node_key": np.int64,
+    "node_type": np.uint8, "node_in_ptr": np.int32, "node_in_links": np.int32, "node_in_phase": np.uint8,
+    "node_in_prio": np.int32, "node_out_ptr": np.int32, "node_out_links": np.int32, "node_turn_ptr": np.int64,
+    "turn_angle": np.float64, "agent_key": np.int64, "agent_origin": np.int32, "agent_destin": np.int32,
+    "agent_dept": np.int32, "agent_vlen": np.int32, "agent_status": np.uint8, "route_ptr": np.int64,
+    "route_links": np.int32,
+}
+
+
+class SqNetDesc(C.Structure):
+    _fields_ = _FIELDS
+
+
+def make_desc(flat, seed):
+    """-> (SqNetDesc, keepalive list).  `flat` is a flatten.FlatNetwork (or anything with the same arrays)."""
+    d = SqNetDesc()
+    keep = []
+    d.n_nodes = len(flat.node_key)
+    d.n_links = len(flat.link_end_node)
+    d.n_agents = len(flat.agent_key)
+    d.seed = int(seed)
+    for name, dt in _DTYPES.items():
+        a = np.ascontiguousarray(getattr(flat, name), dtype=dt)
+        if a.size == 0:
+            a = np.zeros(1, dt)
+        keep.append(a)
+        setattr(d, name, a.ctypes.data)
+    return d, keep
+
+
+class _SimBase:
+    """Shared read-back / control surface; subclasses bind the function prefix of a library."""
+    _prefix = None
+
+    def _fn(self, name):
+        raise NotImplementedError
+
+    def _check(self, rc, what):
+        raise NotImplementedError
+
+    def step(self, t):
+        self._check(self._fn("step")(self._h, int(t)), "step")
+
+    def run(self, t0, n):
+        self._check(self._fn("run")(self._h, int(t0), int(n)), "run")
+
+    def set_routes(self, agent_idx, ptr, links):
+        a = np.ascontiguousarray(agent_idx, np.int32)
+        p = np.ascontiguousarray(ptr, np.int64)
+        l = np.ascontiguousarray(links, np.int32)
+        if l.size == 0:
+            l = np.zeros(1, np.int32)
+        self._check(self._fn("set_routes")(self._h, len(a), a.ctypes.data, p.ctypes.data, l.ctypes.data), "set_routes")
+
+    def set_link_closed(self, link_idx, closed):
+        a = np.ascontiguousarray(link_idx, np.int32)
+        c = np.ascontiguousarray(closed, np.uint8)
+        self._check(self._fn("set_link_closed")(self._h, len(a), a.ctypes.data, c.ctypes.data), "set_link_closed")
+
+    def link_state(self):
+        L = self.n_links
+        q, r, left = np.empty(L, np.int32), np.empty(L, np.int32), np.empty(L, np.int32)
+        ic, oc, sc = np.empty(L), np.empty(L), np.empty(L)
+        self._check(self._fn("get_link_state")(self._h, q.ctypes.data, r.ctypes.data, left.ctypes.data, ic.ctypes.data,
+                                               oc.ctypes.data, sc.ctypes.data), "get_link_state")
+        return dict(q=q, r=r, left=left, in_c=ic, out_c=oc, storage_c=sc)
+
+    def link_vehicles(self):
+        ptr = np.empty(self.n_links + 1, np.int64)
+        ag = np.empty(max(self.n_agents, 1), np.int32)
+        self._check(self._fn("get_link_vehicles")(self._h, ptr.ctypes.data, ag.ctypes.data), "get_link_vehicles")
+        return ptr, ag[: ptr[-1]]
+
+    def agent_state(self):
+        A = self.n_agents
+        st = np.empty(A, np.uint8)
+        cur, nxt, ent, arr = (np.empty(A, np.int32) for _ in range(4))
+        self._check(self._fn("get_agent_state")(self._h, st.ctypes.data, cur.ctypes.data, nxt.ctypes.data,
+                                                ent.ctypes.data, arr.ctypes.data), "get_agent_state")
+        return dict(status=st, cur=cur, nxt=nxt, enter=ent, arrive_tick=arr)
+
+    def node_state(self):
+        nm = np.empty(self.n_nodes, np.int64)
+        self._check(self._fn("get_node_state")(self._h, nm.ctypes.data), "get_node_state")
+        return dict(node_move=nm)
+
+    def link_weights(self):
+        w = np.empty(self.n_links, np.float64)
+        self._check(self._fn("get_link_weights")(self._h, w.ctypes.data), "get_link_weights")
+        return w
+
+    def counters(self):
+        out = np.zeros(6, np.int64)
+        self._check(self._fn("get_counters")(self._h, out.ctypes.data), "get_counters")
+        return dict(zip(("ticks", "agent_steps", "moves", "active_nodes", "arrivals", "launches"), out.tolist()))
+
+    def state(self):
+        """Everything the parity digest covers, in the layout of oracle.ref_harness.Recorder.state()."""
+        ls, ag, nd = self.link_state(), self.agent_state(), self.node_state()
+        _, order = self.link_vehicles()
+        return dict(q=ls["q"], r=ls["r"], left=ls["left"], order=order, status=ag["status"].astype(np.int32),
+                    cur=ag["cur"], nxt=ag["nxt"], enter=ag["enter"], node_move=nd["node_move"],
+                    arrive_tick=ag["arrive_tick"], in_c=ls["in_c"], out_c=ls["out_c"], storage_c=ls["storage_c"])
+
+
+class DeviceSim(_SimBase):
+    """The GPU tick.  Raises B200LibraryError when the library or the device is missing."""
+
+    def __init__(self, flat, seed=0):
+        L = _lib.lib()
+        self._L = L
+        self.n_nodes, self.n_links, self.n_agents = len(flat.node_key), len(flat.link_end_node), len(flat.agent_key)
+        desc, keep = make_desc(flat, seed)
+        self._h = L.sq_create(C.byref(desc))
+        if not self._h:
+            raise _lib.B200LibraryError("sq_create failed: " + L.sq_last_error().decode())
+
+    def _fn(self, name):
+        return getattr(self._L, "sq_" + name)
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise _lib.B200LibraryError(f"sq_{what} failed ({rc}): {self._L.sq_last_error().decode()}")
+
+    def sync(self):
+        self._check(self._L.sq_sync(self._h), "sync")
+
+    def close(self):
+        if self._h:
+            self._L.sq_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

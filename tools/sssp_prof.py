@@ -1,0 +1,21 @@
+"""One launch of the SSSP tree kernel on the C5 grid, for ncu (run on the GPU box)."""
+import sys, os, json
+R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
+import numpy as np, torch
+from conftest import grid_graph
+from spatial_queue_b200 import sp_interface as spi
+n = int(os.environ.get("GRID", 224)); B = int(os.environ.get("BATCH", 2048))
+t, c, d, q = json.loads(os.environ.get("CFG", "[256,0,4.0,1024]"))
+s, e, w = grid_graph(n, seed=1)
+g = spi.from_arrays(s, e, w); V = n * n
+g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
+origins = np.random.default_rng(0).permutation(V)[:B].astype(np.int32)
+o = torch.from_numpy(origins).cuda()
+dist = torch.empty((B, V), dtype=torch.float64, device="cuda"); par = torch.empty((B, V), dtype=torch.int32, device="cuda")
+for _ in range(2):
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(); g.sssp_batch_device(o, dist, par); ev1.record(); torch.cuda.synchronize()
+    print("ms", ev0.elapsed_time(ev1), "trees/s", B / ev0.elapsed_time(ev1) * 1e3)
+dd, pp = g.sssp_batch(origins[:64])
+st = g.last_stats(); print(st, "relax/tree", st["relaxations"] / 64, "rounds/tree", st["rounds"] / 64, "trans/tree", st["transitions"] / 64, "E", len(s))

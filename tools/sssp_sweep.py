@@ -1,0 +1,33 @@
+"""Tuning sweep for the SSSP tree kernel on the C5 grid (run on the GPU box)."""
+import sys, os, time, json, itertools
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import numpy as np
+import torch
+from conftest import grid_graph
+from spatial_queue_b200 import sp_interface as spi
+
+n = int(os.environ.get("GRID", 224))
+B = int(os.environ.get("BATCH", 4096))
+s, e, w = grid_graph(n, seed=1)
+g = spi.from_arrays(s, e, w)
+V = n * n
+origins = torch.from_numpy(np.random.default_rng(0).permutation(V)[:B].astype(np.int32)).cuda()
+dist = torch.empty((B, V), dtype=torch.float64, device="cuda")
+par = torch.empty((B, V), dtype=torch.int32, device="cuda")
+btree = 20 * len(s) + 24 * V
+configs = json.loads(os.environ.get("CONFIGS", "null")) or [
+    (t, c, d, q) for t in (128, 256, 512) for c in (0, 2, 4) for d in (1.0, 2.0, 4.0, 8.0) for q in (1024,)]
+for (t, c, d, q) in configs:
+    try:
+        g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
+        g.sssp_batch_device(origins[:256], dist, par); torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(); g.sssp_batch_device(origins, dist, par); ev1.record(); torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        tps = B / ms * 1e3
+        st = g.last_stats()
+        print(json.dumps({"threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "trees_per_s": round(tps),
+                          "frac_hbm": round(tps * btree / 6562.3e9, 4)}), flush=True)
+    except Exception as ex:
+        print("ERR", t, c, d, q, ex, flush=True)
