@@ -53,6 +53,25 @@ def _declare(L):
     L.sp_kernel_launches.restype = C.c_longlong; L.sp_kernel_launches.argtypes = []
 
 
+    # ---- tick surface (include/sq_tick.h) ----
+    i32, i64 = C.c_int32, C.c_int64
+    L.sq_create.restype = vp; L.sq_create.argtypes = [vp]
+    L.sq_destroy.restype = None; L.sq_destroy.argtypes = [vp]
+    L.sq_step.restype = ci; L.sq_step.argtypes = [vp, i32]
+    L.sq_run.restype = ci; L.sq_run.argtypes = [vp, i32, i32]
+    L.sq_sync.restype = ci; L.sq_sync.argtypes = [vp]
+    L.sq_set_routes.restype = ci; L.sq_set_routes.argtypes = [vp, i32, vp, vp, vp]
+    L.sq_set_link_closed.restype = ci; L.sq_set_link_closed.argtypes = [vp, i32, vp, vp]
+    L.sq_get_link_state.restype = ci; L.sq_get_link_state.argtypes = [vp] * 7
+    L.sq_get_link_vehicles.restype = ci; L.sq_get_link_vehicles.argtypes = [vp, vp, vp]
+    L.sq_get_agent_state.restype = ci; L.sq_get_agent_state.argtypes = [vp] * 6
+    L.sq_get_node_state.restype = ci; L.sq_get_node_state.argtypes = [vp, vp]
+    L.sq_get_link_weights.restype = ci; L.sq_get_link_weights.argtypes = [vp, vp]
+    L.sq_get_counters.restype = ci; L.sq_get_counters.argtypes = [vp, vp]
+    L.sq_last_error.restype = C.c_char_p; L.sq_last_error.argtypes = []
+    L.sq_kernel_launches.restype = C.c_longlong; L.sq_kernel_launches.argtypes = []
+
+
 def check(rc, what="call"):
     if rc != 0:
         raise B200LibraryError(f"{what} failed ({rc}): {lib().sp_last_error().decode()}")

@@ -1,0 +1,901 @@
+// tick.cu -- the one-second spatial-queue tick on B200 (include/sq_tick.h).
+//
+// What it replaces (reference file:line, projects/bolinas_civic/): the three Python loops a driver runs every
+// simulated second -- Agent.load_vehicle (queue_class.py:587-596), Link.run_link_model (:445-455) and
+// Node.run_node_model / non_conflict_vehicles (:226-394) driven by run_traffic_simulation.py:52-69, 111.
+//
+// Design (not a translation of those loops):
+//  * Every link owns a ring of {agent, ready_tick} slots in HBM.  queue_vehicles is ring[head, qtail),
+//    run_vehicles is ring[qtail, tail): one entry-ordered sequence with a moving boundary, because the
+//    reference only ever appends to the run list and promotes a prefix of it.  `ready_tick` is the first tick
+//    at which the reference's f64 predicate `enter_time < t - fft` (:447) holds, computed once at entry with
+//    that same f64 expression, so the link model is a boundary advance instead of a list rebuild.
+//  * Source (virtual) links have their whole departure sequence written at creation in (departure, agent)
+//    order -- the order load_vehicle appends in -- so loading is a tail advance.
+//  * Storage is an integer occupancy (length entered - length left) subtracted from the f64 capacity once
+//    per tick, exactly the reference's single subtraction (:453); the node model then subtracts lengths one
+//    by one in f64 like :348.
+//  * Link state is split by writer: {head, out_c, total_left, len_out} belong to the link's end node,
+//    {tail, in_c, storage_c, len_in} to its start node.  Within a tick a node only touches the in-side of its
+//    in-links and the out-side of its out-links, so nodes are independent: one thread per node, no atomics on
+//    simulation state, bit-reproducible.  Atomics appear only on run counters (warp-aggregated).
+//  * Turn conflicts: a 64-bit left-turn mask per in-link (bit j = angle to the j-th out-link >= 50 deg, :263)
+//    and the node's f64 angle table for the opposite-approach argmin (:277), both built from the reference's
+//    own add_connectivity output.
+//  * Randomness: counter-based contract of spatial_queue_b200/rng.py.
+#include <algorithm>
+#include <cfloat>
+#include <climits>
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <numeric>
+#include <vector>
+
+#include "../../include/sq_tick.h"
+#include "sq_common.cuh"
+
+using sq::SQ_ERR_ARG;
+using sq::SQ_ERR_CUDA;
+using sq::SQ_ERR_LIMIT;
+using sq::SQ_ERR_STATE;
+using sq::SQ_OK;
+
+typedef unsigned long long u64;
+
+// =================================================================================================
+// Device state
+// =================================================================================================
+struct TickState {
+  int N, L, A;
+  u64 seed;
+  // links, static
+  const int* l_start; const int* l_end; const int* l_lanes; const int* l_rev;
+  const unsigned char* l_virtual; unsigned char* l_closed;
+  const double* l_cap_s; const double* l_storage; const double* l_fft;
+  const long long* l_ring_base; const unsigned* l_ring_mask; const int* l_vcount;
+  const unsigned char* l_in_local; const unsigned char* l_out_local; const u64* l_left_mask;
+  // links, dynamic
+  unsigned* head; unsigned* qtail; unsigned* tail;
+  double* out_c; double* in_c; double* storage_c;
+  long long* len_in; long long* len_out; int* total_left;
+  int2* ring;
+  // nodes
+  const long long* n_key; const unsigned char* n_type;
+  const int* in_ptr; const int* in_links; const unsigned char* in_phase; const int* in_prio;
+  const int* out_ptr;
+  const long long* turn_ptr; const double* turn;
+  long long* node_move;
+  // agents
+  int4* a_rec;  // x next_link, y cur_link, z enter_time, w status | vlen << 8
+  const int* a_destin;
+  long long* a_route_off; int* a_route_len; int* a_route_pos; int* a_arrive;
+  const int* route_pool;
+  // run control
+  int* tick_link;  // tick the next link-phase launch simulates
+  int* tick_node;  // tick the next node-phase launch simulates
+  u64* counters;   // [0] ticks [1] agent_steps [2] moves [3] active nodes [4] arrivals [5] loaded [6] loaded, frozen
+  int* err;        // [0] code (0 = ok) [1] agent [2] node [3] link
+};
+
+__device__ __forceinline__ u64 fmix64(u64 x) {
+  x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+  return x;
+}
+// spatial_queue_b200/rng.py: u(seed, t, node, k)
+__device__ __forceinline__ double rng_uniform(u64 seed, int t, long long node, int k) {
+  u64 h = seed ^ 0x243F6A8885A308D3ull;
+  h = fmix64(h + (u64)(long long)t * 0x9E3779B97F4A7C15ull);
+  h = fmix64(h + (u64)node * 0xBF58476D1CE4E5B9ull);
+  h = fmix64(h + (u64)(long long)k * 0x94D049BB133111EBull);
+  return (double)(h >> 11) * (1.0 / 9007199254740992.0);
+}
+
+__device__ __forceinline__ void raise_error(const TickState& s, int code, int agent, int node, int link) {
+  if (atomicCAS(&s.err[0], 0, code) == 0) { s.err[1] = agent; s.err[2] = node; s.err[3] = link; }
+}
+
+// First tick t' with (double)t_enter < (double)t' - fft, the promotion test of queue_class.py:447.
+__device__ __forceinline__ int ready_tick(int t_enter, double fft) {
+  if (!(fft < 1.0e9)) return INT_MAX;
+  int r = t_enter + (int)floor(fft) + 1;
+  const double te = (double)t_enter;
+  while (!(te < (double)r - fft)) ++r;
+  while (te < (double)(r - 1) - fft) --r;
+  return r;
+}
+
+// ---- phase 1: load + link model, one thread per link ---------------------------------------------------
+__global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = *s.tick_link;
+  if (l == 0) {
+    *s.tick_node = t;
+    // vehicles on links after the previous tick = loaded - arrived up to then; counters[6] is the loaded
+    // count frozen by the previous node phase (this launch is adding to counters[5] concurrently)
+    if (s.counters[0] > 0) s.counters[1] += s.counters[6] - s.counters[4];
+    s.counters[0] += 1;
+  }
+  int loaded = 0;
+  if (l < s.L) {
+    unsigned tl = s.tail[l];
+    unsigned qt = s.qtail[l];
+    const long long base = s.l_ring_base[l];
+    const unsigned mask = s.l_ring_mask[l];
+    long long li = s.len_in[l];
+    if (s.l_virtual[l]) {
+      // load_vehicle (:587-596): the next entries of the prefilled departure sequence whose departure == t
+      const unsigned cnt = (unsigned)s.l_vcount[l];
+      while (tl < cnt) {
+        const int2 e = s.ring[base + tl];
+        if (e.y - 1 > t) break;
+        int4 rec = s.a_rec[e.x];
+        rec.z = e.y - 1;                                  // current_link_enter_time = departure tick
+        rec.w = (rec.w & ~0xff) | SQ_ENROUTE;
+        s.a_rec[e.x] = rec;
+        li += (rec.w >> 8) & 0xff;
+        ++tl; ++loaded;
+      }
+      if (loaded) { s.tail[l] = tl; s.len_in[l] = li; }
+    }
+    // run -> queue promotion (:446-449): advance the boundary over entries whose ready tick has come
+    if (qt != tl) {
+      const unsigned qt0 = qt;
+      while (qt != tl && s.ring[base + (qt & mask)].y <= t) ++qt;
+      if (qt != qt0) s.qtail[l] = qt;
+    }
+    // capacities (:453-455)
+    s.storage_c[l] = s.l_storage[l] - (double)(li - s.len_out[l]);
+    const double c = s.l_cap_s[l];
+    s.out_c[l] = c;
+    s.in_c[l] = s.l_closed[l] ? 0.0 : c;
+  }
+  const unsigned any = __ballot_sync(0xffffffffu, loaded > 0);
+  if (any) {
+    int tot = loaded;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if (sq::lane_id() == 0) atomicAdd(&s.counters[5], (u64)tot);
+  }
+}
+
+// ---- phase 2: node model, one thread per node ---------------------------------------------------------------
+struct AdmitCtx {
+  int t, node, toss, moves, arrivals;
+  long long key;
+};
+
+// Admit loop of run_node_model (:304-386) over the first k queued vehicles of in-link `il`; `secondary`
+// applies the "no more left turns from the opposite approach" skip of :289-292.
+__device__ void admit_from_link(const TickState& s, AdmitCtx& c, int il, int k, bool secondary) {
+  const long long base = s.l_ring_base[il];
+  const unsigned mask = s.l_ring_mask[il];
+  const unsigned h = s.head[il];
+  const u64 left = s.l_left_mask[il];
+  double out_c = s.out_c[il];
+  u64 stay_lo = 0, stay_hi = 0;  // bit i = vehicle i stays in the queue
+  int moved = 0;
+  long long moved_len = 0;
+  for (int i = 0; i < k; ++i) {
+    const int agent = s.ring[base + ((h + (unsigned)i) & mask)].x;
+    const int4 rec = s.a_rec[agent];
+    const int ol = rec.x;
+    const int vlen = (rec.w >> 8) & 0xff;
+    bool stay = true;
+    if (secondary && ol >= 0 && ((left >> s.l_out_local[ol]) & 1ull)) {
+      // left turn from the opposite approach: not a go-vehicle this second
+    } else if (c.node == s.a_destin[agent]) {                                     // arrival (:321-328)
+      stay = false;
+      out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
+      s.a_rec[agent] = make_int4(rec.x, rec.y, rec.z, (rec.w & ~0xff) | SQ_ARRIVE);
+      s.a_arrive[agent] = c.t;
+      ++c.arrivals;
+    } else if (ol < 0) {
+      raise_error(s, 1, agent, c.node, il);                                       // :312-314
+    } else if (s.storage_c[ol] < (double)vlen) {                                  // spill-back (:333)
+    } else {
+      double in_c = s.in_c[ol];
+      bool go;
+      if (out_c >= 1.0 && in_c >= 1.0) {                                          // :336
+        go = true;
+      } else {                                                                    // :358-361
+        const double cc = out_c < in_c ? out_c : in_c;
+        const double w0 = 1.0 - cc;
+        const double total = w0 + cc;
+        const double u = rng_uniform(s.seed, c.t, c.key, 2 + c.toss);
+        ++c.toss;
+        go = !(u * total < w0);
+        if (!go) {                                                                // :380-386
+          if (out_c < in_c) { out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0; }
+          else if (out_c > in_c) { in_c = in_c - 1.0; s.in_c[ol] = in_c > 0.0 ? in_c : 0.0; }
+          else {
+            out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
+            in_c = in_c - 1.0; s.in_c[ol] = in_c > 0.0 ? in_c : 0.0;
+          }
+        }
+      }
+      if (go) {                                                                   // :337-349 / :362-374
+        stay = false;
+        out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
+        in_c = in_c - 1.0; s.in_c[ol] = in_c > 0.0 ? in_c : 0.0;
+        s.storage_c[ol] = s.storage_c[ol] - (double)vlen;
+        // append to the out-link's run list
+        const unsigned tl = s.tail[ol];
+        const unsigned omask = s.l_ring_mask[ol];
+        if (tl - s.head[ol] > omask) raise_error(s, 3, agent, c.node, ol);
+        s.ring[s.l_ring_base[ol] + (tl & omask)] = make_int2(agent, ready_tick(c.t, s.l_fft[ol]));
+        s.tail[ol] = tl + 1u;
+        s.len_in[ol] += vlen;
+        // move_agent_to_next_link + find_next_link (:610-615, :598-608)
+        const int pos = s.a_route_pos[agent] + 1;
+        const int nxt = pos < s.a_route_len[agent] ? s.route_pool[s.a_route_off[agent] + pos] : -1;
+        s.a_route_pos[agent] = pos;
+        s.a_rec[agent] = make_int4(nxt, ol, c.t, rec.w);
+      }
+    }
+    if (stay) { if (i < 64) stay_lo |= 1ull << i; else stay_hi |= 1ull << (i - 64); }
+    else { ++moved; moved_len += vlen; }
+  }
+  if (moved) {
+    // close the gaps: stayers slide to the back of the window [h, h+k), preserving order
+    int j = k - 1;
+    for (int i = k - 1; i >= 0; --i) {
+      const bool st = i < 64 ? ((stay_lo >> i) & 1ull) : ((stay_hi >> (i - 64)) & 1ull);
+      if (st) {
+        if (j != i) s.ring[base + ((h + (unsigned)j) & mask)] = s.ring[base + ((h + (unsigned)i) & mask)];
+        --j;
+      }
+    }
+    s.head[il] = h + (unsigned)moved;
+    s.len_out[il] += moved_len;
+    s.total_left[il] += moved;
+    c.moves += moved;
+  }
+  s.out_c[il] = out_c;
+}
+
+__global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = *s.tick_node;
+  if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; }
+  int moves = 0, arrivals = 0, active = 0;
+  if (n < s.N) {
+    const int ib = s.in_ptr[n];
+    const int indeg = s.in_ptr[n + 1] - ib;
+    // candidate in-links: non-empty queue, incoming_links order (:230)
+    u64 cand = 0;
+    for (int i = 0; i < indeg; ++i) {
+      const int l = s.in_links[ib + i];
+      if (s.qtail[l] != s.head[l]) cand |= 1ull << i;
+    }
+    if (cand) {
+      active = 1;
+      const long long key = s.n_key[n];
+      const int type = s.n_type[n];
+      int primary = -1;  // local index of the primary in-link
+      // `order` semantics: after the shuffle replacement the list is [c_r, rest in original order].
+      int first = -1;    // local index moved to the front by the last shuffle (ties in :277 see it first)
+      if (type == 2) {                                                            // priority list (:237-238)
+        int best_rank = INT_MAX;
+        u64 listed = 0;
+        for (int i = 0; i < indeg; ++i) {
+          const int r = s.in_prio[ib + i];
+          if (r >= 0 && ((cand >> i) & 1ull)) { listed |= 1ull << i; if (r < best_rank) { best_rank = r; primary = i; } }
+        }
+        cand = listed;
+      } else {
+        int cnt = __popcll(cand);
+        int r = 0;
+        if (cnt >= 2) r = (int)(rng_uniform(s.seed, t, key, 0) * (double)cnt);   // shuffle slot 0 (:231)
+        {
+          u64 m = cand;
+          for (int j = 0; j < r; ++j) m &= m - 1;
+          first = __ffsll((long long)m) - 1;
+        }
+        if (type == 1) {                                                          // signal phase (:233-236)
+          const int want = (t % 60 < 30) ? 1 : 2;
+          u64 f = 0;
+          for (int i = 0; i < indeg; ++i)
+            if (((cand >> i) & 1ull) && (s.in_phase[ib + i] & want)) f |= 1ull << i;
+          // filtered list order: [first (if kept), others in original order]
+          const bool first_kept = (f >> first) & 1ull;
+          cnt = __popcll(f);
+          cand = f;
+          if (cnt == 0) { primary = -1; }
+          else {
+            int r2 = 0;
+            if (cnt >= 2) r2 = (int)(rng_uniform(s.seed, t, key, 1) * (double)cnt);   // shuffle slot 1
+            // element r2 of [first?, rest...]
+            if (first_kept) {
+              if (r2 == 0) primary = first;
+              else { u64 m = f & ~(1ull << first); for (int j = 0; j < r2 - 1; ++j) m &= m - 1; primary = __ffsll((long long)m) - 1; }
+            } else {
+              u64 m = f; for (int j = 0; j < r2; ++j) m &= m - 1; primary = __ffsll((long long)m) - 1;
+              first = -1;
+            }
+            // after the second shuffle the list is [primary, (first if kept and != primary), rest]
+            if (first == primary) first = -1;
+          }
+        } else {
+          primary = first;
+          first = -1;
+        }
+      }
+      if (primary >= 0) {
+        AdmitCtx c;
+        c.t = t; c.node = n; c.toss = 0; c.moves = 0; c.arrivals = 0; c.key = key;
+        const int lp = s.in_links[ib + primary];
+        const int qlen_p = (int)(s.qtail[lp] - s.head[lp]);
+        const int kp = min(s.l_lanes[lp], qlen_p);
+        // pass 1 over the primary vehicles: does any of them turn left? (:248-263)
+        bool left_phase = false;
+        {
+          const long long base = s.l_ring_base[lp];
+          const unsigned mask = s.l_ring_mask[lp];
+          const unsigned h = s.head[lp];
+          const u64 left = s.l_left_mask[lp];
+          for (int i = 0; i < kp; ++i) {
+            const int agent = s.ring[base + ((h + (unsigned)i) & mask)].x;
+            const int ol = s.a_rec[agent].x;
+            if (ol >= 0) {
+              if (s.l_start[ol] != n) raise_error(s, 2, agent, n, ol);            // KeyError of :257-262
+              else if ((left >> s.l_out_local[ol]) & 1ull) left_phase = true;
+            }
+          }
+        }
+        // opposite approach (:267-293), chosen before anything moves
+        int secondary = -1;
+        const u64 rest = cand & ~(1ull << primary);
+        const int rev = s.l_rev[lp];
+        if (!left_phase && rest && rev >= 0) {
+          const int outdeg = s.out_ptr[n + 1] - s.out_ptr[n];
+          const double* tb = s.turn + s.turn_ptr[n];
+          const int rcol = s.l_out_local[rev];
+          double best = 0.0;
+          // iteration order of the remaining list: [first (if any), others in original order]; the priority
+          // branch iterates in priority order
+          if (type == 2) {
+            int done_rank = -1;
+            for (;;) {
+              int br = INT_MAX, bi = -1;
+              for (int i = 0; i < indeg; ++i) {
+                const int r = s.in_prio[ib + i];
+                if (((rest >> i) & 1ull) && r > done_rank && r < br) { br = r; bi = i; }
+              }
+              if (bi < 0) break;
+              done_rank = br;
+              const double a = fabs(tb[bi * outdeg + rcol]);
+              if (secondary < 0 || a < best) { secondary = bi; best = a; }
+            }
+          } else {
+            if (first >= 0 && ((rest >> first) & 1ull)) { secondary = first; best = fabs(tb[first * outdeg + rcol]); }
+            for (int i = 0; i < indeg; ++i) {
+              if (!((rest >> i) & 1ull) || i == first) continue;
+              const double a = fabs(tb[i * outdeg + rcol]);
+              if (secondary < 0 || a < best) { secondary = i; best = a; }
+            }
+          }
+        }
+        int ls = -1, ks = 0;
+        if (secondary >= 0) {
+          ls = s.in_links[ib + secondary];
+          ks = min(s.l_lanes[ls], (int)(s.qtail[ls] - s.head[ls]));
+          // a turn outside the table is an error for the opposite approach too (:291)
+          const long long base = s.l_ring_base[ls];
+          const unsigned mask = s.l_ring_mask[ls];
+          const unsigned h = s.head[ls];
+          for (int i = 0; i < ks; ++i) {
+            const int agent = s.ring[base + ((h + (unsigned)i) & mask)].x;
+            const int ol = s.a_rec[agent].x;
+            if (ol >= 0 && s.l_start[ol] != n) raise_error(s, 2, agent, n, ol);
+          }
+        }
+        admit_from_link(s, c, lp, kp, false);
+        if (ls >= 0) admit_from_link(s, c, ls, ks, true);
+        if (c.moves) s.node_move[n] += c.moves;
+        moves = c.moves; arrivals = c.arrivals;
+      }
+    }
+  }
+  // run counters: one atomic per warp
+  const unsigned any = __ballot_sync(0xffffffffu, active != 0);
+  if (any) {
+    int m = moves, a = arrivals, ac = active;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      m += __shfl_xor_sync(0xffffffffu, m, o);
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      ac += __shfl_xor_sync(0xffffffffu, ac, o);
+    }
+    if (sq::lane_id() == 0) {
+      if (m) atomicAdd(&s.counters[2], (u64)m);
+      atomicAdd(&s.counters[3], (u64)ac);
+      if (a) atomicAdd(&s.counters[4], (u64)a);
+    }
+  }
+}
+
+// ---- route replacement (Agent.get_path + find_next_link) -----------------------------------------------
+__global__ void k_set_routes(const TickState s, int n, const int* agent_idx, const long long* new_off, const int* new_len) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int a = agent_idx[i];
+  int4 rec = s.a_rec[a];
+  const int st = rec.w & 0xff;
+  if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
+  s.a_route_off[a] = new_off[i];
+  s.a_route_len[a] = new_len[i];
+  s.a_route_pos[a] = 0;
+  rec.x = new_len[i] > 0 ? s.route_pool[new_off[i]] : -1;
+  s.a_rec[a] = rec;
+}
+
+__global__ void k_set_closed(const TickState s, int n, const int* link_idx, const unsigned char* closed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) s.l_closed[link_idx[i]] = closed[i];
+}
+
+// =================================================================================================
+// Host side
+// =================================================================================================
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+struct SqSim {
+  TickState st;
+  std::vector<void*> allocs;
+  int N = 0, L = 0, A = 0;
+  long long ring_slots = 0;
+  // host copies needed by getters
+  std::vector<long long> h_ring_base;
+  std::vector<unsigned> h_ring_mask;
+  std::vector<unsigned char> h_virtual, h_closed;
+  std::vector<double> h_capacity, h_maxmph, h_fft;
+  // route pool management
+  int* d_pool = nullptr;
+  long long pool_cap = 0, pool_used = 0;
+  cudaStream_t stream = nullptr;
+  int next_t = INT_MIN;  // tick the device counters are armed for
+  long long launches = 0;
+  cudaGraphExec_t graph = nullptr;
+  int graph_ticks = 0;
+};
+
+template <typename T>
+static int dev_upload(SqSim* sim, const T** dst, const std::vector<T>& v) {
+  T* d = nullptr;
+  const size_t n = std::max<size_t>(v.size(), 1);
+  SQ_CUDA_TRY(cudaMalloc(&d, n * sizeof(T)));
+  sim->allocs.push_back(d);
+  if (!v.empty()) SQ_CUDA_TRY(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *dst = d;
+  return SQ_OK;
+}
+template <typename T>
+static int dev_upload_rw(SqSim* sim, T** dst, const std::vector<T>& v) {
+  const T* c = nullptr;
+  int rc = dev_upload(sim, &c, v);
+  *dst = const_cast<T*>(c);
+  return rc;
+}
+template <typename T>
+static int dev_upload_ptr(SqSim* sim, const T** dst, const T* src, size_t n) {
+  std::vector<T> v(src, src + n);
+  return dev_upload(sim, dst, v);
+}
+
+static int sim_build(SqSim* sim, const SqNetDesc* d) {
+  if (int rc = sq::require_device()) return rc;
+  const int N = d->n_nodes, L = d->n_links, A = d->n_agents;
+  if (N <= 0 || L <= 0 || A < 0) return sq::set_error(SQ_ERR_ARG, "sq_create: empty network (N=%d L=%d A=%d)", N, L, A);
+  sim->N = N; sim->L = L; sim->A = A;
+  TickState& s = sim->st;
+  s.N = N; s.L = L; s.A = A; s.seed = d->seed;
+  SQ_CUDA_TRY(cudaStreamCreateWithFlags(&sim->stream, cudaStreamNonBlocking));
+
+  for (long long k = 0; k < d->route_ptr[A]; ++k)
+    if (d->route_links[k] < 0 || d->route_links[k] >= L)
+      return sq::set_error(SQ_ERR_ARG, "route entry %lld is link %d, outside 0..%d", k, d->route_links[k], L - 1);
+  // ---- per-link local indices, left-turn masks ----
+  std::vector<unsigned char> in_local(L, 0), out_local(L, 0);
+  std::vector<u64> left_mask(L, 0);
+  for (int n = 0; n < N; ++n) {
+    const int ib = d->node_in_ptr[n], ie = d->node_in_ptr[n + 1], ob = d->node_out_ptr[n], oe = d->node_out_ptr[n + 1];
+    if (ie - ib > 64 || oe - ob > 64)
+      return sq::set_error(SQ_ERR_LIMIT, "node %d has in/out degree %d/%d; the turn masks hold 64", n, ie - ib, oe - ob);
+    for (int j = ob; j < oe; ++j) out_local[d->node_out_links[j]] = (unsigned char)(j - ob);
+    for (int i = ib; i < ie; ++i) {
+      const int l = d->node_in_links[i];
+      in_local[l] = (unsigned char)(i - ib);
+      u64 m = 0;
+      for (int j = ob; j < oe; ++j)
+        if (d->turn_angle[d->node_turn_ptr[n] + (long long)(i - ib) * (oe - ob) + (j - ob)] >= 50) m |= 1ull << (j - ob);
+      left_mask[l] = m;
+    }
+  }
+  // ---- rings ----
+  int min_vlen = 255;
+  for (int a = 0; a < A; ++a) {
+    if (d->agent_vlen[a] < 1 || d->agent_vlen[a] > 255)
+      return sq::set_error(SQ_ERR_LIMIT, "agent %d has vehicle length %d; 1..255 supported", a, d->agent_vlen[a]);
+    min_vlen = std::min(min_vlen, d->agent_vlen[a]);
+  }
+  if (A == 0) min_vlen = 8;
+  std::vector<int> virt_of_node(N, -1);
+  for (int l = 0; l < L; ++l) {
+    if (d->link_lanes_floor[l] > 128)
+      return sq::set_error(SQ_ERR_LIMIT, "link %d has %d lanes; 128 supported", l, d->link_lanes_floor[l]);
+    if (d->link_is_virtual[l]) virt_of_node[d->link_end_node[l]] = l;
+  }
+  std::vector<std::vector<int>> departures(L);
+  for (int a = 0; a < A; ++a) {
+    if (d->agent_status[a] != SQ_UNLOADED) continue;  // shelter_p agents never load (queue_class.py:509, :589)
+    const int vl = virt_of_node[d->agent_origin[a]];
+    if (vl < 0) return sq::set_error(SQ_ERR_ARG, "agent %d: origin node %d has no source link", a, d->agent_origin[a]);
+    departures[vl].push_back(a);
+  }
+  std::vector<long long> ring_base(L);
+  std::vector<unsigned> ring_mask(L);
+  std::vector<int> vcount(L, 0);
+  long long slots = 0;
+  for (int l = 0; l < L; ++l) {
+    long long need;
+    if (d->link_is_virtual[l]) {
+      need = (long long)departures[l].size();
+      vcount[l] = (int)need;
+    } else {
+      need = (long long)std::floor(d->link_storage_cap[l] / (double)min_vlen) + 2;
+    }
+    long long cap = 1;
+    while (cap < need) cap <<= 1;
+    if (cap > (1ll << 30)) return sq::set_error(SQ_ERR_LIMIT, "link %d needs a ring of %lld slots", l, cap);
+    ring_base[l] = slots;
+    ring_mask[l] = (unsigned)(cap - 1);
+    slots += cap;
+  }
+  sim->ring_slots = slots;
+  std::vector<int2> ring((size_t)slots, make_int2(-1, INT_MAX));
+  for (int l = 0; l < L; ++l) {
+    auto& v = departures[l];
+    std::stable_sort(v.begin(), v.end(), [&](int a, int b) { return d->agent_dept[a] < d->agent_dept[b]; });
+    for (size_t i = 0; i < v.size(); ++i) ring[(size_t)ring_base[l] + i] = make_int2(v[i], d->agent_dept[v[i]] + 1);
+  }
+
+  // ---- uploads ----
+  int rc;
+#define UP(field, ptr, n) if ((rc = dev_upload_ptr(sim, &s.field, ptr, (size_t)(n)))) return rc
+  UP(l_start, d->link_start_node, L); UP(l_end, d->link_end_node, L); UP(l_lanes, d->link_lanes_floor, L);
+  UP(l_rev, d->link_reverse, L); UP(l_virtual, d->link_is_virtual, L);
+  UP(l_cap_s, d->link_cap_per_s, L); UP(l_storage, d->link_storage_cap, L); UP(l_fft, d->link_fft, L);
+  UP(n_type, d->node_type, N); UP(in_ptr, d->node_in_ptr, N + 1); UP(in_links, d->node_in_links, d->node_in_ptr[N]);
+  UP(in_phase, d->node_in_phase, d->node_in_ptr[N]); UP(in_prio, d->node_in_prio, d->node_in_ptr[N]);
+  UP(out_ptr, d->node_out_ptr, N + 1);
+  UP(turn, d->turn_angle, d->node_turn_ptr[N]); UP(a_destin, d->agent_destin, A);
+#undef UP
+  {
+    std::vector<long long> key(d->node_key, d->node_key + N), tp(d->node_turn_ptr, d->node_turn_ptr + N + 1);
+    if ((rc = dev_upload(sim, &s.n_key, key))) return rc;
+    if ((rc = dev_upload(sim, &s.turn_ptr, tp))) return rc;
+  }
+  {
+    std::vector<unsigned char> closed(d->link_closed, d->link_closed + L);
+    if ((rc = dev_upload_rw(sim, &s.l_closed, closed))) return rc;
+    sim->h_closed = closed;
+  }
+  if ((rc = dev_upload(sim, &s.l_ring_base, ring_base))) return rc;
+  if ((rc = dev_upload(sim, &s.l_ring_mask, ring_mask))) return rc;
+  if ((rc = dev_upload(sim, &s.l_vcount, vcount))) return rc;
+  if ((rc = dev_upload(sim, &s.l_in_local, in_local))) return rc;
+  if ((rc = dev_upload(sim, &s.l_out_local, out_local))) return rc;
+  if ((rc = dev_upload(sim, &s.l_left_mask, left_mask))) return rc;
+  if ((rc = dev_upload_rw(sim, &s.ring, ring))) return rc;
+  {
+    std::vector<unsigned> z(L, 0u);
+    if ((rc = dev_upload_rw(sim, &s.head, z))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.qtail, z))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.tail, z))) return rc;
+    std::vector<double> caps(d->link_cap_per_s, d->link_cap_per_s + L), stor(d->link_storage_cap, d->link_storage_cap + L);
+    if ((rc = dev_upload_rw(sim, &s.out_c, caps))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.in_c, caps))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.storage_c, stor))) return rc;
+    std::vector<long long> zl(L, 0);
+    if ((rc = dev_upload_rw(sim, &s.len_in, zl))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.len_out, zl))) return rc;
+    std::vector<int> zi(L, 0);
+    if ((rc = dev_upload_rw(sim, &s.total_left, zi))) return rc;
+    std::vector<long long> zn(N, 0);
+    if ((rc = dev_upload_rw(sim, &s.node_move, zn))) return rc;
+  }
+  // agents
+  {
+    std::vector<int4> rec((size_t)A);
+    std::vector<long long> off((size_t)A);
+    std::vector<int> len((size_t)A), pos((size_t)A, 0), arr((size_t)A, -1);
+    for (int a = 0; a < A; ++a) {
+      const long long b = d->route_ptr[a], e = d->route_ptr[a + 1];
+      off[a] = b; len[a] = (int)(e - b);
+      const int vl = virt_of_node[d->agent_origin[a]];
+      rec[a] = make_int4(e > b ? d->route_links[b] : -1, vl, -1, (int)d->agent_status[a] | (d->agent_vlen[a] << 8));
+      if (d->agent_status[a] == SQ_UNLOADED && e == b)
+        return sq::set_error(SQ_ERR_ARG, "agent %d is to be loaded but has an empty route (queue_class.py:595 raises KeyError)", a);
+    }
+    if ((rc = dev_upload_rw(sim, &s.a_rec, rec))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.a_route_off, off))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.a_route_len, len))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.a_route_pos, pos))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.a_arrive, arr))) return rc;
+    const long long used = d->route_ptr[A];
+    sim->pool_cap = used + used / 2 + 4096;
+    sim->pool_used = used;
+    SQ_CUDA_TRY(cudaMalloc(&sim->d_pool, sizeof(int) * (size_t)sim->pool_cap));
+    if (used > 0) SQ_CUDA_TRY(cudaMemcpy(sim->d_pool, d->route_links, sizeof(int) * (size_t)used, cudaMemcpyHostToDevice));
+    s.route_pool = sim->d_pool;
+  }
+  {
+    std::vector<int> z2(1, 0);
+    if ((rc = dev_upload_rw(sim, &s.tick_link, z2))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.tick_node, z2))) return rc;
+    std::vector<u64> zc(8, 0);
+    if ((rc = dev_upload_rw(sim, &s.counters, zc))) return rc;
+    std::vector<int> ze(4, 0);
+    if ((rc = dev_upload_rw(sim, &s.err, ze))) return rc;
+  }
+  sim->h_ring_base = ring_base; sim->h_ring_mask = ring_mask;
+  sim->h_virtual.assign(d->link_is_virtual, d->link_is_virtual + L);
+  sim->h_capacity.assign(d->link_capacity, d->link_capacity + L);
+  sim->h_maxmph.assign(d->link_maxmph, d->link_maxmph + L);
+  sim->h_fft.assign(d->link_fft, d->link_fft + L);
+  return SQ_OK;
+}
+
+static int launch_tick(SqSim* sim, cudaStream_t st) {
+  const int L = sim->L, N = sim->N;
+  k_link_phase<<<(L + 255) / 256, 256, 0, st>>>(sim->st);
+  k_node_phase<<<(N + 63) / 64, 64, 0, st>>>(sim->st);
+  return SQ_OK;
+}
+
+static int arm_tick(SqSim* sim, int t) {
+  if (sim->next_t != t) {
+    SQ_CUDA_TRY(cudaMemcpyAsync(sim->st.tick_link, &t, sizeof(int), cudaMemcpyHostToDevice, sim->stream));
+    SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));  // &t is a stack variable
+  }
+  return SQ_OK;
+}
+
+static int check_device_error(SqSim* sim) {
+  int e[4];
+  SQ_CUDA_TRY(cudaMemcpyAsync(e, sim->st.err, sizeof(e), cudaMemcpyDeviceToHost, sim->stream));
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  if (e[0] == 0) return SQ_OK;
+  static const char* what[] = {"", "queued vehicle has no next link away from its destination (queue_class.py:312-314)",
+                               "vehicle's next link does not leave this node (KeyError at queue_class.py:257-262)",
+                               "vehicle ring overflow (link storage bound violated)"};
+  return sq::set_error(SQ_ERR_STATE, "%s: agent %d, node %d, link %d", what[e[0] < 4 ? e[0] : 0], e[1], e[2], e[3]);
+}
+
+extern "C" {
+
+SqSim* sq_create(const SqNetDesc* desc) {
+  if (!desc) { sq::set_error(SQ_ERR_ARG, "sq_create: null description"); return nullptr; }
+  SqSim* sim = new SqSim();
+  if (sim_build(sim, desc) != SQ_OK) { sq_destroy(sim); return nullptr; }
+  return sim;
+}
+
+void sq_destroy(SqSim* sim) {
+  if (!sim) return;
+  if (sim->graph) cudaGraphExecDestroy(sim->graph);
+  for (void* p : sim->allocs) cudaFree(p);
+  cudaFree(sim->d_pool);
+  if (sim->stream) cudaStreamDestroy(sim->stream);
+  delete sim;
+}
+
+int sq_step(SqSim* sim, int32_t t) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_step: null sim");
+  if (int rc = arm_tick(sim, t)) return rc;
+  launch_tick(sim, sim->stream);
+  SQ_CUDA_TRY(cudaGetLastError());
+  sq::count_launch(2); sim->launches += 2;
+  sim->next_t = t + 1;
+  return SQ_OK;
+}
+
+int sq_run(SqSim* sim, int32_t t0, int32_t n) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_run: null sim");
+  if (n <= 0) return SQ_OK;
+  if (int rc = arm_tick(sim, t0)) return rc;
+  const int G = 32;  // ticks per graph launch
+  if (!sim->graph && n >= G) {
+    cudaGraph_t g;
+    SQ_CUDA_TRY(cudaStreamBeginCapture(sim->stream, cudaStreamCaptureModeThreadLocal));
+    for (int i = 0; i < G; ++i) launch_tick(sim, sim->stream);
+    SQ_CUDA_TRY(cudaStreamEndCapture(sim->stream, &g));
+    SQ_CUDA_TRY(cudaGraphInstantiate(&sim->graph, g, 0));
+    cudaGraphDestroy(g);
+    sim->graph_ticks = G;
+  }
+  int left = n;
+  while (sim->graph && left >= sim->graph_ticks) {
+    SQ_CUDA_TRY(cudaGraphLaunch(sim->graph, sim->stream));
+    left -= sim->graph_ticks;
+  }
+  for (int i = 0; i < left; ++i) launch_tick(sim, sim->stream);
+  SQ_CUDA_TRY(cudaGetLastError());
+  sq::count_launch(2ll * n); sim->launches += 2ll * n;
+  sim->next_t = t0 + n;
+  return SQ_OK;
+}
+
+int sq_sync(SqSim* sim) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_sync: null sim");
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  return check_device_error(sim);
+}
+
+int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t* ptr, const int32_t* links) {
+  if (!sim || (n > 0 && (!agent_idx || !ptr))) return sq::set_error(SQ_ERR_ARG, "sq_set_routes: null argument");
+  if (n <= 0) return SQ_OK;
+  const long long add = ptr[n] - ptr[0];
+  for (int i = 0; i < n; ++i)
+    if (agent_idx[i] < 0 || agent_idx[i] >= sim->A) return sq::set_error(SQ_ERR_ARG, "sq_set_routes: agent index %d out of range", agent_idx[i]);
+  for (long long k = ptr[0]; k < ptr[n]; ++k)
+    if (links[k] < 0 || links[k] >= sim->L) return sq::set_error(SQ_ERR_ARG, "sq_set_routes: link %d out of range", links[k]);
+  if (sim->pool_used + add > sim->pool_cap) {
+    // grow the pool (old routes stay where they are; superseded ones become garbage until the next rebuild)
+    const long long ncap = (sim->pool_used + add) * 2 + 4096;
+    int* np_ = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&np_, sizeof(int) * (size_t)ncap));
+    SQ_CUDA_TRY(cudaMemcpyAsync(np_, sim->d_pool, sizeof(int) * (size_t)sim->pool_used, cudaMemcpyDeviceToDevice, sim->stream));
+    SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+    cudaFree(sim->d_pool);
+    sim->d_pool = np_; sim->pool_cap = ncap; sim->st.route_pool = np_;
+    if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel params changed
+  }
+  std::vector<long long> off(n);
+  std::vector<int> len(n);
+  for (int i = 0; i < n; ++i) { off[i] = sim->pool_used + (ptr[i] - ptr[0]); len[i] = (int)(ptr[i + 1] - ptr[i]); }
+  int* d_idx = nullptr; long long* d_off = nullptr; int* d_len = nullptr;
+  SQ_CUDA_TRY(cudaMalloc(&d_idx, sizeof(int) * (size_t)n));
+  SQ_CUDA_TRY(cudaMalloc(&d_off, sizeof(long long) * (size_t)n));
+  SQ_CUDA_TRY(cudaMalloc(&d_len, sizeof(int) * (size_t)n));
+  if (add > 0)
+    SQ_CUDA_TRY(cudaMemcpyAsync(sim->d_pool + sim->pool_used, links + ptr[0], sizeof(int) * (size_t)add, cudaMemcpyHostToDevice, sim->stream));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_idx, agent_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, sim->stream));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_off, off.data(), sizeof(long long) * (size_t)n, cudaMemcpyHostToDevice, sim->stream));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_len, len.data(), sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, sim->stream));
+  k_set_routes<<<(n + 127) / 128, 128, 0, sim->stream>>>(sim->st, n, d_idx, d_off, d_len);
+  sq::count_launch(); sim->launches += 1;
+  SQ_CUDA_TRY(cudaGetLastError());
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  cudaFree(d_idx); cudaFree(d_off); cudaFree(d_len);
+  sim->pool_used += add;
+  return SQ_OK;
+}
+
+int sq_set_link_closed(SqSim* sim, int32_t n, const int32_t* link_idx, const uint8_t* closed) {
+  if (!sim || (n > 0 && (!link_idx || !closed))) return sq::set_error(SQ_ERR_ARG, "sq_set_link_closed: null argument");
+  if (n <= 0) return SQ_OK;
+  for (int i = 0; i < n; ++i) {
+    if (link_idx[i] < 0 || link_idx[i] >= sim->L) return sq::set_error(SQ_ERR_ARG, "link index %d out of range", link_idx[i]);
+    sim->h_closed[link_idx[i]] = closed[i];
+  }
+  int* d_idx = nullptr; unsigned char* d_c = nullptr;
+  SQ_CUDA_TRY(cudaMalloc(&d_idx, sizeof(int) * (size_t)n));
+  SQ_CUDA_TRY(cudaMalloc(&d_c, (size_t)n));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_idx, link_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, sim->stream));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_c, closed, (size_t)n, cudaMemcpyHostToDevice, sim->stream));
+  k_set_closed<<<(n + 127) / 128, 128, 0, sim->stream>>>(sim->st, n, d_idx, d_c);
+  sq::count_launch(); sim->launches += 1;
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  cudaFree(d_idx); cudaFree(d_c);
+  return SQ_OK;
+}
+
+}  // extern "C"
+
+template <typename T>
+static int fetch(SqSim* sim, std::vector<T>& h, const T* d, size_t n) {
+  h.resize(n);
+  SQ_CUDA_TRY(cudaMemcpyAsync(h.data(), d, n * sizeof(T), cudaMemcpyDeviceToHost, sim->stream));
+  return SQ_OK;
+}
+
+extern "C" {
+
+int sq_get_link_state(SqSim* sim, int32_t* q, int32_t* r, int32_t* left, double* in_c, double* out_c, double* st) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "null sim");
+  const size_t L = (size_t)sim->L;
+  std::vector<unsigned> h, qt, tl;
+  int rc;
+  if ((rc = fetch(sim, h, sim->st.head, L)) || (rc = fetch(sim, qt, sim->st.qtail, L)) || (rc = fetch(sim, tl, sim->st.tail, L))) return rc;
+  if (left) SQ_CUDA_TRY(cudaMemcpyAsync(left, sim->st.total_left, L * sizeof(int), cudaMemcpyDeviceToHost, sim->stream));
+  if (in_c) SQ_CUDA_TRY(cudaMemcpyAsync(in_c, sim->st.in_c, L * sizeof(double), cudaMemcpyDeviceToHost, sim->stream));
+  if (out_c) SQ_CUDA_TRY(cudaMemcpyAsync(out_c, sim->st.out_c, L * sizeof(double), cudaMemcpyDeviceToHost, sim->stream));
+  if (st) SQ_CUDA_TRY(cudaMemcpyAsync(st, sim->st.storage_c, L * sizeof(double), cudaMemcpyDeviceToHost, sim->stream));
+  if ((rc = sq_sync(sim))) return rc;
+  for (size_t l = 0; l < L; ++l) {
+    if (q) q[l] = (int)(qt[l] - h[l]);
+    if (r) r[l] = (int)(tl[l] - qt[l]);
+  }
+  return SQ_OK;
+}
+
+int sq_get_link_vehicles(SqSim* sim, int64_t* ptr, int32_t* agents) {
+  if (!sim || !ptr || !agents) return sq::set_error(SQ_ERR_ARG, "null argument");
+  const size_t L = (size_t)sim->L;
+  std::vector<unsigned> h, tl;
+  std::vector<int2> ring;
+  int rc;
+  if ((rc = fetch(sim, h, sim->st.head, L)) || (rc = fetch(sim, tl, sim->st.tail, L)) ||
+      (rc = fetch(sim, ring, (const int2*)sim->st.ring, (size_t)sim->ring_slots))) return rc;
+  if ((rc = sq_sync(sim))) return rc;
+  int64_t n = 0;
+  for (size_t l = 0; l < L; ++l) {
+    ptr[l] = n;
+    for (unsigned i = h[l]; i != tl[l]; ++i) {
+      if (n >= sim->A) return sq::set_error(SQ_ERR_STATE, "more vehicles on links than agents");
+      agents[n++] = ring[(size_t)sim->h_ring_base[l] + (i & sim->h_ring_mask[l])].x;
+    }
+  }
+  ptr[L] = n;
+  return SQ_OK;
+}
+
+int sq_get_agent_state(SqSim* sim, uint8_t* status, int32_t* cur, int32_t* next, int32_t* enter, int32_t* arrive) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "null sim");
+  const size_t A = (size_t)sim->A;
+  std::vector<int4> rec;
+  int rc;
+  if ((rc = fetch(sim, rec, (const int4*)sim->st.a_rec, A))) return rc;
+  if (arrive) SQ_CUDA_TRY(cudaMemcpyAsync(arrive, sim->st.a_arrive, A * sizeof(int), cudaMemcpyDeviceToHost, sim->stream));
+  if ((rc = sq_sync(sim))) return rc;
+  for (size_t a = 0; a < A; ++a) {
+    if (status) status[a] = (uint8_t)(rec[a].w & 0xff);
+    if (cur) cur[a] = rec[a].y;
+    if (next) next[a] = rec[a].x;
+    if (enter) enter[a] = rec[a].z;
+  }
+  return SQ_OK;
+}
+
+int sq_get_node_state(SqSim* sim, int64_t* node_move) {
+  if (!sim || !node_move) return sq::set_error(SQ_ERR_ARG, "null argument");
+  SQ_CUDA_TRY(cudaMemcpyAsync(node_move, sim->st.node_move, sizeof(long long) * (size_t)sim->N, cudaMemcpyDeviceToHost, sim->stream));
+  return sq_sync(sim);
+}
+
+int sq_get_link_weights(SqSim* sim, double* w) {
+  if (!sim || !w) return sq::set_error(SQ_ERR_ARG, "null argument");
+  const size_t L = (size_t)sim->L;
+  std::vector<unsigned> h, qt;
+  int rc;
+  if ((rc = fetch(sim, h, sim->st.head, L)) || (rc = fetch(sim, qt, sim->st.qtail, L))) return rc;
+  if ((rc = sq_sync(sim))) return rc;
+  for (size_t l = 0; l < L; ++l) {
+    if (sim->h_closed[l] || sim->h_virtual[l]) { w[l] = NAN; continue; }
+    const double q = (double)(int)(qt[l] - h[l]);
+    w[l] = q / (sim->h_capacity[l] + 0.1) * 3600 * 25 / sim->h_maxmph[l] + sim->h_fft[l];
+  }
+  return SQ_OK;
+}
+
+int sq_get_counters(SqSim* sim, int64_t* out6) {
+  if (!sim || !out6) return sq::set_error(SQ_ERR_ARG, "null argument");
+  u64 c[8];
+  SQ_CUDA_TRY(cudaMemcpyAsync(c, sim->st.counters, sizeof(c), cudaMemcpyDeviceToHost, sim->stream));
+  if (int rc = sq_sync(sim)) return rc;
+  out6[0] = (int64_t)c[0];
+  out6[1] = (int64_t)(c[1] + (c[0] > 0 ? c[5] - c[4] : 0));  // + vehicles on links after the last tick
+  out6[2] = (int64_t)c[2]; out6[3] = (int64_t)c[3]; out6[4] = (int64_t)c[4];
+  out6[5] = sim->launches;
+  return SQ_OK;
+}
+
+const char* sq_last_error(void) { return sq::err_buf(); }
+long long sq_kernel_launches(void) { return sq::launch_counter().load(); }
+
+}  // extern "C"
