@@ -1,0 +1,440 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurements of the two hot paths on B200 (contract: task brief, section 4).
+
+Top level of the JSON line = HP-2, the batched reroute SSSP (BASELINE.json config 5: 224x224 grid, 199,808
+links, 50,176 nodes), because that is the path that shards across GPUs.  One step = one batch of `--batch`
+origins per GPU, full f64 trees + canonical predecessors written to HBM; N>1 is weak scaling (every rank
+gets its own `--batch` origins) and the step then ends with the all-gather of the int32 next-hop tables.
+The `tick` object (N=1, rank 0) = HP-1 on BASELINE.json config 4: 159x159 grid (100,488 real + 25,281 source
+links), 1M agents departing over 2 h, 14,400 one-second ticks, measured as agent-steps/s.
+
+`--impl reference` times the CPU side instead: oracle/_ref/liblsp.so (the reference's own sp library compiled
+from its sources) on every host core for HP-2, and the C restatement of the tick (oracle/tick_oracle.c, one
+core: the reference tick has no parallel mode and is Python, which cannot travel to the GPU box) for HP-1.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from spatial_queue_b200 import synth  # noqa: E402
+
+SSSP_GRID = 224
+TICK_GRID = 159
+TICK_AGENTS = 1_000_000
+TICK_TICKS = 14_400
+TICK_HORIZON = 7_200
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [x for x in sm if mx and x > 0.5 * mx[0]] or sm
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": mx[0] if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# HP-2 workload
+# ---------------------------------------------------------------------------------------------------------------
+def sssp_workload(n=SSSP_GRID):
+    f = synth.flat_grid(n, seed=1)
+    return f.edge_start, f.edge_end, f.edge_fft, n * n
+
+
+def origins_for(rank, batch, V, step=0):
+    perm = np.random.default_rng(1234 + step).permutation(V)
+    idx = (np.arange(batch) + rank * batch) % V
+    return perm[idx].astype(np.int32)
+
+
+def _ref_worker(args):
+    s, e, w, origins = args
+    from oracle import sssp as osssp
+    g = osssp.RefGraph(s, e, w, max_vertex_id=int(max(s.max(), e.max())))
+    t0 = time.perf_counter()
+    g.time_trees(origins)
+    return time.perf_counter() - t0
+
+
+def sssp_reference_trees_per_s(s, e, w, V, n_trees_per_core, cores):
+    """The reference's own library on `cores` processes (its only parallel strategy, util/dta_meso.py:513-536)."""
+    import multiprocessing as mp
+    from oracle import sssp as osssp
+    if not osssp.ref_available():
+        return None
+    chunks = [(s, e, w, origins_for(c, n_trees_per_core, V, step=99)) for c in range(cores)]
+    ctx = mp.get_context("fork")
+    t0 = time.perf_counter()
+    with ctx.Pool(cores) as pool:
+        pool.map(_ref_worker, chunks)
+    wall = time.perf_counter() - t0
+    return cores * n_trees_per_core / wall
+
+
+def calibrate_ref_trees(s, e, w, V, target_s):
+    from oracle import sssp as osssp
+    g = osssp.RefGraph(s, e, w, max_vertex_id=V - 1)
+    t0 = time.perf_counter()
+    g.time_trees(origins_for(0, 8, V, step=98))
+    per = (time.perf_counter() - t0) / 8
+    return max(8, int(target_s / per)), per
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# HP-1 workload
+# ---------------------------------------------------------------------------------------------------------------
+def tick_bytes(counters, n_links):
+    """Algorithmic bytes of a run: 48 B per link per tick + 8 B per on-link vehicle-step + 48 B per
+    move + 16 B per active node."""
+    return (48 * n_links * counters["ticks"] + 8 * counters["agent_steps"] + 48 * counters["moves"]
+            + 16 * counters["active_nodes"])
+
+
+def flat_nbytes(f):
+    return int(sum(v.nbytes for v in f.as_dict().values()))
+
+
+def run_tick_gpu(args, torch, peak):
+    from spatial_queue_b200.tick import DeviceSim
+    t0 = time.perf_counter()
+    flat = synth.grid_scenario(args.tick_grid, args.tick_agents, horizon=TICK_HORIZON, seed=1)
+    build_s = time.perf_counter() - t0
+    L = len(flat.link_end_node)
+    stream = torch.cuda.current_stream().cuda_stream
+    res = {}
+    # device-resident run: state already in HBM when the clock starts
+    warm = DeviceSim(flat, seed=7)                       # throwaway instance: first-launch costs, cold caches
+    warm.set_stream(stream)
+    warm.run(0, 256); warm.sync(); warm.close()
+    best = None
+    for rep in range(max(1, args.tick_reps)):
+        sim = DeviceSim(flat, seed=7)
+        sim.set_stream(stream)
+        sim.sync()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evw = torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        sim.run(0, args.cpu_window)
+        evw.record()
+        sim.run(args.cpu_window, args.tick_ticks - args.cpu_window)
+        ev1.record()
+        sim.sync()
+        ms = ev0.elapsed_time(ev1)
+        c = sim.counters()
+        if best is None or ms < best[0]:
+            best = (ms, ev0.elapsed_time(evw), c)
+        if rep + 1 < max(1, args.tick_reps):
+            sim.close()
+    ms, ms_window, c = best
+    res["value"] = c["agent_steps"] / (ms / 1e3)
+    res["ms_per_tick"] = ms / args.tick_ticks
+    res["counters"] = c
+    nbytes = tick_bytes(c, L)
+    res["roofline"] = {"bound": "hbm", "achieved": nbytes / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                       "traffic": None, "bytes_per_tick": nbytes / max(c["ticks"], 1)}
+    res["roofline"]["frac"] = res["roofline"]["achieved"] / peak
+    arrive = sim.agent_state()["arrive_tick"]
+    sim.close()
+    # end to end: host arrays in, full run, arrival ticks + link state out
+    t0 = time.perf_counter()
+    sim = DeviceSim(flat, seed=7)
+    sim.run(0, args.tick_ticks)
+    ag = sim.agent_state()
+    ls = sim.link_state()
+    wall = time.perf_counter() - t0
+    assert (ag["arrive_tick"] == arrive).all(), "two runs of the same scenario differ"
+    c2 = sim.counters()
+    sim.close()
+    res["e2e"] = {"value": c2["agent_steps"] / wall, "unit": "agent-steps/s", "wall_s": wall,
+                  "h2d_bytes_per_step": flat_nbytes(flat),
+                  "d2h_bytes_per_step": int(sum(v.nbytes for v in ag.values()) + sum(v.nbytes for v in ls.values()))}
+    res["window_ticks"] = args.cpu_window
+    res["window_ms"] = ms_window
+    res["build_s"] = build_s
+    res["arrived"] = int((arrive >= 0).sum())
+    return res, flat
+
+
+def run_tick_cpu(flat, ticks):
+    from oracle.tick import OracleSim
+    sim = OracleSim(flat, seed=7)
+    t0 = time.perf_counter()
+    sim.run(0, ticks)
+    wall = time.perf_counter() - t0
+    c = sim.counters()
+    sim.close()
+    return c["agent_steps"] / wall, wall, c
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def reference_arm(args, rank, world):
+    """CPU implementation of both paths on the host cores; rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import sssp as osssp
+    from oracle import tick as _  # noqa: F401  (builds nothing; import check)
+    s, e, w, V = sssp_workload(args.sssp_grid)
+    cores = os.cpu_count() or 1
+    kind = "reference" if osssp.ref_available() else "port"
+    per_core, per_tree = calibrate_ref_trees(s, e, w, V, target_s=args.ref_seconds) if kind == "reference" else (64, None)
+    times = []
+    for step in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        if kind == "reference":
+            tps = sssp_reference_trees_per_s(s, e, w, V, per_core, cores)
+        else:
+            og = osssp.OracleGraph(s, e, w)
+            t1 = time.perf_counter()
+            og.sssp_batch(origins_for(0, per_core, V, step=99))
+            tps = per_core / (time.perf_counter() - t1)
+            cores = 1
+        if step >= args.warmup:
+            times.append(tps)
+    value = float(np.mean(times))
+    sample = f"{per_core} full trees per core x {cores} processes per step on the {args.sssp_grid}x{args.sssp_grid} grid"
+    line = {"impl": "reference", "metric": "sssp_trees_per_s", "value": value, "unit": "trees/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * cores * per_core / value,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid",
+                       "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "trees/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "trees/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    if not args.no_tick:
+        def router(rs, re_, rw, roots):
+            og = osssp.OracleGraph(rs, re_, rw)
+            return og.sssp_batch(roots.astype(np.int32), want_dist=False)[1]
+        flat = synth.grid_scenario(args.tick_grid, args.tick_agents, horizon=TICK_HORIZON, seed=1, router=router)
+        rate, wall, c = run_tick_cpu(flat, args.cpu_window)
+        line["tick"] = {"metric": "agent_steps_per_s", "value": rate, "unit": "agent-steps/s",
+                        "cpu_baseline": {"value": rate, "unit": "agent-steps/s", "cores": 1, "kind": "port",
+                                         "sample": f"ticks 0..{args.cpu_window - 1} of config 4 ({wall:.1f} s)"}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=8192, help="SSSP origins per GPU per step")
+    ap.add_argument("--sssp-grid", type=int, default=SSSP_GRID)
+    ap.add_argument("--tick-grid", type=int, default=TICK_GRID)
+    ap.add_argument("--tick-agents", type=int, default=TICK_AGENTS)
+    ap.add_argument("--tick-ticks", type=int, default=TICK_TICKS)
+    ap.add_argument("--tick-reps", type=int, default=1)
+    ap.add_argument("--cpu-window", type=int, default=1800, help="ticks of config 4 the CPU tick baseline runs")
+    ap.add_argument("--ref-seconds", type=float, default=10.0, help="CPU seconds per reference-arm step")
+    ap.add_argument("--no-tick", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-gather", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from spatial_queue_b200 import _lib, sp_interface as spi
+    peak, peak_src = measured_peaks()
+
+    # ---- HP-2 -------------------------------------------------------------------------------------------------
+    s, e, w, V = sssp_workload(args.sssp_grid)
+    E = len(s)
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.sync()
+    B = args.batch
+    bytes_per_tree = 20 * E + 24 * V
+    dist_dev = torch.empty((B, V), dtype=torch.float64, device="cuda")
+    par_dev = torch.empty((B, V), dtype=torch.int32, device="cuda")
+    gathered = None
+    if world > 1 and not args.no_gather:
+        gathered = torch.empty((world * B, V), dtype=torch.int32, device="cuda")
+    origins_dev = [torch.from_numpy(origins_for(rank, B, V, step=i)).cuda() for i in range(args.warmup + args.steps)]
+    launches0 = _lib.lib().sp_kernel_launches()
+
+    def step(i, ev=None):
+        if ev:
+            ev[0].record()
+        g.sssp_batch_device(origins_dev[i], dist_dev, par_dev)
+        if ev:
+            ev[1].record()
+        if gathered is not None:
+            dist.all_gather_into_tensor(gathered, par_dev)
+
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_ev0, t_ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_ev0.record()
+    for i in range(args.steps):
+        step(args.warmup + i, kev[i])
+    t_ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms_total = t_ev0.elapsed_time(t_ev1)
+    if world > 1:
+        tmax = torch.tensor([ms_total], device="cuda")
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        ms_total = float(tmax.item())
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
+    launches = _lib.lib().sp_kernel_launches() - launches0 - 0
+    value = world * B * args.steps / (ms_total / 1e3)
+
+    # ---- e2e through the host-buffer C ABI (origins in host memory -> dist + parent in host memory) -------------
+    e2e = None
+    if rank == 0 or world > 1:
+        eb = min(B, 2048)
+        oh = origins_for(rank, eb, V, step=7)
+        g.sssp_batch(oh[:64])
+        t0 = time.perf_counter()
+        reps = 2
+        for _ in range(reps):
+            dh, ph = g.sssp_batch(oh)
+        wall = time.perf_counter() - t0
+        e2e_val = world * eb * reps / wall
+        if world > 1:
+            tw = torch.tensor([wall], device="cuda")
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+            e2e_val = world * eb * reps / float(tw.item())
+        e2e = {"value": e2e_val, "unit": "trees/s", "h2d_bytes_per_step": int(oh.nbytes),
+               "d2h_bytes_per_step": int(dh.nbytes + ph.nbytes), "trees_per_call": eb}
+
+    clocks = sampler.stop() if rank == 0 else None
+    line = None
+    if rank == 0:
+        achieved = bytes_per_tree * B / (kernel_ms / 1e3) / 1e9
+        line = {"metric": "sssp_trees_per_s", "value": value, "unit": "trees/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid "
+                                       f"({E} links, {V} nodes), {B} origins per GPU per step, full trees + canonical "
+                                       f"predecessors" + (", int32 next-hop tables all-gathered" if gathered is not None else ""),
+                           "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
+                           "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "kernel": "sssp_nearfar_kernel", "kernel_ms": kernel_ms,
+                             "bytes_per_tree": bytes_per_tree, "peak_source": peak_src},
+                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+
+    # ---- HP-1 + CPU baselines: single GPU, rank 0 ----------------------------------------------------------------
+    if rank == 0 and world == 1:
+        del dist_dev, par_dev
+        torch.cuda.empty_cache()
+        if not args.no_cpu:
+            from oracle import sssp as osssp
+            cores = os.cpu_count() or 1
+            if osssp.ref_available():
+                per_core, per_tree = calibrate_ref_trees(s, e, w, V, target_s=args.ref_seconds)
+                tps = sssp_reference_trees_per_s(s, e, w, V, per_core, cores)
+                line["cpu_baseline"] = {"value": tps, "unit": "trees/s", "cores": cores, "kind": "reference",
+                                        "sample": f"{per_core} full trees per core x {cores} processes, same graph "
+                                                  f"(oracle/_ref/liblsp.so; one core: {1 / per_tree:.1f} trees/s)"}
+            else:
+                og = osssp.OracleGraph(s, e, w)
+                t1 = time.perf_counter()
+                og.sssp_batch(origins_for(0, 256, V, step=99))
+                line["cpu_baseline"] = {"value": 256 / (time.perf_counter() - t1), "unit": "trees/s", "cores": 1,
+                                        "kind": "port", "sample": "256 full trees, oracle/sssp_oracle.c"}
+        if not args.no_tick:
+            l0 = _lib.lib().sq_kernel_launches()
+            tick, flat = run_tick_gpu(args, torch, peak)
+            tick_line = {"metric": "agent_steps_per_s", "value": tick["value"], "unit": "agent-steps/s",
+                         "ms_per_tick": tick["ms_per_tick"], "dtype": "i32 state + f64 capacities",
+                         "config": {"workload": f"config 4: {args.tick_grid}x{args.tick_grid} grid, "
+                                                f"{len(flat.link_end_node)} links, {args.tick_agents} agents over "
+                                                f"{TICK_HORIZON} s, {args.tick_ticks} ticks, routes fixed at t=0"},
+                         "counters": tick["counters"], "arrived": tick["arrived"], "roofline": tick["roofline"],
+                         "e2e": tick["e2e"], "gpu_launches": int(_lib.lib().sq_kernel_launches() - l0)}
+            if not args.no_cpu:
+                rate, wall, c = run_tick_cpu(flat, args.cpu_window)
+                gpu_same = c["agent_steps"] / ((tick["window_ms"]) / 1e3)
+                tick_line["cpu_baseline"] = {"value": rate, "unit": "agent-steps/s", "cores": 1, "kind": "port",
+                                             "sample": f"ticks 0..{args.cpu_window - 1} of the same run "
+                                                       f"({wall:.1f} s, oracle/tick_oracle.c)",
+                                             "gpu_same_window": gpu_same}
+            line["tick"] = tick_line
+            line["gpu_launches"] += tick_line["gpu_launches"]
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -80,6 +80,9 @@ void sq_destroy(SqSim* sim);
 int sq_step(SqSim* sim, int32_t t);
 /* n consecutive ticks t0 .. t0+n-1 (replayed as CUDA graphs of tick pairs). */
 int sq_run(SqSim* sim, int32_t t0, int32_t n);
+/* Run all later work of this sim on `stream` (a cudaStream_t passed as void*, e.g. torch's current stream)
+ * instead of the sim's own stream, so a caller can bracket it with its own events. */
+int sq_set_stream(SqSim* sim, void* stream);
 /* Wait for the device and report any device-side error. */
 int sq_sync(SqSim* sim);
 

@@ -60,6 +60,7 @@ def _declare(L):
     L.sq_step.restype = ci; L.sq_step.argtypes = [vp, i32]
     L.sq_run.restype = ci; L.sq_run.argtypes = [vp, i32, i32]
     L.sq_sync.restype = ci; L.sq_sync.argtypes = [vp]
+    L.sq_set_stream.restype = ci; L.sq_set_stream.argtypes = [vp, vp]
     L.sq_set_routes.restype = ci; L.sq_set_routes.argtypes = [vp, i32, vp, vp, vp]
     L.sq_set_link_closed.restype = ci; L.sq_set_link_closed.argtypes = [vp, i32, vp, vp]
     L.sq_get_link_state.restype = ci; L.sq_get_link_state.argtypes = [vp] * 7

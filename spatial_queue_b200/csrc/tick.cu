@@ -457,6 +457,7 @@ struct SqSim {
   int* d_pool = nullptr;
   long long pool_cap = 0, pool_used = 0;
   cudaStream_t stream = nullptr;
+  bool own_stream = true;
   int next_t = INT_MIN;  // tick the device counters are armed for
   long long launches = 0;
   cudaGraphExec_t graph = nullptr;
@@ -657,6 +658,20 @@ static int launch_tick(SqSim* sim, cudaStream_t st) {
   return SQ_OK;
 }
 
+static const int kGraphTicks = 32;  // ticks per CUDA-graph launch
+
+static int build_graph(SqSim* sim) {
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }
+  cudaGraph_t g;
+  SQ_CUDA_TRY(cudaStreamBeginCapture(sim->stream, cudaStreamCaptureModeThreadLocal));
+  for (int i = 0; i < kGraphTicks; ++i) launch_tick(sim, sim->stream);
+  SQ_CUDA_TRY(cudaStreamEndCapture(sim->stream, &g));
+  SQ_CUDA_TRY(cudaGraphInstantiate(&sim->graph, g, 0));
+  cudaGraphDestroy(g);
+  sim->graph_ticks = kGraphTicks;
+  return SQ_OK;
+}
+
 static int arm_tick(SqSim* sim, int t) {
   if (sim->next_t != t) {
     SQ_CUDA_TRY(cudaMemcpyAsync(sim->st.tick_link, &t, sizeof(int), cudaMemcpyHostToDevice, sim->stream));
@@ -681,7 +696,7 @@ extern "C" {
 SqSim* sq_create(const SqNetDesc* desc) {
   if (!desc) { sq::set_error(SQ_ERR_ARG, "sq_create: null description"); return nullptr; }
   SqSim* sim = new SqSim();
-  if (sim_build(sim, desc) != SQ_OK) { sq_destroy(sim); return nullptr; }
+  if (sim_build(sim, desc) != SQ_OK || build_graph(sim) != SQ_OK) { sq_destroy(sim); return nullptr; }
   return sim;
 }
 
@@ -690,7 +705,7 @@ void sq_destroy(SqSim* sim) {
   if (sim->graph) cudaGraphExecDestroy(sim->graph);
   for (void* p : sim->allocs) cudaFree(p);
   cudaFree(sim->d_pool);
-  if (sim->stream) cudaStreamDestroy(sim->stream);
+  if (sim->stream && sim->own_stream) cudaStreamDestroy(sim->stream);
   delete sim;
 }
 
@@ -708,16 +723,8 @@ int sq_run(SqSim* sim, int32_t t0, int32_t n) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_run: null sim");
   if (n <= 0) return SQ_OK;
   if (int rc = arm_tick(sim, t0)) return rc;
-  const int G = 32;  // ticks per graph launch
-  if (!sim->graph && n >= G) {
-    cudaGraph_t g;
-    SQ_CUDA_TRY(cudaStreamBeginCapture(sim->stream, cudaStreamCaptureModeThreadLocal));
-    for (int i = 0; i < G; ++i) launch_tick(sim, sim->stream);
-    SQ_CUDA_TRY(cudaStreamEndCapture(sim->stream, &g));
-    SQ_CUDA_TRY(cudaGraphInstantiate(&sim->graph, g, 0));
-    cudaGraphDestroy(g);
-    sim->graph_ticks = G;
-  }
+  if (!sim->graph && n >= kGraphTicks)
+    if (int rc = build_graph(sim)) return rc;
   int left = n;
   while (sim->graph && left >= sim->graph_ticks) {
     SQ_CUDA_TRY(cudaGraphLaunch(sim->graph, sim->stream));
@@ -727,6 +734,14 @@ int sq_run(SqSim* sim, int32_t t0, int32_t n) {
   SQ_CUDA_TRY(cudaGetLastError());
   sq::count_launch(2ll * n); sim->launches += 2ll * n;
   sim->next_t = t0 + n;
+  return SQ_OK;
+}
+
+int sq_set_stream(SqSim* sim, void* stream) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_set_stream: null sim");
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  if (sim->own_stream) { cudaStreamDestroy(sim->stream); sim->own_stream = false; }
+  sim->stream = (cudaStream_t)stream;
   return SQ_OK;
 }
 

@@ -68,3 +68,180 @@ def grid_od(n, n_agents, seed=2, horizon=7200, exits=None):
     dept = 1 + (np.arange(n_agents) * horizon) // max(n_agents, 1)
     return pd.DataFrame({"origin_osmid": 10_000_000 + origin, "destin_osmid": 10_000_000 + destin,
                          "dept_time": dept, "type": "local"})
+
+
+# ---- direct flat construction for large synthetic cases (no Python objects) ----------------------------------
+
+def _utm10n_np(lon, lat):
+    """Vectorised twin of geo.utm10n."""
+    from . import geo
+    phi = np.radians(lat)
+    lam = np.radians(lon) - geo._LON0
+    e = 2.0 * np.sqrt(geo._N) / (1.0 + geo._N)
+    t = np.sinh(np.arctanh(np.sin(phi)) - e * np.arctanh(e * np.sin(phi)))
+    xi = np.arctan2(t, np.cos(lam))
+    eta = np.arctanh(np.sin(lam) / np.sqrt(1.0 + t * t))
+    x, y = eta.copy(), xi.copy()
+    for j, a in enumerate(geo._ALPHA, start=1):
+        x += a * np.cos(2 * j * xi) * np.sinh(2 * j * eta)
+        y += a * np.sin(2 * j * xi) * np.cosh(2 * j * eta)
+    return geo._FE + geo._K0 * geo._AHAT * x, geo._K0 * geo._AHAT * y
+
+
+def flat_grid(n, seed=1, arterial_every=8):
+    """FlatNetwork (without agents) of the n x n grid, built with array operations only but following the
+    loader's rules (queue_class.py:54-62, 137-176, 416): virtual source links first in node order, then the real
+    links in edge order; incoming order = that order filtered by end node; turn angles from the projected
+    two-point geometry with the reference's wrap rule."""
+    from .flatten import FlatNetwork
+    lon, lat = grid_coords(n, seed)
+    s, e = grid_edges(n)
+    length, lanes, maxmph = grid_attributes(n, s, e, lon, lat, arterial_every)
+    N, E = n * n, len(s)
+    L = N + E
+    fft = length / maxmph * 2.237
+    capacity = (1900 * lanes).astype(np.float64)
+    x, y = _utm10n_np(lon, lat)
+    ang = np.arctan2(y[e] - y[s], x[e] - x[s])   # in_angle == out_angle for a straight two-point link
+
+    f = FlatNetwork()
+    f.node_key = np.arange(N, dtype=np.int64)
+    f.link_start_node = np.concatenate([np.full(N, -1), s]).astype(np.int32)
+    f.link_end_node = np.concatenate([np.arange(N), e]).astype(np.int32)
+    f.link_is_virtual = np.concatenate([np.ones(N), np.zeros(E)]).astype(np.uint8)
+    f.link_lanes_floor = np.concatenate([np.full(N, 100), lanes]).astype(np.int32)
+    cap_all = np.concatenate([np.full(N, 100000.0), capacity])
+    f.link_capacity = cap_all
+    f.link_cap_per_s = cap_all / 3600
+    f.link_storage_cap = np.concatenate([np.full(N, 18.0), np.maximum(18, length * lanes)])
+    f.link_fft = np.concatenate([np.zeros(N), fft])
+    f.link_closed = np.zeros(L, np.uint8)
+    f.link_maxmph = np.concatenate([np.full(N, 1e5), length / fft * 2.23694])
+    # reverse link: (e -> s) exists for every grid link
+    key = s * N + e
+    order = np.argsort(key, kind="stable")
+    pos = np.searchsorted(key[order], e * N + s)
+    f.link_reverse = np.concatenate([np.full(N, -1), N + order[pos]]).astype(np.int32)
+
+    # CSR of incoming (virtual first, then real in edge order) and outgoing links
+    in_order = np.argsort(e, kind="stable")
+    in_cnt = np.bincount(e, minlength=N) + 1
+    f.node_in_ptr = np.concatenate([[0], np.cumsum(in_cnt)]).astype(np.int32)
+    in_links = np.empty(f.node_in_ptr[-1], np.int32)
+    in_links[f.node_in_ptr[:-1]] = np.arange(N)
+    real_pos = np.arange(E) - np.repeat(np.concatenate([[0], np.cumsum(in_cnt - 1)])[:-1], in_cnt - 1)
+    in_links[np.repeat(f.node_in_ptr[:-1] + 1, in_cnt - 1) + real_pos] = N + in_order
+    f.node_in_links = in_links
+    out_order = np.argsort(s, kind="stable")
+    out_cnt = np.bincount(s, minlength=N)
+    f.node_out_ptr = np.concatenate([[0], np.cumsum(out_cnt)]).astype(np.int32)
+    f.node_out_links = (N + out_order).astype(np.int32)
+    f.node_in_phase = np.zeros(len(in_links), np.uint8)
+    f.node_in_prio = np.full(len(in_links), -1, np.int32)
+    f.node_type = np.zeros(N, np.uint8)
+
+    # turn table (queue_class.py:166-176)
+    tcnt = in_cnt * out_cnt
+    f.node_turn_ptr = np.concatenate([[0], np.cumsum(tcnt)]).astype(np.int64)
+    node_of_entry = np.repeat(np.arange(N), tcnt)
+    k = np.arange(f.node_turn_ptr[-1]) - f.node_turn_ptr[node_of_entry]
+    i_loc, j_loc = k // out_cnt[node_of_entry], k % out_cnt[node_of_entry]
+    il = in_links[f.node_in_ptr[node_of_entry] + i_loc]
+    ol = f.node_out_links[f.node_out_ptr[node_of_entry] + j_loc]
+    ang_all = np.concatenate([np.zeros(N), ang])
+    turn = -ang_all[il] + ang_all[ol]
+    turn = np.where(turn >= np.pi, 2 * np.pi - turn, turn)
+    turn = np.where(turn <= -np.pi, 2 * np.pi + turn, turn)
+    turn = turn / np.pi * 180
+    turn = np.where(il < N, 0.0, turn)
+    f.turn_angle = turn
+    # (start, end) -> link table
+    f.pair_start, f.pair_end, f.pair_link = s.astype(np.int32), e.astype(np.int32), (N + np.arange(E)).astype(np.int32)
+    f.edge_start, f.edge_end, f.edge_fft = s.astype(np.int32), e.astype(np.int32), fft
+    f.n_grid = n
+    return f
+
+
+def routes_from_next_hop(next_link, link_end, origin, dest_idx, max_hops):
+    """Materialise link sequences: next_link[d, v] is the link to take at node v towards destination slot d
+    (-1 at the destination).  Returns (route_ptr, route_links)."""
+    A = len(origin)
+    cur = origin.astype(np.int64).copy()
+    alive = np.arange(A)
+    cols = []
+    for _ in range(max_hops):
+        l = next_link[dest_idx[alive], cur[alive]]
+        keep = l >= 0
+        alive = alive[keep]
+        if len(alive) == 0:
+            break
+        l = l[keep]
+        cols.append((alive.copy(), l))
+        cur[alive] = link_end[l]
+    lens = np.zeros(A, np.int64)
+    for a, _ in cols:
+        lens[a] += 1
+    ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    links = np.empty(ptr[-1], np.int32)
+    for h, (a, l) in enumerate(cols):
+        links[ptr[a] + h] = l
+    return ptr, links
+
+
+def add_agents(f, origin, destin, dept, vlen, next_link, dest_nodes):
+    """Attach agents (already in network.agents order) and their routes to a flat network."""
+    A = len(origin)
+    f.agent_key = np.arange(A, dtype=np.int64)
+    f.agent_origin = origin.astype(np.int32)
+    f.agent_destin = destin.astype(np.int32)
+    f.agent_dept = dept.astype(np.int32)
+    f.agent_vlen = vlen.astype(np.int32)
+    f.agent_status = np.zeros(A, np.uint8)
+    slot = {int(d): i for i, d in enumerate(dest_nodes)}
+    dest_idx = np.array([slot[int(d)] for d in destin], np.int64) if A < 100000 else \
+        np.searchsorted(np.sort(dest_nodes), destin)
+    if A >= 100000:
+        srt = np.argsort(dest_nodes)
+        dest_idx = srt[dest_idx]
+    f.route_ptr, f.route_links = routes_from_next_hop(next_link, f.link_end_node, origin, dest_idx,
+                                                      max_hops=4 * int(np.sqrt(len(f.node_key))) + 8)
+    return f
+
+
+def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=None, router=None):
+    """The C4-style workload: n x n grid, agents from uniform origins to the exit nodes with
+    staggered departures, routed at t=0 on free-flow weights.
+
+    Routing runs on the GPU through the product library: one tree per exit on the reversed graph gives the
+    next hop of every node towards that exit (`router` may supply a callable (starts, ends, w, roots) ->
+    parent[len(roots), V] instead, which is how the CPU tests inject the oracle)."""
+    f = flat_grid(n, seed, arterial_every)
+    N = n * n
+    exits = grid_exits(n) if exits is None else np.asarray(exits, np.int64)
+    od = grid_od(n, n_agents, seed + 1, horizon, exits)
+    origin = (od.origin_osmid.values - 10_000_000).astype(np.int64)
+    destin = (od.destin_osmid.values - 10_000_000).astype(np.int64)
+    rng = np.random.default_rng(seed + 2)
+    perm = rng.permutation(n_agents)            # add_demand shuffles the OD rows (queue_class.py:198)
+    origin, destin, dept = origin[perm], destin[perm], od.dept_time.values[perm]
+    s, e, w = f.edge_start, f.edge_end, f.edge_fft
+    if router is None:
+        from . import sp_interface
+        g = sp_interface.from_arrays(e, s, w, max_vertex_id=N - 1)      # reversed graph
+        _, parent = g.sssp_batch(exits.astype(np.int32), want_dist=False)
+        g.free()
+    else:
+        parent = router(e, s, w, exits)
+    # next link at node v towards exit d: the link (v -> parent[d, v])
+    key = s.astype(np.int64) * N + e
+    order = np.argsort(key)
+    v = np.arange(N, dtype=np.int64)
+    next_link = np.full((len(exits), N), -1, np.int32)
+    for d in range(len(exits)):
+        p = parent[d].astype(np.int64)
+        ok = p >= 0
+        pos = np.searchsorted(key[order], v[ok] * N + p[ok])
+        next_link[d, v[ok]] = N + order[pos]
+    f.next_link_table = next_link
+    add_agents(f, origin, destin, dept, np.full(n_agents, 8), next_link, exits)
+    return f

@@ -148,6 +148,9 @@ class DeviceSim(_SimBase):
     def sync(self):
         self._check(self._L.sq_sync(self._h), "sync")
 
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._L.sq_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "set_stream")
+
     def close(self):
         if self._h:
             self._L.sq_destroy(self._h)
