@@ -1,0 +1,151 @@
+"""The object mirror (spatial_queue_b200/queue_class.py) against the reference's own objects.
+
+CPU part: the mirror's loader + add_connectivity + add_demand, flattened, must equal the flattening of the
+REFERENCE's objects stored in the golden files (tests/golden/tick_*.npz `flat_*`, written by make_tick_golden.py
+from the unmodified reference loader on the same CSV inputs).  GPU part: `use_gpu()` + `step(t)` + device-side
+batched rerouting replays the reference's whole run, digest for digest.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tickcheck import load_golden, state_digest
+
+from spatial_queue_b200 import flatten as fl, queue_class as qc, synth
+
+REF_BOLINAS = "/root/reference/projects/bolinas_civic"
+EMPTY = {"signal": {}, "priority": {}, "prohibition": {}, "closure": []}
+
+STATIC_FIELDS = ["node_key", "link_start_node", "link_end_node", "link_is_virtual", "link_lanes_floor", "link_cap_per_s",
+                 "link_storage_cap", "link_fft", "link_closed", "link_reverse", "link_capacity", "link_maxmph",
+                 "node_type", "node_in_ptr", "node_in_links", "node_in_phase", "node_in_prio", "node_out_ptr",
+                 "node_out_links", "node_turn_ptr", "turn_angle", "pair_start", "pair_end", "pair_link",
+                 "agent_key", "agent_origin", "agent_destin", "agent_dept", "agent_vlen"]
+
+
+def grid7s_special(n=7):
+    edges, _ = synth.grid_frames(n, seed=1, arterial_every=4)
+
+    def ins(node):
+        return [int(x) for x in edges.loc[edges.nid_e == node, "eid"]]
+    sig = {}
+    for node in (8, 24, 40):
+        il = ins(node)
+        sig[str(node)] = {"phase_1": il[0::2], "phase_2": il[1::2]}
+    pri = {str(node): list(reversed(ins(node))) for node in (16, 32)}
+    return {"signal": sig, "priority": pri, "prohibition": {}, "closure": [5, 30]}
+
+
+SCENARIOS = {
+    "grid8": dict(n=8, agents=1500, horizon=60, exits=[0, 63], special=EMPTY),
+    "grid7s": dict(n=7, agents=1200, horizon=80, exits=[0, 48, 6], special=grid7s_special()),
+}
+
+
+def build_grid(name, tmp_path):
+    """Same inputs and call sequence as tests/golden/make_tick_golden.py:grid, through the mirror."""
+    sc = SCENARIOS[name]
+    edges, nodes = synth.grid_frames(sc["n"], seed=1, arterial_every=4)
+    od = synth.grid_od(sc["n"], sc["agents"], seed=2, horizon=sc["horizon"], exits=sc["exits"])
+    wp = str(tmp_path)
+    edges.to_csv(wp + "/edges.csv", index=False)
+    nodes.to_csv(wp + "/nodes.csv", index=False)
+    od.to_csv(wp + "/od.csv", index=False)
+    np.random.seed(0)
+    net = qc.Network()
+    net.dataframe_to_network(project_location="", network_file_edges=wp + "/edges.csv",
+                             network_file_nodes=wp + "/nodes.csv", special_nodes=sc["special"], scen_nm=name)
+    net.add_connectivity()
+    net.add_demand(demand_files=["/od.csv"], write_path=wp)
+    return net, sc["special"]
+
+
+def assert_static_equal(flat, gold):
+    for k in STATIC_FIELDS:
+        a, b = np.asarray(getattr(flat, k)), np.asarray(getattr(gold, k))
+        assert a.shape == b.shape, k
+        assert a.tobytes() == b.astype(a.dtype).tobytes(), f"{k} differs from the reference's objects"
+
+
+@pytest.mark.parametrize("name", ["grid8", "grid7s"])
+def test_mirror_loader_matches_reference_objects(name, tmp_path):
+    z, gold = load_golden(name)
+    net, special = build_grid(name, tmp_path)
+    flat = fl.flatten_network(net, special)
+    assert_static_equal(flat, gold)
+    # string ids of the virtual elements (queue_class.py:210, 213)
+    assert net.links["n3_vl"].start_nid == "vn3" and net.links["n3_vl"].end_nid == 3
+    assert net.node2link_dict[("vn3", 3)] == "n3_vl"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_BOLINAS), reason="Bolinas inputs live in /root/reference (build container only)")
+def test_mirror_loader_bolinas_matches_reference_objects(tmp_path):
+    """The shipped Bolinas network through the mirror == through the reference's loader (golden flat arrays)."""
+    import pandas as pd
+    z, gold = load_golden("bolinas")
+    rng = np.random.default_rng(1)
+    res = pd.read_csv(REF_BOLINAS + "/network_inputs/osm_nodes.csv")
+    vis = pd.read_csv(REF_BOLINAS + "/network_inputs/osm_nodes_visitor_parking.csv")
+    ok = set(pd.read_csv(REF_BOLINAS + "/network_inputs/bolinas_nodes_sim.csv").osmid)
+    r = rng.choice([o for o in res.node_osmid if o in ok and o != 110397253], 900)
+    v = rng.choice([o for o in vis.node_osmid if o in ok and o != 110397253], 300)
+    od = pd.DataFrame({"origin_osmid": np.concatenate([r, v]), "destin_osmid": 110397253, "dept_time": 0,
+                       "type": ["local"] * 900 + ["visitor"] * 300})
+    od.to_csv(str(tmp_path) + "/od.csv", index=False)
+    special = json.load(open(REF_BOLINAS + "/network_inputs/bolinas_special_nodes.json"))
+    np.random.seed(0)
+    net = qc.Network()
+    old, qc.abs_path = qc.abs_path, REF_BOLINAS
+    try:
+        net.dataframe_to_network(project_location="", network_file_edges="/network_inputs/bolinas_edges_sim.csv",
+                                 network_file_nodes="/network_inputs/bolinas_nodes_sim.csv", special_nodes=special)
+    finally:
+        qc.abs_path = old
+    net.add_connectivity()
+    net.add_demand(demand_files=["/od.csv"], write_path=str(tmp_path))
+    # run_traffic_simulation.py:86-88 overwrites the departure times at t == 0 from numpy's global stream
+    # (the golden generator reseeds right before that first one_step call)
+    np.random.seed(0)
+    for a in net.agents.values():
+        a.departure_time = np.random.randint(1, 100)
+    flat = fl.flatten_network(net, special)
+    assert_static_equal(flat, gold)
+
+
+def test_host_tick_methods_refuse_to_run(tmp_path):
+    """No CPU tick: the per-object methods of the reference API fail loudly instead of computing on the host."""
+    from spatial_queue_b200._lib import B200LibraryError
+    net, _ = build_grid("grid8", tmp_path)
+    link = next(iter(net.links.values()))
+    node = net.nodes[0]
+    agent = next(iter(net.agents.values()))
+    for call in (lambda: link.run_link_model(0, agent_id_dict=net.agents),
+                 lambda: node.run_node_model(0, node_id_dict=net.nodes, link_id_dict=net.links),
+                 lambda: agent.load_vehicle(0, node2link_dict=net.node2link_dict, link_id_dict=net.links),
+                 lambda: net.step(0)):
+        with pytest.raises(B200LibraryError):
+            call()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["grid8", "grid7s"])
+def test_mirror_on_gpu_replays_reference_run(name, tmp_path):
+    """One call per tick (`network.step`) with the reroutes computed by the GPU library reproduces the
+    reference's run: initial routes, every later route change, and the per-tick state digests."""
+    z, gold = load_golden(name)
+    net, special = build_grid(name, tmp_path)
+    net.use_gpu(seed=int(z["seed"]), special_nodes=special, reroute_freq=300, weight_freq=100)
+    assert net._flat.route_ptr.tobytes() == gold.route_ptr.tobytes()
+    assert net._flat.route_links.tobytes() == gold.route_links.tobytes()
+    n = int(z["n_ticks"])
+    for t in range(n):
+        net.step(t)
+        assert state_digest(net.sim.state()) == int(z["digests"][t]), f"tick {t}"
+    net.sync_to_host()
+    arrived = {aid: v[1] - 1 for aid, v in net.agents_stopped.items()}
+    gold_arr = {int(gold.agent_key[i]): int(t) for i, t in enumerate(z["arrive_tick"]) if t >= 0}
+    assert arrived == gold_arr
+    assert sum(len(l.queue_vehicles) + len(l.run_vehicles) for l in net.links.values()) == int(z["on_link"][n - 1])
+    assert sum(nd.node_move for nd in net.nodes.values() if nd.node_type == "real") == int(z["moves"][:n].sum())
