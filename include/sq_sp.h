@@ -85,13 +85,18 @@ int sp_set_weights(Graph* graph, const double* weights, int nedges);
  * Called implicitly by every compute entry point. */
 int sp_sync(Graph* graph);
 
-/* Tuning knobs for the tree kernel: threads per CTA (128..1024, multiple of 32), CTAs per SM
- * (0 = fill shared memory), delta = delta_factor x mean finite edge weight (<=0 keeps current),
- * shared-memory queue slots per queue (0 = default). */
+/* Tuning knobs for the tree kernels: threads per CTA = per tree (ELL kernel: 32, 64, 128 or 256; bitmap
+ * kernel: 128..1024), CTAs per SM (0 = default), delta = delta_factor x mean finite edge weight (<=0 keeps
+ * current), shared-memory queue slots per queue of the bitmap kernel (0 = default). */
 int sp_set_tuning(Graph* graph, int threads, int ctas_per_sm, double delta_factor, int smem_queue);
 
+/* Kernel choice: 0 (default) = ELL kernel (four-edge vertex records, tagged queue entries; trees whose queues
+ * overflow queue_factor x V entries are rerun by the bitmap kernel), 1 = bitmap kernel only (CSR, per-vertex
+ * shared-memory bitmaps).  Both produce identical results.  queue_factor <= 0 keeps the current value. */
+int sp_set_algo(Graph* graph, int algo, double queue_factor);
+
 /* Statistics of the last batch: [0] trees, [1] rounds, [2] relaxations, [3] bucket transitions,
- * [4] queue overflows into global scratch.  Filled only when stats were enabled at build time
+ * [4] trees the ELL kernel handed to the bitmap kernel (queue overflow).  Filled only when stats were enabled at build time
  * (SQ_SSSP_STATS); otherwise zeros. */
 int sp_last_stats(Graph* graph, long long* out5);
 

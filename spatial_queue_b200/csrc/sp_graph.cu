@@ -64,6 +64,18 @@ struct TreeParams {
   double delta;
   int nq;               // shared-memory slots per queue
   int words;            // ceil(V/32)
+  // bitmap kernel as the fallback of the ELL kernel: trees to run come from a device list
+  const int* tree_list;   // nullptr: trees 0..n_trees-1
+  const int* n_list;      // device count of tree_list entries
+  // ELL kernel
+  const EdgeRec* ell;     // [V][4] forward, slot 0/1 .pad = overflow start / count
+  const EdgeRec* ovf;     // forward edges beyond the fourth of a vertex
+  const EdgeRec* rell;    // [V][4] reverse
+  const EdgeRec* rovf;
+  int2* q2scratch;        // [grid][2*near_cap + 2*far_cap] (vertex, low 32 bits of its distance when pushed)
+  int near_cap, far_cap;
+  int* fail_list;         // trees whose queues overflowed (rerun by the bitmap kernel)
+  int* fail_count;
 };
 
 #define DIST_INF_BITS 0x7FEFFFFFFFFFFFFFull  // DBL_MAX, what the reference leaves in unreached slots
@@ -136,7 +148,11 @@ __global__ void __launch_bounds__(THREADS) sssp_nearfar_kernel(const TreeParams 
   long long st_rounds = 0, st_relax = 0, st_trans = 0;
 
   for (;;) {
-    if (tid == 0) s_tree = atomicAdd(p.tree_counter, 1);
+    if (tid == 0) {
+      int k = atomicAdd(p.tree_counter, 1);
+      if (p.tree_list) k = (k < *p.n_list) ? p.tree_list[k] : p.n_trees;
+      s_tree = k;
+    }
     __syncthreads();
     const int tree = s_tree;
     if (tree >= p.n_trees) break;
@@ -313,6 +329,271 @@ __global__ void __launch_bounds__(THREADS) sssp_nearfar_kernel(const TreeParams 
   }
 }
 
+
+// -------------------------------------------------------------------------------------------------
+// ELL kernel: the same near-far schedule without per-vertex bitmaps and without row pointers.
+//
+//  * adjacency = one 64-byte record of four 16-byte edges per vertex (road networks rarely exceed
+//    degree 4; further edges sit in an overflow list).  Four adjacent lanes own one frontier vertex, so a
+//    warp step touches 8 lines for its 32 edges instead of 32, and there is no row_ptr load in the chain.
+//  * queue entries are (vertex, low 32 bits of its distance when pushed).  An entry whose tag no longer
+//    matches dist[vertex] is stale: the thread that lowered the distance pushed a newer entry.  This
+//    replaces the three shared-memory bitmaps (and their ATOMS traffic); duplicates are possible, so
+//    queues are bounded by a capacity and a tree that overflows is rerun by the bitmap kernel.
+//  * queues live in a per-CTA global scratch row (L2-resident, read with ld.cg, written coalesced);
+//    shared memory only holds the four counters, so many trees fit on an SM.
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int2 ld_cg_int2(const int2* p) {
+  int2 v;
+  asm volatile("ld.global.cg.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  return v;
+}
+
+// Append from any subset of a warp's lanes to a CTA-wide queue: one shared atomicAdd per warp.
+__device__ __forceinline__ void cta_push(bool want, int v, unsigned tag, int2* q, int* cnt, int cap, int* fail) {
+  const unsigned m = __ballot_sync(0xffffffffu, want);
+  if (m == 0) return;
+  const int leader = __ffs(m) - 1;
+  int base = 0;
+  if ((int)sq::lane_id() == leader) base = atomicAdd(cnt, __popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (want) {
+    const int pos = base + __popc(m & sq::lanemask_lt());
+    if (pos < cap) q[pos] = make_int2(v, (int)tag);
+    else *fail = 1;
+  }
+}
+
+template <int NW>
+__global__ void __launch_bounds__(NW * 32) sssp_ell_kernel(const TreeParams p) {
+  constexpr int THREADS = NW * 32;
+  __shared__ int s_cnt[4];  // near0, near1, far0, far1
+  __shared__ int s_tree, s_fail;
+  __shared__ u64 s_min;
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int slot = lane & 3, grp = lane >> 2;
+  const int V = p.V;
+  int2* qbase = p.q2scratch + (size_t)blockIdx.x * (2 * (size_t)p.near_cap + 2 * (size_t)p.far_cap);
+  auto NEAR = [&](int i) -> int2* { return qbase + (size_t)i * p.near_cap; };
+  auto FAR = [&](int i) -> int2* { return qbase + 2 * (size_t)p.near_cap + (size_t)i * p.far_cap; };
+
+  long long st_rounds = 0, st_relax = 0, st_trans = 0;
+
+  for (;;) {
+    if (tid == 0) s_tree = atomicAdd(p.tree_counter, 1);
+    __syncthreads();
+    const int tree = s_tree;
+    if (tree >= p.n_trees) break;
+
+    u64* dist = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)blockIdx.x * V;
+    const int src = p.origins[tree];
+    const bool valid = (src >= 0 && src < V);
+
+    // dist rows are 8-byte aligned; use 16-byte stores on the aligned middle
+    {
+      const int head = (int)(((uintptr_t)dist >> 3) & 1);  // 1 if the row starts on an odd 8-byte slot
+      if (tid == 0 && head && V > 0) dist[0] = DIST_INF_BITS;
+      const int pairs = (V - head) >> 1;
+      ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dist + head);
+      const ulonglong2 inf2 = make_ulonglong2(DIST_INF_BITS, DIST_INF_BITS);
+      for (int i = tid; i < pairs; i += THREADS) d2[i] = inf2;
+      if (tid == 0 && ((V - head) & 1)) dist[V - 1] = DIST_INF_BITS;
+    }
+    if (tid < 4) s_cnt[tid] = 0;
+    if (tid == 0) s_fail = 0;
+    __syncthreads();
+    if (tid == 0 && valid) {
+      dist[src] = 0ull;
+      NEAR(0)[0] = make_int2(src, 0);
+      s_cnt[0] = 1;
+    }
+    __syncthreads();
+
+    double T = p.delta;
+    int cur = 0, fcur = 0;
+
+    while (valid) {
+      const int n = min(s_cnt[cur], p.near_cap);
+      if (s_fail) break;
+      if (n == 0) {
+        // ---- bucket transition: split the far pile against the next threshold --------------------
+        int nf = min(s_cnt[2 + fcur], p.far_cap);
+        if (nf == 0) break;
+        for (;;) {
+          __syncthreads();
+          if (tid == 0) { s_min = DIST_INF_BITS; s_cnt[2 + (fcur ^ 1)] = 0; }
+          __syncthreads();
+          const double Told = T;
+          T = Told + p.delta;
+          u64 lmin = DIST_INF_BITS;
+          const int2* fin = FAR(fcur);
+          int2* fout = FAR(fcur ^ 1);
+          int2* nout = NEAR(cur);
+          for (int i0 = 0; i0 < nf; i0 += THREADS) {
+            const int i = i0 + tid;
+            bool to_near = false, to_far = false;
+            int2 ent = make_int2(0, 0);
+            if (i < nf) {
+              ent = ld_cg_int2(&fin[i]);
+              const u64 db = sq::ld_cg_u64(&dist[ent.x]);
+              if ((unsigned)db == (unsigned)ent.y) {  // else stale: a newer entry exists
+                if (__longlong_as_double((long long)db) < T) to_near = true;
+                else { to_far = true; lmin = db < lmin ? db : lmin; }
+              }
+            }
+            cta_push(to_near, ent.x, (unsigned)ent.y, nout, &s_cnt[cur], p.near_cap, &s_fail);
+            cta_push(to_far, ent.x, (unsigned)ent.y, fout, &s_cnt[2 + (fcur ^ 1)], p.far_cap, &s_fail);
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(0xffffffffu, lmin, o);
+            lmin = other < lmin ? other : lmin;
+          }
+          if (lane == 0 && lmin != DIST_INF_BITS) atomicMin(&s_min, lmin);
+          __syncthreads();
+          fcur ^= 1;
+          nf = min(s_cnt[2 + fcur], p.far_cap);
+          ++st_trans;
+          if (s_cnt[cur] > 0 || nf == 0 || s_fail) break;
+          T = __longlong_as_double((long long)s_min);  // nothing in range: jump to the smallest far distance
+        }
+        continue;
+      }
+
+      // ---- one relaxation round: 4 lanes per frontier vertex, 8 vertices per warp step -----------
+      const int2* qin = NEAR(cur);
+      int2* qnear = NEAR(cur ^ 1);
+      int2* qfar = FAR(fcur);
+      int* cnt_near = &s_cnt[cur ^ 1];
+      int* cnt_far = &s_cnt[2 + fcur];
+      for (int base = warp * 8; base < n; base += NW * 8) {
+        const int idx = base + grp;
+        bool act = idx < n;
+        int u = 0;
+        u64 dub = 0ull;
+        if (act) {
+          const int2 ent = ld_cg_int2(&qin[idx]);
+          u = ent.x;
+          dub = sq::ld_cg_u64(&dist[u]);
+          act = ((unsigned)dub == (unsigned)ent.y);
+        }
+        EdgeRec rec;
+        rec.w = 0.0; rec.v = -1; rec.pad = 0;
+        if (act) {
+          const int4 raw = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u * 4 + slot]));
+          rec.w = __hiloint2double(raw.y, raw.x);
+          rec.v = raw.z;
+          rec.pad = raw.w;
+        }
+        const double du = __longlong_as_double((long long)dub);
+        {
+          const bool has = rec.v >= 0;
+          const u64 ndb = (u64)__double_as_longlong(du + rec.w);
+          u64 old = 0ull;
+          if (has) old = atomicMin(&dist[rec.v], ndb);
+          const bool imp = has && ndb < old;
+          const bool is_near = __longlong_as_double((long long)ndb) < T;
+          cta_push(imp && is_near, rec.v, (unsigned)ndb, qnear, cnt_near, p.near_cap, &s_fail);
+          cta_push(imp && !is_near, rec.v, (unsigned)ndb, qfar, cnt_far, p.far_cap, &s_fail);
+          st_relax += has;
+        }
+        // edges beyond the fourth (rare on road networks)
+        const int ovf_b = __shfl_sync(0xffffffffu, rec.pad, lane & ~3);
+        const int ovf_n = __shfl_sync(0xffffffffu, rec.pad, (lane & ~3) + 1);
+        const int max_o = __reduce_max_sync(0xffffffffu, act ? ovf_n : 0);
+        for (int k = slot; k - slot < max_o; k += 4) {
+          const bool has = act && k < ovf_n;
+          int v2 = 0;
+          u64 ndb = DIST_INF_BITS, old = 0ull;
+          if (has) {
+            const EdgeRec er = ld_edge(&p.ovf[ovf_b + k]);
+            v2 = er.v;
+            ndb = (u64)__double_as_longlong(du + er.w);
+            old = atomicMin(&dist[v2], ndb);
+          }
+          const bool imp = has && ndb < old;
+          const bool is_near = __longlong_as_double((long long)ndb) < T;
+          cta_push(imp && is_near, v2, (unsigned)ndb, qnear, cnt_near, p.near_cap, &s_fail);
+          cta_push(imp && !is_near, v2, (unsigned)ndb, qfar, cnt_far, p.far_cap, &s_fail);
+          st_relax += has;
+        }
+      }
+      __syncthreads();
+      if (tid == 0) s_cnt[cur] = 0;
+      cur ^= 1;
+      ++st_rounds;
+      __syncthreads();
+    }
+    __syncthreads();
+
+    if (s_fail) {
+      // queue capacity exceeded: hand the tree to the bitmap kernel (its queues cannot overflow)
+      if (tid == 0) p.fail_list[atomicAdd(p.fail_count, 1)] = tree;
+      __syncthreads();
+      continue;
+    }
+
+    // ---- canonical predecessor pass: parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]} -------------
+    if (p.parent_out) {
+      int* parent = p.parent_out + (size_t)tree * V;
+      for (int v0 = 0; v0 < V; v0 += THREADS / 4) {
+        const int v = v0 + (tid >> 2);
+        const bool ok = valid && v < V && v != src;
+        u64 dvb = DIST_INF_BITS;
+        EdgeRec rec;
+        rec.w = 0.0; rec.v = -1; rec.pad = 0;
+        if (ok) {
+          dvb = sq::ld_cg_u64(&dist[v]);
+          if (dvb != DIST_INF_BITS) {
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(&p.rell[(size_t)v * 4 + slot]));
+            rec.w = __hiloint2double(raw.y, raw.x);
+            rec.v = raw.z;
+            rec.pad = raw.w;
+          }
+        }
+        int best = INT_MAX;
+        if (rec.v >= 0) {
+          const u64 dub = sq::ld_cg_u64(&dist[rec.v]);
+          if (dub != DIST_INF_BITS) {
+            const double cand = __longlong_as_double((long long)dub) + rec.w;
+            if ((u64)__double_as_longlong(cand) == dvb) best = rec.v;
+          }
+        }
+        const int ovf_b = __shfl_sync(0xffffffffu, rec.pad, lane & ~3);
+        const int ovf_n = __shfl_sync(0xffffffffu, rec.pad, (lane & ~3) + 1);
+        const int max_o = __reduce_max_sync(0xffffffffu, ovf_n);
+        for (int k = slot; k - slot < max_o; k += 4) {
+          if (k < ovf_n) {
+            const EdgeRec er = ld_edge(&p.rovf[ovf_b + k]);
+            const u64 dub = sq::ld_cg_u64(&dist[er.v]);
+            if (dub != DIST_INF_BITS) {
+              const double cand = __longlong_as_double((long long)dub) + er.w;
+              if ((u64)__double_as_longlong(cand) == dvb && er.v < best) best = er.v;
+            }
+          }
+        }
+        best = min(best, __shfl_xor_sync(0xffffffffu, best, 1));
+        best = min(best, __shfl_xor_sync(0xffffffffu, best, 2));
+        if (slot == 0 && v < V) parent[v] = (best == INT_MAX) ? -1 : best;
+      }
+    }
+    __syncthreads();
+  }
+
+  if (p.stats) {
+    long long r = st_relax;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    if (lane == 0) atomicAdd((u64*)&p.stats[2], (u64)r);
+    if (tid == 0) {
+      atomicAdd((u64*)&p.stats[1], (u64)st_rounds);
+      atomicAdd((u64*)&p.stats[3], (u64)st_trans);
+    }
+  }
+}
+
 // =================================================================================================
 // Host side
 // =================================================================================================
@@ -331,6 +612,7 @@ struct SqGraph {
   bool topo_dirty = true, w_dirty = true;
   std::vector<int> edge_slot, edge_rslot;  // edge id -> position in adj / radj
   std::vector<EdgeRec> h_adj, h_radj;
+  std::vector<int> h_rp, h_rrp;
   int V = 0, E = 0;
 
   // device
@@ -349,9 +631,19 @@ struct SqGraph {
   u64* d_dist_buf = nullptr;
   int* d_parent_buf = nullptr;
   size_t dist_buf_elems = 0, parent_buf_elems = 0;
+  // ELL form (four edges per vertex + overflow), forward and reverse
+  std::vector<EdgeRec> h_ell, h_ovf, h_rell, h_rovf;
+  EdgeRec* d_ell = nullptr; EdgeRec* d_ovf = nullptr; EdgeRec* d_rell = nullptr; EdgeRec* d_rovf = nullptr;
+  size_t ovf_cap = 0, rovf_cap = 0;
+  int2* d_q2scratch = nullptr;
+  int q2_grid = 0, q2_near = 0, q2_far = 0;
+  int* d_fail = nullptr;       // [0] count, [1] fallback tree counter, [2..] list
+  int fail_cap = 0;
+  int algo = 0;                // 0 = ELL kernel (bitmap kernel only as its fallback), 1 = bitmap kernel
+  double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
 
   // tuning
-  int threads = 256;
+  int threads = 128;
   int ctas_per_sm = 0;
   double delta_factor = 2.0;
   double delta = 1.0;
@@ -378,7 +670,30 @@ static void g_add_edge(SqGraph* g, int v1, int v2, double w) {
 
 static void g_free_device(SqGraph* g) {
   cudaFree(g->d_row_ptr); cudaFree(g->d_rrow_ptr); cudaFree(g->d_adj); cudaFree(g->d_radj);
+  cudaFree(g->d_ell); cudaFree(g->d_rell); cudaFree(g->d_ovf); cudaFree(g->d_rovf);
   g->d_row_ptr = g->d_rrow_ptr = nullptr; g->d_adj = g->d_radj = nullptr;
+  g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
+  g->ovf_cap = g->rovf_cap = 0;
+}
+
+// CSR -> four-wide ELL + overflow list.  Slot 0 / slot 1 of a vertex carry the overflow start / count in .pad.
+static void build_ell(const std::vector<int>& rp, const std::vector<EdgeRec>& adj, int V, std::vector<EdgeRec>& ell,
+                      std::vector<EdgeRec>& ovf) {
+  ell.assign((size_t)4 * std::max(V, 1), EdgeRec{0.0, -1, 0});
+  ovf.clear();
+  for (int v = 0; v < V; ++v) {
+    const int b = rp[v], deg = rp[v + 1] - rp[v];
+    for (int j = 0; j < std::min(deg, 4); ++j) {
+      EdgeRec r = adj[b + j];
+      r.pad = 0;
+      ell[(size_t)4 * v + j] = r;
+    }
+    if (deg > 4) {
+      ell[(size_t)4 * v + 0].pad = (int)ovf.size();
+      ell[(size_t)4 * v + 1].pad = deg - 4;
+      for (int j = 4; j < deg; ++j) ovf.push_back(adj[b + j]);
+    }
+  }
 }
 
 static int g_build_and_upload(SqGraph* g) {
@@ -411,6 +726,9 @@ static int g_build_and_upload(SqGraph* g) {
     }
     g_free_device(g);
     g->V = V; g->E = E;
+    g->h_rp = rp; g->h_rrp = rrp;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_ell, sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_rell, sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_row_ptr, sizeof(int) * (size_t)(V + 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_rrow_ptr, sizeof(int) * (size_t)(V + 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_adj, sizeof(EdgeRec) * (size_t)std::max(E, 1)));
@@ -434,6 +752,24 @@ static int g_build_and_upload(SqGraph* g) {
       SQ_CUDA_TRY(cudaMemcpy(g->d_adj, g->h_adj.data(), sizeof(EdgeRec) * (size_t)g->E, cudaMemcpyHostToDevice));
       SQ_CUDA_TRY(cudaMemcpy(g->d_radj, g->h_radj.data(), sizeof(EdgeRec) * (size_t)g->E, cudaMemcpyHostToDevice));
     }
+    build_ell(g->h_rp, g->h_adj, g->V, g->h_ell, g->h_ovf);
+    build_ell(g->h_rrp, g->h_radj, g->V, g->h_rell, g->h_rovf);
+    if (g->h_ovf.size() + 1 > g->ovf_cap) {
+      cudaFree(g->d_ovf); g->d_ovf = nullptr;
+      g->ovf_cap = g->h_ovf.size() + 1;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_ovf, sizeof(EdgeRec) * g->ovf_cap));
+    }
+    if (g->h_rovf.size() + 1 > g->rovf_cap) {
+      cudaFree(g->d_rovf); g->d_rovf = nullptr;
+      g->rovf_cap = g->h_rovf.size() + 1;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_rovf, sizeof(EdgeRec) * g->rovf_cap));
+    }
+    SQ_CUDA_TRY(cudaMemcpy(g->d_ell, g->h_ell.data(), sizeof(EdgeRec) * g->h_ell.size(), cudaMemcpyHostToDevice));
+    SQ_CUDA_TRY(cudaMemcpy(g->d_rell, g->h_rell.data(), sizeof(EdgeRec) * g->h_rell.size(), cudaMemcpyHostToDevice));
+    if (!g->h_ovf.empty())
+      SQ_CUDA_TRY(cudaMemcpy(g->d_ovf, g->h_ovf.data(), sizeof(EdgeRec) * g->h_ovf.size(), cudaMemcpyHostToDevice));
+    if (!g->h_rovf.empty())
+      SQ_CUDA_TRY(cudaMemcpy(g->d_rovf, g->h_rovf.data(), sizeof(EdgeRec) * g->h_rovf.size(), cudaMemcpyHostToDevice));
     // delta = factor x mean weight of the "open" edges (closed links carry 1e8, queue_class.py:469)
     double sum = 0.0; long long cnt = 0;
     for (int i = 0; i < g->E; ++i) {
@@ -460,6 +796,29 @@ static int launch_trees(SqGraph* g, TreeParams& p, int grid, size_t smem, cudaSt
   return SQ_OK;
 }
 
+static int launch_bitmap_kernel(SqGraph* g, TreeParams& p, int grid, size_t smem, int threads, cudaStream_t st) {
+  switch (threads) {
+    case 128: return launch_trees<128>(g, p, grid, smem, st);
+    case 256: return launch_trees<256>(g, p, grid, smem, st);
+    case 512: return launch_trees<512>(g, p, grid, smem, st);
+    case 1024: return launch_trees<1024>(g, p, grid, smem, st);
+    default: return sq::set_error(SQ_ERR_ARG, "bitmap kernel: threads must be 128, 256, 512 or 1024 (got %d)", threads);
+  }
+}
+
+static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t st) {
+  switch (threads) {
+    case 32: sssp_ell_kernel<1><<<grid, 32, 0, st>>>(p); break;
+    case 64: sssp_ell_kernel<2><<<grid, 64, 0, st>>>(p); break;
+    case 128: sssp_ell_kernel<4><<<grid, 128, 0, st>>>(p); break;
+    case 256: sssp_ell_kernel<8><<<grid, 256, 0, st>>>(p); break;
+    default: return sq::set_error(SQ_ERR_ARG, "ELL kernel: threads must be 32, 64, 128 or 256 (got %d)", threads);
+  }
+  sq::count_launch();
+  SQ_CUDA_TRY(cudaGetLastError());
+  return SQ_OK;
+}
+
 // Runs n trees; origins_dev / outputs are device pointers (outputs may be null).
 static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* dist_dev, int* parent_dev,
                               cudaStream_t st) {
@@ -467,37 +826,52 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   if (int rc = g_build_and_upload(g)) return rc;
   const int V = g->V;
   if (V <= 0) return sq::set_error(SQ_ERR_ARG, "graph has no vertices");
-  cudaDeviceProp prop;
+  static cudaDeviceProp prop;
+  static int prop_dev = -1;
   int dev = 0;
   SQ_CUDA_TRY(cudaGetDevice(&dev));
-  SQ_CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+  if (prop_dev != dev) {
+    SQ_CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+    prop_dev = dev;
+  }
+  const int n_sm = prop.multiProcessorCount;
+
+  // ---- bitmap kernel geometry (main kernel when algo == 1, else the fallback of the ELL kernel) ----
   const int words = (V + 31) / 32;
   const size_t bits_bytes = (size_t)3 * words * sizeof(unsigned);
-  if (bits_bytes > 160 * 1024)
+  const bool bitmap_fits = bits_bytes <= 160 * 1024;
+  if (g->algo == 1 && !bitmap_fits)
     return sq::set_error(SQ_ERR_LIMIT, "graph too large for the shared-memory vertex bitmaps (V=%d, limit ~436k vertices)", V);
   int nq = g->smem_queue > 0 ? g->smem_queue : 2048;
   nq = std::min(nq, std::max(32, V));
   while (bits_bytes + (size_t)4 * nq * sizeof(int) > 196 * 1024 && nq > 32) nq /= 2;
   const size_t smem = bits_bytes + (size_t)4 * nq * sizeof(int);
-  const int threads = g->threads;
-  int per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (smem + 1024 + 64));
-  per_sm = std::max(1, std::min(per_sm, 2048 / threads));
-  per_sm = std::min(per_sm, 32);
-  if (g->ctas_per_sm > 0) per_sm = std::min(per_sm, g->ctas_per_sm);
-  int grid = std::min(n, prop.multiProcessorCount * per_sm);
+  const int bm_threads = (g->algo == 1 && g->threads >= 128) ? g->threads : 256;
+  int bm_per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (smem + 1024 + 64));
+  bm_per_sm = std::max(1, std::min(bm_per_sm, 2048 / bm_threads));
+  bm_per_sm = std::min(bm_per_sm, 32);
+  if (g->algo == 1 && g->ctas_per_sm > 0) bm_per_sm = std::min(bm_per_sm, g->ctas_per_sm);
+  if (g->algo != 1) bm_per_sm = 1;  // fallback use only: keep its scratch small
+  const int bm_grid = std::min(n, n_sm * bm_per_sm);
 
-  if (g->scratch_grid < grid || g->scratch_V < V) {
+  if (bitmap_fits && (g->scratch_grid < bm_grid || g->scratch_V < V)) {
     cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
     g->d_dist_scratch = nullptr; g->d_qscratch = nullptr;
-    const int sg = std::max(grid, prop.multiProcessorCount * per_sm);
-    SQ_CUDA_TRY(cudaMalloc(&g->d_dist_scratch, sizeof(u64) * (size_t)sg * V));
-    SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)sg * 4 * V));
-    g->scratch_grid = sg; g->scratch_V = V;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_dist_scratch, sizeof(u64) * (size_t)bm_grid * V));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)bm_grid * 4 * V));
+    g->scratch_grid = bm_grid; g->scratch_V = V;
+  }
+  if (g->fail_cap < n + 2) {
+    cudaFree(g->d_fail); g->d_fail = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_fail, sizeof(int) * (size_t)(n + 2)));
+    g->fail_cap = n + 2;
   }
   SQ_CUDA_TRY(cudaMemsetAsync(g->d_counter, 0, sizeof(int), st));
   SQ_CUDA_TRY(cudaMemsetAsync(g->d_stats, 0, sizeof(long long) * 5, st));
+  SQ_CUDA_TRY(cudaMemsetAsync(g->d_fail, 0, sizeof(int) * 2, st));
 
   TreeParams p;
+  memset(&p, 0, sizeof(p));
   p.V = V; p.n_trees = n;
   p.row_ptr = g->d_row_ptr; p.adj = g->d_adj; p.rrow_ptr = g->d_rrow_ptr; p.radj = g->d_radj;
   p.origins = origins_dev; p.dist_out = dist_dev; p.parent_out = parent_dev;
@@ -509,16 +883,49 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   p.stats = nullptr;
 #endif
   p.delta = g->delta; p.nq = nq; p.words = words;
+  p.ell = g->d_ell; p.ovf = g->d_ovf; p.rell = g->d_rell; p.rovf = g->d_rovf;
+  p.fail_count = g->d_fail; p.fail_list = g->d_fail + 2;
 
-  int rc;
-  switch (threads) {
-    case 128: rc = launch_trees<128>(g, p, grid, smem, st); break;
-    case 256: rc = launch_trees<256>(g, p, grid, smem, st); break;
-    case 512: rc = launch_trees<512>(g, p, grid, smem, st); break;
-    case 1024: rc = launch_trees<1024>(g, p, grid, smem, st); break;
-    default: return sq::set_error(SQ_ERR_ARG, "threads must be 128, 256, 512 or 1024 (got %d)", threads);
+  if (g->algo == 1) {
+    if (int rc = launch_bitmap_kernel(g, p, bm_grid, smem, bm_threads, st)) return rc;
+    g->last_stats[0] = n;
+    return SQ_OK;
   }
-  if (rc) return rc;
+
+  // ---- ELL kernel -------------------------------------------------------------------------------
+  const int threads = std::min(g->threads, 256);
+  int per_sm = g->ctas_per_sm > 0 ? g->ctas_per_sm : 12;
+  per_sm = std::max(1, std::min(per_sm, std::min(32, 2048 / threads)));
+  const int grid = std::min(n, n_sm * per_sm);
+  const int near_cap = std::max(32, (int)(g->queue_factor * V));
+  const int far_cap = 2 * near_cap;
+  if (g->q2_grid < grid || g->q2_near != near_cap) {
+    cudaFree(g->d_q2scratch); g->d_q2scratch = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_q2scratch, sizeof(int2) * (size_t)grid * (2 * (size_t)near_cap + 2 * (size_t)far_cap)));
+    g->q2_grid = grid; g->q2_near = near_cap; g->q2_far = far_cap;
+  }
+  p.q2scratch = g->d_q2scratch; p.near_cap = near_cap; p.far_cap = far_cap;
+  if (!dist_dev) {
+    // timing-only mode keeps distances in a per-CTA scratch row
+    if (g->scratch_grid < grid || g->scratch_V < V || !g->d_dist_scratch) {
+      cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
+      g->d_dist_scratch = nullptr; g->d_qscratch = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_dist_scratch, sizeof(u64) * (size_t)grid * V));
+      SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)grid * 4 * V));
+      g->scratch_grid = grid; g->scratch_V = V;
+      p.dist_scratch = g->d_dist_scratch; p.qscratch = g->d_qscratch;
+    }
+  }
+  if (int rc = launch_ell_kernel(p, grid, threads, st)) return rc;
+  // fallback pass over the trees whose queues overflowed (normally none: its CTAs exit at once)
+  if (bitmap_fits) {
+    TreeParams pf = p;
+    pf.tree_counter = g->d_fail + 1;
+    pf.tree_list = g->d_fail + 2;
+    pf.n_list = g->d_fail;
+    pf.stats = nullptr;
+    if (int rc = launch_bitmap_kernel(g, pf, bm_grid, smem, bm_threads, st)) return rc;
+  }
   g->last_stats[0] = n;
   return SQ_OK;
 }
@@ -529,6 +936,11 @@ static int g_fetch_stats(SqGraph* g) {
   SQ_CUDA_TRY(cudaMemcpy(tmp, g->d_stats, sizeof(tmp), cudaMemcpyDeviceToHost));
   for (int i = 1; i < 5; ++i) g->last_stats[i] = tmp[i];
 #endif
+  if (g->d_fail) {
+    int nfail = 0;
+    SQ_CUDA_TRY(cudaMemcpy(&nfail, g->d_fail, sizeof(int), cudaMemcpyDeviceToHost));
+    g->last_stats[4] = nfail;
+  }
   return SQ_OK;
 }
 
@@ -651,19 +1063,30 @@ void sp_free_graph(Graph* g) {
   g_free_device(g);
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
+  cudaFree(g->d_q2scratch); cudaFree(g->d_fail);
   delete g;
 }
 
 int sp_set_tuning(Graph* g, int threads, int ctas_per_sm, double delta_factor, int smem_queue) {
   if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_tuning: null graph");
   if (threads > 0) {
-    if (threads != 128 && threads != 256 && threads != 512 && threads != 1024)
-      return sq::set_error(SQ_ERR_ARG, "threads must be 128, 256, 512 or 1024");
+    if (threads != 32 && threads != 64 && threads != 128 && threads != 256 && threads != 512 && threads != 1024)
+      return sq::set_error(SQ_ERR_ARG, "threads must be 32, 64, 128, 256, 512 or 1024");
     g->threads = threads;
   }
   if (ctas_per_sm >= 0) g->ctas_per_sm = ctas_per_sm;
   if (delta_factor > 0.0) { g->delta_factor = delta_factor; g->w_dirty = true; }
   if (smem_queue >= 0) g->smem_queue = smem_queue;
+  return SQ_OK;
+}
+
+int sp_set_algo(Graph* g, int algo, double queue_factor) {
+  if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: null graph");
+  if (algo != 0 && algo != 1) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL) or 1 (bitmap)");
+  g->algo = algo;
+  if (algo == 1 && g->threads < 128) g->threads = 256;
+  if (algo == 0 && g->threads > 256) g->threads = 128;
+  if (queue_factor > 0.0) g->queue_factor = queue_factor;
   return SQ_OK;
 }
 

@@ -97,6 +97,10 @@ class Graph:
     def set_tuning(self, threads=0, ctas_per_sm=-1, delta_factor=0.0, smem_queue=-1):
         check(lib().sp_set_tuning(self._h, threads, ctas_per_sm, float(delta_factor), smem_queue), "sp_set_tuning")
 
+    def set_algo(self, algo=0, queue_factor=0.0):
+        """0 = ELL kernel (default), 1 = bitmap kernel; see include/sq_sp.h."""
+        check(lib().sp_set_algo(self._h, int(algo), float(queue_factor)), "sp_set_algo")
+
     def sync(self):
         check(lib().sp_sync(self._h), "sp_sync")
 

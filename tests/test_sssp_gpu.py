@@ -62,8 +62,10 @@ def test_network_mtx_golden(spi):
 
 
 @pytest.mark.parametrize("directed", [True, False])
-@pytest.mark.parametrize("threads,smemq", [(256, 0), (128, 32), (1024, 64)])
-def test_random_graphs_bit_exact(spi, directed, threads, smemq):
+@pytest.mark.parametrize("threads,smemq,algo,qfac", [(256, 0, 1, 0), (128, 32, 1, 0), (1024, 64, 1, 0),   # bitmap kernel
+                                                      (128, 0, 0, 0), (64, 0, 0, 0), (32, 0, 0, 0),       # ELL kernel
+                                                      (256, 0, 0, 4.0), (64, 0, 0, 0.02)])               # roomy / overflowing queues
+def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
     from oracle import sssp as osssp
     rng = np.random.default_rng(11 + threads)
     for trial in range(5):
@@ -75,9 +77,12 @@ def test_random_graphs_bit_exact(spi, directed, threads, smemq):
         w = np.where(rng.random(E) < 0.3, np.round(w) + 1.0, w)  # ties, strictly positive
         og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1, directed=directed)
         g = spi.from_arrays(s, e, w, max_vertex_id=V - 1, directed=directed)
+        g.set_algo(algo, qfac)
         g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
         origins = np.concatenate([rng.integers(0, V, 7), [-1, V, V + 5]]).astype(np.int32)
         d, p = g.sssp_batch(origins)
+        if algo == 0 and qfac == 0.02 and E > 2 * V and V > 1500:
+            assert g.last_stats()["overflows"] > 0     # the fallback path really ran
         do, po = og.sssp_batch(origins)
         assert d.tobytes() == do.tobytes()
         assert (p == po).all()
@@ -104,12 +109,14 @@ def test_weight_updates_reach_the_device(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
 
 
-def test_grid_batch_and_device_api(spi):
+@pytest.mark.parametrize("algo", [0, 1])
+def test_grid_batch_and_device_api(spi, algo):
     import torch
     from oracle import sssp as osssp
     n = 64
     s, e, w = grid_graph(n, seed=1)
     g = spi.from_arrays(s, e, w)
+    g.set_algo(algo)
     og = osssp.OracleGraph(s, e, w)
     origins = np.random.default_rng(2).permutation(n * n)[:300].astype(np.int32)
     o_dev = torch.from_numpy(origins).cuda()

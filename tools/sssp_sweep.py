@@ -16,8 +16,12 @@ origins = torch.from_numpy(np.random.default_rng(0).permutation(V)[:B].astype(np
 dist = torch.empty((B, V), dtype=torch.float64, device="cuda")
 par = torch.empty((B, V), dtype=torch.int32, device="cuda")
 btree = 20 * len(s) + 24 * V
-configs = json.loads(os.environ.get("CONFIGS", "null")) or [
-    (t, c, d, q) for t in (128, 256, 512) for c in (0, 2, 4) for d in (1.0, 2.0, 4.0, 8.0) for q in (1024,)]
+ALGO = int(os.environ.get("ALGO", 0))
+g.set_algo(ALGO)
+configs = json.loads(os.environ.get("CONFIGS", "null")) or (
+    [(t, c, d, 0) for t in (32, 64, 128, 256) for c in (4, 8, 12, 16, 24, 32) for d in (1.0, 2.0, 4.0) if t * c <= 2048]
+    if ALGO == 0 else
+    [(t, c, d, q) for t in (128, 256, 512) for c in (0, 2, 4) for d in (1.0, 2.0, 4.0, 8.0) for q in (1024,)])
 for (t, c, d, q) in configs:
     try:
         g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
@@ -27,7 +31,10 @@ for (t, c, d, q) in configs:
         ms = ev0.elapsed_time(ev1)
         tps = B / ms * 1e3
         st = g.last_stats()
-        print(json.dumps({"threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "trees_per_s": round(tps),
-                          "frac_hbm": round(tps * btree / 6562.3e9, 4)}), flush=True)
+        g.sssp_batch(np.random.default_rng(0).permutation(V)[:64].astype(np.int32), want_dist=False)
+        st = g.last_stats()
+        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "trees_per_s": round(tps),
+                          "frac_hbm": round(tps * btree / 6547.2e9, 4), "relax_per_tree": st["relaxations"] / 64,
+                          "rounds_per_tree": st["rounds"] / 64, "overflows": st["overflows"]}), flush=True)
     except Exception as ex:
         print("ERR", t, c, d, q, ex, flush=True)
