@@ -72,7 +72,8 @@ struct TreeParams {
   const EdgeRec* ovf;     // forward edges beyond the fourth of a vertex
   const EdgeRec* rell;    // [V][4] reverse
   const EdgeRec* rovf;
-  int2* q2scratch;        // [grid][2*near_cap + 2*far_cap] (vertex, low 32 bits of its distance when pushed)
+  int2* q2scratch;        // [grid][4*near_cap + 2*far_cap] u64 distances of the global queue parts
+  int* q2v;               // same shape, vertex ids
   int near_cap, far_cap;
   int* fail_list;         // trees whose queues overflowed (rerun by the bitmap kernel)
   int* fail_count;
@@ -331,17 +332,23 @@ __global__ void __launch_bounds__(THREADS) sssp_nearfar_kernel(const TreeParams 
 
 
 // -------------------------------------------------------------------------------------------------
-// ELL kernel: the same near-far schedule without per-vertex bitmaps and without row pointers.
+// ELL kernel: the near-far schedule without per-vertex bitmaps, row pointers or far-pile rescans.
 //
 //  * adjacency = one 64-byte record of four 16-byte edges per vertex (road networks rarely exceed
 //    degree 4; further edges sit in an overflow list).  Four adjacent lanes own one frontier vertex, so a
 //    warp step touches 8 lines for its 32 edges instead of 32, and there is no row_ptr load in the chain.
-//  * queue entries are (vertex, low 32 bits of its distance when pushed).  An entry whose tag no longer
-//    matches dist[vertex] is stale: the thread that lowered the distance pushed a newer entry.  This
-//    replaces the three shared-memory bitmaps (and their ATOMS traffic); duplicates are possible, so
-//    queues are bounded by a capacity and a tree that overflows is rerun by the bitmap kernel.
-//  * queues live in a per-CTA global scratch row (L2-resident, read with ld.cg, written coalesced);
-//    shared memory only holds the four counters, so many trees fit on an SM.
+//  * queue entries are (vertex, distance when pushed).  An entry whose distance no longer equals
+//    dist[vertex] is stale: the thread that lowered the distance pushed a newer entry.  This replaces the
+//    three shared-memory bitmaps (and their ATOMS traffic); duplicates are possible, so queues are
+//    bounded and a tree that overflows is rerun by the bitmap kernel.
+//  * three buckets instead of two: improvements below T go to the next round of the current bucket,
+//    those in [T, T+delta) straight into the queue of the next bucket (which simply becomes the current
+//    queue at the transition: no rescan, no dist reload), and only those beyond T+delta into a far pile
+//    (empty on road networks whose link times stay below delta; closed links at 1e8 end up there).
+//  * queues are hybrids: the first QS entries in shared memory, the rest in a per-CTA global scratch row;
+//    four of them rotate (current / next round / spare being reset / next bucket) so that a round needs a
+//    single __syncthreads.
+//  * predecessors are a separate kernel (sssp_parent_kernel) at full occupancy.
 // -------------------------------------------------------------------------------------------------
 __device__ __forceinline__ int2 ld_cg_int2(const int2* p) {
   int2 v;
@@ -349,25 +356,49 @@ __device__ __forceinline__ int2 ld_cg_int2(const int2* p) {
   return v;
 }
 
-// Append from any subset of a warp's lanes to a CTA-wide queue: one shared atomicAdd per warp.
-__device__ __forceinline__ void cta_push(bool want, int v, unsigned tag, int2* q, int* cnt, int cap, int* fail) {
-  const unsigned m = __ballot_sync(0xffffffffu, want);
-  if (m == 0) return;
-  const int leader = __ffs(m) - 1;
-  int base = 0;
-  if ((int)sq::lane_id() == leader) base = atomicAdd(cnt, __popc(m));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (want) {
-    const int pos = base + __popc(m & sq::lanemask_lt());
-    if (pos < cap) q[pos] = make_int2(v, (int)tag);
+constexpr int QS = 384;  // shared-memory entries per queue
+
+// Queue entry = (vertex, vertex it was reached from, distance when pushed).  The 'from' vertex lets the
+// relaxation skip the edge straight back (it can never improve: weights are >= 0), a quarter of all atomics
+// on a grid.  Stored as int2 {v, from} + u64.
+struct HQ2 {
+  int2* sv;  // shared part
+  u64* sd;
+  int2* gv;  // global part
+  u64* gd;
+  __device__ __forceinline__ void get(int pos, int2& v, u64& d) const {
+    if (pos < QS) { v = sv[pos]; d = sd[pos]; }
+    else { v = ld_cg_int2(&gv[pos - QS]); d = sq::ld_cg_u64(&gd[pos - QS]); }
+  }
+  __device__ __forceinline__ void put(int pos, int2 v, u64 d, int gcap, int* fail) const {
+    if (pos < QS) { sv[pos] = v; sd[pos] = d; }
+    else if (pos - QS < gcap) { gv[pos - QS] = v; gd[pos - QS] = d; }
     else *fail = 1;
   }
+};
+
+// Append up to two entries per lane to one CTA-wide queue: one shared atomicAdd per warp.
+__device__ __forceinline__ void cta_push2(bool w0, int2 v0, u64 d0, bool w1, int2 v1, u64 d1, const HQ2& q, int* cnt,
+                                          int gcap, int* fail) {
+  const unsigned m0 = __ballot_sync(0xffffffffu, w0);
+  const unsigned m1 = __ballot_sync(0xffffffffu, w1);
+  if ((m0 | m1) == 0) return;
+  const int c0 = __popc(m0);
+  int base = 0;
+  if (sq::lane_id() == 0) base = atomicAdd(cnt, c0 + __popc(m1));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  const unsigned lt = sq::lanemask_lt();
+  if (w0) q.put(base + __popc(m0 & lt), v0, d0, gcap, fail);
+  if (w1) q.put(base + c0 + __popc(m1 & lt), v1, d1, gcap, fail);
 }
 
 template <int NW>
-__global__ void __launch_bounds__(NW * 32) sssp_ell_kernel(const TreeParams p) {
+__global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreeParams p) {
   constexpr int THREADS = NW * 32;
-  __shared__ int s_cnt[4];  // near0, near1, far0, far1
+  __shared__ int2 s_qv[4][QS];
+  __shared__ u64 s_qd[4][QS];
+  __shared__ int s_cnt[4];   // one counter per physical queue
+  __shared__ int s_fcnt[2];  // far piles
   __shared__ int s_tree, s_fail;
   __shared__ u64 s_min;
 
@@ -375,11 +406,16 @@ __global__ void __launch_bounds__(NW * 32) sssp_ell_kernel(const TreeParams p) {
   const int lane = tid & 31, warp = tid >> 5;
   const int slot = lane & 3, grp = lane >> 2;
   const int V = p.V;
-  int2* qbase = p.q2scratch + (size_t)blockIdx.x * (2 * (size_t)p.near_cap + 2 * (size_t)p.far_cap);
-  auto NEAR = [&](int i) -> int2* { return qbase + (size_t)i * p.near_cap; };
-  auto FAR = [&](int i) -> int2* { return qbase + 2 * (size_t)p.near_cap + (size_t)i * p.far_cap; };
+  const int gcap = p.near_cap, fcap = p.far_cap;
+  // per-CTA global scratch: 4 queue tails + 2 far piles, vertex ids then distances
+  const size_t per_cta = 4 * (size_t)gcap + 2 * (size_t)fcap;
+  u64* gd_base = reinterpret_cast<u64*>(p.q2scratch) + (size_t)blockIdx.x * per_cta;
+  int2* gv_base = reinterpret_cast<int2*>(p.q2v) + (size_t)blockIdx.x * per_cta;
+  auto Q = [&](int i) -> HQ2 { return HQ2{s_qv[i], s_qd[i], gv_base + (size_t)i * gcap, gd_base + (size_t)i * gcap}; };
+  auto FARV = [&](int i) -> int2* { return gv_base + 4 * (size_t)gcap + (size_t)i * fcap; };
+  auto FARD = [&](int i) -> u64* { return gd_base + 4 * (size_t)gcap + (size_t)i * fcap; };
 
-  long long st_rounds = 0, st_relax = 0, st_trans = 0;
+  int st_rounds = 0, st_relax = 0, st_trans = 0;  // per launch; 32 bits are plenty per thread
 
   for (;;) {
     if (tid == 0) s_tree = atomicAdd(p.tree_counter, 1);
@@ -391,9 +427,8 @@ __global__ void __launch_bounds__(NW * 32) sssp_ell_kernel(const TreeParams p) {
     const int src = p.origins[tree];
     const bool valid = (src >= 0 && src < V);
 
-    // dist rows are 8-byte aligned; use 16-byte stores on the aligned middle
-    {
-      const int head = (int)(((uintptr_t)dist >> 3) & 1);  // 1 if the row starts on an odd 8-byte slot
+    {  // dist rows are 8-byte aligned; 16-byte stores on the aligned middle
+      const int head = (int)(((uintptr_t)dist >> 3) & 1);
       if (tid == 0 && head && V > 0) dist[0] = DIST_INF_BITS;
       const int pairs = (V - head) >> 1;
       ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dist + head);
@@ -402,182 +437,201 @@ __global__ void __launch_bounds__(NW * 32) sssp_ell_kernel(const TreeParams p) {
       if (tid == 0 && ((V - head) & 1)) dist[V - 1] = DIST_INF_BITS;
     }
     if (tid < 4) s_cnt[tid] = 0;
+    if (tid < 2) s_fcnt[tid] = 0;
     if (tid == 0) s_fail = 0;
     __syncthreads();
     if (tid == 0 && valid) {
       dist[src] = 0ull;
-      NEAR(0)[0] = make_int2(src, 0);
+      s_qv[0][0] = make_int2(src, -1);
+      s_qd[0][0] = 0ull;
       s_cnt[0] = 1;
     }
-    __syncthreads();
 
-    double T = p.delta;
-    int cur = 0, fcur = 0;
+    double T = p.delta;          // current bucket: d < T; next bucket: T <= d < T + delta
+    int cur = 0, nxt = 1, spare = 2, bkt = 3, fcur = 0;
 
     while (valid) {
-      const int n = min(s_cnt[cur], p.near_cap);
+      __syncthreads();
+      const int n = s_cnt[cur];
       if (s_fail) break;
+      if (tid == 0) s_cnt[spare] = 0;
       if (n == 0) {
-        // ---- bucket transition: split the far pile against the next threshold --------------------
-        int nf = min(s_cnt[2 + fcur], p.far_cap);
-        if (nf == 0) break;
+        // ---- bucket transition ---------------------------------------------------------------------
+        bool done = false;
         for (;;) {
-          __syncthreads();
-          if (tid == 0) { s_min = DIST_INF_BITS; s_cnt[2 + (fcur ^ 1)] = 0; }
-          __syncthreads();
-          const double Told = T;
-          T = Told + p.delta;
-          u64 lmin = DIST_INF_BITS;
-          const int2* fin = FAR(fcur);
-          int2* fout = FAR(fcur ^ 1);
-          int2* nout = NEAR(cur);
-          for (int i0 = 0; i0 < nf; i0 += THREADS) {
-            const int i = i0 + tid;
-            bool to_near = false, to_far = false;
-            int2 ent = make_int2(0, 0);
-            if (i < nf) {
-              ent = ld_cg_int2(&fin[i]);
-              const u64 db = sq::ld_cg_u64(&dist[ent.x]);
-              if ((unsigned)db == (unsigned)ent.y) {  // else stale: a newer entry exists
-                if (__longlong_as_double((long long)db) < T) to_near = true;
-                else { to_far = true; lmin = db < lmin ? db : lmin; }
+          const int nb = s_cnt[bkt];
+          const int nf = min(s_fcnt[fcur], fcap);
+          if (nb == 0 && nf == 0) { done = true; break; }
+          bool advanced = false;
+          if (nb > 0) {  // the next bucket becomes the current queue as it is
+            T += p.delta;
+            const int t = cur; cur = bkt; bkt = t;
+            advanced = true;
+          }
+          if (nf > 0) {
+            // split the far pile against the new next-bucket range [T, T + delta)
+            __syncthreads();
+            if (tid == 0) { s_min = DIST_INF_BITS; s_fcnt[fcur ^ 1] = 0; }
+            __syncthreads();
+            const double T2 = T + p.delta;
+            u64 lmin = DIST_INF_BITS;
+            const int2* fiv = FARV(fcur);
+            const u64* fid = FARD(fcur);
+            const HQ2 qb = Q(bkt);
+            const HQ2 qf{nullptr, nullptr, FARV(fcur ^ 1), FARD(fcur ^ 1)};  // global only: positions start at QS
+            for (int i0 = 0; i0 < nf; i0 += THREADS) {
+              const int i = i0 + tid;
+              bool to_b = false, to_f = false;
+              int2 v = make_int2(0, -1);
+              u64 d = 0ull;
+              if (i < nf) {
+                v = ld_cg_int2(&fiv[i]);
+                d = sq::ld_cg_u64(&fid[i]);
+                if (sq::ld_cg_u64(&dist[v.x]) == d) {  // else stale: a newer entry exists
+                  if (__longlong_as_double((long long)d) < T2) to_b = true;
+                  else { to_f = true; lmin = d < lmin ? d : lmin; }
+                }
+              }
+              cta_push2(to_b, v, d, false, v, 0ull, qb, &s_cnt[bkt], gcap, &s_fail);
+              // far pile: positions start at QS in HQ2 terms so that put() takes its global branch
+              {
+                const unsigned m = __ballot_sync(0xffffffffu, to_f);
+                if (m) {
+                  int base = 0;
+                  if (lane == 0) base = atomicAdd(&s_fcnt[fcur ^ 1], __popc(m));
+                  base = __shfl_sync(0xffffffffu, base, 0);
+                  if (to_f) qf.put(QS + base + __popc(m & sq::lanemask_lt()), v, d, fcap, &s_fail);
+                }
               }
             }
-            cta_push(to_near, ent.x, (unsigned)ent.y, nout, &s_cnt[cur], p.near_cap, &s_fail);
-            cta_push(to_far, ent.x, (unsigned)ent.y, fout, &s_cnt[2 + (fcur ^ 1)], p.far_cap, &s_fail);
-          }
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            const u64 other = __shfl_xor_sync(0xffffffffu, lmin, o);
-            lmin = other < lmin ? other : lmin;
+            for (int o = 16; o > 0; o >>= 1) {
+              const u64 other = __shfl_xor_sync(0xffffffffu, lmin, o);
+              lmin = other < lmin ? other : lmin;
+            }
+            if (lane == 0 && lmin != DIST_INF_BITS) atomicMin(&s_min, lmin);
+            __syncthreads();
+            fcur ^= 1;
+            ++st_trans;
+            if (!advanced && s_cnt[bkt] == 0 && s_fcnt[fcur] > 0 && !s_fail) {
+              // nothing within reach: move the window so that the smallest far distance opens the next bucket
+              T = __longlong_as_double((long long)s_min);
+              continue;
+            }
           }
-          if (lane == 0 && lmin != DIST_INF_BITS) atomicMin(&s_min, lmin);
-          __syncthreads();
-          fcur ^= 1;
-          nf = min(s_cnt[2 + fcur], p.far_cap);
-          ++st_trans;
-          if (s_cnt[cur] > 0 || nf == 0 || s_fail) break;
-          T = __longlong_as_double((long long)s_min);  // nothing in range: jump to the smallest far distance
+          if (advanced || s_fail) break;
         }
+        if (done) break;
         continue;
       }
 
-      // ---- one relaxation round: 4 lanes per frontier vertex, 8 vertices per warp step -----------
-      const int2* qin = NEAR(cur);
-      int2* qnear = NEAR(cur ^ 1);
-      int2* qfar = FAR(fcur);
-      int* cnt_near = &s_cnt[cur ^ 1];
-      int* cnt_far = &s_cnt[2 + fcur];
-      for (int base = warp * 8; base < n; base += NW * 8) {
-        const int idx = base + grp;
-        bool act = idx < n;
-        int u = 0;
-        u64 dub = 0ull;
-        if (act) {
-          const int2 ent = ld_cg_int2(&qin[idx]);
-          u = ent.x;
-          dub = sq::ld_cg_u64(&dist[u]);
-          act = ((unsigned)dub == (unsigned)ent.y);
+      // ---- one relaxation round: 4 lanes per frontier vertex, 16 vertices per warp iteration -------
+      const HQ2 qin = Q(cur), qn = Q(nxt), qb = Q(bkt);
+      const HQ2 qf{nullptr, nullptr, FARV(fcur), FARD(fcur)};
+      const double T2 = T + p.delta;
+      for (int base = warp * 16; base < n; base += NW * 16) {
+        int u[2], from[2];
+        u64 dub[2];
+        bool act[2];
+        EdgeRec rec[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int idx = base + j * 8 + grp;
+          act[j] = idx < n;
+          int2 ent = make_int2(0, -1);
+          dub[j] = 0ull;
+          if (act[j]) qin.get(idx, ent, dub[j]);
+          u[j] = ent.x; from[j] = ent.y;
         }
-        EdgeRec rec;
-        rec.w = 0.0; rec.v = -1; rec.pad = 0;
-        if (act) {
-          const int4 raw = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u * 4 + slot]));
-          rec.w = __hiloint2double(raw.y, raw.x);
-          rec.v = raw.z;
-          rec.pad = raw.w;
-        }
-        const double du = __longlong_as_double((long long)dub);
-        {
-          const bool has = rec.v >= 0;
-          const u64 ndb = (u64)__double_as_longlong(du + rec.w);
-          u64 old = 0ull;
-          if (has) old = atomicMin(&dist[rec.v], ndb);
-          const bool imp = has && ndb < old;
-          const bool is_near = __longlong_as_double((long long)ndb) < T;
-          cta_push(imp && is_near, rec.v, (unsigned)ndb, qnear, cnt_near, p.near_cap, &s_fail);
-          cta_push(imp && !is_near, rec.v, (unsigned)ndb, qfar, cnt_far, p.far_cap, &s_fail);
-          st_relax += has;
-        }
-        // edges beyond the fourth (rare on road networks)
-        const int ovf_b = __shfl_sync(0xffffffffu, rec.pad, lane & ~3);
-        const int ovf_n = __shfl_sync(0xffffffffu, rec.pad, (lane & ~3) + 1);
-        const int max_o = __reduce_max_sync(0xffffffffu, act ? ovf_n : 0);
-        for (int k = slot; k - slot < max_o; k += 4) {
-          const bool has = act && k < ovf_n;
-          int v2 = 0;
-          u64 ndb = DIST_INF_BITS, old = 0ull;
-          if (has) {
-            const EdgeRec er = ld_edge(&p.ovf[ovf_b + k]);
-            v2 = er.v;
-            ndb = (u64)__double_as_longlong(du + er.w);
-            old = atomicMin(&dist[v2], ndb);
+        u64 dnow[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          rec[j].w = 0.0; rec[j].v = -1; rec[j].pad = 0;
+          dnow[j] = 0ull;
+          if (act[j]) {
+            dnow[j] = sq::ld_cg_u64(&dist[u[j]]);
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u[j] * 4 + slot]));
+            rec[j].w = __hiloint2double(raw.y, raw.x);
+            rec[j].v = raw.z;
+            rec[j].pad = raw.w;
           }
-          const bool imp = has && ndb < old;
-          const bool is_near = __longlong_as_double((long long)ndb) < T;
-          cta_push(imp && is_near, v2, (unsigned)ndb, qnear, cnt_near, p.near_cap, &s_fail);
-          cta_push(imp && !is_near, v2, (unsigned)ndb, qfar, cnt_far, p.far_cap, &s_fail);
-          st_relax += has;
+        }
+        u64 ndb[2], old[2];
+        bool has[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          act[j] = act[j] && dnow[j] == dub[j];
+          has[j] = act[j] && rec[j].v >= 0 && rec[j].v != from[j];
+          ndb[j] = (u64)__double_as_longlong(__longlong_as_double((long long)dub[j]) + rec[j].w);
+          old[j] = 0ull;
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+          if (has[j]) old[j] = atomicMin(&dist[rec[j].v], ndb[j]);
+        bool imp[2];
+        double nd[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          imp[j] = has[j] && ndb[j] < old[j];
+          nd[j] = __longlong_as_double((long long)ndb[j]);
+          st_relax += has[j];
+        }
+        const int2 e0 = make_int2(rec[0].v, u[0]), e1 = make_int2(rec[1].v, u[1]);
+        cta_push2(imp[0] && nd[0] < T, e0, ndb[0], imp[1] && nd[1] < T, e1, ndb[1], qn, &s_cnt[nxt], gcap, &s_fail);
+        cta_push2(imp[0] && nd[0] >= T && nd[0] < T2, e0, ndb[0], imp[1] && nd[1] >= T && nd[1] < T2, e1, ndb[1], qb,
+                  &s_cnt[bkt], gcap, &s_fail);
+        if (__any_sync(0xffffffffu, (imp[0] && nd[0] >= T2) || (imp[1] && nd[1] >= T2))) {
+          const bool f0 = imp[0] && nd[0] >= T2, f1 = imp[1] && nd[1] >= T2;
+          const unsigned m0 = __ballot_sync(0xffffffffu, f0), m1 = __ballot_sync(0xffffffffu, f1);
+          int fb = 0;
+          if (lane == 0) fb = atomicAdd(&s_fcnt[fcur], __popc(m0) + __popc(m1));
+          fb = __shfl_sync(0xffffffffu, fb, 0);
+          if (f0) qf.put(QS + fb + __popc(m0 & sq::lanemask_lt()), e0, ndb[0], fcap, &s_fail);
+          if (f1) qf.put(QS + fb + __popc(m0) + __popc(m1 & sq::lanemask_lt()), e1, ndb[1], fcap, &s_fail);
+        }
+        // edges beyond the fourth of a vertex (rare on road networks)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int my_pad = act[j] ? rec[j].pad : 0;
+          if (!__any_sync(0xffffffffu, my_pad != 0)) continue;
+          const int ovf_b = __shfl_sync(0xffffffffu, my_pad, lane & ~3);
+          const int ovf_n = __shfl_sync(0xffffffffu, my_pad, (lane & ~3) + 1);
+          const int max_o = __reduce_max_sync(0xffffffffu, ovf_n);
+          const double du = __longlong_as_double((long long)dub[j]);
+          for (int k = slot; k - slot < max_o; k += 4) {
+            const bool h2 = act[j] && k < ovf_n;
+            int2 v2 = make_int2(0, u[j]);
+            u64 nb2 = DIST_INF_BITS, old2 = 0ull;
+            if (h2) {
+              const EdgeRec er = ld_edge(&p.ovf[ovf_b + k]);
+              v2.x = er.v;
+              nb2 = (u64)__double_as_longlong(du + er.w);
+              old2 = atomicMin(&dist[v2.x], nb2);
+            }
+            const bool imp2 = h2 && nb2 < old2;
+            const double nd2 = __longlong_as_double((long long)nb2);
+            cta_push2(imp2 && nd2 < T, v2, nb2, false, v2, 0ull, qn, &s_cnt[nxt], gcap, &s_fail);
+            cta_push2(imp2 && nd2 >= T && nd2 < T2, v2, nb2, false, v2, 0ull, qb, &s_cnt[bkt], gcap, &s_fail);
+            const bool f2 = imp2 && nd2 >= T2;
+            const unsigned m2 = __ballot_sync(0xffffffffu, f2);
+            if (m2) {
+              int fb = 0;
+              if (lane == 0) fb = atomicAdd(&s_fcnt[fcur], __popc(m2));
+              fb = __shfl_sync(0xffffffffu, fb, 0);
+              if (f2) qf.put(QS + fb + __popc(m2 & sq::lanemask_lt()), v2, nb2, fcap, &s_fail);
+            }
+            st_relax += h2;
+          }
         }
       }
-      __syncthreads();
-      if (tid == 0) s_cnt[cur] = 0;
-      cur ^= 1;
+      { const int t = cur; cur = nxt; nxt = spare; spare = t; }
       ++st_rounds;
-      __syncthreads();
     }
     __syncthreads();
 
     if (s_fail) {
       // queue capacity exceeded: hand the tree to the bitmap kernel (its queues cannot overflow)
       if (tid == 0) p.fail_list[atomicAdd(p.fail_count, 1)] = tree;
-      __syncthreads();
-      continue;
-    }
-
-    // ---- canonical predecessor pass: parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]} -------------
-    if (p.parent_out) {
-      int* parent = p.parent_out + (size_t)tree * V;
-      for (int v0 = 0; v0 < V; v0 += THREADS / 4) {
-        const int v = v0 + (tid >> 2);
-        const bool ok = valid && v < V && v != src;
-        u64 dvb = DIST_INF_BITS;
-        EdgeRec rec;
-        rec.w = 0.0; rec.v = -1; rec.pad = 0;
-        if (ok) {
-          dvb = sq::ld_cg_u64(&dist[v]);
-          if (dvb != DIST_INF_BITS) {
-            const int4 raw = __ldg(reinterpret_cast<const int4*>(&p.rell[(size_t)v * 4 + slot]));
-            rec.w = __hiloint2double(raw.y, raw.x);
-            rec.v = raw.z;
-            rec.pad = raw.w;
-          }
-        }
-        int best = INT_MAX;
-        if (rec.v >= 0) {
-          const u64 dub = sq::ld_cg_u64(&dist[rec.v]);
-          if (dub != DIST_INF_BITS) {
-            const double cand = __longlong_as_double((long long)dub) + rec.w;
-            if ((u64)__double_as_longlong(cand) == dvb) best = rec.v;
-          }
-        }
-        const int ovf_b = __shfl_sync(0xffffffffu, rec.pad, lane & ~3);
-        const int ovf_n = __shfl_sync(0xffffffffu, rec.pad, (lane & ~3) + 1);
-        const int max_o = __reduce_max_sync(0xffffffffu, ovf_n);
-        for (int k = slot; k - slot < max_o; k += 4) {
-          if (k < ovf_n) {
-            const EdgeRec er = ld_edge(&p.rovf[ovf_b + k]);
-            const u64 dub = sq::ld_cg_u64(&dist[er.v]);
-            if (dub != DIST_INF_BITS) {
-              const double cand = __longlong_as_double((long long)dub) + er.w;
-              if ((u64)__double_as_longlong(cand) == dvb && er.v < best) best = er.v;
-            }
-          }
-        }
-        best = min(best, __shfl_xor_sync(0xffffffffu, best, 1));
-        best = min(best, __shfl_xor_sync(0xffffffffu, best, 2));
-        if (slot == 0 && v < V) parent[v] = (best == INT_MAX) ? -1 : best;
-      }
     }
     __syncthreads();
   }
@@ -591,6 +645,58 @@ __global__ void __launch_bounds__(NW * 32) sssp_ell_kernel(const TreeParams p) {
       atomicAdd((u64*)&p.stats[1], (u64)st_rounds);
       atomicAdd((u64*)&p.stats[3], (u64)st_trans);
     }
+  }
+}
+
+// Canonical predecessors for a batch of finished trees: parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]}, -1 for
+// the origin and for unreached vertices.  One thread per vertex; its (up to four) in-edges come from a
+// slot-major copy of the reverse ELL (coalesced) and stay in registers while blockIdx.y strides over trees, so
+// the graph is read once per ~16 trees and every dist / parent access of a warp is a run of 32 vertices.
+__global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, const int* __restrict__ rs_v,
+                                                          const double* __restrict__ rs_w, const EdgeRec* __restrict__ rell,
+                                                          const EdgeRec* __restrict__ rovf, int has_ovf,
+                                                          const int* __restrict__ origins, const u64* __restrict__ dist_all,
+                                                          int* __restrict__ parent_all) {
+  const int v = blockIdx.x * 256 + threadIdx.x;
+  if (v >= V) return;
+  int nv[4];
+  double nw[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    nv[j] = __ldg(&rs_v[(size_t)j * V + v]);
+    nw[j] = __ldg(&rs_w[(size_t)j * V + v]);
+  }
+  int ovf_b = 0, ovf_n = 0;
+  if (has_ovf) {
+    ovf_b = __ldg(&rell[(size_t)v * 4 + 0].pad);
+    ovf_n = __ldg(&rell[(size_t)v * 4 + 1].pad);
+  }
+  for (int tree = blockIdx.y; tree < n_trees; tree += gridDim.y) {
+    const u64* dist = dist_all + (size_t)tree * V;
+    const u64 dvb = __ldg(&dist[v]);
+    int best = INT_MAX;
+    if (dvb != DIST_INF_BITS) {
+      u64 dub[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dub[j] = nv[j] >= 0 ? __ldg(&dist[nv[j]]) : DIST_INF_BITS;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (dub[j] != DIST_INF_BITS) {
+          const double cand = __longlong_as_double((long long)dub[j]) + nw[j];
+          if ((u64)__double_as_longlong(cand) == dvb && nv[j] < best) best = nv[j];
+        }
+      }
+      for (int k = 0; k < ovf_n; ++k) {
+        const EdgeRec er = ld_edge(&rovf[ovf_b + k]);
+        const u64 du = __ldg(&dist[er.v]);
+        if (du != DIST_INF_BITS) {
+          const double cand = __longlong_as_double((long long)du) + er.w;
+          if ((u64)__double_as_longlong(cand) == dvb && er.v < best) best = er.v;
+        }
+      }
+    }
+    const int src = __ldg(&origins[tree]);
+    parent_all[(size_t)tree * V + v] = (best == INT_MAX || v == src) ? -1 : best;
   }
 }
 
@@ -635,7 +741,12 @@ struct SqGraph {
   std::vector<EdgeRec> h_ell, h_ovf, h_rell, h_rovf;
   EdgeRec* d_ell = nullptr; EdgeRec* d_ovf = nullptr; EdgeRec* d_rell = nullptr; EdgeRec* d_rovf = nullptr;
   size_t ovf_cap = 0, rovf_cap = 0;
+  int* d_rs_v = nullptr;       // slot-major reverse ELL for the predecessor kernel
+  double* d_rs_w = nullptr;
   int2* d_q2scratch = nullptr;
+  int* d_q2v = nullptr;
+  u64* d_dist_tmp = nullptr;   // distances of parent-only batches
+  size_t dist_tmp_elems = 0;
   int q2_grid = 0, q2_near = 0, q2_far = 0;
   int* d_fail = nullptr;       // [0] count, [1] fallback tree counter, [2..] list
   int fail_cap = 0;
@@ -671,6 +782,7 @@ static void g_add_edge(SqGraph* g, int v1, int v2, double w) {
 static void g_free_device(SqGraph* g) {
   cudaFree(g->d_row_ptr); cudaFree(g->d_rrow_ptr); cudaFree(g->d_adj); cudaFree(g->d_radj);
   cudaFree(g->d_ell); cudaFree(g->d_rell); cudaFree(g->d_ovf); cudaFree(g->d_rovf);
+  cudaFree(g->d_rs_v); cudaFree(g->d_rs_w); g->d_rs_v = nullptr; g->d_rs_w = nullptr;
   g->d_row_ptr = g->d_rrow_ptr = nullptr; g->d_adj = g->d_radj = nullptr;
   g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
   g->ovf_cap = g->rovf_cap = 0;
@@ -729,6 +841,8 @@ static int g_build_and_upload(SqGraph* g) {
     g->h_rp = rp; g->h_rrp = rrp;
     SQ_CUDA_TRY(cudaMalloc(&g->d_ell, sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_rell, sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_rs_v, sizeof(int) * 4 * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_rs_w, sizeof(double) * 4 * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_row_ptr, sizeof(int) * (size_t)(V + 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_rrow_ptr, sizeof(int) * (size_t)(V + 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_adj, sizeof(EdgeRec) * (size_t)std::max(E, 1)));
@@ -766,6 +880,18 @@ static int g_build_and_upload(SqGraph* g) {
     }
     SQ_CUDA_TRY(cudaMemcpy(g->d_ell, g->h_ell.data(), sizeof(EdgeRec) * g->h_ell.size(), cudaMemcpyHostToDevice));
     SQ_CUDA_TRY(cudaMemcpy(g->d_rell, g->h_rell.data(), sizeof(EdgeRec) * g->h_rell.size(), cudaMemcpyHostToDevice));
+    {
+      const size_t Vs = (size_t)std::max(g->V, 1);
+      std::vector<int> sv(4 * Vs, -1);
+      std::vector<double> sw(4 * Vs, 0.0);
+      for (int v = 0; v < g->V; ++v)
+        for (int j = 0; j < 4; ++j) {
+          sv[(size_t)j * Vs + v] = g->h_rell[(size_t)4 * v + j].v;
+          sw[(size_t)j * Vs + v] = g->h_rell[(size_t)4 * v + j].w;
+        }
+      SQ_CUDA_TRY(cudaMemcpy(g->d_rs_v, sv.data(), sizeof(int) * sv.size(), cudaMemcpyHostToDevice));
+      SQ_CUDA_TRY(cudaMemcpy(g->d_rs_w, sw.data(), sizeof(double) * sw.size(), cudaMemcpyHostToDevice));
+    }
     if (!g->h_ovf.empty())
       SQ_CUDA_TRY(cudaMemcpy(g->d_ovf, g->h_ovf.data(), sizeof(EdgeRec) * g->h_ovf.size(), cudaMemcpyHostToDevice));
     if (!g->h_rovf.empty())
@@ -894,18 +1020,30 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
 
   // ---- ELL kernel -------------------------------------------------------------------------------
   const int threads = std::min(g->threads, 256);
-  int per_sm = g->ctas_per_sm > 0 ? g->ctas_per_sm : 12;
-  per_sm = std::max(1, std::min(per_sm, std::min(32, 2048 / threads)));
+  int per_sm = g->ctas_per_sm > 0 ? g->ctas_per_sm : std::min(9, 1024 / threads);
+  per_sm = std::max(1, std::min(per_sm, std::min(9, 2048 / threads)));
   const int grid = std::min(n, n_sm * per_sm);
   const int near_cap = std::max(32, (int)(g->queue_factor * V));
   const int far_cap = 2 * near_cap;
+  const size_t per_cta = 4 * (size_t)near_cap + 2 * (size_t)far_cap;
   if (g->q2_grid < grid || g->q2_near != near_cap) {
     cudaFree(g->d_q2scratch); g->d_q2scratch = nullptr;
-    SQ_CUDA_TRY(cudaMalloc(&g->d_q2scratch, sizeof(int2) * (size_t)grid * (2 * (size_t)near_cap + 2 * (size_t)far_cap)));
+    cudaFree(g->d_q2v); g->d_q2v = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_q2scratch, sizeof(u64) * (size_t)grid * per_cta));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_q2v, sizeof(int2) * (size_t)grid * per_cta));
     g->q2_grid = grid; g->q2_near = near_cap; g->q2_far = far_cap;
   }
-  p.q2scratch = g->d_q2scratch; p.near_cap = near_cap; p.far_cap = far_cap;
-  if (!dist_dev) {
+  p.q2scratch = g->d_q2scratch; p.q2v = g->d_q2v; p.near_cap = near_cap; p.far_cap = far_cap;
+  if (parent_dev && !dist_dev) {
+    // predecessors need the finished distances of every tree: keep them in a library buffer
+    if (g->dist_tmp_elems < (size_t)n * V) {
+      cudaFree(g->d_dist_tmp); g->d_dist_tmp = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_dist_tmp, sizeof(u64) * (size_t)n * V));
+      g->dist_tmp_elems = (size_t)n * V;
+    }
+    p.dist_out = g->d_dist_tmp;
+  }
+  if (!p.dist_out) {
     // timing-only mode keeps distances in a per-CTA scratch row
     if (g->scratch_grid < grid || g->scratch_V < V || !g->d_dist_scratch) {
       cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
@@ -913,9 +1051,10 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
       SQ_CUDA_TRY(cudaMalloc(&g->d_dist_scratch, sizeof(u64) * (size_t)grid * V));
       SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)grid * 4 * V));
       g->scratch_grid = grid; g->scratch_V = V;
-      p.dist_scratch = g->d_dist_scratch; p.qscratch = g->d_qscratch;
     }
+    p.dist_scratch = g->d_dist_scratch; p.qscratch = g->d_qscratch;
   }
+  p.parent_out = nullptr;  // predecessors come from sssp_parent_kernel below
   if (int rc = launch_ell_kernel(p, grid, threads, st)) return rc;
   // fallback pass over the trees whose queues overflowed (normally none: its CTAs exit at once)
   if (bitmap_fits) {
@@ -925,6 +1064,14 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     pf.n_list = g->d_fail;
     pf.stats = nullptr;
     if (int rc = launch_bitmap_kernel(g, pf, bm_grid, smem, bm_threads, st)) return rc;
+  }
+  if (parent_dev) {
+    // each thread keeps its in-edge record in registers and walks over ~16 trees
+    dim3 pgrid((unsigned)(((size_t)V + 255) / 256), (unsigned)std::max(1, std::min((n + 15) / 16, 32768)));
+    sssp_parent_kernel<<<pgrid, 256, 0, st>>>(V, n, g->d_rs_v, g->d_rs_w, g->d_rell, g->d_rovf, g->h_rovf.empty() ? 0 : 1,
+                                              origins_dev, p.dist_out, parent_dev);
+    sq::count_launch();
+    SQ_CUDA_TRY(cudaGetLastError());
   }
   g->last_stats[0] = n;
   return SQ_OK;
@@ -1063,7 +1210,7 @@ void sp_free_graph(Graph* g) {
   g_free_device(g);
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
-  cudaFree(g->d_q2scratch); cudaFree(g->d_fail);
+  cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail);
   delete g;
 }
 

@@ -30,10 +30,12 @@ for (t, c, d, q) in configs:
         ev0.record(); g.sssp_batch_device(origins, dist, par); ev1.record(); torch.cuda.synchronize()
         ms = ev0.elapsed_time(ev1)
         tps = B / ms * 1e3
+        ev0.record(); g.sssp_batch_device(origins, dist, None); ev1.record(); torch.cuda.synchronize()
+        ms_tree = ev0.elapsed_time(ev1)
         st = g.last_stats()
         g.sssp_batch(np.random.default_rng(0).permutation(V)[:64].astype(np.int32), want_dist=False)
         st = g.last_stats()
-        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "trees_per_s": round(tps),
+        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "ms_trees_only": round(ms_tree, 2), "trees_per_s": round(tps),
                           "frac_hbm": round(tps * btree / 6547.2e9, 4), "relax_per_tree": st["relaxations"] / 64,
                           "rounds_per_tree": st["rounds"] / 64, "overflows": st["overflows"]}), flush=True)
     except Exception as ex:
