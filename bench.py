@@ -32,6 +32,9 @@ TICK_GRID = 159
 TICK_AGENTS = 1_000_000
 TICK_TICKS = 14_400
 TICK_HORIZON = 7_200
+# dram__bytes_read.sum + dram__bytes_write.sum of sssp_ell_kernel per tree, from the committed ncu --set full capture
+# (profiles/); None until measured for the current kernel
+SSSP_TRAFFIC_PER_TREE = None
 
 
 def measured_peaks():
@@ -272,7 +275,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=8192, help="SSSP origins per GPU per step")
+    ap.add_argument("--batch", type=int, default=16384, help="SSSP origins per GPU per step")
     ap.add_argument("--sssp-grid", type=int, default=SSSP_GRID)
     ap.add_argument("--tick-grid", type=int, default=TICK_GRID)
     ap.add_argument("--tick-agents", type=int, default=TICK_AGENTS)
@@ -359,13 +362,15 @@ def main():
     # ---- e2e through the host-buffer C ABI (origins in host memory -> dist + parent in host memory) -------------
     e2e = None
     if rank == 0 or world > 1:
-        eb = min(B, 2048)
+        # host origins in, page-locked host distance + predecessor arrays out (the copies are inside the call)
+        eb = min(B, 4096)
         oh = origins_for(rank, eb, V, step=7)
-        g.sssp_batch(oh[:64])
+        dh, ph = spi.pinned_empty((eb, V), np.float64), spi.pinned_empty((eb, V), np.int32)
+        g.sssp_batch(oh[:256], out=(dh[:256], ph[:256]))
         t0 = time.perf_counter()
         reps = 2
         for _ in range(reps):
-            dh, ph = g.sssp_batch(oh)
+            g.sssp_batch(oh, out=(dh, ph))
         wall = time.perf_counter() - t0
         e2e_val = world * eb * reps / wall
         if world > 1:
@@ -388,7 +393,8 @@ def main():
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "sssp_nearfar_kernel", "kernel_ms": kernel_ms,
+                             "traffic": SSSP_TRAFFIC_PER_TREE * B if SSSP_TRAFFIC_PER_TREE else None,
+                             "kernel": "sssp_ell_kernel (+ sssp_parent_kernel, both inside kernel_ms)", "kernel_ms": kernel_ms,
                              "bytes_per_tree": bytes_per_tree, "peak_source": peak_src},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 

@@ -17,6 +17,7 @@
 #define SQ_SP_H_
 
 #include <stdbool.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -69,6 +70,11 @@ int sp_nedges(Graph* graph); /* adjacency entries (duplicates included) */
  * parent_out[n][V] (i32, -1 = none); either may be NULL.  Predecessors follow the canonical rule
  * parent[v] = min{u : fl(dist[u] + w(u,v)) == dist[v]}.  Returns 0, or a negative error code. */
 int sp_sssp_batch(Graph* graph, const int* origins, int n, double* dist_out, int* parent_out);
+
+/* Page-locked host memory for sp_sssp_batch outputs: with both destinations allocated here the device-to-host
+ * copies overlap the computation of the next chunk of trees (PCIe-bound instead of staging-bound). */
+void* sp_alloc_host(size_t bytes);
+void sp_free_host(void* ptr);
 
 /* Same with device pointers (CUDA device memory owned by the caller, e.g. a torch tensor's
  * data_ptr()); `stream` is a cudaStream_t passed as void* (NULL = default stream).  Asynchronous

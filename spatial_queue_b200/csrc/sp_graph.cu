@@ -750,13 +750,15 @@ struct SqGraph {
   int q2_grid = 0, q2_near = 0, q2_far = 0;
   int* d_fail = nullptr;       // [0] count, [1] fallback tree counter, [2..] list
   int fail_cap = 0;
+  cudaStream_t s_compute = nullptr, s_copy = nullptr;
+  cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   int algo = 0;                // 0 = ELL kernel (bitmap kernel only as its fallback), 1 = bitmap kernel
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
 
   // tuning
-  int threads = 128;
+  int threads = 256;
   int ctas_per_sm = 0;
-  double delta_factor = 2.0;
+  double delta_factor = 4.0;
   double delta = 1.0;
   int smem_queue = 0;
   long long last_stats[5] = {0, 0, 0, 0, 0};
@@ -1211,6 +1213,10 @@ void sp_free_graph(Graph* g) {
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
   cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail);
+  if (g->s_compute) {
+    cudaStreamDestroy(g->s_compute); cudaStreamDestroy(g->s_copy);
+    for (int i = 0; i < 2; ++i) { cudaEventDestroy(g->ev_done[i]); cudaEventDestroy(g->ev_copied[i]); }
+  }
   delete g;
 }
 
@@ -1251,6 +1257,30 @@ int sp_sssp_batch_device(Graph* g, const int* origins_dev, int n, double* dist_d
   return g_run_batch_device(g, origins_dev, n, reinterpret_cast<u64*>(dist_dev), parent_dev, (cudaStream_t)stream);
 }
 
+static bool is_pinned_host(const void* ptr) {
+  if (!ptr) return true;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
+void* sp_alloc_host(size_t bytes) {
+  void* ptr = nullptr;
+  if (sq::require_device()) return nullptr;
+  if (cudaHostAlloc(&ptr, std::max<size_t>(bytes, 1), cudaHostAllocDefault) != cudaSuccess) {
+    sq::set_error(SQ_ERR_CUDA, "sp_alloc_host: cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  return ptr;
+}
+
+void sp_free_host(void* ptr) {
+  if (ptr) cudaFreeHost(ptr);
+}
+
 int sp_sssp_batch(Graph* g, const int* origins, int n, double* dist_out, int* parent_out) {
   if (!g || (!origins && n > 0)) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch: null argument");
   if (n <= 0) return SQ_OK;
@@ -1262,30 +1292,50 @@ int sp_sssp_batch(Graph* g, const int* origins, int n, double* dist_out, int* pa
     g->origins_cap = n;
   }
   SQ_CUDA_TRY(cudaMemcpy(g->d_origins, origins, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
-  // chunk so that the staging buffers stay below ~2 GiB
+  // Trees are produced in chunks into two device buffers; while chunk i is computed on one stream, chunk i-1
+  // travels to the host on another.  With page-locked destinations (sp_alloc_host) the copies are asynchronous
+  // and the call runs at PCIe speed; pageable destinations still work, the driver then stages every copy.
   const size_t per_tree = V * (sizeof(u64) + sizeof(int));
-  size_t chunk = std::max<size_t>(1, std::min<size_t>((size_t)n, ((size_t)2 << 30) / std::max<size_t>(per_tree, 1)));
-  if (dist_out && g->dist_buf_elems < chunk * V) {
+  size_t chunk = std::max<size_t>(1, std::min<size_t>((size_t)n, ((size_t)1 << 29) / std::max<size_t>(per_tree, 1)));
+  if ((size_t)n > chunk) chunk = std::max<size_t>(chunk, 64);
+  if (dist_out && g->dist_buf_elems < 2 * chunk * V) {
     cudaFree(g->d_dist_buf); g->d_dist_buf = nullptr;
-    SQ_CUDA_TRY(cudaMalloc(&g->d_dist_buf, sizeof(u64) * chunk * V));
-    g->dist_buf_elems = chunk * V;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_dist_buf, sizeof(u64) * 2 * chunk * V));
+    g->dist_buf_elems = 2 * chunk * V;
   }
-  if (parent_out && g->parent_buf_elems < chunk * V) {
+  if (parent_out && g->parent_buf_elems < 2 * chunk * V) {
     cudaFree(g->d_parent_buf); g->d_parent_buf = nullptr;
-    SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * chunk * V));
-    g->parent_buf_elems = chunk * V;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * 2 * chunk * V));
+    g->parent_buf_elems = 2 * chunk * V;
   }
-  for (size_t off = 0; off < (size_t)n; off += chunk) {
+  if (!g->s_compute) {
+    SQ_CUDA_TRY(cudaStreamCreateWithFlags(&g->s_compute, cudaStreamNonBlocking));
+    SQ_CUDA_TRY(cudaStreamCreateWithFlags(&g->s_copy, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_done[i], cudaEventDisableTiming));
+      SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_copied[i], cudaEventDisableTiming));
+    }
+  }
+  const bool pinned = is_pinned_host(dist_out) && is_pinned_host(parent_out);
+  int k = 0;
+  for (size_t off = 0; off < (size_t)n; off += chunk, ++k) {
     const int m = (int)std::min(chunk, (size_t)n - off);
-    if (int rc = g_run_batch_device(g, g->d_origins + off, m, dist_out ? g->d_dist_buf : nullptr,
-                                    parent_out ? g->d_parent_buf : nullptr, 0))
-      return rc;
+    const int b = k & 1;
+    u64* dbuf = dist_out ? g->d_dist_buf + (size_t)b * chunk * V : nullptr;
+    int* pbuf = parent_out ? g->d_parent_buf + (size_t)b * chunk * V : nullptr;
+    if (k >= 2) SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_compute, g->ev_copied[b], 0));  // buffer b is free again
+    if (int rc = g_run_batch_device(g, g->d_origins + off, m, dbuf, pbuf, g->s_compute)) return rc;
+    SQ_CUDA_TRY(cudaEventRecord(g->ev_done[b], g->s_compute));
+    SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_copy, g->ev_done[b], 0));
+    if (!pinned) SQ_CUDA_TRY(cudaStreamSynchronize(g->s_compute));  // pageable copies block the host anyway
     if (dist_out)
-      SQ_CUDA_TRY(cudaMemcpy(dist_out + off * V, g->d_dist_buf, sizeof(u64) * (size_t)m * V, cudaMemcpyDeviceToHost));
+      SQ_CUDA_TRY(cudaMemcpyAsync(dist_out + off * V, dbuf, sizeof(u64) * (size_t)m * V, cudaMemcpyDeviceToHost, g->s_copy));
     if (parent_out)
-      SQ_CUDA_TRY(cudaMemcpy(parent_out + off * V, g->d_parent_buf, sizeof(int) * (size_t)m * V, cudaMemcpyDeviceToHost));
-    SQ_CUDA_TRY(cudaDeviceSynchronize());
+      SQ_CUDA_TRY(cudaMemcpyAsync(parent_out + off * V, pbuf, sizeof(int) * (size_t)m * V, cudaMemcpyDeviceToHost, g->s_copy));
+    SQ_CUDA_TRY(cudaEventRecord(g->ev_copied[b], g->s_copy));
   }
+  SQ_CUDA_TRY(cudaStreamSynchronize(g->s_compute));
+  SQ_CUDA_TRY(cudaStreamSynchronize(g->s_copy));
   g->last_stats[0] = n;
   return g_fetch_stats(g);
 }

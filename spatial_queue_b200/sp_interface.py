@@ -17,6 +17,20 @@ from ._lib import lib, check
 DBL_MAX = np.finfo(np.float64).max
 
 
+def pinned_empty(shape, dtype):
+    """numpy array over page-locked host memory from the library (sp_alloc_host); freed with the array."""
+    import weakref
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    ptr = lib().sp_alloc_host(nbytes)
+    if not ptr:
+        raise MemoryError(f"sp_alloc_host({nbytes}) failed: {lib().sp_last_error().decode()}")
+    buf = (C.c_char * max(nbytes, 1)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    weakref.finalize(buf, lib().sp_free_host, ptr)
+    return arr
+
+
 class ShortestPath:
     """One shortest-path tree (reference: interface.py:15-32, struct ShortestPath in sp/include/graph.h:20-53)."""
 
@@ -104,12 +118,20 @@ class Graph:
     def sync(self):
         check(lib().sp_sync(self._h), "sp_sync")
 
-    def sssp_batch(self, origins, want_dist=True, want_parent=True):
-        """Full trees for `origins` -> (dist f64[n,V] or None, parent i32[n,V] or None), host arrays."""
+    def sssp_batch(self, origins, want_dist=True, want_parent=True, pinned=True, out=None):
+        """Full trees for `origins` -> (dist f64[n,V] or None, parent i32[n,V] or None), host arrays.
+
+        The results land in page-locked memory by default so that the device-to-host copies overlap the
+        computation (`pinned=False` gives ordinary numpy arrays; `out=(dist, parent)` reuses caller arrays)."""
         o = np.ascontiguousarray(origins, dtype=np.int32)
         V = self.nvertices
-        d = np.empty((len(o), V), dtype=np.float64) if want_dist else None
-        p = np.empty((len(o), V), dtype=np.int32) if want_parent else None
+        if out is not None:
+            d, p = out
+        else:
+            alloc = pinned_empty if (pinned and len(o) * V >= (1 << 16)) else np.empty
+            d = alloc((len(o), V), np.float64) if want_dist else None
+            p = alloc((len(o), V), np.int32) if want_parent else None
+        want_dist, want_parent = d is not None, p is not None
         check(lib().sp_sssp_batch(self._h, o.ctypes.data, len(o),
                                   d.ctypes.data if want_dist else None,
                                   p.ctypes.data if want_parent else None), "sp_sssp_batch")
