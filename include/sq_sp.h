@@ -83,6 +83,17 @@ void sp_free_host(void* ptr);
 int sp_sssp_batch_device(Graph* graph, const int* origins_dev, int n, double* dist_dev,
                          int* parent_dev, void* stream);
 
+/* sp_sssp_batch_device with a direction flag: reverse != 0 runs the trees on the reversed graph, i.e.
+ * dist[i][v] = shortest distance from v TO origins[i] and parent[i][v] = the next vertex on that path (canonical:
+ * smallest id among exact ties).  One reverse tree per destination routes every agent heading there
+ * (Agent.get_path, queue_class.py:491-512, calls dijkstra once per agent instead). */
+int sp_sssp_batch_device_ex(Graph* graph, const int* origins_dev, int n, double* dist_dev, int* parent_dev,
+                            void* stream, int reverse);
+
+/* Device-side sp_set_weights: weights_dev[nedges] in creategraph order (device memory), NaN = keep the current
+ * weight.  Rewrites the device graph in place with one kernel; the host edge log is kept in step. */
+int sp_set_weights_device(Graph* graph, const double* weights_dev, int nedges, void* stream);
+
 /* Bulk weight refresh, one weight per edge in insertion order (creategraph order); replaces n calls
  * to update_edge (queue_class.py:463-466 is called once per link every 100 ticks). */
 int sp_set_weights(Graph* graph, const double* weights, int nedges);

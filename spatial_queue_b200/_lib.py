@@ -45,6 +45,8 @@ def _declare(L):
     L.sp_nedges.restype = ci; L.sp_nedges.argtypes = [vp]
     L.sp_sssp_batch.restype = ci; L.sp_sssp_batch.argtypes = [vp, vp, ci, vp, vp]
     L.sp_sssp_batch_device.restype = ci; L.sp_sssp_batch_device.argtypes = [vp, vp, ci, vp, vp, vp]
+    L.sp_sssp_batch_device_ex.restype = ci; L.sp_sssp_batch_device_ex.argtypes = [vp, vp, ci, vp, vp, vp, ci]
+    L.sp_set_weights_device.restype = ci; L.sp_set_weights_device.argtypes = [vp, vp, ci, vp]
     L.sp_set_weights.restype = ci; L.sp_set_weights.argtypes = [vp, vp, ci]
     L.sp_sync.restype = ci; L.sp_sync.argtypes = [vp]
     L.sp_set_tuning.restype = ci; L.sp_set_tuning.argtypes = [vp, ci, ci, cd, ci]

@@ -700,6 +700,31 @@ __global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, co
   }
 }
 
+// Device-side weight refresh: weights[i] belongs to edge i of the insertion log; NaN keeps the current weight.
+// Every copy of the weight (CSR/CSC records, ELL + overflow records, slot-major arrays) is rewritten in place.
+struct WeightSlots {
+  const int* adj; const int* radj;    // CSR / CSC record index, -1 = edge not in the graph
+  const int* ell; const int* rell;    // >= 0: index into the ELL array; < 0: -(overflow index + 1)
+};
+__global__ void __launch_bounds__(256) scatter_weights_kernel(int n, int V, const double* __restrict__ w, WeightSlots ws,
+                                                              EdgeRec* adj, EdgeRec* radj, EdgeRec* ell, EdgeRec* ovf,
+                                                              EdgeRec* rell, EdgeRec* rovf, double* fs_w, double* rs_w) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const double x = w[i];
+  if (x != x) return;
+  const int a = ws.adj[i];
+  if (a < 0) return;
+  adj[a].w = x;
+  radj[ws.radj[i]].w = x;
+  const int e = ws.ell[i];
+  if (e >= 0) { ell[e].w = x; fs_w[(size_t)(e & 3) * V + (e >> 2)] = x; }
+  else ovf[-(e + 1)].w = x;
+  const int r = ws.rell[i];
+  if (r >= 0) { rell[r].w = x; rs_w[(size_t)(r & 3) * V + (r >> 2)] = x; }
+  else rovf[-(r + 1)].w = x;
+}
+
 // =================================================================================================
 // Host side
 // =================================================================================================
@@ -719,6 +744,7 @@ struct SqGraph {
   std::vector<int> edge_slot, edge_rslot;  // edge id -> position in adj / radj
   std::vector<EdgeRec> h_adj, h_radj;
   std::vector<int> h_rp, h_rrp;
+  std::vector<double> w_stage;
   int V = 0, E = 0;
 
   // device
@@ -743,6 +769,10 @@ struct SqGraph {
   size_t ovf_cap = 0, rovf_cap = 0;
   int* d_rs_v = nullptr;       // slot-major reverse ELL for the predecessor kernel
   double* d_rs_w = nullptr;
+  int* d_fs_v = nullptr;       // slot-major forward ELL (predecessors of trees on the reversed graph)
+  double* d_fs_w = nullptr;
+  int* d_wslots = nullptr;     // 4 x n_log: where the weight of edge i lives (scatter_weights_kernel)
+  size_t wslots_n = 0;
   int2* d_q2scratch = nullptr;
   int* d_q2v = nullptr;
   u64* d_dist_tmp = nullptr;   // distances of parent-only batches
@@ -785,6 +815,8 @@ static void g_free_device(SqGraph* g) {
   cudaFree(g->d_row_ptr); cudaFree(g->d_rrow_ptr); cudaFree(g->d_adj); cudaFree(g->d_radj);
   cudaFree(g->d_ell); cudaFree(g->d_rell); cudaFree(g->d_ovf); cudaFree(g->d_rovf);
   cudaFree(g->d_rs_v); cudaFree(g->d_rs_w); g->d_rs_v = nullptr; g->d_rs_w = nullptr;
+  cudaFree(g->d_fs_v); cudaFree(g->d_fs_w); g->d_fs_v = nullptr; g->d_fs_w = nullptr;
+  cudaFree(g->d_wslots); g->d_wslots = nullptr; g->wslots_n = 0;
   g->d_row_ptr = g->d_rrow_ptr = nullptr; g->d_adj = g->d_radj = nullptr;
   g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
   g->ovf_cap = g->rovf_cap = 0;
@@ -845,6 +877,8 @@ static int g_build_and_upload(SqGraph* g) {
     SQ_CUDA_TRY(cudaMalloc(&g->d_rell, sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_rs_v, sizeof(int) * 4 * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_rs_w, sizeof(double) * 4 * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_fs_v, sizeof(int) * 4 * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_fs_w, sizeof(double) * 4 * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_row_ptr, sizeof(int) * (size_t)(V + 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_rrow_ptr, sizeof(int) * (size_t)(V + 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_adj, sizeof(EdgeRec) * (size_t)std::max(E, 1)));
@@ -886,13 +920,35 @@ static int g_build_and_upload(SqGraph* g) {
       const size_t Vs = (size_t)std::max(g->V, 1);
       std::vector<int> sv(4 * Vs, -1);
       std::vector<double> sw(4 * Vs, 0.0);
-      for (int v = 0; v < g->V; ++v)
-        for (int j = 0; j < 4; ++j) {
-          sv[(size_t)j * Vs + v] = g->h_rell[(size_t)4 * v + j].v;
-          sw[(size_t)j * Vs + v] = g->h_rell[(size_t)4 * v + j].w;
-        }
-      SQ_CUDA_TRY(cudaMemcpy(g->d_rs_v, sv.data(), sizeof(int) * sv.size(), cudaMemcpyHostToDevice));
-      SQ_CUDA_TRY(cudaMemcpy(g->d_rs_w, sw.data(), sizeof(double) * sw.size(), cudaMemcpyHostToDevice));
+      for (int dir = 0; dir < 2; ++dir) {
+        const std::vector<EdgeRec>& src = dir ? g->h_ell : g->h_rell;
+        for (int v = 0; v < g->V; ++v)
+          for (int j = 0; j < 4; ++j) {
+            sv[(size_t)j * Vs + v] = src[(size_t)4 * v + j].v;
+            sw[(size_t)j * Vs + v] = src[(size_t)4 * v + j].w;
+          }
+        SQ_CUDA_TRY(cudaMemcpy(dir ? g->d_fs_v : g->d_rs_v, sv.data(), sizeof(int) * sv.size(), cudaMemcpyHostToDevice));
+        SQ_CUDA_TRY(cudaMemcpy(dir ? g->d_fs_w : g->d_rs_w, sw.data(), sizeof(double) * sw.size(), cudaMemcpyHostToDevice));
+      }
+    }
+    if (g->wslots_n != g->es.size()) {
+      // where each logged edge's weight lives on the device (for sp_set_weights_device)
+      const size_t n = g->es.size();
+      std::vector<int> slots(4 * std::max<size_t>(n, 1), -1);
+      for (size_t i = 0; i < n; ++i) {
+        const int a = g->edge_slot[i], r = g->edge_rslot[i];
+        if (a < 0) continue;
+        slots[i] = a;
+        slots[n + i] = r;
+        const int v = g->es[i], ja = a - g->h_rp[v];
+        slots[2 * n + i] = ja < 4 ? 4 * v + ja : -(g->h_ell[(size_t)4 * v].pad + (ja - 4) + 1);
+        const int u = g->ee[i], jr = r - g->h_rrp[u];
+        slots[3 * n + i] = jr < 4 ? 4 * u + jr : -(g->h_rell[(size_t)4 * u].pad + (jr - 4) + 1);
+      }
+      cudaFree(g->d_wslots); g->d_wslots = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_wslots, sizeof(int) * slots.size()));
+      SQ_CUDA_TRY(cudaMemcpy(g->d_wslots, slots.data(), sizeof(int) * slots.size(), cudaMemcpyHostToDevice));
+      g->wslots_n = n;
     }
     if (!g->h_ovf.empty())
       SQ_CUDA_TRY(cudaMemcpy(g->d_ovf, g->h_ovf.data(), sizeof(EdgeRec) * g->h_ovf.size(), cudaMemcpyHostToDevice));
@@ -949,7 +1005,7 @@ static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t 
 
 // Runs n trees; origins_dev / outputs are device pointers (outputs may be null).
 static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* dist_dev, int* parent_dev,
-                              cudaStream_t st) {
+                              cudaStream_t st, bool reverse = false) {
   if (n <= 0) return SQ_OK;
   if (int rc = g_build_and_upload(g)) return rc;
   const int V = g->V;
@@ -1013,6 +1069,10 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   p.delta = g->delta; p.nq = nq; p.words = words;
   p.ell = g->d_ell; p.ovf = g->d_ovf; p.rell = g->d_rell; p.rovf = g->d_rovf;
   p.fail_count = g->d_fail; p.fail_list = g->d_fail + 2;
+  if (reverse) {  // trees on the reversed graph: distances *to* the origin, parent = next vertex towards it
+    std::swap(p.row_ptr, p.rrow_ptr); std::swap(p.adj, p.radj);
+    std::swap(p.ell, p.rell); std::swap(p.ovf, p.rovf);
+  }
 
   if (g->algo == 1) {
     if (int rc = launch_bitmap_kernel(g, p, bm_grid, smem, bm_threads, st)) return rc;
@@ -1070,8 +1130,12 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   if (parent_dev) {
     // each thread keeps its in-edge record in registers and walks over ~16 trees
     dim3 pgrid((unsigned)(((size_t)V + 255) / 256), (unsigned)std::max(1, std::min((n + 15) / 16, 32768)));
-    sssp_parent_kernel<<<pgrid, 256, 0, st>>>(V, n, g->d_rs_v, g->d_rs_w, g->d_rell, g->d_rovf, g->h_rovf.empty() ? 0 : 1,
-                                              origins_dev, p.dist_out, parent_dev);
+    if (reverse)
+      sssp_parent_kernel<<<pgrid, 256, 0, st>>>(V, n, g->d_fs_v, g->d_fs_w, g->d_ell, g->d_ovf, g->h_ovf.empty() ? 0 : 1,
+                                                origins_dev, p.dist_out, parent_dev);
+    else
+      sssp_parent_kernel<<<pgrid, 256, 0, st>>>(V, n, g->d_rs_v, g->d_rs_w, g->d_rell, g->d_rovf, g->h_rovf.empty() ? 0 : 1,
+                                                origins_dev, p.dist_out, parent_dev);
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
   }
@@ -1251,6 +1315,39 @@ int sp_last_stats(Graph* g, long long* out5) {
 
 const char* sp_last_error(void) { return sq::err_buf(); }
 long long sp_kernel_launches(void) { return sq::launch_counter().load(); }
+
+int sp_sssp_batch_device_ex(Graph* g, const int* origins_dev, int n, double* dist_dev, int* parent_dev, void* stream,
+                            int reverse) {
+  if (!g || (!origins_dev && n > 0)) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch_device_ex: null argument");
+  return g_run_batch_device(g, origins_dev, n, reinterpret_cast<u64*>(dist_dev), parent_dev, (cudaStream_t)stream, reverse != 0);
+}
+
+int sp_set_weights_device(Graph* g, const double* weights_dev, int nedges, void* stream) {
+  if (!g || !weights_dev) return sq::set_error(SQ_ERR_ARG, "sp_set_weights_device: null argument");
+  if (nedges != (int)g->ew.size())
+    return sq::set_error(SQ_ERR_ARG, "sp_set_weights_device: %d weights for %d edges", nedges, (int)g->ew.size());
+  if (int rc = g_build_and_upload(g)) return rc;  // pending host edits first: the device copy is about to lead
+  if (nedges == 0) return SQ_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t n = (size_t)nedges;
+  WeightSlots ws{g->d_wslots, g->d_wslots + n, g->d_wslots + 2 * n, g->d_wslots + 3 * n};
+  scatter_weights_kernel<<<(nedges + 255) / 256, 256, 0, st>>>(nedges, g->V, weights_dev, ws, g->d_adj, g->d_radj, g->d_ell,
+                                                             g->d_ovf, g->d_rell, g->d_rovf, g->d_fs_w, g->d_rs_w);
+  sq::count_launch();
+  SQ_CUDA_TRY(cudaGetLastError());
+  // keep the host log in step (it is what update_edge / writegraph / the next structural rebuild start from)
+  g->w_stage.resize(n);
+  SQ_CUDA_TRY(cudaMemcpyAsync(g->w_stage.data(), weights_dev, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+  SQ_CUDA_TRY(cudaStreamSynchronize(st));
+  for (size_t i = 0; i < n; ++i) {
+    const double x = g->w_stage[i];
+    if (x != x) continue;
+    g->ew[i] = x;
+    const int a = g->edge_slot[i];
+    if (a >= 0) { g->h_adj[a].w = x; g->h_radj[g->edge_rslot[i]].w = x; }
+  }
+  return SQ_OK;
+}
 
 int sp_sssp_batch_device(Graph* g, const int* origins_dev, int n, double* dist_dev, int* parent_dev, void* stream) {
   if (!g || (!origins_dev && n > 0)) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch_device: null argument");

@@ -137,7 +137,14 @@ class Graph:
                                   p.ctypes.data if want_parent else None), "sp_sssp_batch")
         return d, p
 
-    def sssp_batch_device(self, origins_dev, dist_dev=None, parent_dev=None, stream=None):
+    def set_weights_device(self, weights_dev, stream=None):
+        """Per-edge weights from a torch CUDA float64 tensor (creategraph order, NaN = keep)."""
+        import torch
+        sp = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
+        check(lib().sp_set_weights_device(self._h, C.c_void_p(weights_dev.data_ptr()), int(weights_dev.numel()), sp),
+              "sp_set_weights_device")
+
+    def sssp_batch_device(self, origins_dev, dist_dev=None, parent_dev=None, stream=None, reverse=False):
         """Device-resident batch.  Arguments are torch CUDA tensors (int32 origins [n]; float64 dist [n,V];
         int32 parent [n,V]); only their data pointers cross the C ABI.  Asynchronous on `stream`."""
         n = int(origins_dev.numel())
@@ -145,10 +152,10 @@ class Graph:
         if stream is None:
             import torch
             sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        check(lib().sp_sssp_batch_device(self._h, C.c_void_p(origins_dev.data_ptr()), n,
-                                         C.c_void_p(dist_dev.data_ptr()) if dist_dev is not None else None,
-                                         C.c_void_p(parent_dev.data_ptr()) if parent_dev is not None else None,
-                                         sp), "sp_sssp_batch_device")
+        check(lib().sp_sssp_batch_device_ex(self._h, C.c_void_p(origins_dev.data_ptr()), n,
+                                            C.c_void_p(dist_dev.data_ptr()) if dist_dev is not None else None,
+                                            C.c_void_p(parent_dev.data_ptr()) if parent_dev is not None else None,
+                                            sp, 1 if reverse else 0), "sp_sssp_batch_device")
 
     def last_stats(self):
         out = (C.c_longlong * 5)()

@@ -173,3 +173,44 @@ def test_full_size_properties(spi):
     dr, _ = gr.sssp_batch(origins[:1])
     # path costs are summed in opposite orders, so equality is to rounding only
     assert np.allclose(dr[0][origins[1]], d[1][origins[0]], rtol=1e-12)
+
+
+def test_reverse_trees_and_device_weight_refresh(spi):
+    """reverse=True == the oracle on the transposed edge list (bit-exact); sp_set_weights_device == sp_set_weights,
+    with NaN entries leaving weights alone, on a graph with vertices of in/out degree > 4 (overflow records)."""
+    import torch
+    from oracle import sssp as osssp
+    rng = np.random.default_rng(21)
+    V, E = 3000, 14000
+    s = rng.integers(0, V, E).astype(np.int32)
+    e = rng.integers(0, V, E).astype(np.int32)
+    w = rng.random(E) * 50.0 + 0.5
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    dests = rng.integers(0, V, 9).astype(np.int32)
+    o_dev = torch.from_numpy(dests).cuda()
+    d_dev = torch.empty((len(dests), V), dtype=torch.float64, device="cuda")
+    p_dev = torch.empty((len(dests), V), dtype=torch.int32, device="cuda")
+
+    def check(weights):
+        g.sssp_batch_device(o_dev, d_dev, p_dev, reverse=True)
+        torch.cuda.synchronize()
+        do, po = osssp.OracleGraph(e, s, weights, max_vertex_id=V - 1).sssp_batch(dests)
+        assert d_dev.cpu().numpy().tobytes() == do.tobytes()
+        assert (p_dev.cpu().numpy() == po).all()
+        d, p = g.sssp_batch(dests[:3])
+        do, po = osssp.OracleGraph(s, e, weights, max_vertex_id=V - 1).sssp_batch(dests[:3])
+        assert d.tobytes() == do.tobytes() and (p == po).all()
+
+    check(w)
+    w2 = w.copy()
+    upd = rng.random(E) < 0.4
+    w2[upd] = np.where(rng.random(int(upd.sum())) < 0.1, 1e8, rng.random(int(upd.sum())) * 80.0 + 0.1)
+    wd = torch.from_numpy(np.where(upd, w2, np.nan)).cuda()
+    g.set_weights_device(wd)
+    check(w2)
+    # a later host-side edit starts from the refreshed weights, not from stale ones
+    g.update_edge(int(s[0]), int(e[0]), 3.25)
+    last = np.nonzero((s == s[0]) & (e == e[0]))[0][-1]
+    w2[last] = 3.25
+    check(w2)
+    g.free()
