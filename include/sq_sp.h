@@ -65,11 +65,14 @@ int sp_remove_edge(Graph* graph, int vertex1, int vertex2);
 void sp_free_graph(Graph* graph);
 int sp_nvertices(Graph* graph);
 int sp_nedges(Graph* graph); /* adjacency entries (duplicates included) */
+int sp_nedges_logged(Graph* graph); /* edges ever inserted = length of the sp_set_weights arrays */
 
 /* One full tree per origin.  Host buffers: dist_out[n][V] (f64, DBL_MAX = unreachable) and
  * parent_out[n][V] (i32, -1 = none); either may be NULL.  Predecessors follow the canonical rule
  * parent[v] = min{u : fl(dist[u] + w(u,v)) == dist[v]}.  Returns 0, or a negative error code. */
 int sp_sssp_batch(Graph* graph, const int* origins, int n, double* dist_out, int* parent_out);
+/* reverse != 0: trees on the reversed graph (distances to, and next vertex towards, each origin). */
+int sp_sssp_batch_ex(Graph* graph, const int* origins, int n, double* dist_out, int* parent_out, int reverse);
 
 /* Page-locked host memory for sp_sssp_batch outputs: with both destinations allocated here the device-to-host
  * copies overlap the computation of the next chunk of trees (PCIe-bound instead of staging-bound). */

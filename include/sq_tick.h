@@ -29,7 +29,8 @@ extern "C" {
 #endif
 
 typedef struct SqNetDesc {
-  int32_t n_nodes, n_links, n_agents, reserved0;
+  int32_t n_nodes, n_links, n_agents;
+  int32_t reserved0;               /* flags: bit 0 = agents may come without routes (sq_attach_router follows) */
   uint64_t seed;
   /* ---- links (queue_class.py:396-442) ---- */
   const int32_t* link_start_node;  /* real node index, -1 for the virtual start of a source link     */
@@ -68,7 +69,7 @@ typedef struct SqNetDesc {
 typedef struct SqSim SqSim;
 
 /* Agent status codes (spatial_queue_b200/flatten.py STATUS_CODES). */
-enum { SQ_UNLOADED = 0, SQ_ENROUTE = 1, SQ_ARRIVE = 2, SQ_SHELTER_P = 3 };
+enum { SQ_UNLOADED = 0, SQ_ENROUTE = 1, SQ_ARRIVE = 2, SQ_SHELTER_P = 3, SQ_SHELTER_A1 = 4 };
 
 /* Build device state from a network that has not ticked yet.  NULL on failure (sq_last_error). */
 SqSim* sq_create(const SqNetDesc* desc);
@@ -92,6 +93,39 @@ int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t
 /* Link status changes (model/dta_meso_butte.py:77-81, 89-101, 113): closed != 0 zeroes the inflow
  * capacity in the link model (queue_class.py:455). */
 int sq_set_link_closed(SqSim* sim, int32_t n, const int32_t* link_idx, const uint8_t* closed);
+
+/* ---- device-side rerouting (Agent.get_path for every agent, queue_class.py:501-522; the drivers' reroute
+ * trigger and edge-weight refresh, run_traffic_simulation.py:81-84, 107-109) --------------------------------
+ * With a router attached, sq_step / sq_run do by themselves what the driver's agent loop does:
+ *   every weight_freq ticks: link weights from the queue lengths (queue_class.py:463-466) -> the routing graph
+ *                            (sp_set_weights_device), one reverse shortest-path tree per destination
+ *                            (sp_sssp_batch_device_ex) -> next-link tables;
+ *   every tick t > 0:        agents with t % reroute_freq == agent_key % reroute_freq adopt the newest tables from
+ *                            the end node of their current link unless the destination is out of reach (> 1e8).
+ * Attaching routes every agent once on the weights of the empty network (the t == 0 rule).  Agents whose
+ * destination is unreachable at t == 0 must be passed to sq_create as SQ_SHELTER_P (queue_class.py:504-510). */
+typedef struct SqRouterDesc {
+  void* graph;                 /* Graph* of include/sq_sp.h holding the real links as edges                       */
+  int32_t n_graph_edges;       /* edges in creategraph order                                                      */
+  int32_t n_dest;
+  const int32_t* dest_nodes;   /* [n_dest] node indices                                                           */
+  const int32_t* agent_dslot;  /* [n_agents] index into dest_nodes                                                */
+  const int64_t* agent_key;    /* [n_agents] agent ids (reroute stagger)                                          */
+  const int32_t* node_vertex;  /* [n_nodes] graph vertex id of each node                                          */
+  const int32_t* link_edge;    /* [n_links] graph edge that receives the link's weight, -1 = none                 */
+  int32_t n_pairs;             /* node2link_dict restricted to real start nodes (queue_class.py:149-156)          */
+  const int32_t* pair_start; const int32_t* pair_end; const int32_t* pair_link;
+  int32_t reroute_freq, weight_freq;
+} SqRouterDesc;
+int sq_attach_router(SqSim* sim, const SqRouterDesc* router);
+
+/* Agent-loop rule of the drivers (run_traffic_simulation.py:100-104, 113-118): a vehicle that has spent more than
+ * `seconds` on one real link gives up (status SQ_SHELTER_A1) and leaves the link before the link model of that tick.
+ * 0 (default) switches the rule off. */
+int sq_set_shelter_after(SqSim* sim, int32_t seconds);
+/* Per link: vehicles that sheltered on it (sum over a node's in-links = node.shelter_counts); per agent: the tick
+ * at which it arrived or sheltered (-1 otherwise). */
+int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick);
 
 /* ---- state read-back (any pointer may be NULL) ---- */
 int sq_get_link_state(SqSim* sim, int32_t* queue_len, int32_t* run_len, int32_t* total_left, double* inflow_c,

@@ -43,7 +43,9 @@ def _declare(L):
     L.sp_free_graph.restype = None; L.sp_free_graph.argtypes = [vp]
     L.sp_nvertices.restype = ci; L.sp_nvertices.argtypes = [vp]
     L.sp_nedges.restype = ci; L.sp_nedges.argtypes = [vp]
+    L.sp_nedges_logged.restype = ci; L.sp_nedges_logged.argtypes = [vp]
     L.sp_sssp_batch.restype = ci; L.sp_sssp_batch.argtypes = [vp, vp, ci, vp, vp]
+    L.sp_sssp_batch_ex.restype = ci; L.sp_sssp_batch_ex.argtypes = [vp, vp, ci, vp, vp, ci]
     L.sp_sssp_batch_device.restype = ci; L.sp_sssp_batch_device.argtypes = [vp, vp, ci, vp, vp, vp]
     L.sp_sssp_batch_device_ex.restype = ci; L.sp_sssp_batch_device_ex.argtypes = [vp, vp, ci, vp, vp, vp, ci]
     L.sp_set_weights_device.restype = ci; L.sp_set_weights_device.argtypes = [vp, vp, ci, vp]
@@ -67,6 +69,9 @@ def _declare(L):
     L.sq_sync.restype = ci; L.sq_sync.argtypes = [vp]
     L.sq_set_stream.restype = ci; L.sq_set_stream.argtypes = [vp, vp]
     L.sq_set_routes.restype = ci; L.sq_set_routes.argtypes = [vp, i32, vp, vp, vp]
+    L.sq_attach_router.restype = ci; L.sq_attach_router.argtypes = [vp, vp]
+    L.sq_set_shelter_after.restype = ci; L.sq_set_shelter_after.argtypes = [vp, i32]
+    L.sq_get_shelter_state.restype = ci; L.sq_get_shelter_state.argtypes = [vp, vp, vp]
     L.sq_set_link_closed.restype = ci; L.sq_set_link_closed.argtypes = [vp, i32, vp, vp]
     L.sq_get_link_state.restype = ci; L.sq_get_link_state.argtypes = [vp] * 7
     L.sq_get_link_vehicles.restype = ci; L.sq_get_link_vehicles.argtypes = [vp, vp, vp]

@@ -1271,6 +1271,8 @@ int sp_nedges(Graph* g) {
   return n;
 }
 
+int sp_nedges_logged(Graph* g) { return g ? (int)g->es.size() : 0; }
+
 void sp_free_graph(Graph* g) {
   if (!g) return;
   g_free_device(g);
@@ -1379,6 +1381,10 @@ void sp_free_host(void* ptr) {
 }
 
 int sp_sssp_batch(Graph* g, const int* origins, int n, double* dist_out, int* parent_out) {
+  return sp_sssp_batch_ex(g, origins, n, dist_out, parent_out, 0);
+}
+
+int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int* parent_out, int reverse) {
   if (!g || (!origins && n > 0)) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch: null argument");
   if (n <= 0) return SQ_OK;
   if (int rc = g_build_and_upload(g)) return rc;
@@ -1421,7 +1427,7 @@ int sp_sssp_batch(Graph* g, const int* origins, int n, double* dist_out, int* pa
     u64* dbuf = dist_out ? g->d_dist_buf + (size_t)b * chunk * V : nullptr;
     int* pbuf = parent_out ? g->d_parent_buf + (size_t)b * chunk * V : nullptr;
     if (k >= 2) SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_compute, g->ev_copied[b], 0));  // buffer b is free again
-    if (int rc = g_run_batch_device(g, g->d_origins + off, m, dbuf, pbuf, g->s_compute)) return rc;
+    if (int rc = g_run_batch_device(g, g->d_origins + off, m, dbuf, pbuf, g->s_compute, reverse != 0)) return rc;
     SQ_CUDA_TRY(cudaEventRecord(g->ev_done[b], g->s_compute));
     SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_copy, g->ev_done[b], 0));
     if (!pinned) SQ_CUDA_TRY(cudaStreamSynchronize(g->s_compute));  // pageable copies block the host anyway

@@ -32,6 +32,7 @@
 #include <numeric>
 #include <vector>
 
+#include "../../include/sq_sp.h"
 #include "../../include/sq_tick.h"
 #include "sq_common.cuh"
 
@@ -71,10 +72,30 @@ struct TickState {
   const int* a_destin;
   long long* a_route_off; int* a_route_len; int* a_route_pos; int* a_arrive;
   const int* route_pool;
+  // device router (sq_attach_router): per-destination next-link tables, K epochs of them
+  int D, K, freq;
+  const int* n_vertex;       // [N] graph vertex of node n
+  const int* a_dslot;        // [A] destination slot
+  int* a_epoch;              // [A] table epoch slot the agent's route follows (agents with a_route_len < 0)
+  int* next_tbl;             // [K][D][N] link to take at node n towards destination d, -1 at d / unreachable
+  double* dist_tbl;          // [K][D][N] distance to d
+  int* cur_epoch;            // slot of the newest tables
+  const int* bucket_ptr;     // [freq + 1] agents by (key % freq)
+  const int* bucket_agents;
+  const int* l_edge;         // [L] edge of the routing graph the link's weight goes to, -1 = none
+  const double* l_capacity; const double* l_maxmph;
+  double* w_edge;            // [graph edges] staging for sp_set_weights_device
+  int* mat_pool;             // routes materialised on the device (agents that could not be rerouted)
+  long long* mat_used; long long mat_cap;
+  // agent-loop rules of the drivers
+  const int* l_dwell;        // floor(fft) + 2: upper bound of ready_tick - enter_time
+  int* l_shelter;            // vehicles that gave up on this link (shelter_a1)
+  int shelter_after;         // seconds on one link before a vehicle shelters (run_traffic_simulation.py:103), 0 = off
   // run control
   int* tick_link;  // tick the next link-phase launch simulates
   int* tick_node;  // tick the next node-phase launch simulates
   u64* counters;   // [0] ticks [1] agent_steps [2] moves [3] active nodes [4] arrivals [5] loaded [6] loaded, frozen
+                   // [7] sheltered on a link [8] the same, frozen
   int* err;        // [0] code (0 = ok) [1] agent [2] node [3] link
 };
 
@@ -105,6 +126,17 @@ __device__ __forceinline__ int ready_tick(int t_enter, double fft) {
   return r;
 }
 
+// Next link of `agent` once it stands at the end of link `ol` (find_next_link, queue_class.py:598-608).
+// Explicit routes are link sequences in a pool (negative offsets: the device-side pool of k_evacuate);
+// table routes (a_route_len < 0) follow the next-link table of the epoch the agent was last routed on.
+__device__ __forceinline__ int route_link_at(const TickState& s, int agent, int pos) {
+  const long long off = s.a_route_off[agent];
+  return off >= 0 ? s.route_pool[off + pos] : s.mat_pool[-(off + 1) + pos];
+}
+__device__ __forceinline__ size_t tbl_index(const TickState& s, int epoch, int dslot, int node) {
+  return ((size_t)epoch * s.D + dslot) * (size_t)s.N + node;
+}
+
 // ---- phase 1: load + link model, one thread per link ---------------------------------------------------
 __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
   const int l = blockIdx.x * blockDim.x + threadIdx.x;
@@ -113,16 +145,42 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
     *s.tick_node = t;
     // vehicles on links after the previous tick = loaded - arrived up to then; counters[6] is the loaded
     // count frozen by the previous node phase (this launch is adding to counters[5] concurrently)
-    if (s.counters[0] > 0) s.counters[1] += s.counters[6] - s.counters[4];
+    // same for the vehicles that sheltered on a link: counters[8] is counters[7] frozen by the node phase
+    if (s.counters[0] > 0) s.counters[1] += s.counters[6] - s.counters[4] - s.counters[8];
     s.counters[0] += 1;
   }
-  int loaded = 0;
+  int loaded = 0, sheltered = 0;
   if (l < s.L) {
     unsigned tl = s.tail[l];
     unsigned qt = s.qtail[l];
     const long long base = s.l_ring_base[l];
     const unsigned mask = s.l_ring_mask[l];
     long long li = s.len_in[l];
+    if (s.shelter_after > 0 && !s.l_virtual[l]) {
+      // agent loop of the driver (run_traffic_simulation.py:100-104, 113-118): a vehicle that has spent more
+      // than shelter_after seconds on this link gives up (status shelter_a1) and is taken off the link before
+      // the link model runs.  Ring order is entry order, so these vehicles are a prefix of the ring.
+      unsigned h = s.head[l];
+      const int dwell = s.l_dwell[l];
+      long long lo = 0;
+      while (h != tl) {
+        const int2 e = s.ring[base + (h & mask)];
+        if (e.y != INT_MAX && (long long)t - e.y + dwell <= s.shelter_after) break;   // cannot be old enough yet
+        int4 rec = s.a_rec[e.x];
+        if (t - rec.z <= s.shelter_after) break;
+        rec.w = (rec.w & ~0xff) | SQ_SHELTER_A1;
+        s.a_rec[e.x] = rec;
+        s.a_arrive[e.x] = t;
+        lo += (rec.w >> 8) & 0xff;
+        ++h; ++sheltered;
+      }
+      if (sheltered) {
+        s.head[l] = h;
+        s.len_out[l] += lo;
+        s.l_shelter[l] += sheltered;
+        if ((int)(qt - h) < 0) { qt = h; s.qtail[l] = qt; }   // they were still in the run part
+      }
+    }
     if (s.l_virtual[l]) {
       // load_vehicle (:587-596): the next entries of the prefilled departure sequence whose departure == t
       const unsigned cnt = (unsigned)s.l_vcount[l];
@@ -150,12 +208,18 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
     s.out_c[l] = c;
     s.in_c[l] = s.l_closed[l] ? 0.0 : c;
   }
-  const unsigned any = __ballot_sync(0xffffffffu, loaded > 0);
+  const unsigned any = __ballot_sync(0xffffffffu, (loaded | sheltered) > 0);
   if (any) {
-    int tot = loaded;
+    int tot = loaded, sh = sheltered;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    if (sq::lane_id() == 0) atomicAdd(&s.counters[5], (u64)tot);
+    for (int o = 16; o > 0; o >>= 1) {
+      tot += __shfl_xor_sync(0xffffffffu, tot, o);
+      sh += __shfl_xor_sync(0xffffffffu, sh, o);
+    }
+    if (sq::lane_id() == 0) {
+      if (tot) atomicAdd(&s.counters[5], (u64)tot);
+      if (sh) atomicAdd(&s.counters[7], (u64)sh);
+    }
   }
 }
 
@@ -227,9 +291,15 @@ __device__ void admit_from_link(const TickState& s, AdmitCtx& c, int il, int k, 
         s.tail[ol] = tl + 1u;
         s.len_in[ol] += vlen;
         // move_agent_to_next_link + find_next_link (:610-615, :598-608)
-        const int pos = s.a_route_pos[agent] + 1;
-        const int nxt = pos < s.a_route_len[agent] ? s.route_pool[s.a_route_off[agent] + pos] : -1;
-        s.a_route_pos[agent] = pos;
+        const int rlen = s.a_route_len[agent];
+        int nxt;
+        if (rlen < 0) {
+          nxt = s.next_tbl[tbl_index(s, s.a_epoch[agent], s.a_dslot[agent], s.l_end[ol])];
+        } else {
+          const int pos = s.a_route_pos[agent] + 1;
+          nxt = pos < rlen ? route_link_at(s, agent, pos) : -1;
+          s.a_route_pos[agent] = pos;
+        }
         s.a_rec[agent] = make_int4(nxt, ol, c.t, rec.w);
       }
     }
@@ -257,7 +327,7 @@ __device__ void admit_from_link(const TickState& s, AdmitCtx& c, int il, int k, 
 __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   const int t = *s.tick_node;
-  if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; }
+  if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; s.counters[8] = s.counters[7]; }
   int moves = 0, arrivals = 0, active = 0;
   if (n < s.N) {
     const int ib = s.in_ptr[n];
@@ -426,8 +496,96 @@ __global__ void k_set_routes(const TickState s, int n, const int* agent_idx, con
   s.a_route_off[a] = new_off[i];
   s.a_route_len[a] = new_len[i];
   s.a_route_pos[a] = 0;
-  rec.x = new_len[i] > 0 ? s.route_pool[new_off[i]] : -1;
+  rec.x = new_len[i] > 0 ? s.route_pool[new_off[i]] : -1;   // host-supplied routes always live in route_pool
   s.a_rec[a] = rec;
+}
+
+// ---- device router ------------------------------------------------------------------------------------------
+// Edge weights for routing (Link.update_travel_time_by_queue_length, queue_class.py:463-466): one thread per
+// link, evaluated left to right like the Python expression; closed and source links keep their weight (NaN).
+__global__ void __launch_bounds__(256) k_link_weights(const TickState s) {
+  const int l = blockIdx.x * 256 + threadIdx.x;
+  if (l >= s.L) return;
+  const int e = s.l_edge[l];
+  if (e < 0) return;
+  double w = __longlong_as_double(0x7ff8000000000000ll);
+  if (!s.l_closed[l] && !s.l_virtual[l]) {
+    const double q = (double)(int)(s.qtail[l] - s.head[l]);
+    w = q / (s.l_capacity[l] + 0.1) * 3600.0 * 25.0 / s.l_maxmph[l] + s.l_fft[l];
+  }
+  s.w_edge[e] = w;
+}
+
+// Reverse trees (dist / next vertex towards each destination, indexed by graph vertex) -> tables indexed by
+// node: the link to take is the node2link choice for (node, next node) (queue_class.py:149-156, 605).
+__global__ void __launch_bounds__(256) k_build_tables(const TickState s, int slot, int V, const double* __restrict__ tdist,
+                                                      const int* __restrict__ tnext, const int* __restrict__ pair_ptr,
+                                                      const int* __restrict__ pair_endv, const int* __restrict__ pair_link) {
+  const int n = blockIdx.x * 256 + threadIdx.x;
+  const int d = blockIdx.y;
+  if (n >= s.N) return;
+  const int v = s.n_vertex[n];
+  const double dist = tdist[(size_t)d * V + v];
+  const int succ = tnext[(size_t)d * V + v];
+  int link = -1;
+  if (succ >= 0)
+    for (int k = pair_ptr[n]; k < pair_ptr[n + 1]; ++k)
+      if (pair_endv[k] == succ) { link = pair_link[k]; break; }
+  const size_t i = tbl_index(s, slot, d, n);
+  s.dist_tbl[i] = dist;
+  s.next_tbl[i] = link;
+  if (n == 0 && d == 0) *s.cur_epoch = slot;
+}
+
+// Agent.get_path + find_next_link for the agents due this tick (t % freq == agent_id % freq,
+// run_traffic_simulation.py:107-109): adopt the newest tables unless the destination is out of reach
+// (distance > 1e8 keeps the old route, queue_class.py:511-513).  `all` != 0 routes every agent (t == 0).
+__global__ void __launch_bounds__(128) k_reroute(const TickState s, int all) {
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  int a;
+  if (all) {
+    if (i >= s.A) return;
+    a = i;
+  } else {
+    const int t = *s.tick_link;
+    if (t <= 0) return;
+    const int b = t % s.freq;
+    const int k = s.bucket_ptr[b] + i;
+    if (k >= s.bucket_ptr[b + 1]) return;
+    a = s.bucket_agents[k];
+  }
+  int4 rec = s.a_rec[a];
+  const int st = rec.w & 0xff;
+  if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
+  const int node = s.l_end[rec.y];
+  const int e = *s.cur_epoch;
+  const size_t idx = tbl_index(s, e, s.a_dslot[a], node);
+  if (s.dist_tbl[idx] > 1e8) return;
+  s.a_epoch[a] = e;
+  s.a_route_len[a] = -1;
+  rec.x = s.next_tbl[idx];
+  s.a_rec[a] = rec;
+}
+
+// Before table slot `slot` is overwritten: agents that still follow it (their reroutes kept failing) get
+// their remaining route written out as a link sequence, so that they keep the old route like the reference.
+__global__ void __launch_bounds__(128) k_evacuate(const TickState s, int slot) {
+  const int a = blockIdx.x * 128 + threadIdx.x;
+  if (a >= s.A) return;
+  if (s.a_route_len[a] >= 0 || s.a_epoch[a] != slot) return;
+  const int4 rec = s.a_rec[a];
+  const int st = rec.w & 0xff;
+  if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
+  const int d = s.a_dslot[a];
+  int len = 0;
+  for (int l = rec.x; l >= 0 && len <= s.L; l = s.next_tbl[tbl_index(s, slot, d, s.l_end[l])]) ++len;
+  const long long off = (long long)atomicAdd((u64*)s.mat_used, (u64)len);
+  if (off + len > s.mat_cap) { raise_error(s, 4, a, -1, -1); return; }
+  int k = 0;
+  for (int l = rec.x; l >= 0 && k < len; l = s.next_tbl[tbl_index(s, slot, d, s.l_end[l])]) s.mat_pool[off + k++] = l;
+  s.a_route_off[a] = -(off + 1);
+  s.a_route_len[a] = len;
+  s.a_route_pos[a] = 0;
 }
 
 __global__ void k_set_closed(const TickState s, int n, const int* link_idx, const unsigned char* closed) {
@@ -459,6 +617,16 @@ struct SqSim {
   cudaStream_t stream = nullptr;
   bool own_stream = true;
   int next_t = INT_MIN;  // tick the device counters are armed for
+  long long sheltered = 0;
+  // device router
+  Graph* router_graph = nullptr;
+  int wfreq = 0, max_bucket = 0, graph_V = 0, graph_E = 0;
+  int last_refresh_t = INT_MIN;
+  int host_epoch = 0;
+  int* d_dest_vertex = nullptr;     // [D]
+  double* d_tdist = nullptr;        // [D][V] reverse-tree scratch
+  int* d_tnext = nullptr;
+  int* d_pair_ptr = nullptr; int* d_pair_endv = nullptr; int* d_pair_link = nullptr;
   long long launches = 0;
   cudaGraphExec_t graph = nullptr;
   int graph_ticks = 0;
@@ -609,6 +777,22 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     std::vector<long long> zn(N, 0);
     if ((rc = dev_upload_rw(sim, &s.node_move, zn))) return rc;
   }
+  {
+    std::vector<int> dwell(L), zi(L, 0);
+    for (int l = 0; l < L; ++l) {
+      const double f = d->link_fft[l];
+      dwell[l] = f < 2.0e9 ? (int)std::floor(f) + 2 : INT_MAX / 2;
+    }
+    if ((rc = dev_upload(sim, &s.l_dwell, dwell))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.l_shelter, zi))) return rc;
+    if ((rc = dev_upload_ptr(sim, &s.l_capacity, d->link_capacity, (size_t)L))) return rc;
+    if ((rc = dev_upload_ptr(sim, &s.l_maxmph, d->link_maxmph, (size_t)L))) return rc;
+    s.shelter_after = 0;
+    s.D = 0; s.K = 0; s.freq = 1;
+    s.n_vertex = nullptr; s.a_dslot = nullptr; s.a_epoch = nullptr; s.next_tbl = nullptr; s.dist_tbl = nullptr;
+    s.cur_epoch = nullptr; s.bucket_ptr = nullptr; s.bucket_agents = nullptr; s.l_edge = nullptr; s.w_edge = nullptr;
+    s.mat_pool = nullptr; s.mat_used = nullptr; s.mat_cap = 0;
+  }
   // agents
   {
     std::vector<int4> rec((size_t)A);
@@ -619,7 +803,7 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
       off[a] = b; len[a] = (int)(e - b);
       const int vl = virt_of_node[d->agent_origin[a]];
       rec[a] = make_int4(e > b ? d->route_links[b] : -1, vl, -1, (int)d->agent_status[a] | (d->agent_vlen[a] << 8));
-      if (d->agent_status[a] == SQ_UNLOADED && e == b)
+      if (d->agent_status[a] == SQ_UNLOADED && e == b && !(d->reserved0 & 1))
         return sq::set_error(SQ_ERR_ARG, "agent %d is to be loaded but has an empty route (queue_class.py:595 raises KeyError)", a);
     }
     if ((rc = dev_upload_rw(sim, &s.a_rec, rec))) return rc;
@@ -638,7 +822,7 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     std::vector<int> z2(1, 0);
     if ((rc = dev_upload_rw(sim, &s.tick_link, z2))) return rc;
     if ((rc = dev_upload_rw(sim, &s.tick_node, z2))) return rc;
-    std::vector<u64> zc(8, 0);
+    std::vector<u64> zc(12, 0);
     if ((rc = dev_upload_rw(sim, &s.counters, zc))) return rc;
     std::vector<int> ze(4, 0);
     if ((rc = dev_upload_rw(sim, &s.err, ze))) return rc;
@@ -653,6 +837,8 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
 
 static int launch_tick(SqSim* sim, cudaStream_t st) {
   const int L = sim->L, N = sim->N;
+  if (sim->router_graph && sim->max_bucket > 0)
+    k_reroute<<<(sim->max_bucket + 127) / 128, 128, 0, st>>>(sim->st, 0);
   k_link_phase<<<(L + 255) / 256, 256, 0, st>>>(sim->st);
   k_node_phase<<<(N + 63) / 64, 64, 0, st>>>(sim->st);
   return SQ_OK;
@@ -687,9 +873,40 @@ static int check_device_error(SqSim* sim) {
   if (e[0] == 0) return SQ_OK;
   static const char* what[] = {"", "queued vehicle has no next link away from its destination (queue_class.py:312-314)",
                                "vehicle's next link does not leave this node (KeyError at queue_class.py:257-262)",
-                               "vehicle ring overflow (link storage bound violated)"};
-  return sq::set_error(SQ_ERR_STATE, "%s: agent %d, node %d, link %d", what[e[0] < 4 ? e[0] : 0], e[1], e[2], e[3]);
+                               "vehicle ring overflow (link storage bound violated)",
+                               "device route pool exhausted while keeping the old route of an unroutable agent"};
+  return sq::set_error(SQ_ERR_STATE, "%s: agent %d, node %d, link %d", what[e[0] < 5 ? e[0] : 0], e[1], e[2], e[3]);
 }
+
+// Weight refresh + new routing tables (what the drivers do every `wfreq` ticks before the agent loop,
+// run_traffic_simulation.py:81-84, followed by one reverse tree per destination instead of one Dijkstra per agent).
+static int router_refresh(SqSim* sim, int t) {
+  if (!sim->router_graph || sim->last_refresh_t == t) return SQ_OK;
+  TickState& s = sim->st;
+  cudaStream_t st = sim->stream;
+  const int slot = (sim->host_epoch + 1) % s.K;
+  if (sim->last_refresh_t != INT_MIN) {  // the slot is about to be recycled: stragglers keep their old route
+    k_evacuate<<<(sim->A + 127) / 128, 128, 0, st>>>(s, slot);
+    sq::count_launch(); sim->launches += 1;
+  }
+  k_link_weights<<<(sim->L + 255) / 256, 256, 0, st>>>(s);
+  sq::count_launch(); sim->launches += 1;
+  SQ_CUDA_TRY(cudaGetLastError());
+  if (int rc = sp_set_weights_device(sim->router_graph, s.w_edge, sim->graph_E, (void*)st))
+    return sq::set_error(rc, "router refresh: %s", sp_last_error());
+  if (int rc = sp_sssp_batch_device_ex(sim->router_graph, sim->d_dest_vertex, s.D, sim->d_tdist, sim->d_tnext, (void*)st, 1))
+    return sq::set_error(rc, "router refresh: %s", sp_last_error());
+  dim3 grid((unsigned)((sim->N + 255) / 256), (unsigned)s.D);
+  k_build_tables<<<grid, 256, 0, st>>>(s, slot, sim->graph_V, sim->d_tdist, sim->d_tnext, sim->d_pair_ptr, sim->d_pair_endv,
+                                       sim->d_pair_link);
+  sq::count_launch(); sim->launches += 1;
+  SQ_CUDA_TRY(cudaGetLastError());
+  sim->host_epoch = slot;
+  sim->last_refresh_t = t;
+  return SQ_OK;
+}
+
+static int kernels_per_tick(const SqSim* sim) { return (sim->router_graph && sim->max_bucket > 0) ? 3 : 2; }
 
 extern "C" {
 
@@ -712,9 +929,11 @@ void sq_destroy(SqSim* sim) {
 int sq_step(SqSim* sim, int32_t t) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_step: null sim");
   if (int rc = arm_tick(sim, t)) return rc;
+  if (sim->router_graph && sim->wfreq > 0 && t % sim->wfreq == 0)
+    if (int rc = router_refresh(sim, t)) return rc;
   launch_tick(sim, sim->stream);
   SQ_CUDA_TRY(cudaGetLastError());
-  sq::count_launch(2); sim->launches += 2;
+  sq::count_launch(kernels_per_tick(sim)); sim->launches += kernels_per_tick(sim);
   sim->next_t = t + 1;
   return SQ_OK;
 }
@@ -725,14 +944,26 @@ int sq_run(SqSim* sim, int32_t t0, int32_t n) {
   if (int rc = arm_tick(sim, t0)) return rc;
   if (!sim->graph && n >= kGraphTicks)
     if (int rc = build_graph(sim)) return rc;
-  int left = n;
-  while (sim->graph && left >= sim->graph_ticks) {
-    SQ_CUDA_TRY(cudaGraphLaunch(sim->graph, sim->stream));
-    left -= sim->graph_ticks;
+  // segments between routing refreshes; each is replayed as CUDA graphs of kGraphTicks ticks + single ticks
+  int t = t0;
+  const int end = t0 + n;
+  while (t < end) {
+    int seg_end = end;
+    if (sim->router_graph && sim->wfreq > 0) {
+      if (t % sim->wfreq == 0)
+        if (int rc = router_refresh(sim, t)) return rc;
+      seg_end = std::min(end, (t / sim->wfreq + 1) * sim->wfreq);
+    }
+    int left = seg_end - t;
+    while (sim->graph && left >= sim->graph_ticks) {
+      SQ_CUDA_TRY(cudaGraphLaunch(sim->graph, sim->stream));
+      left -= sim->graph_ticks;
+    }
+    for (int i = 0; i < left; ++i) launch_tick(sim, sim->stream);
+    t = seg_end;
   }
-  for (int i = 0; i < left; ++i) launch_tick(sim, sim->stream);
   SQ_CUDA_TRY(cudaGetLastError());
-  sq::count_launch(2ll * n); sim->launches += 2ll * n;
+  sq::count_launch((long long)kernels_per_tick(sim) * n); sim->launches += (long long)kernels_per_tick(sim) * n;
   sim->next_t = t0 + n;
   return SQ_OK;
 }
@@ -789,6 +1020,122 @@ int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t
   cudaFree(d_idx); cudaFree(d_off); cudaFree(d_len);
   sim->pool_used += add;
   return SQ_OK;
+}
+
+int sq_set_shelter_after(SqSim* sim, int32_t seconds) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_set_shelter_after: null sim");
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  sim->st.shelter_after = seconds > 0 ? seconds : 0;
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel parameters changed
+  return SQ_OK;
+}
+
+int sq_attach_router(SqSim* sim, const SqRouterDesc* r) {
+  if (!sim || !r || !r->graph) return sq::set_error(SQ_ERR_ARG, "sq_attach_router: null argument");
+  if (sim->router_graph) return sq::set_error(SQ_ERR_ARG, "sq_attach_router: a router is already attached");
+  const int N = sim->N, L = sim->L, A = sim->A, D = r->n_dest;
+  if (D <= 0 || r->reroute_freq <= 0 || r->weight_freq <= 0)
+    return sq::set_error(SQ_ERR_ARG, "sq_attach_router: n_dest, reroute_freq and weight_freq must be positive");
+  Graph* g = (Graph*)r->graph;
+  if (int rc = sp_sync(g)) return sq::set_error(rc, "sq_attach_router: %s", sp_last_error());
+  const int V = sp_nvertices(g), E = r->n_graph_edges;
+  for (int n = 0; n < N; ++n)
+    if (r->node_vertex[n] < 0 || r->node_vertex[n] >= V)
+      return sq::set_error(SQ_ERR_ARG, "sq_attach_router: node %d maps to vertex %d outside the graph (%d vertices)", n, r->node_vertex[n], V);
+  for (int l = 0; l < L; ++l)
+    if (r->link_edge[l] >= E) return sq::set_error(SQ_ERR_ARG, "sq_attach_router: link %d maps to edge %d of %d", l, r->link_edge[l], E);
+  for (int a = 0; a < A; ++a)
+    if (r->agent_dslot[a] < 0 || r->agent_dslot[a] >= D) return sq::set_error(SQ_ERR_ARG, "sq_attach_router: agent %d has destination slot %d", a, r->agent_dslot[a]);
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  TickState& s = sim->st;
+  int rc;
+  // epochs kept: a route is at most reroute_freq ticks old when it is renewed; +2 for the slot being built
+  const int K = r->reroute_freq / r->weight_freq + 3;
+  s.D = D; s.K = K; s.freq = r->reroute_freq;
+  if ((rc = dev_upload_ptr(sim, &s.n_vertex, r->node_vertex, (size_t)N))) return rc;
+  if ((rc = dev_upload_ptr(sim, &s.a_dslot, r->agent_dslot, (size_t)A))) return rc;
+  if ((rc = dev_upload_ptr(sim, &s.l_edge, r->link_edge, (size_t)L))) return rc;
+  {
+    std::vector<int> z((size_t)std::max(A, 1), 0);
+    if ((rc = dev_upload_rw(sim, &s.a_epoch, z))) return rc;
+    std::vector<int> one(1, 0);
+    if ((rc = dev_upload_rw(sim, &s.cur_epoch, one))) return rc;
+    std::vector<long long> zl(1, 0);
+    if ((rc = dev_upload_rw(sim, &s.mat_used, zl))) return rc;
+  }
+  const size_t tbl = (size_t)K * D * N;
+  SQ_CUDA_TRY(cudaMalloc(&s.next_tbl, sizeof(int) * tbl)); sim->allocs.push_back(s.next_tbl);
+  SQ_CUDA_TRY(cudaMalloc(&s.dist_tbl, sizeof(double) * tbl)); sim->allocs.push_back(s.dist_tbl);
+  SQ_CUDA_TRY(cudaMalloc(&s.w_edge, sizeof(double) * (size_t)std::max(E, 1))); sim->allocs.push_back(s.w_edge);
+  SQ_CUDA_TRY(cudaMemset(s.w_edge, 0xff, sizeof(double) * (size_t)std::max(E, 1)));  // NaN = keep
+  s.mat_cap = std::max<long long>(1 << 20, 16ll * A);
+  SQ_CUDA_TRY(cudaMalloc(&s.mat_pool, sizeof(int) * (size_t)s.mat_cap)); sim->allocs.push_back(s.mat_pool);
+  SQ_CUDA_TRY(cudaMalloc(&sim->d_tdist, sizeof(double) * (size_t)D * V)); sim->allocs.push_back(sim->d_tdist);
+  SQ_CUDA_TRY(cudaMalloc(&sim->d_tnext, sizeof(int) * (size_t)D * V)); sim->allocs.push_back(sim->d_tnext);
+  {
+    std::vector<int> dv((size_t)D);
+    for (int d = 0; d < D; ++d) {
+      if (r->dest_nodes[d] < 0 || r->dest_nodes[d] >= N) return sq::set_error(SQ_ERR_ARG, "sq_attach_router: destination %d is node %d", d, r->dest_nodes[d]);
+      dv[d] = r->node_vertex[r->dest_nodes[d]];
+    }
+    const int* p = nullptr;
+    if ((rc = dev_upload(sim, &p, dv))) return rc;
+    sim->d_dest_vertex = const_cast<int*>(p);
+  }
+  {  // (start node, end node) -> link table as a CSR over start nodes, end nodes as graph vertices
+    std::vector<int> ptr((size_t)N + 1, 0), endv((size_t)std::max(r->n_pairs, 1)), link((size_t)std::max(r->n_pairs, 1));
+    for (int k = 0; k < r->n_pairs; ++k) {
+      if (r->pair_start[k] < 0 || r->pair_start[k] >= N || r->pair_end[k] < 0 || r->pair_end[k] >= N || r->pair_link[k] < 0 || r->pair_link[k] >= L)
+        return sq::set_error(SQ_ERR_ARG, "sq_attach_router: pair %d is out of range", k);
+      ++ptr[(size_t)r->pair_start[k] + 1];
+    }
+    for (int n = 0; n < N; ++n) ptr[(size_t)n + 1] += ptr[n];
+    std::vector<int> fill(ptr.begin(), ptr.end() - 1);
+    for (int k = 0; k < r->n_pairs; ++k) {
+      const int pos = fill[r->pair_start[k]]++;
+      endv[pos] = r->node_vertex[r->pair_end[k]];
+      link[pos] = r->pair_link[k];
+    }
+    const int* p = nullptr;
+    if ((rc = dev_upload(sim, &p, ptr))) return rc; sim->d_pair_ptr = const_cast<int*>(p);
+    if ((rc = dev_upload(sim, &p, endv))) return rc; sim->d_pair_endv = const_cast<int*>(p);
+    if ((rc = dev_upload(sim, &p, link))) return rc; sim->d_pair_link = const_cast<int*>(p);
+  }
+  {  // agents by (agent id mod reroute_freq): the reroute kernel only visits the bucket of the tick
+    const int F = r->reroute_freq;
+    std::vector<int> ptr((size_t)F + 1, 0), ag((size_t)std::max(A, 1));
+    auto bucket = [&](int a) { long long m = r->agent_key[a] % F; return (int)(m < 0 ? m + F : m); };
+    for (int a = 0; a < A; ++a) ++ptr[(size_t)bucket(a) + 1];
+    sim->max_bucket = 0;
+    for (int b = 0; b < F; ++b) { sim->max_bucket = std::max(sim->max_bucket, ptr[(size_t)b + 1]); ptr[(size_t)b + 1] += ptr[b]; }
+    std::vector<int> fill(ptr.begin(), ptr.end() - 1);
+    for (int a = 0; a < A; ++a) ag[fill[bucket(a)]++] = a;
+    if ((rc = dev_upload(sim, &s.bucket_ptr, ptr))) return rc;
+    if ((rc = dev_upload(sim, &s.bucket_agents, ag))) return rc;
+  }
+  sim->router_graph = g;
+  sim->wfreq = r->weight_freq;
+  sim->graph_V = V; sim->graph_E = E;
+  sim->host_epoch = K - 1;          // the first refresh fills slot 0
+  sim->last_refresh_t = INT_MIN;
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }
+  // t = 0: weights from the empty network, tables, and every agent routed (run_traffic_simulation.py:107)
+  if ((rc = router_refresh(sim, 0))) return rc;
+  if (A > 0) {
+    k_reroute<<<(A + 127) / 128, 128, 0, sim->stream>>>(s, 1);
+    sq::count_launch(); sim->launches += 1;
+  }
+  SQ_CUDA_TRY(cudaGetLastError());
+  return sq_sync(sim);
+}
+
+int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "null sim");
+  if (link_shelter)
+    SQ_CUDA_TRY(cudaMemcpyAsync(link_shelter, sim->st.l_shelter, sizeof(int) * (size_t)sim->L, cudaMemcpyDeviceToHost, sim->stream));
+  if (agent_stop_tick)
+    SQ_CUDA_TRY(cudaMemcpyAsync(agent_stop_tick, sim->st.a_arrive, sizeof(int) * (size_t)sim->A, cudaMemcpyDeviceToHost, sim->stream));
+  return sq_sync(sim);
 }
 
 int sq_set_link_closed(SqSim* sim, int32_t n, const int32_t* link_idx, const uint8_t* closed) {
@@ -873,6 +1220,7 @@ int sq_get_agent_state(SqSim* sim, uint8_t* status, int32_t* cur, int32_t* next,
     if (cur) cur[a] = rec[a].y;
     if (next) next[a] = rec[a].x;
     if (enter) enter[a] = rec[a].z;
+    if (arrive && (rec[a].w & 0xff) != SQ_ARRIVE) arrive[a] = -1;   // the slot also holds shelter ticks
   }
   return SQ_OK;
 }
@@ -900,11 +1248,12 @@ int sq_get_link_weights(SqSim* sim, double* w) {
 
 int sq_get_counters(SqSim* sim, int64_t* out6) {
   if (!sim || !out6) return sq::set_error(SQ_ERR_ARG, "null argument");
-  u64 c[8];
+  u64 c[12];
   SQ_CUDA_TRY(cudaMemcpyAsync(c, sim->st.counters, sizeof(c), cudaMemcpyDeviceToHost, sim->stream));
   if (int rc = sq_sync(sim)) return rc;
+  sim->sheltered = (long long)c[7];
   out6[0] = (int64_t)c[0];
-  out6[1] = (int64_t)(c[1] + (c[0] > 0 ? c[5] - c[4] : 0));  // + vehicles on links after the last tick
+  out6[1] = (int64_t)(c[1] + (c[0] > 0 ? c[5] - c[4] - c[7] : 0));  // + vehicles on links after the last tick
   out6[2] = (int64_t)c[2]; out6[3] = (int64_t)c[3]; out6[4] = (int64_t)c[4];
   out6[5] = sim->launches;
   return SQ_OK;

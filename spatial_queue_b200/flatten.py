@@ -157,3 +157,59 @@ def flatten_agents(f, network):
     f.route_ptr = np.array(ptr, np.int64)
     f.route_links = np.array(links, np.int32)
     return f
+
+
+def router_arrays(f, network):
+    """Arrays sq_attach_router needs (include/sq_tick.h SqRouterDesc), from a flattened network whose routing graph
+    `network.g` was built by the loader (interface.from_dataframe on the real links in links order,
+    queue_class.py:123): destinations, per-agent destination slot, node -> graph vertex, link -> graph edge.
+
+    link_edge follows what `link.update_travel_time_by_queue_length(g)` does to parallel links: every link of a
+    duplicated (start, end) pair calls update_edge(start, end, w), which writes the LAST inserted edge of the pair
+    (graph.cc:13, 34-36), so after the loop over links only the last link's weight survives, on the last edge."""
+    f.node_vertex = f.node_key.astype(np.int32)
+    n_virtual = int(f.link_is_virtual.sum())
+    edge = np.full(len(f.link_ids), -1, np.int32)
+    last_of_pair = {}
+    for i, lid in enumerate(f.link_ids):
+        link = network.links[lid]
+        if link.link_type == "v":
+            continue
+        last_of_pair[(link.start_nid, link.end_nid)] = i
+    for i in last_of_pair.values():
+        edge[i] = i - n_virtual
+    f.link_edge = edge
+    dests = sorted(set(int(d) for d in f.agent_destin))
+    slot = {d: k for k, d in enumerate(dests)}
+    f.dest_nodes = np.array(dests, np.int32)
+    f.agent_dslot = np.array([slot[int(d)] for d in f.agent_destin], np.int32)
+    return f
+
+
+def router_arrays_flat(f):
+    """router_arrays from the flat arrays alone (golden files, synthetic networks): the routing graph is taken to
+    hold the real links in link order (edge k = k-th real link), as the loader builds it."""
+    f.node_vertex = np.asarray(f.node_key).astype(np.int32)
+    virt = np.asarray(f.link_is_virtual).astype(bool)
+    real = np.nonzero(~virt)[0]
+    edge = np.full(len(virt), -1, np.int32)
+    last = {}
+    for k, i in enumerate(real):
+        last[(int(f.link_start_node[i]), int(f.link_end_node[i]))] = (i, k)
+    for i, k in last.values():
+        edge[i] = k
+    f.link_edge = edge
+    dests = sorted(set(int(d) for d in f.agent_destin))
+    slot = {d: k for k, d in enumerate(dests)}
+    f.dest_nodes = np.array(dests, np.int32)
+    f.agent_dslot = np.array([slot[int(d)] for d in f.agent_destin], np.int32)
+    return f
+
+
+def routing_graph_flat(f):
+    """The loader's routing graph rebuilt from flat arrays: real links in order, vertices = node keys, weight = fft."""
+    from . import sp_interface
+    real = np.nonzero(~np.asarray(f.link_is_virtual).astype(bool))[0]
+    key = np.asarray(f.node_key)
+    return sp_interface.from_arrays(key[f.link_start_node[real]], key[f.link_end_node[real]], f.link_fft[real],
+                                    max_vertex_id=int(key.max()))

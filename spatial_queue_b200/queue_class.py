@@ -100,9 +100,23 @@ class Link:
         self.travel_time = fft
         self.total_vehicles_left = 0
         self.congested = 0
-        self.status = "open"
+        self._net = None          # set by Network.use_gpu: status changes are forwarded to the device
+        self._status = "open"
         self.burnt_time = 3600 * 100
         self.closed_time = 3600 * 100
+
+    @property
+    def status(self):
+        return self._status
+
+    @status.setter
+    def status(self, value):
+        """open / closed / burning / burning_closed / burnt_over (model/dta_meso_butte.py:59-115).  'closed' and
+        'burning_closed' zero the inflow capacity in the link model (queue_class.py:444); on the GPU path the change
+        takes effect at the next `network.step`."""
+        self._status = value
+        if self._net is not None:
+            self._net._pending_status[self.link_id] = value in ("closed", "burning_closed")
 
     def run_link_model(self, *a, **k):
         raise B200LibraryError(_NO_HOST_TICK.format("Link.run_link_model"))
@@ -234,6 +248,8 @@ class Network:
         self.special_nodes = None
         self._sim = None
         self._flat = None
+        self.route_mode = "device"
+        self._pending_status = {}
         self.reroute_freq = 300
         self.weight_freq = 100
 
@@ -387,17 +403,46 @@ class Network:
     # ---------------------------------------------------------------------------------------------------------
     # the device switch
     # ---------------------------------------------------------------------------------------------------------
-    def use_gpu(self, seed=0, special_nodes=None, reroute_freq=300, weight_freq=100, route_at_start=True):
+    def use_gpu(self, seed=0, special_nodes=None, reroute_freq=300, weight_freq=100, route_at_start=True,
+                route_mode="device", shelter_after=3 * 3600):
         """Move the simulation onto the GPU.  Call once after `add_demand` (and after any t=0 changes to
-        `agent.departure_time`).  Initial routes are computed here (the reference routes every agent at t=0,
-        run_traffic_simulation.py:107) unless `route_at_start=False` and the agents already carry routes."""
+        `agent.departure_time`).
+
+        route_mode="device" (default): everything the driver's agent loop does stays on the GPU -- the edge-weight
+        refresh every `weight_freq` ticks, one reverse shortest-path tree per destination, the staggered reroute
+        of agents with t % reroute_freq == agent_id % reroute_freq, loading, arrivals and the give-up rule after
+        `shelter_after` seconds on one link (run_traffic_simulation.py:81-118).  `network.step(t)` is one C call.
+        route_mode="host": routes are Python dicts on the agents like in the reference (`agent.route`), recomputed
+        in batches of forward trees and pushed to the device; use it when a driver edits routes itself
+        (e.g. get_partial_path)."""
+        from .flatten import router_arrays
         from .tick import DeviceSim
         if special_nodes is not None:
             self.special_nodes = special_nodes
-        if route_at_start:
-            self.route_agents(0)
-        self._flat = flatten_network(self, self.special_nodes)
-        self._sim = DeviceSim(self._flat, seed=seed)
+        if route_mode not in ("device", "host"):
+            raise ValueError("route_mode must be 'device' or 'host'")
+        self.route_mode = route_mode
+        self._pending_status = {}
+        if route_mode == "host":
+            if route_at_start:
+                self.route_agents(0)
+            self._flat = flatten_network(self, self.special_nodes)
+            self._sim = DeviceSim(self._flat, seed=seed)
+        else:
+            # the t == 0 reachability rule (queue_class.py:494-499) needs the distances to every destination once
+            dests = sorted({a.destin_nid for a in self.agents.values()})
+            slot = {d: k for k, d in enumerate(dests)}
+            dist, _ = self.g.sssp_batch(np.array(dests, np.int32), want_parent=False, reverse=True, pinned=False)
+            for a in self.agents.values():
+                if dist[slot[a.destin_nid], a.origin_nid] > 1e8:
+                    a.route, a.status = {}, "shelter_p"
+            self._flat = router_arrays(flatten_network(self, self.special_nodes), self)
+            self._sim = DeviceSim(self._flat, seed=seed, routes_from_router=True)
+            self._sim.attach_router(self.g, self._flat, reroute_freq=reroute_freq, weight_freq=weight_freq)
+        if shelter_after:
+            self._sim.set_shelter_after(shelter_after)
+        for link in self.links.values():
+            link._net = self
         self._seed = seed
         self.reroute_freq = reroute_freq
         self.weight_freq = weight_freq
@@ -460,23 +505,37 @@ class Network:
         """One simulated second: the edge-weight refresh every `weight_freq` ticks, the staggered reroute
         trigger, then load + link model + node model on the device (sq_step)."""
         sim = self.sim
-        if self.weight_freq and t % self.weight_freq == 0 and t > 0:
-            self.refresh_edge_weights()
-        if t > 0:
-            self._reroute_due(t)
+        self._flush_link_status()
+        if self.route_mode == "host":
+            if self.weight_freq and t % self.weight_freq == 0 and t > 0:
+                self.refresh_edge_weights()
+            if t > 0:
+                self._reroute_due(t)
         sim.step(t)
 
+    def _flush_link_status(self):
+        if self._pending_status:
+            idx = [self._flat.link_index[lid] for lid in self._pending_status]
+            sim = self.sim
+            sim.set_link_closed(idx, [1 if c else 0 for c in self._pending_status.values()])
+            self._pending_status.clear()
+
     def run(self, t0, n):
-        """n ticks without host work in between when no reroute / weight refresh falls inside; else steps."""
-        for t in range(t0, t0 + n):
-            self.step(t)
+        """n consecutive ticks.  In device route mode this is one C call (CUDA-graph replay between the routing
+        refreshes); in host route mode the host reroutes between ticks."""
+        if self.route_mode == "device":
+            self._flush_link_status()
+            self.sim.run(t0, n)
+        else:
+            for t in range(t0, t0 + n):
+                self.step(t)
 
     def sync_to_host(self, t=None):
         """Refresh the object fields drivers read: link vehicle lists / counters / capacities,
         agent status and position, node_move; arrived agents move to `agents_stopped` as the reference's agent
         loop does (run_traffic_simulation.py:95-98, 119-120)."""
         sim = self.sim
-        ls, ag, nd = sim.link_state(), sim.agent_state(), sim.node_state()
+        ls, ag, nd, sh = sim.link_state(), sim.agent_state(), sim.node_state(), sim.shelter_state()
         ptr, veh = sim.link_vehicles()
         ids = self._flat.agent_ids
         for i, link in enumerate(self._link_objs):
@@ -493,10 +552,16 @@ class Network:
             a.this_link = self._flat.link_ids[cur] if cur >= 0 else None
             a.next_link = self._flat.link_ids[nxt] if nxt >= 0 else None
             a.next_link_end_nid = self._end_node_of_link[nxt] if nxt >= 0 else None
-            if a.status == "arrive" and not self._arrive_reported[i]:
+            if a.status in ("arrive", "shelter_a1") and not self._arrive_reported[i]:
                 self._arrive_reported[i] = True
-                self.agents_stopped[a.agent_id] = (a.status, int(ag["arrive_tick"][i]) + 1, a.agent_type)
+                # the reference's agent loop notices an arrival one tick later, a give-up in the same tick
+                when = int(sh["stop_tick"][i]) + (1 if a.status == "arrive" else 0)
+                self.agents_stopped[a.agent_id] = (a.status, when, a.agent_type)
                 self.agents.pop(a.agent_id, None)
         for k, nid in enumerate(self._flat.node_ids):
             self.nodes[nid].node_move = int(nd["node_move"][k])
+            self.nodes[nid].shelter_counts = 0
+        for i, link in enumerate(self._link_objs):
+            if sh["link_shelter"][i]:
+                self.nodes[link.end_nid].shelter_counts += int(sh["link_shelter"][i])
         return self

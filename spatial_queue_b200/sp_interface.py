@@ -101,6 +101,11 @@ class Graph:
     def nedges(self):
         return lib().sp_nedges(self._h)
 
+    @property
+    def nedges_logged(self):
+        """Edges ever inserted (creategraph order; what sp_set_weights / sp_set_weights_device index)."""
+        return lib().sp_nedges_logged(self._h)
+
     def remove_edge(self, v1, v2):
         check(lib().sp_remove_edge(self._h, int(v1), int(v2)), "remove_edge")
 
@@ -118,7 +123,7 @@ class Graph:
     def sync(self):
         check(lib().sp_sync(self._h), "sp_sync")
 
-    def sssp_batch(self, origins, want_dist=True, want_parent=True, pinned=True, out=None):
+    def sssp_batch(self, origins, want_dist=True, want_parent=True, pinned=True, out=None, reverse=False):
         """Full trees for `origins` -> (dist f64[n,V] or None, parent i32[n,V] or None), host arrays.
 
         The results land in page-locked memory by default so that the device-to-host copies overlap the
@@ -132,9 +137,9 @@ class Graph:
             d = alloc((len(o), V), np.float64) if want_dist else None
             p = alloc((len(o), V), np.int32) if want_parent else None
         want_dist, want_parent = d is not None, p is not None
-        check(lib().sp_sssp_batch(self._h, o.ctypes.data, len(o),
-                                  d.ctypes.data if want_dist else None,
-                                  p.ctypes.data if want_parent else None), "sp_sssp_batch")
+        check(lib().sp_sssp_batch_ex(self._h, o.ctypes.data, len(o),
+                                     d.ctypes.data if want_dist else None,
+                                     p.ctypes.data if want_parent else None, 1 if reverse else 0), "sp_sssp_batch")
         return d, p
 
     def set_weights_device(self, weights_dev, stream=None):

@@ -159,6 +159,9 @@ def flat_grid(n, seed=1, arterial_every=8):
     f.pair_start, f.pair_end, f.pair_link = s.astype(np.int32), e.astype(np.int32), (N + np.arange(E)).astype(np.int32)
     f.edge_start, f.edge_end, f.edge_fft = s.astype(np.int32), e.astype(np.int32), fft
     f.n_grid = n
+    # router arrays (flatten.router_arrays): node i is graph vertex i, real link N + k is edge k
+    f.node_vertex = np.arange(N, dtype=np.int32)
+    f.link_edge = np.concatenate([np.full(N, -1), np.arange(E)]).astype(np.int32)
     return f
 
 
@@ -203,12 +206,17 @@ def add_agents(f, origin, destin, dept, vlen, next_link, dest_nodes):
     if A >= 100000:
         srt = np.argsort(dest_nodes)
         dest_idx = srt[dest_idx]
+    f.dest_nodes = np.asarray(dest_nodes, np.int32)
+    f.agent_dslot = np.asarray(dest_idx, np.int32)
+    if next_link is None:      # routes come from the device router (sq_attach_router)
+        f.route_ptr, f.route_links = np.zeros(A + 1, np.int64), np.zeros(0, np.int32)
+        return f
     f.route_ptr, f.route_links = routes_from_next_hop(next_link, f.link_end_node, origin, dest_idx,
                                                       max_hops=4 * int(np.sqrt(len(f.node_key))) + 8)
     return f
 
 
-def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=None, router=None):
+def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=None, router=None, device_routes=False):
     """The C4-style workload: n x n grid, agents from uniform origins to the exit nodes with
     staggered departures, routed at t=0 on free-flow weights.
 
@@ -225,6 +233,10 @@ def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=Non
     perm = rng.permutation(n_agents)            # add_demand shuffles the OD rows (queue_class.py:198)
     origin, destin, dept = origin[perm], destin[perm], od.dept_time.values[perm]
     s, e, w = f.edge_start, f.edge_end, f.edge_fft
+    if device_routes:
+        # no host routing at all: DeviceSim(flat, routes_from_router=True) + attach_router(graph(flat), flat)
+        add_agents(f, origin, destin, dept, np.full(n_agents, 8), None, exits)
+        return f
     if router is None:
         from . import sp_interface
         g = sp_interface.from_arrays(e, s, w, max_vertex_id=N - 1)      # reversed graph
@@ -245,3 +257,10 @@ def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=Non
     f.next_link_table = next_link
     add_agents(f, origin, destin, dept, np.full(n_agents, 8), next_link, exits)
     return f
+
+
+def routing_graph(f):
+    """The routing graph of a flat grid network (what the loader builds with interface.from_dataframe on the real
+    links, queue_class.py:123): edge k = real link N + k, weight = fft."""
+    from . import sp_interface
+    return sp_interface.from_arrays(f.edge_start, f.edge_end, f.edge_fft, max_vertex_id=len(f.node_key) - 1)

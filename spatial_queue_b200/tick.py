@@ -34,9 +34,19 @@ class SqNetDesc(C.Structure):
     _fields_ = _FIELDS
 
 
-def make_desc(flat, seed):
+class SqRouterDesc(C.Structure):
+    """include/sq_tick.h SqRouterDesc."""
+    _fields_ = [("graph", C.c_void_p), ("n_graph_edges", C.c_int32), ("n_dest", C.c_int32),
+                ("dest_nodes", C.c_void_p), ("agent_dslot", C.c_void_p), ("agent_key", C.c_void_p),
+                ("node_vertex", C.c_void_p), ("link_edge", C.c_void_p), ("n_pairs", C.c_int32),
+                ("pair_start", C.c_void_p), ("pair_end", C.c_void_p), ("pair_link", C.c_void_p),
+                ("reroute_freq", C.c_int32), ("weight_freq", C.c_int32)]
+
+
+def make_desc(flat, seed, flags=0):
     """-> (SqNetDesc, keepalive list).  `flat` is a flatten.FlatNetwork (or anything with the same arrays)."""
     d = SqNetDesc()
+    d.reserved0 = int(flags)
     keep = []
     d.n_nodes = len(flat.node_key)
     d.n_links = len(flat.link_end_node)
@@ -129,11 +139,12 @@ class _SimBase:
 class DeviceSim(_SimBase):
     """The GPU tick.  Raises B200LibraryError when the library or the device is missing."""
 
-    def __init__(self, flat, seed=0):
+    def __init__(self, flat, seed=0, routes_from_router=False):
+        """`routes_from_router=True`: agents carry no routes; `attach_router` must follow before the first tick."""
         L = _lib.lib()
         self._L = L
         self.n_nodes, self.n_links, self.n_agents = len(flat.node_key), len(flat.link_end_node), len(flat.agent_key)
-        desc, keep = make_desc(flat, seed)
+        desc, keep = make_desc(flat, seed, flags=1 if routes_from_router else 0)
         self._h = L.sq_create(C.byref(desc))
         if not self._h:
             raise _lib.B200LibraryError("sq_create failed: " + L.sq_last_error().decode())
@@ -144,6 +155,43 @@ class DeviceSim(_SimBase):
     def _check(self, rc, what):
         if rc != 0:
             raise _lib.B200LibraryError(f"sq_{what} failed ({rc}): {self._L.sq_last_error().decode()}")
+
+    def attach_router(self, graph, flat, reroute_freq=300, weight_freq=100):
+        """Device-side rerouting on `graph` (an sp_interface.Graph whose edges are the real links).  `flat` needs
+        the router arrays of flatten.router_arrays / synth.flat_grid: dest_nodes, agent_dslot, node_vertex, link_edge
+        and the (start, end) -> link pairs."""
+        r = SqRouterDesc()
+        keep = []
+
+        def arr(a, dt):
+            a = np.ascontiguousarray(a, dtype=dt)
+            if a.size == 0:
+                a = np.zeros(1, dt)
+            keep.append(a)
+            return a.ctypes.data
+        r.graph = graph._h
+        r.n_graph_edges = int(graph.nedges_logged)
+        r.n_dest = len(flat.dest_nodes)
+        r.dest_nodes = arr(flat.dest_nodes, np.int32)
+        r.agent_dslot = arr(flat.agent_dslot, np.int32)
+        r.agent_key = arr(flat.agent_key, np.int64)
+        r.node_vertex = arr(flat.node_vertex, np.int32)
+        r.link_edge = arr(flat.link_edge, np.int32)
+        r.n_pairs = len(flat.pair_link)
+        r.pair_start = arr(flat.pair_start, np.int32)
+        r.pair_end = arr(flat.pair_end, np.int32)
+        r.pair_link = arr(flat.pair_link, np.int32)
+        r.reroute_freq, r.weight_freq = int(reroute_freq), int(weight_freq)
+        self._check(self._L.sq_attach_router(self._h, C.byref(r)), "attach_router")
+        self._router_graph = graph   # keep the graph alive as long as the sim uses it
+
+    def set_shelter_after(self, seconds):
+        self._check(self._L.sq_set_shelter_after(self._h, int(seconds)), "set_shelter_after")
+
+    def shelter_state(self):
+        ls, st = np.empty(self.n_links, np.int32), np.empty(max(self.n_agents, 1), np.int32)
+        self._check(self._L.sq_get_shelter_state(self._h, ls.ctypes.data, st.ctypes.data), "get_shelter_state")
+        return dict(link_shelter=ls, stop_tick=st[: self.n_agents])
 
     def sync(self):
         self._check(self._L.sq_sync(self._h), "sync")

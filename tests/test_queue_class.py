@@ -130,15 +130,19 @@ def test_host_tick_methods_refuse_to_run(tmp_path):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("route_mode", ["host", "device"])
 @pytest.mark.parametrize("name", ["grid8", "grid7s"])
-def test_mirror_on_gpu_replays_reference_run(name, tmp_path):
+def test_mirror_on_gpu_replays_reference_run(name, route_mode, tmp_path):
     """One call per tick (`network.step`) with the reroutes computed by the GPU library reproduces the
-    reference's run: initial routes, every later route change, and the per-tick state digests."""
+    reference's run: initial routes, every later route change, and the per-tick state digests.  In "host" mode the
+    routes are forward trees walked into `agent.route` dicts; in "device" mode nothing but `sq_step` runs per tick
+    (reverse trees per destination, next-link tables and the reroute trigger all on the GPU)."""
     z, gold = load_golden(name)
     net, special = build_grid(name, tmp_path)
-    net.use_gpu(seed=int(z["seed"]), special_nodes=special, reroute_freq=300, weight_freq=100)
-    assert net._flat.route_ptr.tobytes() == gold.route_ptr.tobytes()
-    assert net._flat.route_links.tobytes() == gold.route_links.tobytes()
+    net.use_gpu(seed=int(z["seed"]), special_nodes=special, reroute_freq=300, weight_freq=100, route_mode=route_mode)
+    if route_mode == "host":
+        assert net._flat.route_ptr.tobytes() == gold.route_ptr.tobytes()
+        assert net._flat.route_links.tobytes() == gold.route_links.tobytes()
     n = int(z["n_ticks"])
     for t in range(n):
         net.step(t)

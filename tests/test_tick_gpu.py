@@ -65,3 +65,49 @@ def test_device_reports_broken_routes():
     with pytest.raises(_lib.B200LibraryError, match="no next link"):
         sim.run(0, 400)
         sim.sync()
+
+
+@pytest.mark.parametrize("name", ["grid8", "grid7s", "bolinas"])
+def test_device_router_replays_reference_golden(name):
+    """The whole agent loop on the device: no routes and no route events from the golden file are used, only the
+    network, the demand and the reference's parameters (reroute every 300 s, staggered by agent id; edge weights
+    from queue lengths every 100 s).  sq_attach_router + sq_step must reproduce the reference run digest for
+    digest -- i.e. the reverse-tree next-link tables pick the very paths the reference's per-agent Dijkstra did."""
+    from spatial_queue_b200 import flatten as fl
+    from spatial_queue_b200.tick import DeviceSim
+    z, flat = load_golden(name)
+    fl.router_arrays_flat(flat)
+    g = fl.routing_graph_flat(flat)
+    sim = DeviceSim(flat, seed=int(z["seed"]), routes_from_router=True)
+    sim.attach_router(g, flat, reroute_freq=300, weight_freq=100)
+    sim.set_shelter_after(3 * 3600)
+    n = int(z["n_ticks"])
+    for t in range(n):
+        sim.step(t)
+        if t % 7 == 0 or t < 50 or t == n - 1:
+            assert state_digest(sim.state()) == int(z["digests"][t]), f"tick {t}"
+    assert (sim.agent_state()["arrive_tick"] == z["arrive_tick"]).all()
+    c = sim.counters()
+    assert c["agent_steps"] == int(z["on_link"][:n].astype(np.int64).sum())
+    sim.close()
+
+
+def test_device_router_run_equals_steps():
+    """sq_run (CUDA graphs between the routing refreshes) == sq_step tick by tick, router attached."""
+    from spatial_queue_b200 import flatten as fl
+    from spatial_queue_b200.tick import DeviceSim
+    z, flat = load_golden("grid8")
+    fl.router_arrays_flat(flat)
+    sims = []
+    for _ in range(2):
+        sim = DeviceSim(flat, seed=3, routes_from_router=True)
+        sim.attach_router(fl.routing_graph_flat(flat), flat, reroute_freq=60, weight_freq=100)
+        sims.append(sim)
+    a, b = sims
+    for t in range(0, 437):
+        a.step(t)
+    b.run(0, 250)
+    b.run(250, 187)
+    sa, sb = a.state(), b.state()
+    assert state_digest(sa) == state_digest(sb)
+    assert a.counters()["agent_steps"] == b.counters()["agent_steps"]
