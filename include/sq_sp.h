@@ -101,6 +101,9 @@ int sp_set_weights_device(Graph* graph, const double* weights_dev, int nedges, v
  * to update_edge (queue_class.py:463-466 is called once per link every 100 ticks). */
 int sp_set_weights(Graph* graph, const double* weights, int nedges);
 
+/* 1 if update_edge / sp_set_weights / structural edits have not reached the device yet. */
+int sp_has_pending_edits(Graph* graph);
+
 /* Push pending host-side edits (update_edge / sp_set_weights / structure) to the device now.
  * Called implicitly by every compute entry point. */
 int sp_sync(Graph* graph);

@@ -21,6 +21,8 @@ def _lib():
         L.oracle_tick_get_node_state.argtypes = [vp, vp]
         L.oracle_tick_get_link_weights.argtypes = [vp, vp]
         L.oracle_tick_get_counters.argtypes = [vp, vp]
+        L.oracle_tick_set_shelter_after.argtypes = [vp, ci]
+        L.oracle_tick_get_shelter_state.argtypes = [vp, vp, vp]
         L.oracle_tick_error.restype = C.c_char_p; L.oracle_tick_error.argtypes = [vp]
         L._tick_declared = True
     return L
@@ -39,6 +41,15 @@ class OracleSim(_SimBase):
     def _check(self, rc, what):
         if rc != 0:
             raise RuntimeError(f"oracle_tick_{what} failed ({rc}): {self._L.oracle_tick_error(self._h).decode()}")
+
+    def set_shelter_after(self, seconds):
+        self._check(self._L.oracle_tick_set_shelter_after(self._h, int(seconds)), "set_shelter_after")
+
+    def shelter_state(self):
+        import numpy as np
+        ls, st = np.empty(self.n_links, np.int32), np.empty(max(self.n_agents, 1), np.int32)
+        self._check(self._L.oracle_tick_get_shelter_state(self._h, ls.ctypes.data, st.ctypes.data), "get_shelter_state")
+        return dict(link_shelter=ls, stop_tick=st[: self.n_agents])
 
     def sync(self):
         pass

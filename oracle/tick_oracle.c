@@ -57,6 +57,8 @@ typedef struct {
   int* virt_of_node;
   int64_t* node_move;
   int64_t counters[6];
+  int shelter_after; /* run_traffic_simulation.py:103: seconds on one real link before status shelter_a1; 0 = rule off */
+  int* l_shelter;
   char err[256];
   int failed;
 } OSim;
@@ -107,6 +109,7 @@ OSim* oracle_tick_create(const SqNetDesc* d) {
   s->out_c = (double*)malloc(sizeof(double) * (size_t)(L ? L : 1));
   s->storage_c = (double*)malloc(sizeof(double) * (size_t)(L ? L : 1));
   s->total_left = (int*)calloc((size_t)(L ? L : 1), sizeof(int));
+  s->l_shelter = (int*)calloc((size_t)(L ? L : 1), sizeof(int));
   for (i = 0; i < L; ++i) { /* Link.__init__ :417-419 */
     s->in_c[i] = s->out_c[i] = s->l_cap_s[i];
     s->storage_c[i] = s->l_storage[i];
@@ -295,6 +298,20 @@ static int run_node_model(OSim* s, int t, int node) {
 int oracle_tick_step(OSim* s, int t) {
   int L = s->n_links, A = s->n_agents, N = s->n_nodes, i, k, rc;
   if (s->failed) return -4;
+  /* agent loop, give-up rule (run_traffic_simulation.py:100-104, 113-118): an enroute agent that has been on a
+   * real link for more than shelter_after seconds becomes shelter_a1 and is stripped from the link's lists */
+  if (s->shelter_after > 0)
+    for (i = 0; i < A; ++i) {
+      int cl;
+      if (s->a_status[i] != SQ_ENROUTE) continue;
+      cl = s->a_cur[i];
+      if (s->l_virtual[cl] || t - s->a_enter[i] <= s->shelter_after) continue;
+      s->a_status[i] = 4; /* shelter_a1 */
+      s->a_arrive[i] = t;
+      iv_remove_value(&s->queue[cl], i);
+      iv_remove_value(&s->run[cl], i);
+      s->l_shelter[cl] += 1;
+    }
   /* agent loop: load_vehicle for every agent in dict order (run_traffic_simulation.py:111) */
   for (i = 0; i < A; ++i)
     if (s->a_status[i] == SQ_UNLOADED && s->a_dept[i] == t) {
@@ -336,6 +353,13 @@ int oracle_tick_step(OSim* s, int t) {
   }
   s->counters[0] += 1;
   for (i = 0; i < L; ++i) s->counters[1] += s->queue[i].n + s->run[i].n;
+  return 0;
+}
+
+int oracle_tick_set_shelter_after(OSim* s, int seconds) { s->shelter_after = seconds > 0 ? seconds : 0; return 0; }
+int oracle_tick_get_shelter_state(OSim* s, int* link_shelter, int* stop_tick) {
+  if (link_shelter) memcpy(link_shelter, s->l_shelter, sizeof(int) * (size_t)s->n_links);
+  if (stop_tick) memcpy(stop_tick, s->a_arrive, sizeof(int) * (size_t)s->n_agents);
   return 0;
 }
 
@@ -398,7 +422,7 @@ int oracle_tick_get_agent_state(OSim* s, uint8_t* status, int* cur, int* next, i
     if (cur) cur[i] = s->a_cur[i];
     if (next) next[i] = s->a_next[i];
     if (enter) enter[i] = s->a_enter[i];
-    if (arrive) arrive[i] = s->a_arrive[i];
+    if (arrive) arrive[i] = s->a_status[i] == SQ_ARRIVE ? s->a_arrive[i] : -1;
   }
   return 0;
 }

@@ -51,6 +51,7 @@ def _declare(L):
     L.sp_set_weights_device.restype = ci; L.sp_set_weights_device.argtypes = [vp, vp, ci, vp]
     L.sp_set_weights.restype = ci; L.sp_set_weights.argtypes = [vp, vp, ci]
     L.sp_sync.restype = ci; L.sp_sync.argtypes = [vp]
+    L.sp_has_pending_edits.restype = ci; L.sp_has_pending_edits.argtypes = [vp]
     L.sp_set_tuning.restype = ci; L.sp_set_tuning.argtypes = [vp, ci, ci, cd, ci]
     L.sp_alloc_host.restype = vp; L.sp_alloc_host.argtypes = [C.c_size_t]
     L.sp_free_host.restype = None; L.sp_free_host.argtypes = [vp]

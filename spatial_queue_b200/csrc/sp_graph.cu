@@ -1271,6 +1271,8 @@ int sp_nedges(Graph* g) {
   return n;
 }
 
+int sp_has_pending_edits(Graph* g) { return (g && (g->topo_dirty || g->w_dirty)) ? 1 : 0; }
+
 int sp_nedges_logged(Graph* g) { return g ? (int)g->es.size() : 0; }
 
 void sp_free_graph(Graph* g) {

@@ -880,8 +880,8 @@ static int check_device_error(SqSim* sim) {
 
 // Weight refresh + new routing tables (what the drivers do every `wfreq` ticks before the agent loop,
 // run_traffic_simulation.py:81-84, followed by one reverse tree per destination instead of one Dijkstra per agent).
-static int router_refresh(SqSim* sim, int t) {
-  if (!sim->router_graph || sim->last_refresh_t == t) return SQ_OK;
+static int router_refresh(SqSim* sim, int t, bool queue_weights = true) {
+  if (!sim->router_graph || (queue_weights && sim->last_refresh_t == t)) return SQ_OK;
   TickState& s = sim->st;
   cudaStream_t st = sim->stream;
   const int slot = (sim->host_epoch + 1) % s.K;
@@ -889,11 +889,13 @@ static int router_refresh(SqSim* sim, int t) {
     k_evacuate<<<(sim->A + 127) / 128, 128, 0, st>>>(s, slot);
     sq::count_launch(); sim->launches += 1;
   }
-  k_link_weights<<<(sim->L + 255) / 256, 256, 0, st>>>(s);
-  sq::count_launch(); sim->launches += 1;
-  SQ_CUDA_TRY(cudaGetLastError());
-  if (int rc = sp_set_weights_device(sim->router_graph, s.w_edge, sim->graph_E, (void*)st))
-    return sq::set_error(rc, "router refresh: %s", sp_last_error());
+  if (queue_weights) {
+    k_link_weights<<<(sim->L + 255) / 256, 256, 0, st>>>(s);
+    sq::count_launch(); sim->launches += 1;
+    SQ_CUDA_TRY(cudaGetLastError());
+    if (int rc = sp_set_weights_device(sim->router_graph, s.w_edge, sim->graph_E, (void*)st))
+      return sq::set_error(rc, "router refresh: %s", sp_last_error());
+  }
   if (int rc = sp_sssp_batch_device_ex(sim->router_graph, sim->d_dest_vertex, s.D, sim->d_tdist, sim->d_tnext, (void*)st, 1))
     return sq::set_error(rc, "router refresh: %s", sp_last_error());
   dim3 grid((unsigned)((sim->N + 255) / 256), (unsigned)s.D);
@@ -902,8 +904,17 @@ static int router_refresh(SqSim* sim, int t) {
   sq::count_launch(); sim->launches += 1;
   SQ_CUDA_TRY(cudaGetLastError());
   sim->host_epoch = slot;
-  sim->last_refresh_t = t;
+  if (queue_weights) sim->last_refresh_t = t;
   return SQ_OK;
+}
+
+// Host-side edits of the routing graph (link.close_link_to_newcomers / open_link_to_newcomers -> update_edge,
+// queue_class.py:467-474) take effect for every later get_path call in the reference: rebuild the tables before
+// the next tick whenever the graph has pending edits.
+static int router_catch_up(SqSim* sim, int t) {
+  if (!sim->router_graph || !sp_has_pending_edits(sim->router_graph)) return SQ_OK;
+  if (sim->wfreq > 0 && t % sim->wfreq == 0 && sim->last_refresh_t != t) return SQ_OK;  // the regular refresh follows
+  return router_refresh(sim, t, false);
 }
 
 static int kernels_per_tick(const SqSim* sim) { return (sim->router_graph && sim->max_bucket > 0) ? 3 : 2; }
@@ -929,6 +940,7 @@ void sq_destroy(SqSim* sim) {
 int sq_step(SqSim* sim, int32_t t) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_step: null sim");
   if (int rc = arm_tick(sim, t)) return rc;
+  if (int rc = router_catch_up(sim, t)) return rc;
   if (sim->router_graph && sim->wfreq > 0 && t % sim->wfreq == 0)
     if (int rc = router_refresh(sim, t)) return rc;
   launch_tick(sim, sim->stream);
@@ -944,6 +956,7 @@ int sq_run(SqSim* sim, int32_t t0, int32_t n) {
   if (int rc = arm_tick(sim, t0)) return rc;
   if (!sim->graph && n >= kGraphTicks)
     if (int rc = build_graph(sim)) return rc;
+  if (int rc = router_catch_up(sim, t0)) return rc;
   // segments between routing refreshes; each is replayed as CUDA graphs of kGraphTicks ticks + single ticks
   int t = t0;
   const int end = t0 + n;

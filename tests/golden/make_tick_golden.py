@@ -78,7 +78,8 @@ def bolinas(qc, rts):
     run("bolinas", data["network"], config["special_nodes"], qc, rts, 5400)
 
 
-def grid(qc, rts, name, n, n_agents, special=None, horizon=100, max_ticks=3000, arterial_every=4, exits=None):
+def grid(qc, rts, name, n, n_agents, special=None, horizon=100, max_ticks=3000, arterial_every=4, exits=None,
+         snapshot_every=50):
     wp = rh.make_write_path()
     edges, nodes = synth.grid_frames(n, seed=1, arterial_every=arterial_every)
     edges.to_csv(wp + "/edges.csv", index=False)
@@ -97,12 +98,12 @@ def grid(qc, rts, name, n, n_agents, special=None, horizon=100, max_ticks=3000, 
     net.add_demand(demand_files=["/od.csv"], write_path=wp)
     qc.abs_path = old_abs
     dept = {aid: int(a.departure_time) for aid, a in net.agents.items()}
-    run(name, net, special_nodes, qc, rts, max_ticks, dept_override=dept, snapshot_every=50)
+    run(name, net, special_nodes, qc, rts, max_ticks, dept_override=dept, snapshot_every=snapshot_every)
 
 
 def main():
     qc, rts = rh.import_reference(seed=SEED)
-    which = sys.argv[1:] or ["bolinas", "grid8", "grid7s"]
+    which = sys.argv[1:] or ["bolinas", "grid8", "grid7s", "grid5x"]
     if "bolinas" in which:
         bolinas(qc, rts)
     if "grid8" in which:
@@ -119,6 +120,17 @@ def main():
         pri = {str(node): list(reversed(ins(node))) for node in (16, 32)}
         grid(qc, rts, "grid7s", n, 1200, special={"signal": sig, "priority": pri, "closure": [5, 30]}, horizon=80,
              exits=[0, 48, 6])
+
+
+    if "grid5x" in which:
+        # a signal whose phases never serve one approach: the vehicles queued there wait for ever and give up after
+        # three hours (status shelter_a1, run_traffic_simulation.py:100-104, 113-118), as do the ones stuck behind
+        n = 5
+        edges, _ = synth.grid_frames(n, seed=1, arterial_every=4)
+        served = [int(x) for x in edges.loc[(edges.nid_e == 1) & (edges.nid_s != 2), "eid"]]
+        sig = {"1": {"phase_1": ["n1_vl"] + served[0:1], "phase_2": ["n1_vl"] + served[1:2]}}   # 2 -> 1 is never served
+        grid(qc, rts, "grid5x", n, 500, special={"signal": sig}, horizon=100, exits=[0, 24], max_ticks=11500,
+             snapshot_every=900)
 
 
 if __name__ == "__main__":

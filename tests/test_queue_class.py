@@ -153,3 +153,39 @@ def test_mirror_on_gpu_replays_reference_run(name, route_mode, tmp_path):
     assert arrived == gold_arr
     assert sum(len(l.queue_vehicles) + len(l.run_vehicles) for l in net.links.values()) == int(z["on_link"][n - 1])
     assert sum(nd.node_move for nd in net.nodes.values() if nd.node_type == "real") == int(z["moves"][:n].sum())
+
+
+@pytest.mark.gpu
+def test_closures_host_and_device_routing_agree(tmp_path):
+    """Fire-style closures (model/dta_meso_butte.py:88-115): `link.close_link_to_newcomers(g)` + status 'closed' on
+    both approaches of an exit makes it unreachable, so the agents heading there keep their old routes
+    (queue_class.py:501-503) and pile up; 900 s later the links reopen.  The two routing modes of the mirror --
+    per-agent route dicts recomputed on the host vs next-link tables on the device, including the hand-over of
+    routes that outlive their table epoch -- must produce the same run, tick for tick."""
+    runs = []
+    for mode in ("host", "device"):
+        net, special = build_grid("grid8", tmp_path)
+        net.use_gpu(seed=11, special_nodes=special, reroute_freq=300, weight_freq=100, route_mode=mode)
+        runs.append(net)
+    closing = [lid for lid, l in runs[0].links.items() if l.link_type != "v" and l.end_nid == 0]
+    assert len(closing) == 2
+    digests = [[], []]
+    for k, net in enumerate(runs):
+        for t in range(1400):
+            if t == 120:
+                for lid in closing:
+                    net.links[lid].close_link_to_newcomers(g=net.g)
+                    net.links[lid].status = "closed"
+            if t == 1020:
+                for lid in closing:
+                    net.links[lid].open_link_to_newcomers(g=net.g)
+                    net.links[lid].status = "burnt_over"
+            net.step(t)
+            if t % 10 == 0 or t in (119, 120, 121, 1019, 1020, 1021):
+                digests[k].append(state_digest(net.sim.state()))
+    assert digests[0] == digests[1]
+    a, b = runs[0].sim.agent_state(), runs[1].sim.agent_state()
+    assert (a["arrive_tick"] == b["arrive_tick"]).all()
+    # the closure really bit: once the vehicles already on the two links are through, arrivals at node 0 pause
+    arr = a["arrive_tick"][runs[0]._flat.agent_destin == runs[0]._flat.node_index[0]]
+    assert ((arr > 400) & (arr < 1020)).sum() == 0 and (arr >= 1020).sum() > 0

@@ -8,11 +8,12 @@ from tickcheck import load_golden, replay, route_events, state_digest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("name,every", [("grid8", 1), ("grid7s", 1), ("bolinas", 1)])
+@pytest.mark.parametrize("name,every", [("grid8", 1), ("grid7s", 1), ("bolinas", 1), ("grid5x", 5)])
 def test_device_replays_reference_golden(name, every):
     from spatial_queue_b200.tick import DeviceSim
     z, flat = load_golden(name)
     sim = DeviceSim(flat, seed=int(z["seed"]))
+    sim.set_shelter_after(3 * 3600)
     n = replay(sim, z, every=every)
     ag = sim.agent_state()
     assert (ag["arrive_tick"] == z["arrive_tick"]).all()
@@ -67,7 +68,7 @@ def test_device_reports_broken_routes():
         sim.sync()
 
 
-@pytest.mark.parametrize("name", ["grid8", "grid7s", "bolinas"])
+@pytest.mark.parametrize("name", ["grid8", "grid7s", "bolinas", "grid5x"])
 def test_device_router_replays_reference_golden(name):
     """The whole agent loop on the device: no routes and no route events from the golden file are used, only the
     network, the demand and the reference's parameters (reroute every 300 s, staggered by agent id; edge weights
