@@ -615,6 +615,7 @@ struct SqSim {
   int* d_pool = nullptr;
   long long pool_cap = 0, pool_used = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t cap_stream = nullptr;
   bool own_stream = true;
   int next_t = INT_MIN;  // tick the device counters are armed for
   long long sheltered = 0;
@@ -849,9 +850,12 @@ static const int kGraphTicks = 32;  // ticks per CUDA-graph launch
 static int build_graph(SqSim* sim) {
   if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }
   cudaGraph_t g;
-  SQ_CUDA_TRY(cudaStreamBeginCapture(sim->stream, cudaStreamCaptureModeThreadLocal));
-  for (int i = 0; i < kGraphTicks; ++i) launch_tick(sim, sim->stream);
-  SQ_CUDA_TRY(cudaStreamEndCapture(sim->stream, &g));
+  // capture on a private stream: the run stream may be the caller's (sq_set_stream), e.g. the legacy default
+  // stream, which cannot be captured
+  if (!sim->cap_stream) SQ_CUDA_TRY(cudaStreamCreateWithFlags(&sim->cap_stream, cudaStreamNonBlocking));
+  SQ_CUDA_TRY(cudaStreamBeginCapture(sim->cap_stream, cudaStreamCaptureModeThreadLocal));
+  for (int i = 0; i < kGraphTicks; ++i) launch_tick(sim, sim->cap_stream);
+  SQ_CUDA_TRY(cudaStreamEndCapture(sim->cap_stream, &g));
   SQ_CUDA_TRY(cudaGraphInstantiate(&sim->graph, g, 0));
   cudaGraphDestroy(g);
   sim->graph_ticks = kGraphTicks;
@@ -934,6 +938,7 @@ void sq_destroy(SqSim* sim) {
   for (void* p : sim->allocs) cudaFree(p);
   cudaFree(sim->d_pool);
   if (sim->stream && sim->own_stream) cudaStreamDestroy(sim->stream);
+  if (sim->cap_stream) cudaStreamDestroy(sim->cap_stream);
   delete sim;
 }
 
