@@ -327,21 +327,46 @@ def main():
     B = args.batch
     bytes_per_tree = 20 * E + 24 * V
     dist_dev = torch.empty((B, V), dtype=torch.float64, device="cuda")
-    par_dev = torch.empty((B, V), dtype=torch.int32, device="cuda")
+    # N > 1: the int32 predecessor (next-hop) tables of every rank are all-gathered to every rank.  The batch is
+    # cut into chunks; the gather of chunk k runs on a side stream while chunk k+1 is computed, and the tables
+    # are double-buffered across steps so that a step never waits for the previous step's last gather.
+    n_chunks = 4 if (world > 1 and not args.no_gather) else 1
+    assert B % n_chunks == 0, "--batch must be a multiple of 4 for N > 1"
+    cb = B // n_chunks
+    par_bufs = [torch.empty((B, V), dtype=torch.int32, device="cuda") for _ in range(2 if n_chunks > 1 else 1)]
     gathered = None
+    comm_stream = None
     if world > 1 and not args.no_gather:
-        gathered = torch.empty((world * B, V), dtype=torch.int32, device="cuda")
+        gathered = [torch.empty((world * cb, V), dtype=torch.int32, device="cuda") for _ in range(n_chunks)]
+        comm_stream = torch.cuda.Stream()
+        buf_free = [None, None]      # event: all gathers reading par_bufs[k] are done
     origins_dev = [torch.from_numpy(origins_for(rank, B, V, step=i)).cuda() for i in range(args.warmup + args.steps)]
     launches0 = _lib.lib().sp_kernel_launches()
 
     def step(i, ev=None):
+        par_dev = par_bufs[i % len(par_bufs)]
+        cur = torch.cuda.current_stream()
+        if gathered is not None and buf_free[i % 2] is not None:
+            cur.wait_event(buf_free[i % 2])
         if ev:
             ev[0].record()
-        g.sssp_batch_device(origins_dev[i], dist_dev, par_dev)
+        for c in range(n_chunks):
+            sl = slice(c * cb, (c + 1) * cb if c + 1 < n_chunks else B)
+            g.sssp_batch_device(origins_dev[i][sl], dist_dev[sl], par_dev[sl])
+            if gathered is not None:
+                done = torch.cuda.Event()
+                done.record(cur)
+                comm_stream.wait_event(done)
+                with torch.cuda.stream(comm_stream):
+                    dist.all_gather_into_tensor(gathered[c], par_dev[sl])
         if ev:
             ev[1].record()
         if gathered is not None:
-            dist.all_gather_into_tensor(gathered, par_dev)
+            e = torch.cuda.Event()
+            e.record(comm_stream)
+            buf_free[i % 2] = e
+            if i == args.warmup + args.steps - 1 or i == args.warmup - 1:
+                cur.wait_event(e)      # the timed region ends when the last gather has landed
 
     for i in range(args.warmup):
         step(i)
@@ -401,7 +426,8 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid "
                                        f"({E} links, {V} nodes), {B} origins per GPU per step, full trees + canonical "
-                                       f"predecessors" + (", int32 next-hop tables all-gathered" if gathered is not None else ""),
+                                       f"predecessors" + (f", int32 next-hop tables all-gathered in {n_chunks} chunks overlapped with "
+                                                          f"the next chunk's trees" if gathered is not None else ""),
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -412,7 +438,7 @@ def main():
 
     # ---- HP-1 + CPU baselines: single GPU, rank 0 ----------------------------------------------------------------
     if rank == 0 and world == 1:
-        del dist_dev, par_dev
+        del dist_dev, par_bufs
         torch.cuda.empty_cache()
         if not args.no_cpu:
             from oracle import sssp as osssp
