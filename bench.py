@@ -333,11 +333,17 @@ def main():
     n_chunks = 4 if (world > 1 and not args.no_gather) else 1
     assert B % n_chunks == 0, "--batch must be a multiple of 4 for N > 1"
     cb = B // n_chunks
-    par_bufs = [torch.empty((B, V), dtype=torch.int32, device="cuda") for _ in range(2 if n_chunks > 1 else 1)]
+    # N > 1 ships the tables as one-byte in-edge codes (sp_set_parent_format 1): every rank holds the graph, so
+    # the code of the predecessor edge is all the simulating GPU needs; N = 1 writes plain int32 vertex ids
+    compact = world > 1 and not args.no_gather
+    pdt = torch.uint8 if compact else torch.int32
+    if compact:
+        g.set_parent_format(1)
+    par_bufs = [torch.empty((B, V), dtype=pdt, device="cuda") for _ in range(2 if n_chunks > 1 else 1)]
     gathered = None
     comm_stream = None
     if world > 1 and not args.no_gather:
-        gathered = [torch.empty((world * cb, V), dtype=torch.int32, device="cuda") for _ in range(n_chunks)]
+        gathered = [torch.empty((world * cb, V), dtype=pdt, device="cuda") for _ in range(n_chunks)]
         comm_stream = torch.cuda.Stream()
         buf_free = [None, None]      # event: all gathers reading par_bufs[k] are done
     origins_dev = [torch.from_numpy(origins_for(rank, B, V, step=i)).cuda() for i in range(args.warmup + args.steps)]
@@ -396,6 +402,8 @@ def main():
     launches = _lib.lib().sp_kernel_launches() - launches0 - 0
     value = world * B * args.steps / (ms_total / 1e3)
 
+    if compact:
+        g.set_parent_format(0)
     # ---- e2e through the host-buffer C ABI (origins in host memory -> dist + parent in host memory) -------------
     e2e = None
     if rank == 0 or world > 1:
@@ -426,7 +434,7 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid "
                                        f"({E} links, {V} nodes), {B} origins per GPU per step, full trees + canonical "
-                                       f"predecessors" + (f", int32 next-hop tables all-gathered in {n_chunks} chunks overlapped with "
+                                       f"predecessors" + (f", one-byte next-hop tables all-gathered in {n_chunks} chunks overlapped with "
                                                           f"the next chunk's trees" if gathered is not None else ""),
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},

@@ -93,6 +93,14 @@ int sp_sssp_batch_device(Graph* graph, const int* origins_dev, int n, double* di
 int sp_sssp_batch_device_ex(Graph* graph, const int* origins_dev, int n, double* dist_dev, int* parent_dev,
                             void* stream, int reverse);
 
+/* Predecessor output format of the device batches: 0 (default) = int32 vertex ids; 1 = one byte per vertex, the
+ * index of the in-edge (creation order at that vertex) that attains the distance, 255 = none.  The compact form
+ * is what the multi-GPU path all-gathers (4x less NVLink traffic); sp_decode_parents_device expands it with the
+ * graph replica every rank holds.  Host batches (sp_sssp_batch) always return vertex ids. */
+int sp_set_parent_format(Graph* graph, int format);
+int sp_decode_parents_device(Graph* graph, const unsigned char* codes_dev, int n, int* parent_dev, void* stream,
+                             int reverse);
+
 /* Device-side sp_set_weights: weights_dev[nedges] in creategraph order (device memory), NaN = keep the current
  * weight.  Rewrites the device graph in place with one kernel; the host edge log is kept in step. */
 int sp_set_weights_device(Graph* graph, const double* weights_dev, int nedges, void* stream);

@@ -55,6 +55,8 @@ def _declare(L):
     L.sp_set_tuning.restype = ci; L.sp_set_tuning.argtypes = [vp, ci, ci, cd, ci]
     L.sp_alloc_host.restype = vp; L.sp_alloc_host.argtypes = [C.c_size_t]
     L.sp_free_host.restype = None; L.sp_free_host.argtypes = [vp]
+    L.sp_set_parent_format.restype = ci; L.sp_set_parent_format.argtypes = [vp, ci]
+    L.sp_decode_parents_device.restype = ci; L.sp_decode_parents_device.argtypes = [vp, vp, ci, vp, vp, ci]
     L.sp_set_algo.restype = ci; L.sp_set_algo.argtypes = [vp, ci, cd]
     L.sp_last_stats.restype = ci; L.sp_last_stats.argtypes = [vp, vp]
     L.sp_last_error.restype = C.c_char_p; L.sp_last_error.argtypes = []

@@ -656,7 +656,7 @@ __global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, co
                                                           const double* __restrict__ rs_w, const EdgeRec* __restrict__ rell,
                                                           const EdgeRec* __restrict__ rovf, int has_ovf,
                                                           const int* __restrict__ origins, const u64* __restrict__ dist_all,
-                                                          int* __restrict__ parent_all) {
+                                                          int* __restrict__ parent_all, int codes) {
   const int v = blockIdx.x * 256 + threadIdx.x;
   if (v >= V) return;
   int nv[4];
@@ -674,7 +674,7 @@ __global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, co
   for (int tree = blockIdx.y; tree < n_trees; tree += gridDim.y) {
     const u64* dist = dist_all + (size_t)tree * V;
     const u64 dvb = __ldg(&dist[v]);
-    int best = INT_MAX;
+    int best = INT_MAX, slot = 255;
     if (dvb != DIST_INF_BITS) {
       u64 dub[4];
 #pragma unroll
@@ -683,7 +683,7 @@ __global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, co
       for (int j = 0; j < 4; ++j) {
         if (dub[j] != DIST_INF_BITS) {
           const double cand = __longlong_as_double((long long)dub[j]) + nw[j];
-          if ((u64)__double_as_longlong(cand) == dvb && nv[j] < best) best = nv[j];
+          if ((u64)__double_as_longlong(cand) == dvb && nv[j] < best) { best = nv[j]; slot = j; }
         }
       }
       for (int k = 0; k < ovf_n; ++k) {
@@ -691,12 +691,33 @@ __global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, co
         const u64 du = __ldg(&dist[er.v]);
         if (du != DIST_INF_BITS) {
           const double cand = __longlong_as_double((long long)du) + er.w;
-          if ((u64)__double_as_longlong(cand) == dvb && er.v < best) best = er.v;
+          if ((u64)__double_as_longlong(cand) == dvb && er.v < best) { best = er.v; slot = min(4 + k, 254); }
         }
       }
     }
     const int src = __ldg(&origins[tree]);
-    parent_all[(size_t)tree * V + v] = (best == INT_MAX || v == src) ? -1 : best;
+    const bool none = best == INT_MAX || v == src;
+    if (codes) reinterpret_cast<unsigned char*>(parent_all)[(size_t)tree * V + v] = none ? (unsigned char)255 : (unsigned char)slot;
+    else parent_all[(size_t)tree * V + v] = none ? -1 : best;
+  }
+}
+
+// Expands one-byte predecessor codes (sp_set_parent_format 1: index of the in-edge that attains the distance,
+// 255 = none) back into vertex ids.
+__global__ void __launch_bounds__(256) decode_parents_kernel(int V, int n_trees, const int* __restrict__ rs_v,
+                                                             const EdgeRec* __restrict__ rell, const EdgeRec* __restrict__ rovf,
+                                                             const unsigned char* __restrict__ codes, int* __restrict__ parent_all) {
+  const int v = blockIdx.x * 256 + threadIdx.x;
+  if (v >= V) return;
+  int nv[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) nv[j] = __ldg(&rs_v[(size_t)j * V + v]);
+  for (int tree = blockIdx.y; tree < n_trees; tree += gridDim.y) {
+    const int c = codes[(size_t)tree * V + v];
+    int par = -1;
+    if (c < 4) par = c == 0 ? nv[0] : c == 1 ? nv[1] : c == 2 ? nv[2] : nv[3];
+    else if (c != 255) par = rovf[__ldg(&rell[(size_t)v * 4].pad) + (c - 4)].v;
+    parent_all[(size_t)tree * V + v] = par;
   }
 }
 
@@ -782,6 +803,7 @@ struct SqGraph {
   int fail_cap = 0;
   cudaStream_t s_compute = nullptr, s_copy = nullptr;
   cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+  int parent_format = 0;       // 0 = int32 vertex ids, 1 = one-byte in-edge codes (device batches only)
   int algo = 0;                // 0 = ELL kernel (bitmap kernel only as its fallback), 1 = bitmap kernel
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
 
@@ -1128,14 +1150,21 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     if (int rc = launch_bitmap_kernel(g, pf, bm_grid, smem, bm_threads, st)) return rc;
   }
   if (parent_dev) {
+    const int codes = g->parent_format;
+    if (codes) {
+      size_t worst = 0;
+      const std::vector<int>& rp = reverse ? g->h_rp : g->h_rrp;
+      for (int v = 0; v < V; ++v) worst = std::max<size_t>(worst, (size_t)(rp[v + 1] - rp[v]));
+      if (worst > 254) return sq::set_error(SQ_ERR_LIMIT, "one-byte predecessor codes need in-degree <= 254 (found %zu)", worst);
+    }
     // each thread keeps its in-edge record in registers and walks over ~16 trees
     dim3 pgrid((unsigned)(((size_t)V + 255) / 256), (unsigned)std::max(1, std::min((n + 15) / 16, 32768)));
     if (reverse)
       sssp_parent_kernel<<<pgrid, 256, 0, st>>>(V, n, g->d_fs_v, g->d_fs_w, g->d_ell, g->d_ovf, g->h_ovf.empty() ? 0 : 1,
-                                                origins_dev, p.dist_out, parent_dev);
+                                                origins_dev, p.dist_out, parent_dev, codes);
     else
       sssp_parent_kernel<<<pgrid, 256, 0, st>>>(V, n, g->d_rs_v, g->d_rs_w, g->d_rell, g->d_rovf, g->h_rovf.empty() ? 0 : 1,
-                                                origins_dev, p.dist_out, parent_dev);
+                                                origins_dev, p.dist_out, parent_dev, codes);
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
   }
@@ -1311,6 +1340,26 @@ int sp_set_algo(Graph* g, int algo, double queue_factor) {
   return SQ_OK;
 }
 
+int sp_set_parent_format(Graph* g, int format) {
+  if (!g || (format != 0 && format != 1)) return sq::set_error(SQ_ERR_ARG, "sp_set_parent_format: format must be 0 or 1");
+  g->parent_format = format;
+  return SQ_OK;
+}
+
+int sp_decode_parents_device(Graph* g, const unsigned char* codes_dev, int n, int* parent_dev, void* stream, int reverse) {
+  if (!g || !codes_dev || !parent_dev) return sq::set_error(SQ_ERR_ARG, "sp_decode_parents_device: null argument");
+  if (n <= 0) return SQ_OK;
+  if (int rc = g_build_and_upload(g)) return rc;
+  dim3 grid((unsigned)(((size_t)g->V + 255) / 256), (unsigned)std::max(1, std::min((n + 15) / 16, 32768)));
+  if (reverse)
+    decode_parents_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g->V, n, g->d_fs_v, g->d_ell, g->d_ovf, codes_dev, parent_dev);
+  else
+    decode_parents_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g->V, n, g->d_rs_v, g->d_rell, g->d_rovf, codes_dev, parent_dev);
+  sq::count_launch();
+  SQ_CUDA_TRY(cudaGetLastError());
+  return SQ_OK;
+}
+
 int sp_last_stats(Graph* g, long long* out5) {
   if (!g || !out5) return SQ_ERR_ARG;
   for (int i = 0; i < 5; ++i) out5[i] = g->last_stats[i];
@@ -1429,7 +1478,11 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
     u64* dbuf = dist_out ? g->d_dist_buf + (size_t)b * chunk * V : nullptr;
     int* pbuf = parent_out ? g->d_parent_buf + (size_t)b * chunk * V : nullptr;
     if (k >= 2) SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_compute, g->ev_copied[b], 0));  // buffer b is free again
-    if (int rc = g_run_batch_device(g, g->d_origins + off, m, dbuf, pbuf, g->s_compute, reverse != 0)) return rc;
+    const int fmt = g->parent_format;
+    g->parent_format = 0;  // host batches always return vertex ids
+    const int rc_run = g_run_batch_device(g, g->d_origins + off, m, dbuf, pbuf, g->s_compute, reverse != 0);
+    g->parent_format = fmt;
+    if (rc_run) return rc_run;
     SQ_CUDA_TRY(cudaEventRecord(g->ev_done[b], g->s_compute));
     SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_copy, g->ev_done[b], 0));
     if (!pinned) SQ_CUDA_TRY(cudaStreamSynchronize(g->s_compute));  // pageable copies block the host anyway

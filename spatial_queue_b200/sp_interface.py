@@ -116,6 +116,17 @@ class Graph:
     def set_tuning(self, threads=0, ctas_per_sm=-1, delta_factor=0.0, smem_queue=-1):
         check(lib().sp_set_tuning(self._h, threads, ctas_per_sm, float(delta_factor), smem_queue), "sp_set_tuning")
 
+    def set_parent_format(self, fmt):
+        """0 = int32 vertex ids, 1 = one-byte in-edge codes (device batches; include/sq_sp.h)."""
+        check(lib().sp_set_parent_format(self._h, int(fmt)), "sp_set_parent_format")
+
+    def decode_parents_device(self, codes_dev, parent_dev, stream=None, reverse=False):
+        import torch
+        sp = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
+        check(lib().sp_decode_parents_device(self._h, C.c_void_p(codes_dev.data_ptr()), int(codes_dev.shape[0]),
+                                             C.c_void_p(parent_dev.data_ptr()), sp, 1 if reverse else 0),
+              "sp_decode_parents_device")
+
     def set_algo(self, algo=0, queue_factor=0.0):
         """0 = ELL kernel (default), 1 = bitmap kernel; see include/sq_sp.h."""
         check(lib().sp_set_algo(self._h, int(algo), float(queue_factor)), "sp_set_algo")

@@ -214,3 +214,30 @@ def test_reverse_trees_and_device_weight_refresh(spi):
     w2[last] = 3.25
     check(w2)
     g.free()
+
+
+@pytest.mark.parametrize("reverse", [False, True])
+def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse):
+    """The compact table the multi-GPU path all-gathers (one byte per vertex) expands to exactly the int32 tree."""
+    import torch
+    rng = np.random.default_rng(31)
+    V, E = 2500, 13000                      # in-degrees beyond 4: overflow codes are exercised
+    s = rng.integers(0, V, E).astype(np.int32)
+    e = rng.integers(0, V, E).astype(np.int32)
+    w = np.round(rng.random(E) * 20.0) + 1.0   # many exact ties
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    origins = torch.from_numpy(rng.integers(0, V, 40).astype(np.int32)).cuda()
+    d = torch.empty((40, V), dtype=torch.float64, device="cuda")
+    p32 = torch.empty((40, V), dtype=torch.int32, device="cuda")
+    g.sssp_batch_device(origins, d, p32, reverse=reverse)
+    g.set_parent_format(1)
+    codes = torch.empty((40, V), dtype=torch.uint8, device="cuda")
+    g.sssp_batch_device(origins, d, codes, reverse=reverse)
+    out = torch.empty((40, V), dtype=torch.int32, device="cuda")
+    g.decode_parents_device(codes, out, reverse=reverse)
+    torch.cuda.synchronize()
+    assert torch.equal(out, p32)
+    g.set_parent_format(0)
+    dh, ph = g.sssp_batch(origins.cpu().numpy()[:5], reverse=reverse)
+    assert (ph == p32[:5].cpu().numpy()).all()
+    g.free()
