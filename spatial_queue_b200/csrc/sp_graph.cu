@@ -68,7 +68,7 @@ struct TreeParams {
   const int* tree_list;   // nullptr: trees 0..n_trees-1
   const int* n_list;      // device count of tree_list entries
   // ELL kernel
-  const EdgeRec* ell;     // [V][4] forward, slot 0/1 .pad = overflow start / count
+  const EdgeRec* ell;     // [V][4] forward; .pad = back-edge slot (3 bits, 7 = none) | (slot 0: overflow start, slot 1: count) << 3
   const EdgeRec* ovf;     // forward edges beyond the fourth of a vertex
   const EdgeRec* rell;    // [V][4] reverse
   const EdgeRec* rovf;
@@ -77,6 +77,14 @@ struct TreeParams {
   int near_cap, far_cap;
   int* fail_list;         // trees whose queues overflowed (rerun by the bitmap kernel)
   int* fail_count;
+  // warp kernel
+  unsigned* wfar;         // [warps in grid][2][wfar_cap] far piles
+  int wfar_cap;
+  int ring_cap;           // entries per shared-memory ring (power of two)
+  int vbits;              // bits of a queue entry that hold the vertex id
+  int pf_ahead;           // ring entries the L2 prefetcher may run ahead of the consumer (0 = off)
+  int sm_sched;           // > 0: number of SMs; every SM works through its own contiguous range of trees
+  unsigned* wring;        // [warps in grid][2][ring_cap] rings in global memory (GR variant)
 };
 
 #define DIST_INF_BITS 0x7FEFFFFFFFFFFFFFull  // DBL_MAX, what the reference leaves in unreached slots
@@ -592,7 +600,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
         // edges beyond the fourth of a vertex (rare on road networks)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          const int my_pad = act[j] ? rec[j].pad : 0;
+          const int my_pad = act[j] ? (rec[j].pad >> 3) : 0;
           if (!__any_sync(0xffffffffu, my_pad != 0)) continue;
           const int ovf_b = __shfl_sync(0xffffffffu, my_pad, lane & ~3);
           const int ovf_n = __shfl_sync(0xffffffffu, my_pad, (lane & ~3) + 1);
@@ -648,6 +656,316 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
   }
 }
 
+// -------------------------------------------------------------------------------------------------
+// Warp kernel: one tree per WARP, no CTA barriers, no shared-memory atomics.
+//
+// The CTA-per-tree kernels spend their time on per-round overhead at low lane fill: a road-network wavefront
+// holds a few hundred vertices, so 256 threads find 1-2 passes of work between barriers (ncu, r1b: 27 %
+// barrier stalls, 40 % issue utilisation, 1.33 M warp instructions per tree).  Here a warp owns the tree:
+//  * queue state (head / tail / bucket count) lives in registers and is warp-uniform; pushes are a ballot
+//    and a popc, visibility is a __syncwarp;
+//  * the current bucket is a FIFO ring in shared memory (pops 8 x ILP vertices per step, four lanes per
+//    vertex = one 64-byte ELL record), improvements below T are appended to the same ring, those in
+//    [T, T + delta) to the next-bucket buffer, which becomes the ring at the transition; the rest go to a far
+//    pile in global memory (closed links at 1e8);
+//  * a queue entry is 4 bytes: vertex id | slot of the edge straight back (skipped: it cannot improve) | hash
+//    of the distance the vertex had when pushed.  An entry whose hash no longer matches dist[vertex] is stale
+//    (a newer entry exists).  A hash collision only makes a stale entry look valid, and valid entries are
+//    relaxed with the distance read from memory, so collisions cost a duplicate pass, never a wrong result;
+//  * trees whose wavefront outgrows the ring are handed to the fallback kernel through fail_list.
+// Latency (queue -> dist/ELL loads -> L2 atomicMin) is hidden by 16-32 resident warps per SM, each on its own
+// tree.
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned dist_hash(u64 d) {
+  return ((unsigned)d * 0x9E3779B1u) ^ ((unsigned)(d >> 32) * 0x85EBCA6Bu);
+}
+
+__device__ __forceinline__ unsigned ld_ring(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+// GR = rings in global memory (no shared memory at all: the whole 256 KB array of the SM works as L1, whose
+// lines bound the number of loads in flight); otherwise rings in dynamic shared memory.
+template <int ILP, bool GR>
+__global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
+  extern __shared__ unsigned s_rings[];
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = lane & 3, grp = lane >> 2;
+  const unsigned lt = sq::lanemask_lt();
+  const int V = p.V;
+  const int C = p.ring_cap, Cm = C - 1;
+  const int vbits = p.vbits;
+  const unsigned vmask = (1u << vbits) - 1u;
+  const unsigned himask = ~((1u << (vbits + 3)) - 1u);
+  const int fcap = p.wfar_cap;
+  const int gwarp = blockIdx.x * (blockDim.x >> 5) + warp;
+  unsigned* ring_a = GR ? p.wring + (size_t)gwarp * 2 * C : s_rings + (size_t)warp * 2 * C;
+  unsigned* far_base = p.wfar + (size_t)gwarp * 2 * fcap;
+  const double delta = p.delta;
+  const int pf_ahead = p.pf_ahead;
+
+  int st_steps = 0, st_relax = 0, st_trans = 0;
+
+  for (;;) {
+    int tree = 0;
+    if (p.sm_sched > 0) {
+      // trees of one SM are neighbours in the output arrays: its warps share translation pages
+      unsigned smid;
+      asm("mov.u32 %0, %%smid;" : "=r"(smid));
+      const int lo = (int)(((long long)p.n_trees * smid) / p.sm_sched);
+      const int hi = (int)(((long long)p.n_trees * (smid + 1)) / p.sm_sched);
+      if (lane == 0) tree = lo + atomicAdd(p.tree_counter + 1 + smid, 1);
+      tree = __shfl_sync(FULL, tree, 0);
+      if (tree >= hi || smid >= (unsigned)p.sm_sched) break;
+    } else {
+      if (lane == 0) tree = atomicAdd(p.tree_counter, 1);
+      tree = __shfl_sync(FULL, tree, 0);
+      if (tree >= p.n_trees) break;
+    }
+
+    u64* dist = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)gwarp * V;
+    const int src = p.origins[tree];
+    const bool valid_src = (src >= 0 && src < V);
+    {  // distance row = DBL_MAX (graph.cc:178); rows are 8-byte aligned, 16-byte stores on the aligned middle
+      const int head = (int)(((uintptr_t)dist >> 3) & 1);
+      if (lane == 0 && head && V > 0) dist[0] = DIST_INF_BITS;
+      const int pairs = (V - head) >> 1;
+      ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dist + head);
+      const ulonglong2 inf2 = make_ulonglong2(DIST_INF_BITS, DIST_INF_BITS);
+#pragma unroll 4
+      for (int i = lane; i < pairs; i += 32) d2[i] = inf2;
+      if (lane == 0 && ((V - head) & 1)) dist[V - 1] = DIST_INF_BITS;
+    }
+    __syncwarp();
+    if (!valid_src) continue;
+
+    unsigned* cur = ring_a;
+    unsigned* bkt = ring_a + C;
+    int ch = 0, ct = 1, bt = 0;    // ring head / tail (monotonic), next-bucket count
+    int nf = 0, fcur = 0;          // far pile
+    bool fail = false;
+    if (lane == 0) {
+      dist[src] = 0ull;
+      cur[0] = (unsigned)src | (7u << vbits) | (dist_hash(0ull) & himask);
+    }
+    __syncwarp();
+    double T = delta, T2 = delta + delta;
+    // L2 prefetcher: a second ring cursor that runs up to pf_ahead entries in front of the consumer and touches
+    // the distance words of the neighbours those entries will relax.  Most of them were last written when the
+    // row was set to DBL_MAX and have left L2 since (thousands of rows are in flight); without this the first
+    // atomicMin on each sector pays a DRAM round trip in the middle of the warp's only dependency chain.
+    int pf_pos = 0;
+    int pfv[ILP];
+    unsigned pfe[ILP];
+    bool pfe_ok[ILP];
+#pragma unroll
+    for (int j = 0; j < ILP; ++j) { pfv[j] = -1; pfe[j] = 0u; pfe_ok[j] = false; }
+    // entries of the next step, loaded one step early: pre[j] belongs to ring position ch + 8 j + grp and is
+    // valid if that position is below pre_ct (the tail when it was loaded)
+    unsigned pre[ILP];
+    int pre_ct = 0;
+#pragma unroll
+    for (int j = 0; j < ILP; ++j) pre[j] = 0u;
+
+    // Classifies one candidate per lane and appends it to the ring / next bucket / far pile.  Convergent.
+    auto push = [&](bool imp, u64 ndb, unsigned ent) {
+      const double nd = __longlong_as_double((long long)ndb);
+      const bool nr = imp && nd < T;
+      const bool md = imp && !nr && nd < T2;
+      const bool fr = imp && !nr && !md;
+      const unsigned mn = __ballot_sync(FULL, nr), mm = __ballot_sync(FULL, md), mf = __ballot_sync(FULL, fr);
+      if (nr) cur[(ct + __popc(mn & lt)) & Cm] = ent;
+      ct += __popc(mn);
+      if (md) {
+        const int pos = bt + __popc(mm & lt);
+        if (pos < C) bkt[pos] = ent;
+      }
+      bt += __popc(mm);
+      if (mf) {
+        if (fr) {
+          const int pos = nf + __popc(mf & lt);
+          if (pos < fcap) far_base[(size_t)fcur * fcap + pos] = ent;
+        }
+        nf += __popc(mf);
+      }
+    };
+
+    for (;;) {
+      if (ch == ct) {
+        // ---- bucket transition (warp-uniform) ---------------------------------------------------------
+        if (bt == 0) {
+          if (nf == 0) break;  // tree finished
+          // nothing within reach: open the next bucket at the smallest live far distance
+          u64 lmin = DIST_INF_BITS;
+          const unsigned* fp = far_base + (size_t)fcur * fcap;
+          for (int i = lane; i < nf; i += 32) {
+            const unsigned e = (unsigned)sq::ld_cg_s32(reinterpret_cast<const int*>(fp + i));
+            const u64 d = sq::ld_cg_u64(&dist[e & vmask]);
+            if (((dist_hash(d) ^ e) & himask) == 0 && d < lmin) lmin = d;
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(FULL, lmin, o);
+            lmin = other < lmin ? other : lmin;
+          }
+          if (lmin == DIST_INF_BITS) break;  // only stale entries were left
+          T2 = __longlong_as_double((long long)lmin);
+        }
+        { unsigned* t = cur; cur = bkt; bkt = t; }
+        ch = 0; ct = bt; bt = 0;
+        pf_pos = 0;
+        pre_ct = 0;
+#pragma unroll
+        for (int j = 0; j < ILP; ++j) { pfv[j] = -1; pfe_ok[j] = false; }
+        T = T2; T2 = T + delta;
+        ++st_trans;
+        if (nf > 0) {
+          // split the far pile against the new next-bucket range [T, T2)
+          const unsigned* fp = far_base + (size_t)fcur * fcap;
+          unsigned* fq = far_base + (size_t)(fcur ^ 1) * fcap;
+          int nf2 = 0;
+          for (int i0 = 0; i0 < nf; i0 += 32) {
+            const int i = i0 + lane;
+            unsigned e = 0u;
+            bool live = false;
+            double d = 0.0;
+            if (i < nf) {
+              e = (unsigned)sq::ld_cg_s32(reinterpret_cast<const int*>(fp + i));
+              const u64 db = sq::ld_cg_u64(&dist[e & vmask]);
+              live = ((dist_hash(db) ^ e) & himask) == 0;
+              d = __longlong_as_double((long long)db);
+            }
+            const bool to_b = live && d < T2, to_f = live && !to_b;
+            const unsigned mb = __ballot_sync(FULL, to_b), mf = __ballot_sync(FULL, to_f);
+            if (to_b) {
+              const int pos = bt + __popc(mb & lt);
+              if (pos < C) bkt[pos] = e;
+            }
+            bt += __popc(mb);
+            if (to_f) fq[nf2 + __popc(mf & lt)] = e;  // nf2 <= i0 <= fcap: cannot overflow
+            nf2 += __popc(mf);
+          }
+          nf = nf2;
+          fcur ^= 1;
+          if (bt > C) { fail = true; break; }
+        }
+        __syncwarp();
+        continue;
+      }
+
+      // ---- one step: 8 x ILP frontier vertices, four lanes (= one 64-byte ELL record) per vertex -------
+      ++st_steps;
+      unsigned ent[ILP];
+      bool act[ILP];
+#pragma unroll
+      for (int j = 0; j < ILP; ++j) {
+        const int idx = ch + j * 8 + grp;
+        act[j] = idx < ct;
+        ent[j] = pre[j];
+        if (act[j] && idx >= pre_ct) ent[j] = GR ? ld_ring(&cur[idx & Cm]) : cur[idx & Cm];  // pushed by the last step
+        if (!act[j]) ent[j] = 0u;
+      }
+      if (pf_ahead > 0) {
+        // three stages, one per step: ring entry -> head of its ELL edge -> prefetch of that distance word
+#pragma unroll
+        for (int j = 0; j < ILP; ++j)
+          if (pfv[j] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(&dist[pfv[j]]));
+#pragma unroll
+        for (int j = 0; j < ILP; ++j) {
+          pfv[j] = -1;
+          if (pfe_ok[j]) pfv[j] = __ldg(&p.ell[(size_t)(pfe[j] & vmask) * 4 + slot].v);
+        }
+        pf_pos = max(pf_pos, ch + 8 * ILP);
+        const int pf_end = min(ct, ch + 8 * ILP + pf_ahead);
+#pragma unroll
+        for (int j = 0; j < ILP; ++j) {
+          const int idx = pf_pos + j * 8 + grp;
+          pfe_ok[j] = idx < pf_end;
+          if (pfe_ok[j]) pfe[j] = GR ? ld_ring(&cur[idx & Cm]) : cur[idx & Cm];
+        }
+        pf_pos = min(pf_end, pf_pos + 8 * ILP);
+      }
+      ch = min(ct, ch + 8 * ILP);
+      pre_ct = ct;
+#pragma unroll
+      for (int j = 0; j < ILP; ++j) {
+        const int idx = ch + j * 8 + grp;
+        if (idx < ct) pre[j] = GR ? ld_ring(&cur[idx & Cm]) : cur[idx & Cm];
+      }
+      u64 dnow[ILP];
+      int4 raw[ILP];
+#pragma unroll
+      for (int j = 0; j < ILP; ++j) {
+        dnow[j] = 0ull;
+        raw[j] = make_int4(0, 0, -1, 7);
+        if (act[j]) {
+          const unsigned u = ent[j] & vmask;
+          dnow[j] = sq::ld_cg_u64(&dist[u]);
+          raw[j] = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u * 4 + slot]));
+        }
+      }
+      bool ok[ILP], has[ILP];
+      u64 ndb[ILP], old[ILP];
+#pragma unroll
+      for (int j = 0; j < ILP; ++j) {
+        ok[j] = act[j] && ((dist_hash(dnow[j]) ^ ent[j]) & himask) == 0;
+        has[j] = ok[j] && raw[j].z >= 0 && slot != (int)((ent[j] >> vbits) & 7u);
+        ndb[j] = (u64)__double_as_longlong(__longlong_as_double((long long)dnow[j]) + __hiloint2double(raw[j].y, raw[j].x));
+        old[j] = 0ull;
+      }
+#pragma unroll
+      for (int j = 0; j < ILP; ++j)
+        if (has[j]) old[j] = atomicMin(&dist[raw[j].z], ndb[j]);
+#pragma unroll
+      for (int j = 0; j < ILP; ++j) {
+        st_relax += has[j];
+        const unsigned ne = (unsigned)raw[j].z | ((unsigned)(raw[j].w & 7) << vbits) | (dist_hash(ndb[j]) & himask);
+        push(has[j] && ndb[j] < old[j], ndb[j], ne);
+      }
+      // edges beyond the fourth of a vertex (rare on road networks)
+#pragma unroll
+      for (int j = 0; j < ILP; ++j) {
+        const int my = ok[j] ? (raw[j].w >> 3) : 0;
+        if (!__any_sync(FULL, slot == 1 && my != 0)) continue;
+        const int ovf_b = __shfl_sync(FULL, my, lane & ~3);
+        const int ovf_n = __shfl_sync(FULL, my, (lane & ~3) + 1);
+        const int max_o = __reduce_max_sync(FULL, ovf_n);
+        for (int k = slot; k - slot < max_o; k += 4) {
+          const bool h2 = ok[j] && k < ovf_n;
+          unsigned ne = 0u;
+          u64 nb2 = DIST_INF_BITS, old2 = 0ull;
+          if (h2) {
+            const EdgeRec er = ld_edge(&p.ovf[ovf_b + k]);
+            nb2 = (u64)__double_as_longlong(__longlong_as_double((long long)dnow[j]) + er.w);
+            old2 = atomicMin(&dist[er.v], nb2);
+            ne = (unsigned)er.v | (7u << vbits) | (dist_hash(nb2) & himask);
+          }
+          st_relax += h2;
+          push(h2 && nb2 < old2, nb2, ne);
+        }
+      }
+      if (ct - ch > C || bt > C || nf > fcap) { fail = true; break; }
+      __syncwarp();
+    }
+    __syncwarp();
+    if (fail && lane == 0) p.fail_list[atomicAdd(p.fail_count, 1)] = tree;  // rerun by the fallback kernel
+  }
+
+  if (p.stats) {
+    long long r = st_relax;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(FULL, r, o);
+    if (lane == 0) {
+      atomicAdd((u64*)&p.stats[2], (u64)r);
+      atomicAdd((u64*)&p.stats[1], (u64)st_steps);
+      atomicAdd((u64*)&p.stats[3], (u64)st_trans);
+    }
+  }
+}
+
 // Canonical predecessors for a batch of finished trees: parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]}, -1 for
 // the origin and for unreached vertices.  One thread per vertex; its (up to four) in-edges come from a
 // slot-major copy of the reverse ELL (coalesced) and stay in registers while blockIdx.y strides over trees, so
@@ -668,8 +986,8 @@ __global__ void __launch_bounds__(256) sssp_parent_kernel(int V, int n_trees, co
   }
   int ovf_b = 0, ovf_n = 0;
   if (has_ovf) {
-    ovf_b = __ldg(&rell[(size_t)v * 4 + 0].pad);
-    ovf_n = __ldg(&rell[(size_t)v * 4 + 1].pad);
+    ovf_b = __ldg(&rell[(size_t)v * 4 + 0].pad) >> 3;
+    ovf_n = __ldg(&rell[(size_t)v * 4 + 1].pad) >> 3;
   }
   for (int tree = blockIdx.y; tree < n_trees; tree += gridDim.y) {
     const u64* dist = dist_all + (size_t)tree * V;
@@ -716,7 +1034,7 @@ __global__ void __launch_bounds__(256) decode_parents_kernel(int V, int n_trees,
     const int c = codes[(size_t)tree * V + v];
     int par = -1;
     if (c < 4) par = c == 0 ? nv[0] : c == 1 ? nv[1] : c == 2 ? nv[2] : nv[3];
-    else if (c != 255) par = rovf[__ldg(&rell[(size_t)v * 4].pad) + (c - 4)].v;
+    else if (c != 255) par = rovf[(__ldg(&rell[(size_t)v * 4].pad) >> 3) + (c - 4)].v;
     parent_all[(size_t)tree * V + v] = par;
   }
 }
@@ -804,7 +1122,13 @@ struct SqGraph {
   cudaStream_t s_compute = nullptr, s_copy = nullptr;
   cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   int parent_format = 0;       // 0 = int32 vertex ids, 1 = one-byte in-edge codes (device batches only)
-  int algo = 0;                // 0 = ELL kernel (bitmap kernel only as its fallback), 1 = bitmap kernel
+  int algo = 2;                // 2 = warp kernel (default), 0 = ELL kernel, 1 = bitmap kernel (also everyone's fallback)
+  int warp_ring = 1024, warp_ilp = 2, warp_ctas_per_sm = 0, warp_prefetch = 64;
+  unsigned* d_wfar = nullptr;
+  int wfar_warps = 0, wfar_cap = 0;
+  int warp_global = 0;         // 1 = rings in global memory (no shared memory, largest L1)
+  unsigned* d_wring = nullptr;
+  int wring_warps = 0, wring_cap = 0;
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
 
   // tuning
@@ -844,21 +1168,26 @@ static void g_free_device(SqGraph* g) {
   g->ovf_cap = g->rovf_cap = 0;
 }
 
-// CSR -> four-wide ELL + overflow list.  Slot 0 / slot 1 of a vertex carry the overflow start / count in .pad.
+// CSR -> four-wide ELL + overflow list.  .pad of every record: low 3 bits = the slot, in the head vertex's own
+// record, of an edge leading straight back to this vertex (7 = none; relaxing it can never improve anything
+// since weights are >= 0); slot 0 / slot 1 of a vertex carry the overflow start / count above those bits.
 static void build_ell(const std::vector<int>& rp, const std::vector<EdgeRec>& adj, int V, std::vector<EdgeRec>& ell,
                       std::vector<EdgeRec>& ovf) {
-  ell.assign((size_t)4 * std::max(V, 1), EdgeRec{0.0, -1, 0});
+  ell.assign((size_t)4 * std::max(V, 1), EdgeRec{0.0, -1, 7});
   ovf.clear();
   for (int v = 0; v < V; ++v) {
     const int b = rp[v], deg = rp[v + 1] - rp[v];
     for (int j = 0; j < std::min(deg, 4); ++j) {
       EdgeRec r = adj[b + j];
-      r.pad = 0;
+      r.pad = 7;
+      const int h = r.v, hb = rp[h], hdeg = std::min(rp[h + 1] - rp[h], 4);
+      for (int k = 0; k < hdeg; ++k)
+        if (adj[hb + k].v == v) { r.pad = k; break; }
       ell[(size_t)4 * v + j] = r;
     }
     if (deg > 4) {
-      ell[(size_t)4 * v + 0].pad = (int)ovf.size();
-      ell[(size_t)4 * v + 1].pad = deg - 4;
+      ell[(size_t)4 * v + 0].pad |= (int)ovf.size() << 3;
+      ell[(size_t)4 * v + 1].pad |= (deg - 4) << 3;
       for (int j = 4; j < deg; ++j) ovf.push_back(adj[b + j]);
     }
   }
@@ -907,7 +1236,7 @@ static int g_build_and_upload(SqGraph* g) {
     SQ_CUDA_TRY(cudaMalloc(&g->d_radj, sizeof(EdgeRec) * (size_t)std::max(E, 1)));
     SQ_CUDA_TRY(cudaMemcpy(g->d_row_ptr, rp.data(), sizeof(int) * (size_t)(V + 1), cudaMemcpyHostToDevice));
     SQ_CUDA_TRY(cudaMemcpy(g->d_rrow_ptr, rrp.data(), sizeof(int) * (size_t)(V + 1), cudaMemcpyHostToDevice));
-    if (!g->d_counter) SQ_CUDA_TRY(cudaMalloc(&g->d_counter, sizeof(int)));
+    if (!g->d_counter) SQ_CUDA_TRY(cudaMalloc(&g->d_counter, sizeof(int) * 1024));
     if (!g->d_stats) SQ_CUDA_TRY(cudaMalloc(&g->d_stats, sizeof(long long) * 5));
     g->topo_dirty = false;
     g->w_dirty = true;
@@ -963,9 +1292,9 @@ static int g_build_and_upload(SqGraph* g) {
         slots[i] = a;
         slots[n + i] = r;
         const int v = g->es[i], ja = a - g->h_rp[v];
-        slots[2 * n + i] = ja < 4 ? 4 * v + ja : -(g->h_ell[(size_t)4 * v].pad + (ja - 4) + 1);
+        slots[2 * n + i] = ja < 4 ? 4 * v + ja : -((g->h_ell[(size_t)4 * v].pad >> 3) + (ja - 4) + 1);
         const int u = g->ee[i], jr = r - g->h_rrp[u];
-        slots[3 * n + i] = jr < 4 ? 4 * u + jr : -(g->h_rell[(size_t)4 * u].pad + (jr - 4) + 1);
+        slots[3 * n + i] = jr < 4 ? 4 * u + jr : -((g->h_rell[(size_t)4 * u].pad >> 3) + (jr - 4) + 1);
       }
       cudaFree(g->d_wslots); g->d_wslots = nullptr;
       SQ_CUDA_TRY(cudaMalloc(&g->d_wslots, sizeof(int) * slots.size()));
@@ -1072,7 +1401,7 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     SQ_CUDA_TRY(cudaMalloc(&g->d_fail, sizeof(int) * (size_t)(n + 2)));
     g->fail_cap = n + 2;
   }
-  SQ_CUDA_TRY(cudaMemsetAsync(g->d_counter, 0, sizeof(int), st));
+  SQ_CUDA_TRY(cudaMemsetAsync(g->d_counter, 0, sizeof(int) * 1024, st));
   SQ_CUDA_TRY(cudaMemsetAsync(g->d_stats, 0, sizeof(long long) * 5, st));
   SQ_CUDA_TRY(cudaMemsetAsync(g->d_fail, 0, sizeof(int) * 2, st));
 
@@ -1102,22 +1431,73 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     return SQ_OK;
   }
 
-  // ---- ELL kernel -------------------------------------------------------------------------------
-  const int threads = std::min(g->threads, 256);
-  int per_sm = g->ctas_per_sm > 0 ? g->ctas_per_sm : std::min(9, 1024 / threads);
-  per_sm = std::max(1, std::min(per_sm, std::min(9, 2048 / threads)));
-  const int grid = std::min(n, n_sm * per_sm);
-  const int near_cap = std::max(32, (int)(g->queue_factor * V));
-  const int far_cap = 2 * near_cap;
-  const size_t per_cta = 4 * (size_t)near_cap + 2 * (size_t)far_cap;
-  if (g->q2_grid < grid || g->q2_near != near_cap) {
-    cudaFree(g->d_q2scratch); g->d_q2scratch = nullptr;
-    cudaFree(g->d_q2v); g->d_q2v = nullptr;
-    SQ_CUDA_TRY(cudaMalloc(&g->d_q2scratch, sizeof(u64) * (size_t)grid * per_cta));
-    SQ_CUDA_TRY(cudaMalloc(&g->d_q2v, sizeof(int2) * (size_t)grid * per_cta));
-    g->q2_grid = grid; g->q2_near = near_cap; g->q2_far = far_cap;
+  // ---- warp kernel (algo 2, default) or ELL kernel (algo 0) -------------------------------------------
+  int vbits = 1;
+  while ((1ll << vbits) < (long long)V) ++vbits;
+  const bool use_warp = g->algo == 2 && vbits <= 24;   // >= 5 hash bits per queue entry
+  const int threads = use_warp ? 128 : std::min(g->threads, 256);
+  int per_sm, grid, rows;   // rows = trees in flight (scratch distance rows in timing-only mode)
+  size_t warp_smem = 0;
+  bool use_gr = false;
+  if (use_warp) {
+    int C = 64;
+    while (C < g->warp_ring) C <<= 1;
+    use_gr = g->warp_global != 0;
+    if (const char* e = getenv("SQ_WARP_GR")) use_gr = atoi(e) != 0;
+    if (use_gr) {
+      warp_smem = 0;
+      per_sm = g->warp_ctas_per_sm > 0 ? std::min(g->warp_ctas_per_sm, 16) : 8;
+    } else {
+      warp_smem = (size_t)4 * 2 * C * sizeof(unsigned);
+      if (warp_smem > 200 * 1024) return sq::set_error(SQ_ERR_ARG, "warp kernel: ring capacity %d does not fit shared memory", C);
+      per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (warp_smem + 1024));
+      per_sm = std::max(1, std::min(per_sm, 16));
+      if (g->warp_ctas_per_sm > 0) per_sm = std::min(per_sm, g->warp_ctas_per_sm);
+    }
+    {
+      // all trees of a graph take about the same time, so a batch finishes in whole waves: spread the trees
+      // evenly over the waves instead of leaving the last one mostly empty
+      const int max_rows = n_sm * per_sm * 4;
+      const int waves = (n + max_rows - 1) / max_rows;
+      const int even = (n + waves - 1) / waves;
+      grid = std::min((even + 3) / 4, n_sm * per_sm);
+    }
+    rows = grid * 4;
+    if (use_gr && (g->wring_warps < rows || g->wring_cap != C)) {
+      cudaFree(g->d_wring); g->d_wring = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_wring, sizeof(unsigned) * (size_t)rows * 2 * C));
+      g->wring_warps = rows; g->wring_cap = C;
+    }
+    p.wring = g->d_wring;
+    const int fcap = std::min(std::max(V, 32), std::max(1024, V / 8));
+    if (g->wfar_warps < rows || g->wfar_cap != fcap) {
+      cudaFree(g->d_wfar); g->d_wfar = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_wfar, sizeof(unsigned) * (size_t)rows * 2 * fcap));
+      g->wfar_warps = rows; g->wfar_cap = fcap;
+    }
+    p.wfar = g->d_wfar; p.wfar_cap = fcap; p.ring_cap = C; p.vbits = vbits;
+    p.pf_ahead = g->warp_prefetch;
+    if (const char* e = getenv("SQ_WARP_PF")) p.pf_ahead = atoi(e);
+    p.sm_sched = 0;
+    if (const char* e = getenv("SQ_WARP_SMSCHED")) p.sm_sched = atoi(e) ? n_sm : 0;
+    if (grid % n_sm) p.sm_sched = 0;   // needs the same number of CTAs on every SM
+  } else {
+    per_sm = g->ctas_per_sm > 0 ? g->ctas_per_sm : std::min(9, 1024 / threads);
+    per_sm = std::max(1, std::min(per_sm, std::min(9, 2048 / threads)));
+    grid = std::min(n, n_sm * per_sm);
+    rows = grid;
+    const int near_cap = std::max(32, (int)(g->queue_factor * V));
+    const int far_cap = 2 * near_cap;
+    const size_t per_cta = 4 * (size_t)near_cap + 2 * (size_t)far_cap;
+    if (g->q2_grid < grid || g->q2_near != near_cap) {
+      cudaFree(g->d_q2scratch); g->d_q2scratch = nullptr;
+      cudaFree(g->d_q2v); g->d_q2v = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_q2scratch, sizeof(u64) * (size_t)grid * per_cta));
+      SQ_CUDA_TRY(cudaMalloc(&g->d_q2v, sizeof(int2) * (size_t)grid * per_cta));
+      g->q2_grid = grid; g->q2_near = near_cap; g->q2_far = far_cap;
+    }
+    p.q2scratch = g->d_q2scratch; p.q2v = g->d_q2v; p.near_cap = near_cap; p.far_cap = far_cap;
   }
-  p.q2scratch = g->d_q2scratch; p.q2v = g->d_q2v; p.near_cap = near_cap; p.far_cap = far_cap;
   if (parent_dev && !dist_dev) {
     // predecessors need the finished distances of every tree: keep them in a library buffer
     if (g->dist_tmp_elems < (size_t)n * V) {
@@ -1128,18 +1508,47 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     p.dist_out = g->d_dist_tmp;
   }
   if (!p.dist_out) {
-    // timing-only mode keeps distances in a per-CTA scratch row
-    if (g->scratch_grid < grid || g->scratch_V < V || !g->d_dist_scratch) {
+    // timing-only mode keeps distances in a scratch row per tree in flight
+    if (g->scratch_grid < rows || g->scratch_V < V || !g->d_dist_scratch) {
       cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
       g->d_dist_scratch = nullptr; g->d_qscratch = nullptr;
-      SQ_CUDA_TRY(cudaMalloc(&g->d_dist_scratch, sizeof(u64) * (size_t)grid * V));
-      SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)grid * 4 * V));
-      g->scratch_grid = grid; g->scratch_V = V;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_dist_scratch, sizeof(u64) * (size_t)rows * V));
+      SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)std::max(bm_grid, 1) * 4 * V));
+      g->scratch_grid = rows; g->scratch_V = V;
     }
     p.dist_scratch = g->d_dist_scratch; p.qscratch = g->d_qscratch;
   }
   p.parent_out = nullptr;  // predecessors come from sssp_parent_kernel below
-  if (int rc = launch_ell_kernel(p, grid, threads, st)) return rc;
+  if (use_warp) {
+    typedef void (*WarpKernel)(const TreeParams);
+    static const WarpKernel kernels[6] = {sssp_warp_kernel<1, false>, sssp_warp_kernel<2, false>, sssp_warp_kernel<4, false>,
+                                          sssp_warp_kernel<1, true>, sssp_warp_kernel<2, true>, sssp_warp_kernel<4, true>};
+    static bool attr_set = false;
+    if (!attr_set) {
+      for (int i = 0; i < 3; ++i)
+        SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_set = true;
+    }
+    {
+      // shared memory carve-out = what the resident CTAs need, the rest stays L1 (its lines bound the loads in flight)
+      int pct = (int)((100 * (size_t)per_sm * (warp_smem + 1024) + prop.sharedMemPerMultiprocessor - 1) / prop.sharedMemPerMultiprocessor);
+      if (use_gr) pct = 0;
+      if (const char* e = getenv("SQ_WARP_CARVE")) pct = atoi(e);
+      pct = std::max(0, std::min(100, pct));
+      static int last_pct = -1;
+      if (pct != last_pct) {
+        for (int i = 0; i < 6; ++i)
+          SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        last_pct = pct;
+      }
+    }
+    const int ki = (g->warp_ilp == 1 ? 0 : g->warp_ilp == 4 ? 2 : 1) + (use_gr ? 3 : 0);
+    kernels[ki]<<<grid, 128, warp_smem, st>>>(p);
+    sq::count_launch();
+    SQ_CUDA_TRY(cudaGetLastError());
+  } else {
+    if (int rc = launch_ell_kernel(p, grid, threads, st)) return rc;
+  }
   // fallback pass over the trees whose queues overflowed (normally none: its CTAs exit at once)
   if (bitmap_fits) {
     TreeParams pf = p;
@@ -1309,7 +1718,7 @@ void sp_free_graph(Graph* g) {
   g_free_device(g);
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
-  cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail);
+  cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail); cudaFree(g->d_wfar); cudaFree(g->d_wring);
   if (g->s_compute) {
     cudaStreamDestroy(g->s_compute); cudaStreamDestroy(g->s_copy);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(g->ev_done[i]); cudaEventDestroy(g->ev_copied[i]); }
@@ -1332,11 +1741,20 @@ int sp_set_tuning(Graph* g, int threads, int ctas_per_sm, double delta_factor, i
 
 int sp_set_algo(Graph* g, int algo, double queue_factor) {
   if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: null graph");
-  if (algo != 0 && algo != 1) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL) or 1 (bitmap)");
+  if (algo < 0 || algo > 2) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL), 1 (bitmap) or 2 (warp)");
   g->algo = algo;
   if (algo == 1 && g->threads < 128) g->threads = 256;
   if (algo == 0 && g->threads > 256) g->threads = 128;
   if (queue_factor > 0.0) g->queue_factor = queue_factor;
+  return SQ_OK;
+}
+
+int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
+  if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_warp_tuning: null graph");
+  if (ilp != 0 && ilp != 1 && ilp != 2 && ilp != 4) return sq::set_error(SQ_ERR_ARG, "sp_set_warp_tuning: ilp must be 1, 2 or 4");
+  if (ring_cap > 0) g->warp_ring = ring_cap;
+  if (ilp > 0) g->warp_ilp = ilp;
+  if (ctas_per_sm >= 0) g->warp_ctas_per_sm = ctas_per_sm;
   return SQ_OK;
 }
 

@@ -128,8 +128,11 @@ class Graph:
               "sp_decode_parents_device")
 
     def set_algo(self, algo=0, queue_factor=0.0):
-        """0 = ELL kernel (default), 1 = bitmap kernel; see include/sq_sp.h."""
+        """2 = warp kernel (default), 0 = ELL kernel, 1 = bitmap kernel; see include/sq_sp.h."""
         check(lib().sp_set_algo(self._h, int(algo), float(queue_factor)), "sp_set_algo")
+
+    def set_warp_tuning(self, ring_cap=0, ilp=0, ctas_per_sm=-1):
+        check(lib().sp_set_warp_tuning(self._h, int(ring_cap), int(ilp), int(ctas_per_sm)), "sp_set_warp_tuning")
 
     def sync(self):
         check(lib().sp_sync(self._h), "sp_sync")

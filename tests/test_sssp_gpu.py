@@ -64,7 +64,8 @@ def test_network_mtx_golden(spi):
 @pytest.mark.parametrize("directed", [True, False])
 @pytest.mark.parametrize("threads,smemq,algo,qfac", [(256, 0, 1, 0), (128, 32, 1, 0), (1024, 64, 1, 0),   # bitmap kernel
                                                       (128, 0, 0, 0), (64, 0, 0, 0), (32, 0, 0, 0),       # ELL kernel
-                                                      (256, 0, 0, 4.0), (64, 0, 0, 0.02)])               # roomy / tight queues
+                                                      (256, 0, 0, 4.0), (64, 0, 0, 0.02),                 # roomy / tight queues
+                                                      (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0)])    # warp kernel: (ilp, ring)
 def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
     from oracle import sssp as osssp
     rng = np.random.default_rng(11 + threads)
@@ -78,7 +79,11 @@ def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
         og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1, directed=directed)
         g = spi.from_arrays(s, e, w, max_vertex_id=V - 1, directed=directed)
         g.set_algo(algo, qfac)
-        g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
+        if algo == 2:
+            g.set_warp_tuning(ring_cap=smemq, ilp=threads)
+            g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
+        else:
+            g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
         origins = np.concatenate([rng.integers(0, V, 7), [-1, V, V + 5]]).astype(np.int32)
         d, p = g.sssp_batch(origins)
         do, po = og.sssp_batch(origins)
@@ -106,6 +111,34 @@ def test_queue_overflow_falls_back_to_the_bitmap_kernel(spi):
     g.free()
 
 
+def test_warp_kernel_ring_overflow_falls_back(spi):
+    """Same, for the warp kernel with a 64-entry ring: wavefronts of a dense random graph do not fit, the trees go
+    to the fallback kernel; a grid with a roomy ring must not overflow at all."""
+    from oracle import sssp as osssp
+    rng = np.random.default_rng(6)
+    V, E = 20000, 160000
+    s = rng.integers(0, V, E).astype(np.int32)
+    e = rng.integers(0, V, E).astype(np.int32)
+    w = rng.random(E) * 10.0 + 0.01
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.set_algo(2)
+    g.set_warp_tuning(ring_cap=64, ilp=2)
+    origins = rng.integers(0, V, 24).astype(np.int32)
+    d, p = g.sssp_batch(origins)
+    assert g.last_stats()["overflows"] > 0
+    do, po = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1).sssp_batch(origins)
+    assert d.tobytes() == do.tobytes() and (p == po).all()
+    g.free()
+    s, e, w = grid_graph(100, seed=3)
+    g = spi.from_arrays(s, e, w)
+    origins = rng.integers(0, 100 * 100, 64).astype(np.int32)
+    d, p = g.sssp_batch(origins)
+    assert g.last_stats()["overflows"] == 0
+    do, po = osssp.OracleGraph(s, e, w).sssp_batch(origins)
+    assert d.tobytes() == do.tobytes() and (p == po).all()
+    g.free()
+
+
 def test_weight_updates_reach_the_device(spi):
     from oracle import sssp as osssp
     s, e, w = grid_graph(24, seed=5)
@@ -126,7 +159,7 @@ def test_weight_updates_reach_the_device(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
 
 
-@pytest.mark.parametrize("algo", [0, 1])
+@pytest.mark.parametrize("algo", [0, 1, 2])
 def test_grid_batch_and_device_api(spi, algo):
     import torch
     from oracle import sssp as osssp

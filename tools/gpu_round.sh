@@ -1,0 +1,25 @@
+#!/bin/bash
+# One GPU-box pass: parity tests, bench line, ncu launch lists and --set full captures of the two dominant kernels.
+# Usage (from the build container): gpurun --timeout 2400 -- 'bash tools/gpu_round.sh r1b'
+TAG=${1:-r1x}
+O=gpurun_out/$TAG
+mkdir -p $O
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/smi.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $O/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/smoke.log
+timeout 900 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" | tee -a $O/bench.err
+# launch lists (share of the step per kernel; absolute times under ncu are cold-cache and serialised)
+timeout 600 python bench.py --steps 1 --warmup 3 --batch 2048 --no-tick --no-cpu > $O/bench_small.json 2>&1 && \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/sssp_launches.csv \
+  python bench.py --steps 1 --warmup 3 --batch 2048 --no-tick --no-cpu > $O/ncu_sssp_launches.log 2>&1
+TICKS=700 timeout 600 python tools/tick_prof.py > $O/tick_prof_plain.log 2>&1 && \
+TICKS=700 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 2400 -c 1200 --csv \
+  --log-file $O/tick_launches.csv python tools/tick_prof.py > $O/ncu_tick_launches.log 2>&1
+# full captures
+BATCH=2048 timeout 300 python tools/sssp_prof.py > $O/sssp_prof_plain.log 2>&1 && \
+BATCH=2048 timeout 900 ncu --set full --clock-control none --import-source on -k regex:sssp_ell_kernel -s 1 -c 1 \
+  -o $O/sssp_ell_full -f python tools/sssp_prof.py > $O/ncu_sssp_full.log 2>&1
+TICKS=2600 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_node_phase -s 2500 -c 1 \
+  -o $O/tick_node_full -f python tools/tick_prof.py > $O/ncu_tick_full.log 2>&1
+ls -la $O
+tail -3 $O/pytest_gpu.log; tail -2 $O/smoke.log; head -c 1500 $O/bench.json

@@ -6,11 +6,16 @@ import numpy as np, torch
 from conftest import grid_graph
 from spatial_queue_b200 import sp_interface as spi
 n = int(os.environ.get("GRID", 224)); B = int(os.environ.get("BATCH", 2048))
-t, c, d, q = json.loads(os.environ.get("CFG", "[256,6,2.0,0]"))
+ALGO = int(os.environ.get("ALGO", 2))
+t, c, d, q = json.loads(os.environ.get("CFG", "[2,0,2.0,1024]" if ALGO == 2 else "[256,6,2.0,0]"))
 s, e, w = grid_graph(n, seed=1)
 g = spi.from_arrays(s, e, w); V = n * n
-g.set_algo(int(os.environ.get("ALGO", 0)))
-g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
+g.set_algo(ALGO)
+if ALGO == 2:   # CFG = [ilp, CTAs of four warps per SM, delta factor, ring entries]
+    g.set_warp_tuning(ring_cap=q, ilp=t, ctas_per_sm=c)
+    g.set_tuning(delta_factor=d)
+else:
+    g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
 origins = np.random.default_rng(0).permutation(V)[:B].astype(np.int32)
 o = torch.from_numpy(origins).cuda()
 dist = torch.empty((B, V), dtype=torch.float64, device="cuda"); par = torch.empty((B, V), dtype=torch.int32, device="cuda")

@@ -16,26 +16,43 @@ origins = torch.from_numpy(np.random.default_rng(0).permutation(V)[:B].astype(np
 dist = torch.empty((B, V), dtype=torch.float64, device="cuda")
 par = torch.empty((B, V), dtype=torch.int32, device="cuda")
 btree = 20 * len(s) + 24 * V
-ALGO = int(os.environ.get("ALGO", 0))
+ALGO = int(os.environ.get("ALGO", 2))
 g.set_algo(ALGO)
 configs = json.loads(os.environ.get("CONFIGS", "null")) or (
     [(t, c, d, 0) for t in (32, 64, 128, 256) for c in (4, 8, 12, 16, 24, 32) for d in (1.0, 2.0, 4.0) if t * c <= 2048]
     if ALGO == 0 else
+    [(i, c, d, q) for i in (1, 2, 4) for q in (512, 1024) for c in (0, 4, 8) for d in (1.0, 2.0, 4.0)]
+    if ALGO == 2 else
     [(t, c, d, q) for t in (128, 256, 512) for c in (0, 2, 4) for d in (1.0, 2.0, 4.0, 8.0) for q in (1024,)])
-for (t, c, d, q) in configs:
+for cfg in configs:
+    (t, c, d, q), pf = cfg[:4], (cfg[4] if len(cfg) > 4 else None)
     try:
-        g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
+        if ALGO == 2:   # (ilp, CTAs of four warps per SM, delta factor, ring entries[, prefetch lookahead])
+            if pf is not None:
+                os.environ["SQ_WARP_PF"] = str(pf)
+            os.environ["SQ_WARP_SMSCHED"] = str(cfg[5]) if len(cfg) > 5 else "0"
+            os.environ["SQ_WARP_GR"] = str(cfg[7]) if len(cfg) > 7 else "0"
+            if len(cfg) > 6 and cfg[6] is not None:
+                os.environ["SQ_WARP_CARVE"] = str(cfg[6])
+            else:
+                os.environ.pop("SQ_WARP_CARVE", None)
+            g.set_warp_tuning(ring_cap=q, ilp=t, ctas_per_sm=c)
+            g.set_tuning(delta_factor=d)
+        else:
+            g.set_tuning(threads=t, ctas_per_sm=c, delta_factor=d, smem_queue=q)
         g.sssp_batch_device(origins[:256], dist, par); torch.cuda.synchronize()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record(); g.sssp_batch_device(origins, dist, par); ev1.record(); torch.cuda.synchronize()
-        ms = ev0.elapsed_time(ev1)
+        ms = 1e30
+        for _ in range(3):
+            ev0.record(); g.sssp_batch_device(origins, dist, par); ev1.record(); torch.cuda.synchronize()
+            ms = min(ms, ev0.elapsed_time(ev1))
         tps = B / ms * 1e3
         ev0.record(); g.sssp_batch_device(origins, dist, None); ev1.record(); torch.cuda.synchronize()
         ms_tree = ev0.elapsed_time(ev1)
         st = g.last_stats()
         g.sssp_batch(np.random.default_rng(0).permutation(V)[:64].astype(np.int32), want_dist=False)
         st = g.last_stats()
-        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "ms_trees_only": round(ms_tree, 2), "trees_per_s": round(tps),
+        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "pf": pf, "sm": cfg[5] if len(cfg) > 5 else 0, "carve": cfg[6] if len(cfg) > 6 else None, "gr": cfg[7] if len(cfg) > 7 else 0, "ms": round(ms, 2), "ms_trees_only": round(ms_tree, 2), "trees_per_s": round(tps),
                           "frac_hbm": round(tps * btree / 6547.2e9, 4), "relax_per_tree": st["relaxations"] / 64,
                           "rounds_per_tree": st["rounds"] / 64, "overflows": st["overflows"]}), flush=True)
     except Exception as ex:
