@@ -35,9 +35,9 @@ TICK_HORIZON = 7_200
 REROUTE_FREQ = 60          # BASELINE.json config 4 / north_star: reroute every 60 s
 WEIGHT_FREQ = 100          # run_traffic_simulation.py:83
 SHELTER_AFTER = 3 * 3600   # run_traffic_simulation.py:103
-# dram__bytes_read.sum + dram__bytes_write.sum of sssp_ell_kernel per tree, from the committed ncu --set full capture
+# dram__bytes_read.sum + dram__bytes_write.sum of sssp_warp_kernel per tree, from the committed ncu --set full capture
 # (profiles/); None until measured for the current kernel
-SSSP_TRAFFIC_PER_TREE = None
+SSSP_TRAFFIC_PER_TREE = 2_147_000   # profiles/r1c_sssp_warp_full_ncu.txt: (1.032 + 3.365) GB over 2048 trees
 
 
 def measured_peaks():
@@ -440,7 +440,7 @@ def main():
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": SSSP_TRAFFIC_PER_TREE * B if SSSP_TRAFFIC_PER_TREE else None,
-                             "kernel": "sssp_ell_kernel (+ sssp_parent_kernel, both inside kernel_ms)", "kernel_ms": kernel_ms,
+                             "kernel": "sssp_warp_kernel (+ sssp_parent_kernel, both inside kernel_ms)", "kernel_ms": kernel_ms,
                              "bytes_per_tree": bytes_per_tree, "peak_source": peak_src},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 

@@ -121,15 +121,17 @@ int sp_sync(Graph* graph);
  * current), shared-memory queue slots per queue of the bitmap kernel (0 = default). */
 int sp_set_tuning(Graph* graph, int threads, int ctas_per_sm, double delta_factor, int smem_queue);
 
-/* Kernel choice: 2 (default) = warp kernel (one tree per warp, four-byte hashed queue entries in a shared-memory
- * ring), 0 = ELL kernel (one tree per CTA, four-edge vertex records, tagged queue entries, queues of
+/* Kernel choice: 3 (default) = auto: the warp kernel for batches of at least six trees per SM, the ELL kernel
+ * below that (a lone tree finishes ~10x sooner on a whole CTA); 2 = warp kernel (one tree per warp, four-byte
+ * hashed queue entries in a shared-memory ring), 0 = ELL kernel (one tree per CTA, four-edge vertex records, tagged queue entries, queues of
  * queue_factor x V entries), 1 = bitmap kernel only (CSR, per-vertex shared-memory bitmaps; also the fallback
- * that reruns trees whose queues overflowed in the other two).  All three produce identical results.
+ * that reruns trees whose queues overflowed in the other two).  All produce identical results.
  * queue_factor <= 0 keeps the current value. */
 int sp_set_algo(Graph* graph, int algo, double queue_factor);
 
-/* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps), frontier vertices per step
- * = 8 x ilp (1, 2 or 4; 0 keeps), CTAs of four warps per SM (0 = as many as shared memory allows, < 0 keeps). */
+/* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps; default 1024), frontier
+ * vertices per step = 8 x ilp (1, 2 or 4; 0 keeps; default 4), CTAs of four warps per SM (0 = default 4, at most
+ * what shared memory allows; < 0 keeps). */
 int sp_set_warp_tuning(Graph* graph, int ring_cap, int ilp, int ctas_per_sm);
 
 /* Statistics of the last batch: [0] trees, [1] rounds, [2] relaxations, [3] bucket transitions,

@@ -82,9 +82,6 @@ struct TreeParams {
   int wfar_cap;
   int ring_cap;           // entries per shared-memory ring (power of two)
   int vbits;              // bits of a queue entry that hold the vertex id
-  int pf_ahead;           // ring entries the L2 prefetcher may run ahead of the consumer (0 = off)
-  int sm_sched;           // > 0: number of SMs; every SM works through its own contiguous range of trees
-  unsigned* wring;        // [warps in grid][2][ring_cap] rings in global memory (GR variant)
 };
 
 #define DIST_INF_BITS 0x7FEFFFFFFFFFFFFFull  // DBL_MAX, what the reference leaves in unreached slots
@@ -673,22 +670,16 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
 //    (a newer entry exists).  A hash collision only makes a stale entry look valid, and valid entries are
 //    relaxed with the distance read from memory, so collisions cost a duplicate pass, never a wrong result;
 //  * trees whose wavefront outgrows the ring are handed to the fallback kernel through fail_list.
-// Latency (queue -> dist/ELL loads -> L2 atomicMin) is hidden by 16-32 resident warps per SM, each on its own
-// tree.
+// Latency (queue -> dist/ELL loads -> L2 atomicMin) is hidden by 16 resident warps per SM, each on its own tree,
+// and by ILP independent groups of eight vertices per step.  What bounds the kernel is not HBM but the L1TEX
+// wavefront pipe: every relaxation is an 8-byte atomic on its own cache line (~2 wavefronts per relaxation all
+// told), see DESIGN.md section 2.
 // -------------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned dist_hash(u64 d) {
   return ((unsigned)d * 0x9E3779B1u) ^ ((unsigned)(d >> 32) * 0x85EBCA6Bu);
 }
 
-__device__ __forceinline__ unsigned ld_ring(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p));
-  return v;
-}
-
-// GR = rings in global memory (no shared memory at all: the whole 256 KB array of the SM works as L1, whose
-// lines bound the number of loads in flight); otherwise rings in dynamic shared memory.
-template <int ILP, bool GR>
+template <int ILP>
 __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
   extern __shared__ unsigned s_rings[];
   const unsigned FULL = 0xffffffffu;
@@ -702,29 +693,17 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
   const unsigned himask = ~((1u << (vbits + 3)) - 1u);
   const int fcap = p.wfar_cap;
   const int gwarp = blockIdx.x * (blockDim.x >> 5) + warp;
-  unsigned* ring_a = GR ? p.wring + (size_t)gwarp * 2 * C : s_rings + (size_t)warp * 2 * C;
+  unsigned* ring_a = s_rings + (size_t)warp * 2 * C;
   unsigned* far_base = p.wfar + (size_t)gwarp * 2 * fcap;
   const double delta = p.delta;
-  const int pf_ahead = p.pf_ahead;
 
   int st_steps = 0, st_relax = 0, st_trans = 0;
 
   for (;;) {
     int tree = 0;
-    if (p.sm_sched > 0) {
-      // trees of one SM are neighbours in the output arrays: its warps share translation pages
-      unsigned smid;
-      asm("mov.u32 %0, %%smid;" : "=r"(smid));
-      const int lo = (int)(((long long)p.n_trees * smid) / p.sm_sched);
-      const int hi = (int)(((long long)p.n_trees * (smid + 1)) / p.sm_sched);
-      if (lane == 0) tree = lo + atomicAdd(p.tree_counter + 1 + smid, 1);
-      tree = __shfl_sync(FULL, tree, 0);
-      if (tree >= hi || smid >= (unsigned)p.sm_sched) break;
-    } else {
-      if (lane == 0) tree = atomicAdd(p.tree_counter, 1);
-      tree = __shfl_sync(FULL, tree, 0);
-      if (tree >= p.n_trees) break;
-    }
+    if (lane == 0) tree = atomicAdd(p.tree_counter, 1);
+    tree = __shfl_sync(FULL, tree, 0);
+    if (tree >= p.n_trees) break;
 
     u64* dist = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)gwarp * V;
     const int src = p.origins[tree];
@@ -753,23 +732,6 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
     }
     __syncwarp();
     double T = delta, T2 = delta + delta;
-    // L2 prefetcher: a second ring cursor that runs up to pf_ahead entries in front of the consumer and touches
-    // the distance words of the neighbours those entries will relax.  Most of them were last written when the
-    // row was set to DBL_MAX and have left L2 since (thousands of rows are in flight); without this the first
-    // atomicMin on each sector pays a DRAM round trip in the middle of the warp's only dependency chain.
-    int pf_pos = 0;
-    int pfv[ILP];
-    unsigned pfe[ILP];
-    bool pfe_ok[ILP];
-#pragma unroll
-    for (int j = 0; j < ILP; ++j) { pfv[j] = -1; pfe[j] = 0u; pfe_ok[j] = false; }
-    // entries of the next step, loaded one step early: pre[j] belongs to ring position ch + 8 j + grp and is
-    // valid if that position is below pre_ct (the tail when it was loaded)
-    unsigned pre[ILP];
-    int pre_ct = 0;
-#pragma unroll
-    for (int j = 0; j < ILP; ++j) pre[j] = 0u;
-
     // Classifies one candidate per lane and appends it to the ring / next bucket / far pile.  Convergent.
     auto push = [&](bool imp, u64 ndb, unsigned ent) {
       const double nd = __longlong_as_double((long long)ndb);
@@ -816,10 +778,6 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
         }
         { unsigned* t = cur; cur = bkt; bkt = t; }
         ch = 0; ct = bt; bt = 0;
-        pf_pos = 0;
-        pre_ct = 0;
-#pragma unroll
-        for (int j = 0; j < ILP; ++j) { pfv[j] = -1; pfe_ok[j] = false; }
         T = T2; T2 = T + delta;
         ++st_trans;
         if (nf > 0) {
@@ -864,37 +822,9 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
       for (int j = 0; j < ILP; ++j) {
         const int idx = ch + j * 8 + grp;
         act[j] = idx < ct;
-        ent[j] = pre[j];
-        if (act[j] && idx >= pre_ct) ent[j] = GR ? ld_ring(&cur[idx & Cm]) : cur[idx & Cm];  // pushed by the last step
-        if (!act[j]) ent[j] = 0u;
-      }
-      if (pf_ahead > 0) {
-        // three stages, one per step: ring entry -> head of its ELL edge -> prefetch of that distance word
-#pragma unroll
-        for (int j = 0; j < ILP; ++j)
-          if (pfv[j] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(&dist[pfv[j]]));
-#pragma unroll
-        for (int j = 0; j < ILP; ++j) {
-          pfv[j] = -1;
-          if (pfe_ok[j]) pfv[j] = __ldg(&p.ell[(size_t)(pfe[j] & vmask) * 4 + slot].v);
-        }
-        pf_pos = max(pf_pos, ch + 8 * ILP);
-        const int pf_end = min(ct, ch + 8 * ILP + pf_ahead);
-#pragma unroll
-        for (int j = 0; j < ILP; ++j) {
-          const int idx = pf_pos + j * 8 + grp;
-          pfe_ok[j] = idx < pf_end;
-          if (pfe_ok[j]) pfe[j] = GR ? ld_ring(&cur[idx & Cm]) : cur[idx & Cm];
-        }
-        pf_pos = min(pf_end, pf_pos + 8 * ILP);
+        ent[j] = act[j] ? cur[idx & Cm] : 0u;
       }
       ch = min(ct, ch + 8 * ILP);
-      pre_ct = ct;
-#pragma unroll
-      for (int j = 0; j < ILP; ++j) {
-        const int idx = ch + j * 8 + grp;
-        if (idx < ct) pre[j] = GR ? ld_ring(&cur[idx & Cm]) : cur[idx & Cm];
-      }
       u64 dnow[ILP];
       int4 raw[ILP];
 #pragma unroll
@@ -1122,13 +1052,10 @@ struct SqGraph {
   cudaStream_t s_compute = nullptr, s_copy = nullptr;
   cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   int parent_format = 0;       // 0 = int32 vertex ids, 1 = one-byte in-edge codes (device batches only)
-  int algo = 2;                // 2 = warp kernel (default), 0 = ELL kernel, 1 = bitmap kernel (also everyone's fallback)
-  int warp_ring = 1024, warp_ilp = 2, warp_ctas_per_sm = 0, warp_prefetch = 64;
+  int algo = 3;                // 3 = auto (default), 2 = warp kernel, 0 = ELL kernel, 1 = bitmap kernel (also everyone's fallback)
+  int warp_ring = 1024, warp_ilp = 4, warp_ctas_per_sm = 0;
   unsigned* d_wfar = nullptr;
   int wfar_warps = 0, wfar_cap = 0;
-  int warp_global = 0;         // 1 = rings in global memory (no shared memory, largest L1)
-  unsigned* d_wring = nullptr;
-  int wring_warps = 0, wring_cap = 0;
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
 
   // tuning
@@ -1434,26 +1361,22 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   // ---- warp kernel (algo 2, default) or ELL kernel (algo 0) -------------------------------------------
   int vbits = 1;
   while ((1ll << vbits) < (long long)V) ++vbits;
-  const bool use_warp = g->algo == 2 && vbits <= 24;   // >= 5 hash bits per queue entry
+  // auto (3): a warp per tree wins on throughput once every SM has several trees per scheduler; below that the
+  // CTA-per-tree ELL kernel finishes a tree ~10x sooner (the router's 8 trees per weight refresh)
+  const bool want_warp = g->algo == 2 || (g->algo == 3 && n >= 6 * n_sm);
+  const bool use_warp = want_warp && vbits <= 24;   // >= 5 hash bits per queue entry
   const int threads = use_warp ? 128 : std::min(g->threads, 256);
   int per_sm, grid, rows;   // rows = trees in flight (scratch distance rows in timing-only mode)
   size_t warp_smem = 0;
-  bool use_gr = false;
   if (use_warp) {
     int C = 64;
     while (C < g->warp_ring) C <<= 1;
-    use_gr = g->warp_global != 0;
-    if (const char* e = getenv("SQ_WARP_GR")) use_gr = atoi(e) != 0;
-    if (use_gr) {
-      warp_smem = 0;
-      per_sm = g->warp_ctas_per_sm > 0 ? std::min(g->warp_ctas_per_sm, 16) : 8;
-    } else {
-      warp_smem = (size_t)4 * 2 * C * sizeof(unsigned);
-      if (warp_smem > 200 * 1024) return sq::set_error(SQ_ERR_ARG, "warp kernel: ring capacity %d does not fit shared memory", C);
-      per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (warp_smem + 1024));
-      per_sm = std::max(1, std::min(per_sm, 16));
-      if (g->warp_ctas_per_sm > 0) per_sm = std::min(per_sm, g->warp_ctas_per_sm);
-    }
+    warp_smem = (size_t)4 * 2 * C * sizeof(unsigned);
+    if (warp_smem > 200 * 1024) return sq::set_error(SQ_ERR_ARG, "warp kernel: ring capacity %d does not fit shared memory", C);
+    per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (warp_smem + 1024));
+    // 16 warps per SM measured best on B200 (tools/sssp_sweep.py, profiles/): beyond that the L1TEX wavefront
+    // pipe queues up and every step's two dependent memory waits grow faster than the warp count
+    per_sm = std::max(1, std::min(per_sm, g->warp_ctas_per_sm > 0 ? std::min(g->warp_ctas_per_sm, 16) : 4));
     {
       // all trees of a graph take about the same time, so a batch finishes in whole waves: spread the trees
       // evenly over the waves instead of leaving the last one mostly empty
@@ -1463,12 +1386,6 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
       grid = std::min((even + 3) / 4, n_sm * per_sm);
     }
     rows = grid * 4;
-    if (use_gr && (g->wring_warps < rows || g->wring_cap != C)) {
-      cudaFree(g->d_wring); g->d_wring = nullptr;
-      SQ_CUDA_TRY(cudaMalloc(&g->d_wring, sizeof(unsigned) * (size_t)rows * 2 * C));
-      g->wring_warps = rows; g->wring_cap = C;
-    }
-    p.wring = g->d_wring;
     const int fcap = std::min(std::max(V, 32), std::max(1024, V / 8));
     if (g->wfar_warps < rows || g->wfar_cap != fcap) {
       cudaFree(g->d_wfar); g->d_wfar = nullptr;
@@ -1476,11 +1393,6 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
       g->wfar_warps = rows; g->wfar_cap = fcap;
     }
     p.wfar = g->d_wfar; p.wfar_cap = fcap; p.ring_cap = C; p.vbits = vbits;
-    p.pf_ahead = g->warp_prefetch;
-    if (const char* e = getenv("SQ_WARP_PF")) p.pf_ahead = atoi(e);
-    p.sm_sched = 0;
-    if (const char* e = getenv("SQ_WARP_SMSCHED")) p.sm_sched = atoi(e) ? n_sm : 0;
-    if (grid % n_sm) p.sm_sched = 0;   // needs the same number of CTAs on every SM
   } else {
     per_sm = g->ctas_per_sm > 0 ? g->ctas_per_sm : std::min(9, 1024 / threads);
     per_sm = std::max(1, std::min(per_sm, std::min(9, 2048 / threads)));
@@ -1521,8 +1433,7 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   p.parent_out = nullptr;  // predecessors come from sssp_parent_kernel below
   if (use_warp) {
     typedef void (*WarpKernel)(const TreeParams);
-    static const WarpKernel kernels[6] = {sssp_warp_kernel<1, false>, sssp_warp_kernel<2, false>, sssp_warp_kernel<4, false>,
-                                          sssp_warp_kernel<1, true>, sssp_warp_kernel<2, true>, sssp_warp_kernel<4, true>};
+    static const WarpKernel kernels[3] = {sssp_warp_kernel<1>, sssp_warp_kernel<2>, sssp_warp_kernel<4>};
     static bool attr_set = false;
     if (!attr_set) {
       for (int i = 0; i < 3; ++i)
@@ -1530,20 +1441,18 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
       attr_set = true;
     }
     {
-      // shared memory carve-out = what the resident CTAs need, the rest stays L1 (its lines bound the loads in flight)
+      // shared-memory carve-out = what the resident CTAs need and no more: with the default (largest) carve-out
+      // L1 shrinks to ~28 KB and the kernel loses a quarter of its throughput (measured)
       int pct = (int)((100 * (size_t)per_sm * (warp_smem + 1024) + prop.sharedMemPerMultiprocessor - 1) / prop.sharedMemPerMultiprocessor);
-      if (use_gr) pct = 0;
-      if (const char* e = getenv("SQ_WARP_CARVE")) pct = atoi(e);
       pct = std::max(0, std::min(100, pct));
       static int last_pct = -1;
       if (pct != last_pct) {
-        for (int i = 0; i < 6; ++i)
+        for (int i = 0; i < 3; ++i)
           SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributePreferredSharedMemoryCarveout, pct));
         last_pct = pct;
       }
     }
-    const int ki = (g->warp_ilp == 1 ? 0 : g->warp_ilp == 4 ? 2 : 1) + (use_gr ? 3 : 0);
-    kernels[ki]<<<grid, 128, warp_smem, st>>>(p);
+    kernels[g->warp_ilp == 1 ? 0 : g->warp_ilp == 2 ? 1 : 2]<<<grid, 128, warp_smem, st>>>(p);
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
   } else {
@@ -1718,7 +1627,7 @@ void sp_free_graph(Graph* g) {
   g_free_device(g);
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
-  cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail); cudaFree(g->d_wfar); cudaFree(g->d_wring);
+  cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail); cudaFree(g->d_wfar);
   if (g->s_compute) {
     cudaStreamDestroy(g->s_compute); cudaStreamDestroy(g->s_copy);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(g->ev_done[i]); cudaEventDestroy(g->ev_copied[i]); }
@@ -1741,10 +1650,10 @@ int sp_set_tuning(Graph* g, int threads, int ctas_per_sm, double delta_factor, i
 
 int sp_set_algo(Graph* g, int algo, double queue_factor) {
   if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: null graph");
-  if (algo < 0 || algo > 2) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL), 1 (bitmap) or 2 (warp)");
+  if (algo < 0 || algo > 3) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL), 1 (bitmap), 2 (warp) or 3 (auto)");
   g->algo = algo;
   if (algo == 1 && g->threads < 128) g->threads = 256;
-  if (algo == 0 && g->threads > 256) g->threads = 128;
+  if ((algo == 0 || algo == 3) && g->threads > 256) g->threads = 256;
   if (queue_factor > 0.0) g->queue_factor = queue_factor;
   return SQ_OK;
 }

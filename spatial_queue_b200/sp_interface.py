@@ -127,8 +127,8 @@ class Graph:
                                              C.c_void_p(parent_dev.data_ptr()), sp, 1 if reverse else 0),
               "sp_decode_parents_device")
 
-    def set_algo(self, algo=0, queue_factor=0.0):
-        """2 = warp kernel (default), 0 = ELL kernel, 1 = bitmap kernel; see include/sq_sp.h."""
+    def set_algo(self, algo=3, queue_factor=0.0):
+        """3 = auto (default), 2 = warp kernel, 0 = ELL kernel, 1 = bitmap kernel; see include/sq_sp.h."""
         check(lib().sp_set_algo(self._h, int(algo), float(queue_factor)), "sp_set_algo")
 
     def set_warp_tuning(self, ring_cap=0, ilp=0, ctas_per_sm=-1):

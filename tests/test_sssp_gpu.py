@@ -131,6 +131,7 @@ def test_warp_kernel_ring_overflow_falls_back(spi):
     g.free()
     s, e, w = grid_graph(100, seed=3)
     g = spi.from_arrays(s, e, w)
+    g.set_algo(2)
     origins = rng.integers(0, 100 * 100, 64).astype(np.int32)
     d, p = g.sssp_batch(origins)
     assert g.last_stats()["overflows"] == 0
@@ -159,7 +160,7 @@ def test_weight_updates_reach_the_device(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
 
 
-@pytest.mark.parametrize("algo", [0, 1, 2])
+@pytest.mark.parametrize("algo", [0, 1, 2, 3])
 def test_grid_batch_and_device_api(spi, algo):
     import torch
     from oracle import sssp as osssp
@@ -168,7 +169,8 @@ def test_grid_batch_and_device_api(spi, algo):
     g = spi.from_arrays(s, e, w)
     g.set_algo(algo)
     og = osssp.OracleGraph(s, e, w)
-    origins = np.random.default_rng(2).permutation(n * n)[:300].astype(np.int32)
+    # 1000 origins: above the auto switch-over (six trees per SM), so algo 3 runs the warp kernel here
+    origins = np.random.default_rng(2).permutation(n * n)[:1000].astype(np.int32)
     o_dev = torch.from_numpy(origins).cuda()
     d_dev = torch.empty((len(origins), n * n), dtype=torch.float64, device="cuda")
     p_dev = torch.empty((len(origins), n * n), dtype=torch.int32, device="cuda")

@@ -13,12 +13,12 @@ timeout 600 python bench.py --steps 1 --warmup 3 --batch 2048 --no-tick --no-cpu
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/sssp_launches.csv \
   python bench.py --steps 1 --warmup 3 --batch 2048 --no-tick --no-cpu > $O/ncu_sssp_launches.log 2>&1
 TICKS=700 timeout 600 python tools/tick_prof.py > $O/tick_prof_plain.log 2>&1 && \
-TICKS=700 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 2400 -c 1200 --csv \
+TICKS=700 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 1200 -c 900 --csv \
   --log-file $O/tick_launches.csv python tools/tick_prof.py > $O/ncu_tick_launches.log 2>&1
 # full captures
 BATCH=2048 timeout 300 python tools/sssp_prof.py > $O/sssp_prof_plain.log 2>&1 && \
-BATCH=2048 timeout 900 ncu --set full --clock-control none --import-source on -k regex:sssp_ell_kernel -s 1 -c 1 \
-  -o $O/sssp_ell_full -f python tools/sssp_prof.py > $O/ncu_sssp_full.log 2>&1
+BATCH=2048 timeout 900 ncu --set full --clock-control none --import-source on -k regex:sssp_warp_kernel -s 1 -c 1 \
+  -o $O/sssp_warp_full -f python tools/sssp_prof.py > $O/ncu_sssp_full.log 2>&1
 TICKS=2600 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_node_phase -s 2500 -c 1 \
   -o $O/tick_node_full -f python tools/tick_prof.py > $O/ncu_tick_full.log 2>&1
 ls -la $O

@@ -7,7 +7,7 @@ from conftest import grid_graph
 from spatial_queue_b200 import sp_interface as spi
 n = int(os.environ.get("GRID", 224)); B = int(os.environ.get("BATCH", 2048))
 ALGO = int(os.environ.get("ALGO", 2))
-t, c, d, q = json.loads(os.environ.get("CFG", "[2,0,2.0,1024]" if ALGO == 2 else "[256,6,2.0,0]"))
+t, c, d, q = json.loads(os.environ.get("CFG", "[4,0,2.0,1024]" if ALGO == 2 else "[256,6,2.0,0]"))
 s, e, w = grid_graph(n, seed=1)
 g = spi.from_arrays(s, e, w); V = n * n
 g.set_algo(ALGO)

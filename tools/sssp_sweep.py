@@ -21,21 +21,13 @@ g.set_algo(ALGO)
 configs = json.loads(os.environ.get("CONFIGS", "null")) or (
     [(t, c, d, 0) for t in (32, 64, 128, 256) for c in (4, 8, 12, 16, 24, 32) for d in (1.0, 2.0, 4.0) if t * c <= 2048]
     if ALGO == 0 else
-    [(i, c, d, q) for i in (1, 2, 4) for q in (512, 1024) for c in (0, 4, 8) for d in (1.0, 2.0, 4.0)]
+    [(i, c, d, q) for i in (1, 2, 4) for q in (1024, 2048) for c in (3, 4, 5, 6) for d in (1.0, 2.0, 4.0)]
     if ALGO == 2 else
     [(t, c, d, q) for t in (128, 256, 512) for c in (0, 2, 4) for d in (1.0, 2.0, 4.0, 8.0) for q in (1024,)])
 for cfg in configs:
-    (t, c, d, q), pf = cfg[:4], (cfg[4] if len(cfg) > 4 else None)
+    t, c, d, q = cfg[:4]
     try:
-        if ALGO == 2:   # (ilp, CTAs of four warps per SM, delta factor, ring entries[, prefetch lookahead])
-            if pf is not None:
-                os.environ["SQ_WARP_PF"] = str(pf)
-            os.environ["SQ_WARP_SMSCHED"] = str(cfg[5]) if len(cfg) > 5 else "0"
-            os.environ["SQ_WARP_GR"] = str(cfg[7]) if len(cfg) > 7 else "0"
-            if len(cfg) > 6 and cfg[6] is not None:
-                os.environ["SQ_WARP_CARVE"] = str(cfg[6])
-            else:
-                os.environ.pop("SQ_WARP_CARVE", None)
+        if ALGO == 2:   # (ilp, CTAs of four warps per SM, delta factor, ring entries)
             g.set_warp_tuning(ring_cap=q, ilp=t, ctas_per_sm=c)
             g.set_tuning(delta_factor=d)
         else:
@@ -52,7 +44,7 @@ for cfg in configs:
         st = g.last_stats()
         g.sssp_batch(np.random.default_rng(0).permutation(V)[:64].astype(np.int32), want_dist=False)
         st = g.last_stats()
-        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "pf": pf, "sm": cfg[5] if len(cfg) > 5 else 0, "carve": cfg[6] if len(cfg) > 6 else None, "gr": cfg[7] if len(cfg) > 7 else 0, "ms": round(ms, 2), "ms_trees_only": round(ms_tree, 2), "trees_per_s": round(tps),
+        print(json.dumps({"algo": ALGO, "threads": t, "ctas": c, "delta": d, "q": q, "ms": round(ms, 2), "ms_trees_only": round(ms_tree, 2), "trees_per_s": round(tps),
                           "frac_hbm": round(tps * btree / 6547.2e9, 4), "relax_per_tree": st["relaxations"] / 64,
                           "rounds_per_tree": st["rounds"] / 64, "overflows": st["overflows"]}), flush=True)
     except Exception as ex:
