@@ -229,83 +229,195 @@ struct AdmitCtx {
   long long key;
 };
 
+// The in-side words of a node's out-links (remaining inflow / storage, run-list tail, length sum) are written by
+// this node's thread only.  A vehicle that moves used to pay eight dependent L2 round trips for them; a source
+// link can release 27 vehicles a second, one after the other.  They now live in thread-local memory (L1) for
+// the duration of the node: filled on the first vehicle that heads for the link, written back at the end.
+constexpr int MAXO = 8;     // out-links cached per node (local index < MAXO); further ones take the global path
+struct OutCache {
+  int link[MAXO];           // -1 = slot not filled
+  double in_c[MAXO], storage_c[MAXO];
+  unsigned tail[MAXO], room_end[MAXO], mask[MAXO];
+  long long len_in[MAXO], base[MAXO];
+  int ready[MAXO], end_node[MAXO];
+  bool dirty[MAXO];
+};
+
+__device__ __forceinline__ void outcache_fill(const TickState& s, OutCache& oc, int lc, int ol, int t) {
+  oc.link[lc] = ol;
+  oc.in_c[lc] = s.in_c[ol];
+  oc.storage_c[lc] = s.storage_c[ol];
+  oc.tail[lc] = s.tail[ol];
+  oc.mask[lc] = s.l_ring_mask[ol];
+  // last tail value the ring has room for, from the head as it is now (the link's end node may be advancing
+  // it concurrently, which only adds room)
+  oc.room_end[lc] = s.head[ol] + oc.mask[lc];
+  oc.len_in[lc] = s.len_in[ol];
+  oc.base[lc] = s.l_ring_base[ol];
+  oc.ready[lc] = ready_tick(t, s.l_fft[ol]);
+  oc.end_node[lc] = s.l_end[ol];
+  oc.dirty[lc] = false;
+}
+
+__device__ __forceinline__ void outcache_flush(const TickState& s, const OutCache& oc) {
+#pragma unroll
+  for (int lc = 0; lc < MAXO; ++lc) {
+    if (oc.link[lc] >= 0 && oc.dirty[lc]) {
+      const int ol = oc.link[lc];
+      s.in_c[ol] = oc.in_c[lc];
+      s.storage_c[ol] = oc.storage_c[lc];
+      s.tail[ol] = oc.tail[lc];
+      s.len_in[ol] = oc.len_in[lc];
+    }
+  }
+}
+
+// What the gather phase collected for one queued vehicle.
+struct Veh {
+  int agent, ol, recw, destin, lc, rlen, nxt;   // nxt: next link after ol for table routes (rlen < 0)
+};
+
+// One vehicle of the admit loop (run_node_model :304-386); returns true if it stays in the queue.
+__device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCache& oc, int il, bool secondary, u64 left,
+                                          const Veh& v, double& out_c) {
+  const int ol = v.ol, agent = v.agent;
+  const int vlen = (v.recw >> 8) & 0xff;
+  if (secondary && ol >= 0 && ((left >> v.lc) & 1ull)) return true;   // left turn from the opposite approach (:289-292)
+  if (c.node == v.destin) {                                           // arrival (:321-328)
+    out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
+    s.a_rec[agent].w = (v.recw & ~0xff) | SQ_ARRIVE;
+    s.a_arrive[agent] = c.t;
+    ++c.arrivals;
+    return false;
+  }
+  if (ol < 0) {
+    raise_error(s, 1, agent, c.node, il);                             // :312-314
+    return true;
+  }
+  const int lc = v.lc;
+  const bool cached = lc < MAXO;
+  if (cached && oc.link[lc] != ol) outcache_fill(s, oc, lc, ol, c.t);
+  const double storage = cached ? oc.storage_c[lc] : s.storage_c[ol];
+  if (storage < (double)vlen) return true;                            // spill-back (:333)
+  double in_c = cached ? oc.in_c[lc] : s.in_c[ol];
+  bool go;
+  if (out_c >= 1.0 && in_c >= 1.0) {                                  // :336
+    go = true;
+  } else {                                                            // :358-361
+    const double cc = out_c < in_c ? out_c : in_c;
+    const double w0 = 1.0 - cc;
+    const double total = w0 + cc;
+    const double u = rng_uniform(s.seed, c.t, c.key, 2 + c.toss);
+    ++c.toss;
+    go = !(u * total < w0);
+    if (!go) {                                                        // :380-386
+      if (out_c < in_c) { out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0; }
+      else {
+        if (!(out_c > in_c)) { out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0; }
+        in_c = in_c - 1.0; in_c = in_c > 0.0 ? in_c : 0.0;
+        if (cached) { oc.in_c[lc] = in_c; oc.dirty[lc] = true; } else s.in_c[ol] = in_c;
+      }
+      return true;
+    }
+  }
+  // :337-349 / :362-374
+  out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
+  in_c = in_c - 1.0; in_c = in_c > 0.0 ? in_c : 0.0;
+  if (cached) {
+    oc.in_c[lc] = in_c;
+    oc.storage_c[lc] = storage - (double)vlen;
+    const unsigned tl = oc.tail[lc];
+    if ((int)(tl - oc.room_end[lc]) > 0) raise_error(s, 3, agent, c.node, ol);
+    s.ring[oc.base[lc] + (tl & oc.mask[lc])] = make_int2(agent, oc.ready[lc]);   // append to the run list
+    oc.tail[lc] = tl + 1u;
+    oc.len_in[lc] += vlen;
+    oc.dirty[lc] = true;
+  } else {
+    s.in_c[ol] = in_c;
+    s.storage_c[ol] = storage - (double)vlen;
+    const unsigned tl = s.tail[ol];
+    const unsigned omask = s.l_ring_mask[ol];
+    if (tl - s.head[ol] > omask) raise_error(s, 3, agent, c.node, ol);
+    s.ring[s.l_ring_base[ol] + (tl & omask)] = make_int2(agent, ready_tick(c.t, s.l_fft[ol]));
+    s.tail[ol] = tl + 1u;
+    s.len_in[ol] += vlen;
+  }
+  // move_agent_to_next_link + find_next_link (:610-615, :598-608)
+  int nxt = v.nxt;
+  if (v.rlen >= 0) {
+    const int pos = s.a_route_pos[agent] + 1;
+    nxt = pos < v.rlen ? route_link_at(s, agent, pos) : -1;
+    s.a_route_pos[agent] = pos;
+  }
+  s.a_rec[agent] = make_int4(nxt, ol, c.t, v.recw);
+  return false;
+}
+
+constexpr int GATHER = 16;  // vehicles whose records are gathered together (independent loads in flight)
+
 // Admit loop of run_node_model (:304-386) over the first k queued vehicles of in-link `il`; `secondary`
-// applies the "no more left turns from the opposite approach" skip of :289-292.
-__device__ void admit_from_link(const TickState& s, AdmitCtx& c, int il, int k, bool secondary) {
+// applies the "no more left turns from the opposite approach" skip of :289-292.  Everything a vehicle's
+// decision reads from its own records (ring entry -> agent record, destination, route kind -> next link's
+// start / local index / end -> next-next link from the router table) is gathered for GATHER vehicles at a
+// time, level by level, so the sequential part runs on local data.  For the primary link the same records
+// answer non_conflict_vehicles' question "does any of them turn left" (:248-263): *turns_left is set from the
+// next links the vehicles had before anything moved.
+__device__ void admit_from_link(const TickState& s, AdmitCtx& c, OutCache& oc, int il, int k, bool secondary,
+                                bool* turns_left) {
   const long long base = s.l_ring_base[il];
   const unsigned mask = s.l_ring_mask[il];
   const unsigned h = s.head[il];
   const u64 left = s.l_left_mask[il];
   double out_c = s.out_c[il];
+  const long long len_out0 = s.len_out[il];
+  const int total_left0 = s.total_left[il];
   u64 stay_lo = 0, stay_hi = 0;  // bit i = vehicle i stays in the queue
   int moved = 0;
   long long moved_len = 0;
-  for (int i = 0; i < k; ++i) {
-    const int agent = s.ring[base + ((h + (unsigned)i) & mask)].x;
-    const int4 rec = s.a_rec[agent];
-    const int ol = rec.x;
-    const int vlen = (rec.w >> 8) & 0xff;
-    bool stay = true;
-    if (secondary && ol >= 0 && ((left >> s.l_out_local[ol]) & 1ull)) {
-      // left turn from the opposite approach: not a go-vehicle this second
-    } else if (c.node == s.a_destin[agent]) {                                     // arrival (:321-328)
-      stay = false;
-      out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
-      s.a_rec[agent] = make_int4(rec.x, rec.y, rec.z, (rec.w & ~0xff) | SQ_ARRIVE);
-      s.a_arrive[agent] = c.t;
-      ++c.arrivals;
-    } else if (ol < 0) {
-      raise_error(s, 1, agent, c.node, il);                                       // :312-314
-    } else if (s.storage_c[ol] < (double)vlen) {                                  // spill-back (:333)
-    } else {
-      double in_c = s.in_c[ol];
-      bool go;
-      if (out_c >= 1.0 && in_c >= 1.0) {                                          // :336
-        go = true;
-      } else {                                                                    // :358-361
-        const double cc = out_c < in_c ? out_c : in_c;
-        const double w0 = 1.0 - cc;
-        const double total = w0 + cc;
-        const double u = rng_uniform(s.seed, c.t, c.key, 2 + c.toss);
-        ++c.toss;
-        go = !(u * total < w0);
-        if (!go) {                                                                // :380-386
-          if (out_c < in_c) { out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0; }
-          else if (out_c > in_c) { in_c = in_c - 1.0; s.in_c[ol] = in_c > 0.0 ? in_c : 0.0; }
-          else {
-            out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
-            in_c = in_c - 1.0; s.in_c[ol] = in_c > 0.0 ? in_c : 0.0;
-          }
-        }
-      }
-      if (go) {                                                                   // :337-349 / :362-374
-        stay = false;
-        out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
-        in_c = in_c - 1.0; s.in_c[ol] = in_c > 0.0 ? in_c : 0.0;
-        s.storage_c[ol] = s.storage_c[ol] - (double)vlen;
-        // append to the out-link's run list
-        const unsigned tl = s.tail[ol];
-        const unsigned omask = s.l_ring_mask[ol];
-        if (tl - s.head[ol] > omask) raise_error(s, 3, agent, c.node, ol);
-        s.ring[s.l_ring_base[ol] + (tl & omask)] = make_int2(agent, ready_tick(c.t, s.l_fft[ol]));
-        s.tail[ol] = tl + 1u;
-        s.len_in[ol] += vlen;
-        // move_agent_to_next_link + find_next_link (:610-615, :598-608)
-        const int rlen = s.a_route_len[agent];
-        int nxt;
-        if (rlen < 0) {
-          nxt = s.next_tbl[tbl_index(s, s.a_epoch[agent], s.a_dslot[agent], s.l_end[ol])];
-        } else {
-          const int pos = s.a_route_pos[agent] + 1;
-          nxt = pos < rlen ? route_link_at(s, agent, pos) : -1;
-          s.a_route_pos[agent] = pos;
-        }
-        s.a_rec[agent] = make_int4(nxt, ol, c.t, rec.w);
+  bool any_left = false;
+  for (int i0 = 0; i0 < k; i0 += GATHER) {
+    Veh v[GATHER];
+    int st[GATHER], ep[GATHER], dl[GATHER], en[GATHER];
+    const int cnt = min(GATHER, k - i0);
+#pragma unroll
+    for (int j = 0; j < GATHER; ++j) v[j].agent = j < cnt ? s.ring[base + ((h + (unsigned)(i0 + j)) & mask)].x : -1;
+#pragma unroll
+    for (int j = 0; j < GATHER; ++j) {
+      v[j].ol = -1; v[j].recw = 0; v[j].destin = -1; v[j].rlen = 0; ep[j] = 0; dl[j] = 0;
+      if (v[j].agent >= 0) {
+        const int a = v[j].agent;
+        const int4 rec = s.a_rec[a];
+        v[j].ol = rec.x; v[j].recw = rec.w;
+        v[j].destin = s.a_destin[a];
+        v[j].rlen = s.a_route_len[a];
+        if (s.K > 0) { ep[j] = s.a_epoch[a]; dl[j] = s.a_dslot[a]; }
       }
     }
-    if (stay) { if (i < 64) stay_lo |= 1ull << i; else stay_hi |= 1ull << (i - 64); }
-    else { ++moved; moved_len += vlen; }
+#pragma unroll
+    for (int j = 0; j < GATHER; ++j) {
+      st[j] = c.node; v[j].lc = 0; en[j] = 0;
+      if (v[j].ol >= 0) { st[j] = s.l_start[v[j].ol]; v[j].lc = s.l_out_local[v[j].ol]; en[j] = s.l_end[v[j].ol]; }
+    }
+#pragma unroll
+    for (int j = 0; j < GATHER; ++j) {
+      v[j].nxt = -1;
+      if (v[j].ol >= 0 && v[j].rlen < 0) v[j].nxt = s.next_tbl[tbl_index(s, ep[j], dl[j], en[j])];
+    }
+    for (int j = 0; j < cnt; ++j) {
+      const int i = i0 + j;
+      bool stay;
+      if (v[j].ol >= 0 && st[j] != c.node) {
+        raise_error(s, 2, v[j].agent, c.node, v[j].ol);                              // KeyError of :257-262 / :291
+        stay = true;
+      } else {
+        if (v[j].ol >= 0 && ((left >> v[j].lc) & 1ull)) any_left = true;
+        stay = admit_one(s, c, oc, il, secondary, left, v[j], out_c);
+      }
+      if (stay) { if (i < 64) stay_lo |= 1ull << i; else stay_hi |= 1ull << (i - 64); }
+      else { ++moved; moved_len += (v[j].recw >> 8) & 0xff; }
+    }
   }
+  if (turns_left) *turns_left = any_left;
   if (moved) {
     // close the gaps: stayers slide to the back of the window [h, h+k), preserving order
     int j = k - 1;
@@ -317,8 +429,8 @@ __device__ void admit_from_link(const TickState& s, AdmitCtx& c, int il, int k, 
       }
     }
     s.head[il] = h + (unsigned)moved;
-    s.len_out[il] += moved_len;
-    s.total_left[il] += moved;
+    s.len_out[il] = len_out0 + moved_len;
+    s.total_left[il] = total_left0 + moved;
     c.moves += moved;
   }
   s.out_c[il] = out_c;
@@ -394,26 +506,19 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
       if (primary >= 0) {
         AdmitCtx c;
         c.t = t; c.node = n; c.toss = 0; c.moves = 0; c.arrivals = 0; c.key = key;
+        OutCache oc;
+#pragma unroll
+        for (int i = 0; i < MAXO; ++i) oc.link[i] = -1;
         const int lp = s.in_links[ib + primary];
         const int qlen_p = (int)(s.qtail[lp] - s.head[lp]);
         const int kp = min(s.l_lanes[lp], qlen_p);
-        // pass 1 over the primary vehicles: does any of them turn left? (:248-263)
+        // the primary link's vehicles go first (run_node_model walks the go-list in order); the same pass tells
+        // whether any of them turns left (:248-263), which is all the choice of the opposite approach needs.
+        // Nothing that choice reads (candidate set, angle table, the other links' queues) is touched by the
+        // primary admits, so doing them first gives the reference's result with one gather per vehicle.
         bool left_phase = false;
-        {
-          const long long base = s.l_ring_base[lp];
-          const unsigned mask = s.l_ring_mask[lp];
-          const unsigned h = s.head[lp];
-          const u64 left = s.l_left_mask[lp];
-          for (int i = 0; i < kp; ++i) {
-            const int agent = s.ring[base + ((h + (unsigned)i) & mask)].x;
-            const int ol = s.a_rec[agent].x;
-            if (ol >= 0) {
-              if (s.l_start[ol] != n) raise_error(s, 2, agent, n, ol);            // KeyError of :257-262
-              else if ((left >> s.l_out_local[ol]) & 1ull) left_phase = true;
-            }
-          }
-        }
-        // opposite approach (:267-293), chosen before anything moves
+        admit_from_link(s, c, oc, lp, kp, false, &left_phase);
+        // opposite approach (:267-293)
         int secondary = -1;
         const u64 rest = cand & ~(1ull << primary);
         const int rev = s.l_rev[lp];
@@ -450,18 +555,9 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
         if (secondary >= 0) {
           ls = s.in_links[ib + secondary];
           ks = min(s.l_lanes[ls], (int)(s.qtail[ls] - s.head[ls]));
-          // a turn outside the table is an error for the opposite approach too (:291)
-          const long long base = s.l_ring_base[ls];
-          const unsigned mask = s.l_ring_mask[ls];
-          const unsigned h = s.head[ls];
-          for (int i = 0; i < ks; ++i) {
-            const int agent = s.ring[base + ((h + (unsigned)i) & mask)].x;
-            const int ol = s.a_rec[agent].x;
-            if (ol >= 0 && s.l_start[ol] != n) raise_error(s, 2, agent, n, ol);
-          }
         }
-        admit_from_link(s, c, lp, kp, false);
-        if (ls >= 0) admit_from_link(s, c, ls, ks, true);
+        if (ls >= 0) admit_from_link(s, c, oc, ls, ks, true, nullptr);
+        outcache_flush(s, oc);
         if (c.moves) s.node_move[n] += c.moves;
         moves = c.moves; arrivals = c.arrivals;
       }
