@@ -287,7 +287,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=16384, help="SSSP origins per GPU per step")
+    ap.add_argument("--batch", type=int, default=18944, help="SSSP origins per GPU per step (default: 8 waves of 16 warps on 148 SMs)")
     ap.add_argument("--sssp-grid", type=int, default=SSSP_GRID)
     ap.add_argument("--tick-grid", type=int, default=TICK_GRID)
     ap.add_argument("--tick-agents", type=int, default=TICK_AGENTS)
@@ -298,6 +298,8 @@ def main():
     ap.add_argument("--no-tick", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--nccl-gather", action="store_true", help="N > 1: NCCL all-gather instead of copy-engine pushes")
+    ap.add_argument("--chunks", type=int, default=4, help="N > 1: pieces the batch is cut into (gather of one overlaps the trees of the next)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0))
@@ -330,8 +332,8 @@ def main():
     # N > 1: the int32 predecessor (next-hop) tables of every rank are all-gathered to every rank.  The batch is
     # cut into chunks; the gather of chunk k runs on a side stream while chunk k+1 is computed, and the tables
     # are double-buffered across steps so that a step never waits for the previous step's last gather.
-    n_chunks = 4 if (world > 1 and not args.no_gather) else 1
-    assert B % n_chunks == 0, "--batch must be a multiple of 4 for N > 1"
+    n_chunks = args.chunks if (world > 1 and not args.no_gather) else 1
+    assert B % n_chunks == 0, "--batch must be a multiple of --chunks for N > 1"
     cb = B // n_chunks
     # N > 1 ships the tables as one-byte in-edge codes (sp_set_parent_format 1): every rank holds the graph, so
     # the code of the predecessor edge is all the simulating GPU needs; N = 1 writes plain int32 vertex ids
@@ -342,9 +344,22 @@ def main():
     par_bufs = [torch.empty((B, V), dtype=pdt, device="cuda") for _ in range(2 if n_chunks > 1 else 1)]
     gathered = None
     comm_stream = None
+    peer = None
+    gather_kind = None
     if world > 1 and not args.no_gather:
-        gathered = [torch.empty((world * cb, V), dtype=pdt, device="cuda") for _ in range(n_chunks)]
-        comm_stream = torch.cuda.Stream()
+        if not args.nccl_gather:
+            try:
+                from spatial_queue_b200.shard import PeerTables
+                peer = PeerTables(n_chunks, cb, V, pdt)
+                gather_kind = "copy-engine pushes into symmetric memory"
+            except Exception as ex:       # no symmetric memory on this box: NCCL collective instead
+                if rank == 0:
+                    print(f"symmetric memory unavailable ({type(ex).__name__}: {ex}); using the NCCL all-gather", file=sys.stderr)
+                peer = None
+        if peer is None:
+            gathered = [torch.empty((world * cb, V), dtype=pdt, device="cuda") for _ in range(n_chunks)]
+            comm_stream = torch.cuda.Stream()
+            gather_kind = "NCCL all_gather_into_tensor"
         buf_free = [None, None]      # event: all gathers reading par_bufs[k] are done
     origins_dev = [torch.from_numpy(origins_for(rank, B, V, step=i)).cuda() for i in range(args.warmup + args.steps)]
     launches0 = _lib.lib().sp_kernel_launches()
@@ -352,27 +367,34 @@ def main():
     def step(i, ev=None):
         par_dev = par_bufs[i % len(par_bufs)]
         cur = torch.cuda.current_stream()
-        if gathered is not None and buf_free[i % 2] is not None:
+        gathering = gathered is not None or peer is not None
+        if gathering and buf_free[i % 2] is not None:
             cur.wait_event(buf_free[i % 2])
         if ev:
             ev[0].record()
         for c in range(n_chunks):
             sl = slice(c * cb, (c + 1) * cb if c + 1 < n_chunks else B)
             g.sssp_batch_device(origins_dev[i][sl], dist_dev[sl], par_dev[sl])
-            if gathered is not None:
+            if gathering:
                 done = torch.cuda.Event()
                 done.record(cur)
-                comm_stream.wait_event(done)
-                with torch.cuda.stream(comm_stream):
-                    dist.all_gather_into_tensor(gathered[c], par_dev[sl])
+                if peer is not None:
+                    peer.push(c, par_dev[sl], after=done)
+                else:
+                    comm_stream.wait_event(done)
+                    with torch.cuda.stream(comm_stream):
+                        dist.all_gather_into_tensor(gathered[c], par_dev[sl])
         if ev:
             ev[1].record()
-        if gathered is not None:
-            e = torch.cuda.Event()
-            e.record(comm_stream)
+        if gathering:
+            if peer is not None:
+                e = peer.fence()         # every rank's rows of this step are in every rank's table
+            else:
+                e = torch.cuda.Event()
+                e.record(comm_stream)
             buf_free[i % 2] = e
             if i == args.warmup + args.steps - 1 or i == args.warmup - 1:
-                cur.wait_event(e)      # the timed region ends when the last gather has landed
+                cur.wait_event(e)      # the timed region ends when the last rows have landed
 
     for i in range(args.warmup):
         step(i)
@@ -402,6 +424,21 @@ def main():
     launches = _lib.lib().sp_kernel_launches() - launches0 - 0
     value = world * B * args.steps / (ms_total / 1e3)
 
+    gather_ok = None
+    if gather_kind is not None:
+        # outside the timed region: every rank's block of the gathered table must be what that rank computed
+        last = par_bufs[(args.warmup + args.steps - 1) % len(par_bufs)]
+        mine = torch.stack([last[c * cb:(c + 1) * cb].to(torch.int64).sum() for c in range(n_chunks)])
+        sums = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(sums, mine)
+        ok = True
+        for c in range(n_chunks):
+            tbl = peer.table(c) if peer is not None else gathered[c]
+            for r in range(world):
+                ok = ok and int(tbl[r * cb:(r + 1) * cb].to(torch.int64).sum().item()) == int(sums[r][c].item())
+        flag = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        gather_ok = bool(flag.item())
     if compact:
         g.set_parent_format(0)
     # ---- e2e through the host-buffer C ABI (origins in host memory -> dist + parent in host memory) -------------
@@ -434,8 +471,9 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid "
                                        f"({E} links, {V} nodes), {B} origins per GPU per step, full trees + canonical "
-                                       f"predecessors" + (f", one-byte next-hop tables all-gathered in {n_chunks} chunks overlapped with "
-                                                          f"the next chunk's trees" if gathered is not None else ""),
+                                       f"predecessors" + (f", one-byte next-hop tables gathered on every rank in {n_chunks} chunks ({gather_kind}) "
+                                                          f"overlapped with the next chunk's trees" if gather_kind else ""),
+                           "gather_verified": gather_ok,
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
