@@ -1433,10 +1433,10 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   p.parent_out = nullptr;  // predecessors come from sssp_parent_kernel below
   if (use_warp) {
     typedef void (*WarpKernel)(const TreeParams);
-    static const WarpKernel kernels[3] = {sssp_warp_kernel<1>, sssp_warp_kernel<2>, sssp_warp_kernel<4>};
+    static const WarpKernel kernels[4] = {sssp_warp_kernel<1>, sssp_warp_kernel<2>, sssp_warp_kernel<4>, sssp_warp_kernel<8>};
     static bool attr_set = false;
     if (!attr_set) {
-      for (int i = 0; i < 3; ++i)
+      for (int i = 0; i < 4; ++i)
         SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       attr_set = true;
     }
@@ -1447,12 +1447,12 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
       pct = std::max(0, std::min(100, pct));
       static int last_pct = -1;
       if (pct != last_pct) {
-        for (int i = 0; i < 3; ++i)
+        for (int i = 0; i < 4; ++i)
           SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributePreferredSharedMemoryCarveout, pct));
         last_pct = pct;
       }
     }
-    kernels[g->warp_ilp == 1 ? 0 : g->warp_ilp == 2 ? 1 : 2]<<<grid, 128, warp_smem, st>>>(p);
+    kernels[g->warp_ilp == 1 ? 0 : g->warp_ilp == 2 ? 1 : g->warp_ilp == 8 ? 3 : 2]<<<grid, 128, warp_smem, st>>>(p);
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
   } else {
@@ -1660,7 +1660,7 @@ int sp_set_algo(Graph* g, int algo, double queue_factor) {
 
 int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
   if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_warp_tuning: null graph");
-  if (ilp != 0 && ilp != 1 && ilp != 2 && ilp != 4) return sq::set_error(SQ_ERR_ARG, "sp_set_warp_tuning: ilp must be 1, 2 or 4");
+  if (ilp != 0 && ilp != 1 && ilp != 2 && ilp != 4 && ilp != 8) return sq::set_error(SQ_ERR_ARG, "sp_set_warp_tuning: ilp must be 1, 2, 4 or 8");
   if (ring_cap > 0) g->warp_ring = ring_cap;
   if (ilp > 0) g->warp_ilp = ilp;
   if (ctas_per_sm >= 0) g->warp_ctas_per_sm = ctas_per_sm;
