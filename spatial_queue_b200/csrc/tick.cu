@@ -47,6 +47,14 @@ typedef unsigned long long u64;
 // =================================================================================================
 // Device state
 // =================================================================================================
+struct __align__(32) AgentRec {
+  int4 rec;        // x next_link, y cur_link, z enter_time, w status | vlen << 8
+  int destin;      // destination node
+  int route_len;   // >= 0: explicit route (link sequence in a pool); < 0: follows the router's next-link tables
+  int epoch;       // table epoch slot the route follows (route_len < 0)
+  int dslot;       // destination slot of the router
+};
+
 struct TickState {
   int N, L, A;
   u64 seed;
@@ -56,6 +64,7 @@ struct TickState {
   const double* l_cap_s; const double* l_storage; const double* l_fft;
   const long long* l_ring_base; const unsigned* l_ring_mask; const int* l_vcount;
   const unsigned char* l_in_local; const unsigned char* l_out_local; const u64* l_left_mask;
+  const int4* l_hop;         // {start node, end node, local index among the start node's out-links, 0}: one load per next link
   // links, dynamic
   unsigned* head; unsigned* qtail; unsigned* tail;
   double* out_c; double* in_c; double* storage_c;
@@ -68,15 +77,12 @@ struct TickState {
   const long long* turn_ptr; const double* turn;
   long long* node_move;
   // agents
-  int4* a_rec;  // x next_link, y cur_link, z enter_time, w status | vlen << 8
-  const int* a_destin;
-  long long* a_route_off; int* a_route_len; int* a_route_pos; int* a_arrive;
+  AgentRec* ag;  // one 32-byte sector per agent: everything the node phase gathers per queued vehicle
+  long long* a_route_off; int* a_route_pos; int* a_arrive;
   const int* route_pool;
   // device router (sq_attach_router): per-destination next-link tables, K epochs of them
   int D, K, freq;
   const int* n_vertex;       // [N] graph vertex of node n
-  const int* a_dslot;        // [A] destination slot
-  int* a_epoch;              // [A] table epoch slot the agent's route follows (agents with a_route_len < 0)
   int* next_tbl;             // [K][D][N] link to take at node n towards destination d, -1 at d / unreachable
   double* dist_tbl;          // [K][D][N] distance to d
   int* cur_epoch;            // slot of the newest tables
@@ -166,10 +172,10 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
       while (h != tl) {
         const int2 e = s.ring[base + (h & mask)];
         if (e.y != INT_MAX && (long long)t - e.y + dwell <= s.shelter_after) break;   // cannot be old enough yet
-        int4 rec = s.a_rec[e.x];
+        int4 rec = s.ag[e.x].rec;
         if (t - rec.z <= s.shelter_after) break;
         rec.w = (rec.w & ~0xff) | SQ_SHELTER_A1;
-        s.a_rec[e.x] = rec;
+        s.ag[e.x].rec = rec;
         s.a_arrive[e.x] = t;
         lo += (rec.w >> 8) & 0xff;
         ++h; ++sheltered;
@@ -187,10 +193,10 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
       while (tl < cnt) {
         const int2 e = s.ring[base + tl];
         if (e.y - 1 > t) break;
-        int4 rec = s.a_rec[e.x];
+        int4 rec = s.ag[e.x].rec;
         rec.z = e.y - 1;                                  // current_link_enter_time = departure tick
         rec.w = (rec.w & ~0xff) | SQ_ENROUTE;
-        s.a_rec[e.x] = rec;
+        s.ag[e.x].rec = rec;
         li += (rec.w >> 8) & 0xff;
         ++tl; ++loaded;
       }
@@ -285,7 +291,7 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
   if (secondary && ol >= 0 && ((left >> v.lc) & 1ull)) return true;   // left turn from the opposite approach (:289-292)
   if (c.node == v.destin) {                                           // arrival (:321-328)
     out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0;
-    s.a_rec[agent].w = (v.recw & ~0xff) | SQ_ARRIVE;
+    s.ag[agent].rec.w = (v.recw & ~0xff) | SQ_ARRIVE;
     s.a_arrive[agent] = c.t;
     ++c.arrivals;
     return false;
@@ -349,7 +355,7 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
     nxt = pos < v.rlen ? route_link_at(s, agent, pos) : -1;
     s.a_route_pos[agent] = pos;
   }
-  s.a_rec[agent] = make_int4(nxt, ol, c.t, v.recw);
+  s.ag[agent].rec = make_int4(nxt, ol, c.t, v.recw);
   return false;
 }
 
@@ -386,17 +392,17 @@ __device__ void admit_from_link(const TickState& s, AdmitCtx& c, OutCache& oc, i
       v[j].ol = -1; v[j].recw = 0; v[j].destin = -1; v[j].rlen = 0; ep[j] = 0; dl[j] = 0;
       if (v[j].agent >= 0) {
         const int a = v[j].agent;
-        const int4 rec = s.a_rec[a];
+        const int4* q = reinterpret_cast<const int4*>(&s.ag[a]);
+        const int4 rec = q[0], aux = q[1];
         v[j].ol = rec.x; v[j].recw = rec.w;
-        v[j].destin = s.a_destin[a];
-        v[j].rlen = s.a_route_len[a];
-        if (s.K > 0) { ep[j] = s.a_epoch[a]; dl[j] = s.a_dslot[a]; }
+        v[j].destin = aux.x; v[j].rlen = aux.y;
+        ep[j] = aux.z; dl[j] = aux.w;
       }
     }
 #pragma unroll
     for (int j = 0; j < GATHER; ++j) {
       st[j] = c.node; v[j].lc = 0; en[j] = 0;
-      if (v[j].ol >= 0) { st[j] = s.l_start[v[j].ol]; v[j].lc = s.l_out_local[v[j].ol]; en[j] = s.l_end[v[j].ol]; }
+      if (v[j].ol >= 0) { const int4 hop = s.l_hop[v[j].ol]; st[j] = hop.x; en[j] = hop.y; v[j].lc = hop.z; }
     }
 #pragma unroll
     for (int j = 0; j < GATHER; ++j) {
@@ -586,14 +592,14 @@ __global__ void k_set_routes(const TickState s, int n, const int* agent_idx, con
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int a = agent_idx[i];
-  int4 rec = s.a_rec[a];
+  int4 rec = s.ag[a].rec;
   const int st = rec.w & 0xff;
   if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
   s.a_route_off[a] = new_off[i];
-  s.a_route_len[a] = new_len[i];
+  s.ag[a].route_len = new_len[i];
   s.a_route_pos[a] = 0;
   rec.x = new_len[i] > 0 ? s.route_pool[new_off[i]] : -1;   // host-supplied routes always live in route_pool
-  s.a_rec[a] = rec;
+  s.ag[a].rec = rec;
 }
 
 // ---- device router ------------------------------------------------------------------------------------------
@@ -650,17 +656,17 @@ __global__ void __launch_bounds__(128) k_reroute(const TickState s, int all) {
     if (k >= s.bucket_ptr[b + 1]) return;
     a = s.bucket_agents[k];
   }
-  int4 rec = s.a_rec[a];
+  int4 rec = s.ag[a].rec;
   const int st = rec.w & 0xff;
   if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
   const int node = s.l_end[rec.y];
   const int e = *s.cur_epoch;
-  const size_t idx = tbl_index(s, e, s.a_dslot[a], node);
+  const size_t idx = tbl_index(s, e, s.ag[a].dslot, node);
   if (s.dist_tbl[idx] > 1e8) return;
-  s.a_epoch[a] = e;
-  s.a_route_len[a] = -1;
+  s.ag[a].epoch = e;
+  s.ag[a].route_len = -1;
   rec.x = s.next_tbl[idx];
-  s.a_rec[a] = rec;
+  s.ag[a].rec = rec;
 }
 
 // Before table slot `slot` is overwritten: agents that still follow it (their reroutes kept failing) get
@@ -668,11 +674,11 @@ __global__ void __launch_bounds__(128) k_reroute(const TickState s, int all) {
 __global__ void __launch_bounds__(128) k_evacuate(const TickState s, int slot) {
   const int a = blockIdx.x * 128 + threadIdx.x;
   if (a >= s.A) return;
-  if (s.a_route_len[a] >= 0 || s.a_epoch[a] != slot) return;
-  const int4 rec = s.a_rec[a];
+  if (s.ag[a].route_len >= 0 || s.ag[a].epoch != slot) return;
+  const int4 rec = s.ag[a].rec;
   const int st = rec.w & 0xff;
   if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
-  const int d = s.a_dslot[a];
+  const int d = s.ag[a].dslot;
   int len = 0;
   for (int l = rec.x; l >= 0 && len <= s.L; l = s.next_tbl[tbl_index(s, slot, d, s.l_end[l])]) ++len;
   const long long off = (long long)atomicAdd((u64*)s.mat_used, (u64)len);
@@ -680,7 +686,7 @@ __global__ void __launch_bounds__(128) k_evacuate(const TickState s, int slot) {
   int k = 0;
   for (int l = rec.x; l >= 0 && k < len; l = s.next_tbl[tbl_index(s, slot, d, s.l_end[l])]) s.mat_pool[off + k++] = l;
   s.a_route_off[a] = -(off + 1);
-  s.a_route_len[a] = len;
+  s.ag[a].route_len = len;
   s.a_route_pos[a] = 0;
 }
 
@@ -838,7 +844,7 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
   UP(n_type, d->node_type, N); UP(in_ptr, d->node_in_ptr, N + 1); UP(in_links, d->node_in_links, d->node_in_ptr[N]);
   UP(in_phase, d->node_in_phase, d->node_in_ptr[N]); UP(in_prio, d->node_in_prio, d->node_in_ptr[N]);
   UP(out_ptr, d->node_out_ptr, N + 1);
-  UP(turn, d->turn_angle, d->node_turn_ptr[N]); UP(a_destin, d->agent_destin, A);
+  UP(turn, d->turn_angle, d->node_turn_ptr[N]);
 #undef UP
   {
     std::vector<long long> key(d->node_key, d->node_key + N), tp(d->node_turn_ptr, d->node_turn_ptr + N + 1);
@@ -855,6 +861,11 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
   if ((rc = dev_upload(sim, &s.l_vcount, vcount))) return rc;
   if ((rc = dev_upload(sim, &s.l_in_local, in_local))) return rc;
   if ((rc = dev_upload(sim, &s.l_out_local, out_local))) return rc;
+  {
+    std::vector<int4> hop((size_t)L);
+    for (int l = 0; l < L; ++l) hop[l] = make_int4(d->link_start_node[l], d->link_end_node[l], (int)out_local[l], 0);
+    if ((rc = dev_upload(sim, &s.l_hop, hop))) return rc;
+  }
   if ((rc = dev_upload(sim, &s.l_left_mask, left_mask))) return rc;
   if ((rc = dev_upload_rw(sim, &s.ring, ring))) return rc;
   {
@@ -886,26 +897,26 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     if ((rc = dev_upload_ptr(sim, &s.l_maxmph, d->link_maxmph, (size_t)L))) return rc;
     s.shelter_after = 0;
     s.D = 0; s.K = 0; s.freq = 1;
-    s.n_vertex = nullptr; s.a_dslot = nullptr; s.a_epoch = nullptr; s.next_tbl = nullptr; s.dist_tbl = nullptr;
+    s.n_vertex = nullptr; s.next_tbl = nullptr; s.dist_tbl = nullptr;
     s.cur_epoch = nullptr; s.bucket_ptr = nullptr; s.bucket_agents = nullptr; s.l_edge = nullptr; s.w_edge = nullptr;
     s.mat_pool = nullptr; s.mat_used = nullptr; s.mat_cap = 0;
   }
   // agents
   {
-    std::vector<int4> rec((size_t)A);
+    std::vector<AgentRec> rec((size_t)A);
     std::vector<long long> off((size_t)A);
-    std::vector<int> len((size_t)A), pos((size_t)A, 0), arr((size_t)A, -1);
+    std::vector<int> pos((size_t)A, 0), arr((size_t)A, -1);
     for (int a = 0; a < A; ++a) {
       const long long b = d->route_ptr[a], e = d->route_ptr[a + 1];
-      off[a] = b; len[a] = (int)(e - b);
+      off[a] = b;
       const int vl = virt_of_node[d->agent_origin[a]];
-      rec[a] = make_int4(e > b ? d->route_links[b] : -1, vl, -1, (int)d->agent_status[a] | (d->agent_vlen[a] << 8));
+      rec[a].rec = make_int4(e > b ? d->route_links[b] : -1, vl, -1, (int)d->agent_status[a] | (d->agent_vlen[a] << 8));
+      rec[a].destin = d->agent_destin[a]; rec[a].route_len = (int)(e - b); rec[a].epoch = 0; rec[a].dslot = 0;
       if (d->agent_status[a] == SQ_UNLOADED && e == b && !(d->reserved0 & 1))
         return sq::set_error(SQ_ERR_ARG, "agent %d is to be loaded but has an empty route (queue_class.py:595 raises KeyError)", a);
     }
-    if ((rc = dev_upload_rw(sim, &s.a_rec, rec))) return rc;
+    if ((rc = dev_upload_rw(sim, &s.ag, rec))) return rc;
     if ((rc = dev_upload_rw(sim, &s.a_route_off, off))) return rc;
-    if ((rc = dev_upload_rw(sim, &s.a_route_len, len))) return rc;
     if ((rc = dev_upload_rw(sim, &s.a_route_pos, pos))) return rc;
     if ((rc = dev_upload_rw(sim, &s.a_arrive, arr))) return rc;
     const long long used = d->route_ptr[A];
@@ -1167,11 +1178,14 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* r) {
   const int K = r->reroute_freq / r->weight_freq + 3;
   s.D = D; s.K = K; s.freq = r->reroute_freq;
   if ((rc = dev_upload_ptr(sim, &s.n_vertex, r->node_vertex, (size_t)N))) return rc;
-  if ((rc = dev_upload_ptr(sim, &s.a_dslot, r->agent_dslot, (size_t)A))) return rc;
+  {  // destination slots go into the agents' records (one-time round trip)
+    std::vector<AgentRec> rec((size_t)A);
+    if (A > 0) SQ_CUDA_TRY(cudaMemcpy(rec.data(), s.ag, sizeof(AgentRec) * (size_t)A, cudaMemcpyDeviceToHost));
+    for (int a = 0; a < A; ++a) { rec[a].dslot = r->agent_dslot[a]; rec[a].epoch = 0; }
+    if (A > 0) SQ_CUDA_TRY(cudaMemcpy(s.ag, rec.data(), sizeof(AgentRec) * (size_t)A, cudaMemcpyHostToDevice));
+  }
   if ((rc = dev_upload_ptr(sim, &s.l_edge, r->link_edge, (size_t)L))) return rc;
   {
-    std::vector<int> z((size_t)std::max(A, 1), 0);
-    if ((rc = dev_upload_rw(sim, &s.a_epoch, z))) return rc;
     std::vector<int> one(1, 0);
     if ((rc = dev_upload_rw(sim, &s.cur_epoch, one))) return rc;
     std::vector<long long> zl(1, 0);
@@ -1324,17 +1338,18 @@ int sq_get_link_vehicles(SqSim* sim, int64_t* ptr, int32_t* agents) {
 int sq_get_agent_state(SqSim* sim, uint8_t* status, int32_t* cur, int32_t* next, int32_t* enter, int32_t* arrive) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "null sim");
   const size_t A = (size_t)sim->A;
-  std::vector<int4> rec;
+  std::vector<AgentRec> rec;
   int rc;
-  if ((rc = fetch(sim, rec, (const int4*)sim->st.a_rec, A))) return rc;
+  if ((rc = fetch(sim, rec, (const AgentRec*)sim->st.ag, A))) return rc;
   if (arrive) SQ_CUDA_TRY(cudaMemcpyAsync(arrive, sim->st.a_arrive, A * sizeof(int), cudaMemcpyDeviceToHost, sim->stream));
   if ((rc = sq_sync(sim))) return rc;
   for (size_t a = 0; a < A; ++a) {
-    if (status) status[a] = (uint8_t)(rec[a].w & 0xff);
-    if (cur) cur[a] = rec[a].y;
-    if (next) next[a] = rec[a].x;
-    if (enter) enter[a] = rec[a].z;
-    if (arrive && (rec[a].w & 0xff) != SQ_ARRIVE) arrive[a] = -1;   // the slot also holds shelter ticks
+    const int4 r = rec[a].rec;
+    if (status) status[a] = (uint8_t)(r.w & 0xff);
+    if (cur) cur[a] = r.y;
+    if (next) next[a] = r.x;
+    if (enter) enter[a] = r.z;
+    if (arrive && (r.w & 0xff) != SQ_ARRIVE) arrive[a] = -1;   // the slot also holds shelter ticks
   }
   return SQ_OK;
 }
