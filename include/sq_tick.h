@@ -93,6 +93,14 @@ int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t
 /* Link status changes (model/dta_meso_butte.py:77-81, 89-101, 113): closed != 0 zeroes the inflow
  * capacity in the link model (queue_class.py:455). */
 int sq_set_link_closed(SqSim* sim, int32_t n, const int32_t* link_idx, const uint8_t* closed);
+/* Closure schedule as a device event table (the timed closures and reopenings of
+ * model/dta_meso_butte.py:88-115): event i sets link_idx[i] closed (closed[i] != 0) or open at the start of tick
+ * tick[i], before that tick's link phase -- the same moment a driver would call Link.close_link_to_newcomers /
+ * open_link_to_newcomers and set Link.status before its link_model(t).  With a router attached the routing graph
+ * gets 1e8 / the free-flow time on the link's edge (queue_class.py:467-474) and the next-link tables are rebuilt
+ * at once, all on the device: sq_run keeps replaying CUDA graphs between events.  Replaces any earlier schedule;
+ * events earlier than the next tick run are applied at that tick. */
+int sq_set_closure_schedule(SqSim* sim, int32_t n, const int32_t* tick, const int32_t* link_idx, const uint8_t* closed);
 
 /* ---- device-side rerouting (Agent.get_path for every agent, queue_class.py:501-522; the drivers' reroute
  * trigger and edge-weight refresh, run_traffic_simulation.py:81-84, 107-109) --------------------------------

@@ -77,6 +77,7 @@ def _declare(L):
     L.sq_set_shelter_after.restype = ci; L.sq_set_shelter_after.argtypes = [vp, i32]
     L.sq_get_shelter_state.restype = ci; L.sq_get_shelter_state.argtypes = [vp, vp, vp]
     L.sq_set_link_closed.restype = ci; L.sq_set_link_closed.argtypes = [vp, i32, vp, vp]
+    L.sq_set_closure_schedule.restype = ci; L.sq_set_closure_schedule.argtypes = [vp, i32, vp, vp, vp]
     L.sq_get_link_state.restype = ci; L.sq_get_link_state.argtypes = [vp] * 7
     L.sq_get_link_vehicles.restype = ci; L.sq_get_link_vehicles.argtypes = [vp, vp, vp]
     L.sq_get_agent_state.restype = ci; L.sq_get_agent_state.argtypes = [vp] * 6

@@ -690,6 +690,24 @@ __global__ void __launch_bounds__(128) k_evacuate(const TickState s, int slot) {
   s.a_route_pos[a] = 0;
 }
 
+// Closure schedule (row N3): events [lo, hi) of the device event table take effect.  A closed link gets no
+// inflow from the next link phase on (queue_class.py:455) and weighs 1e8 for routing; a reopened one weighs its
+// free-flow time again (close_link_to_newcomers / open_link_to_newcomers, queue_class.py:467-474).  w_edge was
+// filled with NaN ("keep") by k_fill_nan, so sp_set_weights_device touches only these edges.
+__global__ void k_fill_nan(double* w, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) w[i] = __longlong_as_double(0x7ff8000000000000ll);
+}
+__global__ void k_apply_events(const TickState s, const int* __restrict__ ev_link, const unsigned char* __restrict__ ev_closed,
+                               int lo, int hi, int route) {
+  const int i = lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= hi) return;
+  const int l = ev_link[i];
+  const unsigned char c = ev_closed[i];
+  s.l_closed[l] = c;
+  if (route && s.l_edge[l] >= 0) s.w_edge[s.l_edge[l]] = c ? 1.0e8 : s.l_fft[l];
+}
+
 __global__ void k_set_closed(const TickState s, int n, const int* link_idx, const unsigned char* closed) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) s.l_closed[link_idx[i]] = closed[i];
@@ -712,6 +730,12 @@ struct SqSim {
   std::vector<long long> h_ring_base;
   std::vector<unsigned> h_ring_mask;
   std::vector<unsigned char> h_virtual, h_closed;
+  // closure schedule: host copy (sorted by tick) + device event table
+  std::vector<int> ev_tick, ev_link;
+  std::vector<unsigned char> ev_closed;
+  size_t ev_cursor = 0;
+  int* d_ev_link = nullptr;
+  unsigned char* d_ev_closed = nullptr;
   std::vector<double> h_capacity, h_maxmph, h_fft;
   // route pool management
   int* d_pool = nullptr;
@@ -1028,6 +1052,44 @@ static int router_catch_up(SqSim* sim, int t) {
   return router_refresh(sim, t, false);
 }
 
+// Events of the closure schedule due at or before tick t, applied before that tick's link phase; with a router
+// attached the routing graph and the next-link tables follow at once (the reference's next get_path sees the edit).
+static int apply_closure_events(SqSim* sim, int t) {
+  if (sim->ev_cursor >= sim->ev_tick.size() || sim->ev_tick[sim->ev_cursor] > t) return SQ_OK;
+  const int lo = (int)sim->ev_cursor;
+  int hi = lo;
+  while (hi < (int)sim->ev_tick.size() && sim->ev_tick[hi] <= t) ++hi;
+  sim->ev_cursor = (size_t)hi;
+  TickState& s = sim->st;
+  cudaStream_t st = sim->stream;
+  const int route = sim->router_graph ? 1 : 0;
+  if (route) {
+    k_fill_nan<<<(sim->graph_E + 255) / 256, 256, 0, st>>>(s.w_edge, sim->graph_E);
+    sq::count_launch(); sim->launches += 1;
+  }
+  // one launch per distinct tick so that a link closed and reopened at two past ticks ends in its last state
+  for (int a = lo; a < hi;) {
+    int b = a;
+    while (b < hi && sim->ev_tick[b] == sim->ev_tick[a]) ++b;
+    k_apply_events<<<(b - a + 127) / 128, 128, 0, st>>>(s, sim->d_ev_link, sim->d_ev_closed, a, b, route);
+    sq::count_launch(); sim->launches += 1;
+    a = b;
+  }
+  SQ_CUDA_TRY(cudaGetLastError());
+  for (int i = lo; i < hi; ++i) sim->h_closed[sim->ev_link[i]] = sim->ev_closed[i];
+  if (route) {
+    if (int rc = sp_set_weights_device(sim->router_graph, s.w_edge, sim->graph_E, (void*)st))
+      return sq::set_error(rc, "closure schedule: %s", sp_last_error());
+    if (!(sim->wfreq > 0 && t % sim->wfreq == 0 && sim->last_refresh_t != t))   // else the regular refresh follows
+      if (int rc = router_refresh(sim, t, false)) return rc;
+  }
+  return SQ_OK;
+}
+
+static int next_event_tick(const SqSim* sim) {
+  return sim->ev_cursor < sim->ev_tick.size() ? sim->ev_tick[sim->ev_cursor] : INT_MAX;
+}
+
 static int kernels_per_tick(const SqSim* sim) { return (sim->router_graph && sim->max_bucket > 0) ? 3 : 2; }
 
 extern "C" {
@@ -1044,6 +1106,7 @@ void sq_destroy(SqSim* sim) {
   if (sim->graph) cudaGraphExecDestroy(sim->graph);
   for (void* p : sim->allocs) cudaFree(p);
   cudaFree(sim->d_pool);
+  cudaFree(sim->d_ev_link); cudaFree(sim->d_ev_closed);
   if (sim->stream && sim->own_stream) cudaStreamDestroy(sim->stream);
   if (sim->cap_stream) cudaStreamDestroy(sim->cap_stream);
   delete sim;
@@ -1053,6 +1116,7 @@ int sq_step(SqSim* sim, int32_t t) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_step: null sim");
   if (int rc = arm_tick(sim, t)) return rc;
   if (int rc = router_catch_up(sim, t)) return rc;
+  if (int rc = apply_closure_events(sim, t)) return rc;
   if (sim->router_graph && sim->wfreq > 0 && t % sim->wfreq == 0)
     if (int rc = router_refresh(sim, t)) return rc;
   launch_tick(sim, sim->stream);
@@ -1074,11 +1138,13 @@ int sq_run(SqSim* sim, int32_t t0, int32_t n) {
   const int end = t0 + n;
   while (t < end) {
     int seg_end = end;
+    if (int rc = apply_closure_events(sim, t)) return rc;
     if (sim->router_graph && sim->wfreq > 0) {
       if (t % sim->wfreq == 0)
         if (int rc = router_refresh(sim, t)) return rc;
       seg_end = std::min(end, (t / sim->wfreq + 1) * sim->wfreq);
     }
+    seg_end = std::min(seg_end, next_event_tick(sim));   // > t: everything due by t has just been applied
     int left = seg_end - t;
     while (sim->graph && left >= sim->graph_ticks) {
       SQ_CUDA_TRY(cudaGraphLaunch(sim->graph, sim->stream));
@@ -1264,6 +1330,37 @@ int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_
   if (agent_stop_tick)
     SQ_CUDA_TRY(cudaMemcpyAsync(agent_stop_tick, sim->st.a_arrive, sizeof(int) * (size_t)sim->A, cudaMemcpyDeviceToHost, sim->stream));
   return sq_sync(sim);
+}
+
+int sq_set_closure_schedule(SqSim* sim, int32_t n, const int32_t* tick, const int32_t* link_idx, const uint8_t* closed) {
+  if (!sim || (n > 0 && (!tick || !link_idx || !closed))) return sq::set_error(SQ_ERR_ARG, "sq_set_closure_schedule: null argument");
+  for (int i = 0; i < n; ++i)
+    if (link_idx[i] < 0 || link_idx[i] >= sim->L) return sq::set_error(SQ_ERR_ARG, "sq_set_closure_schedule: link index %d out of range", link_idx[i]);
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  // sort by tick (stable); of several events for one link at one tick the last one given wins
+  std::vector<int> order((size_t)std::max(n, 0));
+  std::iota(order.begin(), order.end(), 0);
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return tick[a] < tick[b]; });
+  sim->ev_tick.clear(); sim->ev_link.clear(); sim->ev_closed.clear();
+  for (size_t k = 0; k < order.size(); ++k) {
+    const int i = order[k];
+    bool superseded = false;
+    for (size_t m = k + 1; m < order.size() && tick[order[m]] == tick[i]; ++m)
+      if (link_idx[order[m]] == link_idx[i]) { superseded = true; break; }
+    if (superseded) continue;
+    sim->ev_tick.push_back(tick[i]); sim->ev_link.push_back(link_idx[i]); sim->ev_closed.push_back(closed[i] ? 1 : 0);
+  }
+  sim->ev_cursor = 0;
+  cudaFree(sim->d_ev_link); cudaFree(sim->d_ev_closed);
+  sim->d_ev_link = nullptr; sim->d_ev_closed = nullptr;
+  const size_t m = sim->ev_tick.size();
+  if (m > 0) {
+    SQ_CUDA_TRY(cudaMalloc(&sim->d_ev_link, sizeof(int) * m));
+    SQ_CUDA_TRY(cudaMalloc(&sim->d_ev_closed, m));
+    SQ_CUDA_TRY(cudaMemcpy(sim->d_ev_link, sim->ev_link.data(), sizeof(int) * m, cudaMemcpyHostToDevice));
+    SQ_CUDA_TRY(cudaMemcpy(sim->d_ev_closed, sim->ev_closed.data(), m, cudaMemcpyHostToDevice));
+  }
+  return SQ_OK;
 }
 
 int sq_set_link_closed(SqSim* sim, int32_t n, const int32_t* link_idx, const uint8_t* closed) {

@@ -513,6 +513,19 @@ class Network:
                 self._reroute_due(t)
         sim.step(t)
 
+    def schedule_closures(self, events):
+        """Timed closures as a device event table: events = [(tick, link_id, closed)], the timed part of
+        model/dta_meso_butte.py:88-115 without a host call per tick.  At the start of tick `tick` the link stops
+        (or resumes) taking vehicles and its routing weight becomes 1e8 (or its free-flow time), exactly as if the
+        driver had called close_link_to_newcomers / open_link_to_newcomers and set `status` before `step(tick)`.
+        Device route mode only (the host router reads the graph the driver edits itself)."""
+        if self.route_mode != "device":
+            raise B200LibraryError("schedule_closures needs route_mode='device'")
+        ev = sorted(((int(t), lid, bool(c)) for t, lid, c in events), key=lambda e: e[0])
+        self.sim.set_closure_schedule([e[0] for e in ev], [self._flat.link_index[e[1]] for e in ev],
+                                      [1 if e[2] else 0 for e in ev])
+        self._closure_events = ev
+
     def _flush_link_status(self):
         if self._pending_status:
             idx = [self._flat.link_index[lid] for lid in self._pending_status]

@@ -156,6 +156,15 @@ class DeviceSim(_SimBase):
         if rc != 0:
             raise _lib.B200LibraryError(f"sq_{what} failed ({rc}): {self._L.sq_last_error().decode()}")
 
+    def set_closure_schedule(self, ticks, link_idx, closed):
+        """Timed closures / reopenings as a device event table (include/sq_tick.h sq_set_closure_schedule)."""
+        t = np.ascontiguousarray(ticks, np.int32)
+        a = np.ascontiguousarray(link_idx, np.int32)
+        c = np.ascontiguousarray(closed, np.uint8)
+        assert len(t) == len(a) == len(c)
+        self._check(self._L.sq_set_closure_schedule(self._h, len(t), t.ctypes.data, a.ctypes.data, c.ctypes.data),
+                    "set_closure_schedule")
+
     def attach_router(self, graph, flat, reroute_freq=300, weight_freq=100):
         """Device-side rerouting on `graph` (an sp_interface.Graph whose edges are the real links).  `flat` needs
         the router arrays of flatten.router_arrays / synth.flat_grid: dest_nodes, agent_dslot, node_vertex, link_edge

@@ -189,3 +189,42 @@ def test_closures_host_and_device_routing_agree(tmp_path):
     # the closure really bit: once the vehicles already on the two links are through, arrivals at node 0 pause
     arr = a["arrive_tick"][runs[0]._flat.agent_destin == runs[0]._flat.node_index[0]]
     assert ((arr > 400) & (arr < 1020)).sum() == 0 and (arr >= 1020).sum() > 0
+
+
+@pytest.mark.gpu
+def test_closure_schedule_equals_per_tick_calls(tmp_path):
+    """Row N3: the same closures given once as a device event table (Network.schedule_closures ->
+    sq_set_closure_schedule) and replayed with sq_run in long stretches == the driver closing and reopening the
+    links by hand before the ticks in question (the run of test_closures_host_and_device_routing_agree)."""
+    nets = []
+    for _ in range(2):
+        net, special = build_grid("grid8", tmp_path)
+        net.use_gpu(seed=11, special_nodes=special, reroute_freq=300, weight_freq=100, route_mode="device")
+        nets.append(net)
+    manual, sched = nets
+    closing = [lid for lid, l in manual.links.items() if l.link_type != "v" and l.end_nid == 0]
+    sched.schedule_closures([(120, lid, True) for lid in closing] + [(1020, lid, False) for lid in closing]
+                            + [(700, closing[0], True), (700, closing[0], True)])        # duplicates are harmless
+    stops = [119, 120, 121, 500, 1019, 1020, 1021, 1399]
+    dm, ds = [], []
+    t = 0
+    for stop in stops:
+        while t <= stop:
+            if t == 120:
+                for lid in closing:
+                    manual.links[lid].close_link_to_newcomers(g=manual.g)
+                    manual.links[lid].status = "closed"
+            if t == 1020:
+                for lid in closing:
+                    manual.links[lid].open_link_to_newcomers(g=manual.g)
+                    manual.links[lid].status = "burnt_over"
+            manual.step(t)
+            t += 1
+        dm.append(state_digest(manual.sim.state()))
+    t = 0
+    for stop in stops:
+        sched.run(t, stop + 1 - t)
+        t = stop + 1
+        ds.append(state_digest(sched.sim.state()))
+    assert dm == ds
+    assert (manual.sim.agent_state()["arrive_tick"] == sched.sim.agent_state()["arrive_tick"]).all()
