@@ -131,6 +131,12 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* router);
  * `seconds` on one real link gives up (status SQ_SHELTER_A1) and leaves the link before the link model of that tick.
  * 0 (default) switches the rule off. */
 int sq_set_shelter_after(SqSim* sim, int32_t seconds);
+/* The congestion counter of the same loop (run_traffic_simulation.py:100-102; model/dta_meso_butte.py:183-185 uses
+ * max(1800, 10 fft)): link.congested is reset every tick (run_traffic_simulation.py:80-82) and then counts the vehicles that have
+ * been on the (real) link for more than `seconds`.  0 (default) switches it off; sq_get_link_congested reads the
+ * per-link counts of the last tick run. */
+int sq_set_congest_after(SqSim* sim, int32_t seconds);
+int sq_get_link_congested(SqSim* sim, int64_t* congested);
 /* Per link: vehicles that sheltered on it (sum over a node's in-links = node.shelter_counts); per agent: the tick
  * at which it arrived or sheltered (-1 otherwise). */
 int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick);

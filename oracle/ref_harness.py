@@ -120,6 +120,7 @@ class Recorder:
         self.active = np.array([STATUS_CODES[a.status] != STATUS_CODES["shelter_p"] for a in self.agents.values()])
         self.snapshot_ticks = set(snapshot_ticks)
         self.digests, self.on_link, self.moves, self.active_nodes = [], [], [], []
+        self.congested_total = []
         self.snapshots = {}
         self.arrive_tick = np.full(len(self.agents), -1, np.int32)
         self._prev_move = 0
@@ -153,13 +154,19 @@ class Recorder:
         self._prev_move = tot
         newly = (s["status"] == STATUS_CODES["arrive"]) & (self.arrive_tick < 0)
         self.arrive_tick[newly] = t
+        cong = np.array([l.congested for l in self.links], np.int32)
+        self.congested_total.append(int(cong.sum()))
         if t in self.snapshot_ticks:
+            s["congested"] = cong
             self.snapshots[t] = s
 
     def to_npz_dict(self):
         out = dict(digests=np.array(self.digests, np.uint64), on_link=np.array(self.on_link, np.int32),
                    moves=np.array(self.moves, np.int32), arrive_tick=self.arrive_tick,
-                   active=self.active.astype(np.uint8), snapshot_ticks=np.array(sorted(self.snapshots), np.int32))
+                   active=self.active.astype(np.uint8), snapshot_ticks=np.array(sorted(self.snapshots), np.int32),
+                   # sum over links of link.congested after each tick (run_traffic_simulation.py:80-82, 100-102: the
+                   # counter is reset every tick); per link in the snapshots
+                   congested_total=np.array(self.congested_total, np.int32))
         for t, s in self.snapshots.items():
             for k, v in s.items():
                 out[f"snap{t}_{k}"] = v

@@ -59,6 +59,8 @@ typedef struct {
   int64_t counters[6];
   int shelter_after; /* run_traffic_simulation.py:103: seconds on one real link before status shelter_a1; 0 = rule off */
   int* l_shelter;
+  int congest_after; /* run_traffic_simulation.py:101: seconds on one real link before the vehicle counts as congested; 0 = off */
+  long long* l_congested;
   char err[256];
   int failed;
 } OSim;
@@ -110,6 +112,7 @@ OSim* oracle_tick_create(const SqNetDesc* d) {
   s->storage_c = (double*)malloc(sizeof(double) * (size_t)(L ? L : 1));
   s->total_left = (int*)calloc((size_t)(L ? L : 1), sizeof(int));
   s->l_shelter = (int*)calloc((size_t)(L ? L : 1), sizeof(int));
+  s->l_congested = (long long*)calloc((size_t)(L ? L : 1), sizeof(long long));
   for (i = 0; i < L; ++i) { /* Link.__init__ :417-419 */
     s->in_c[i] = s->out_c[i] = s->l_cap_s[i];
     s->storage_c[i] = s->l_storage[i];
@@ -143,7 +146,7 @@ void oracle_tick_destroy(OSim* s) {
   free(s->a_origin); free(s->a_destin); free(s->a_dept); free(s->a_vlen);
   free(s->queue); free(s->run); free(s->in_c); free(s->out_c); free(s->storage_c); free(s->total_left);
   free(s->a_status); free(s->a_cur); free(s->a_next); free(s->a_enter); free(s->a_arrive); free(s->a_route);
-  free(s->a_pos); free(s->virt_of_node); free(s->node_move); free(s);
+  free(s->a_pos); free(s->virt_of_node); free(s->node_move); free(s->l_shelter); free(s->l_congested); free(s);
 }
 
 static int fail(OSim* s, const char* msg, int a, int b, int c) {
@@ -300,6 +303,18 @@ int oracle_tick_step(OSim* s, int t) {
   if (s->failed) return -4;
   /* agent loop, give-up rule (run_traffic_simulation.py:100-104, 113-118): an enroute agent that has been on a
    * real link for more than shelter_after seconds becomes shelter_a1 and is stripped from the link's lists */
+  /* agent loop, congestion counter (run_traffic_simulation.py:80-82, 100-102): link.congested is reset every tick and
+   * then counts the vehicles that have been on the (real) link for more than congest_after seconds, before the
+   * give-up test */
+  if (s->congest_after > 0) {
+    memset(s->l_congested, 0, sizeof(long long) * (size_t)(L ? L : 1));
+    for (i = 0; i < A; ++i) {
+      int cl;
+      if (s->a_status[i] != SQ_ENROUTE) continue;
+      cl = s->a_cur[i];
+      if (!s->l_virtual[cl] && t - s->a_enter[i] > s->congest_after) s->l_congested[cl] += 1;
+    }
+  }
   if (s->shelter_after > 0)
     for (i = 0; i < A; ++i) {
       int cl;
@@ -356,6 +371,11 @@ int oracle_tick_step(OSim* s, int t) {
   return 0;
 }
 
+int oracle_tick_set_congest_after(OSim* s, int seconds) { s->congest_after = seconds > 0 ? seconds : 0; return 0; }
+int oracle_tick_get_link_congested(OSim* s, long long* out) {
+  memcpy(out, s->l_congested, sizeof(long long) * (size_t)s->n_links);
+  return 0;
+}
 int oracle_tick_set_shelter_after(OSim* s, int seconds) { s->shelter_after = seconds > 0 ? seconds : 0; return 0; }
 int oracle_tick_get_shelter_state(OSim* s, int* link_shelter, int* stop_tick) {
   if (link_shelter) memcpy(link_shelter, s->l_shelter, sizeof(int) * (size_t)s->n_links);

@@ -97,6 +97,9 @@ struct TickState {
   const int* l_dwell;        // floor(fft) + 2: upper bound of ready_tick - enter_time
   int* l_shelter;            // vehicles that gave up on this link (shelter_a1)
   int shelter_after;         // seconds on one link before a vehicle shelters (run_traffic_simulation.py:103), 0 = off
+  int congest_after;         // seconds on one link before a vehicle counts as congested (run_traffic_simulation.py:101), 0 = off
+  unsigned* cong_pos;        // [L] ring index of the first vehicle not yet congested (lags behind head when the queue moves)
+  long long* l_congested;    // [L] link.congested of the last tick: vehicles on the link for longer than congest_after
   // run control
   int* tick_link;  // tick the next link-phase launch simulates
   int* tick_node;  // tick the next node-phase launch simulates
@@ -162,6 +165,28 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
     const long long base = s.l_ring_base[l];
     const unsigned mask = s.l_ring_mask[l];
     long long li = s.len_in[l];
+    if (s.congest_after > 0 && !s.l_virtual[l]) {
+      // agent loop of the driver (run_traffic_simulation.py:80-82, 100-102): link.congested = vehicles that have
+      // been on this link for more than congest_after seconds, recounted every tick.  Ring order is entry order, so
+      // these vehicles are a prefix [head, p); p only moves forward, and the ready tick in the ring entry brackets
+      // the enter time (ready - dwell <= enter <= ready - 1), so the agent record is read at the boundary only.
+      const unsigned h = s.head[l];
+      unsigned p = s.cong_pos[l];
+      if ((int)(p - h) < 0) p = h;
+      const int dwell = s.l_dwell[l];
+      const long long limit = (long long)t - s.congest_after;   // congested <=> enter < limit
+      while (p != tl) {
+        const int2 e = s.ring[base + (p & mask)];
+        bool old;
+        if (e.y != INT_MAX && (long long)e.y - 1 < limit) old = true;
+        else if (e.y != INT_MAX && (long long)e.y - dwell >= limit) old = false;
+        else old = (long long)s.ag[e.x].rec.z < limit;
+        if (!old) break;
+        ++p;
+      }
+      s.cong_pos[l] = p;
+      s.l_congested[l] = (long long)(p - h);
+    }
     if (s.shelter_after > 0 && !s.l_virtual[l]) {
       // agent loop of the driver (run_traffic_simulation.py:100-104, 113-118): a vehicle that has spent more
       // than shelter_after seconds on this link gives up (status shelter_a1) and is taken off the link before
@@ -920,6 +945,13 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     if ((rc = dev_upload_ptr(sim, &s.l_capacity, d->link_capacity, (size_t)L))) return rc;
     if ((rc = dev_upload_ptr(sim, &s.l_maxmph, d->link_maxmph, (size_t)L))) return rc;
     s.shelter_after = 0;
+    s.congest_after = 0;
+    {
+      std::vector<unsigned> zu((size_t)std::max(L, 1), 0u);
+      std::vector<long long> zl((size_t)std::max(L, 1), 0ll);
+      if ((rc = dev_upload_rw(sim, &s.cong_pos, zu))) return rc;
+      if ((rc = dev_upload_rw(sim, &s.l_congested, zl))) return rc;
+    }
     s.D = 0; s.K = 0; s.freq = 1;
     s.n_vertex = nullptr; s.next_tbl = nullptr; s.dist_tbl = nullptr;
     s.cur_epoch = nullptr; s.bucket_ptr = nullptr; s.bucket_agents = nullptr; s.l_edge = nullptr; s.w_edge = nullptr;
@@ -1211,6 +1243,20 @@ int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t
   cudaFree(d_idx); cudaFree(d_off); cudaFree(d_len);
   sim->pool_used += add;
   return SQ_OK;
+}
+
+int sq_set_congest_after(SqSim* sim, int32_t seconds) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_set_congest_after: null sim");
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  sim->st.congest_after = seconds > 0 ? seconds : 0;
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel parameters changed
+  return SQ_OK;
+}
+
+int sq_get_link_congested(SqSim* sim, int64_t* out) {
+  if (!sim || !out) return sq::set_error(SQ_ERR_ARG, "sq_get_link_congested: null argument");
+  SQ_CUDA_TRY(cudaMemcpyAsync(out, sim->st.l_congested, sizeof(long long) * (size_t)sim->L, cudaMemcpyDeviceToHost, sim->stream));
+  return sq_sync(sim);
 }
 
 int sq_set_shelter_after(SqSim* sim, int32_t seconds) {

@@ -404,14 +404,15 @@ class Network:
     # the device switch
     # ---------------------------------------------------------------------------------------------------------
     def use_gpu(self, seed=0, special_nodes=None, reroute_freq=300, weight_freq=100, route_at_start=True,
-                route_mode="device", shelter_after=3 * 3600):
+                route_mode="device", shelter_after=3 * 3600, congest_after=1800):
         """Move the simulation onto the GPU.  Call once after `add_demand` (and after any t=0 changes to
         `agent.departure_time`).
 
         route_mode="device" (default): everything the driver's agent loop does stays on the GPU -- the edge-weight
         refresh every `weight_freq` ticks, one reverse shortest-path tree per destination, the staggered reroute
         of agents with t % reroute_freq == agent_id % reroute_freq, loading, arrivals and the give-up rule after
-        `shelter_after` seconds on one link (run_traffic_simulation.py:81-118).  `network.step(t)` is one C call.
+        `shelter_after` seconds on one link, the per-tick `link.congested` count of vehicles more than
+        `congest_after` seconds on their link (run_traffic_simulation.py:80-118).  `network.step(t)` is one C call.
         route_mode="host": routes are Python dicts on the agents like in the reference (`agent.route`), recomputed
         in batches of forward trees and pushed to the device; use it when a driver edits routes itself
         (e.g. get_partial_path)."""
@@ -441,6 +442,8 @@ class Network:
             self._sim.attach_router(self.g, self._flat, reroute_freq=reroute_freq, weight_freq=weight_freq)
         if shelter_after:
             self._sim.set_shelter_after(shelter_after)
+        if congest_after:
+            self._sim.set_congest_after(congest_after)
         for link in self.links.values():
             link._net = self
         self._seed = seed
@@ -549,6 +552,7 @@ class Network:
         loop does (run_traffic_simulation.py:95-98, 119-120)."""
         sim = self.sim
         ls, ag, nd, sh = sim.link_state(), sim.agent_state(), sim.node_state(), sim.shelter_state()
+        cong = sim.link_congested()
         ptr, veh = sim.link_vehicles()
         ids = self._flat.agent_ids
         for i, link in enumerate(self._link_objs):
@@ -556,6 +560,7 @@ class Network:
             q = int(ls["q"][i])
             link.queue_vehicles, link.run_vehicles = on[:q], on[q:]
             link.total_vehicles_left = int(ls["left"][i])
+            link.congested = int(cong[i])
             link.remaining_inflow_capacity = float(ls["in_c"][i])
             link.remaining_outflow_capacity = float(ls["out_c"][i])
             link.remaining_storage_capacity = float(ls["storage_c"][i])

@@ -74,6 +74,14 @@ class _SimBase:
     def step(self, t):
         self._check(self._fn("step")(self._h, int(t)), "step")
 
+    def set_congest_after(self, seconds):
+        self._check(self._fn("set_congest_after")(self._h, int(seconds)), "set_congest_after")
+
+    def link_congested(self):
+        out = np.empty(max(self.n_links, 1), np.int64)
+        self._check(self._fn("get_link_congested")(self._h, out.ctypes.data), "get_link_congested")
+        return out[: self.n_links]
+
     def run(self, t0, n):
         self._check(self._fn("run")(self._h, int(t0), int(n)), "run")
 

@@ -112,3 +112,14 @@ def test_device_router_run_equals_steps():
     sa, sb = a.state(), b.state()
     assert state_digest(sa) == state_digest(sb)
     assert a.counters()["agent_steps"] == b.counters()["agent_steps"]
+
+
+def test_device_congestion_counter_matches_reference():
+    """Row A6: link.congested on the device == the reference's, summed every 25 ticks and per link at the snapshots,
+    over the 11.5k-tick run whose stuck vehicles wait half an hour and more."""
+    from spatial_queue_b200.tick import DeviceSim
+    from tickcheck import check_congestion_counter
+    z, flat = load_golden("grid5x")
+    sim = DeviceSim(flat, seed=int(z["seed"]))
+    check_congestion_counter(sim, z)
+    sim.close()

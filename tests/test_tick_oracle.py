@@ -19,3 +19,12 @@ def test_oracle_replays_reference_golden(name, every):
     c = sim.counters()
     assert c["agent_steps"] == int(z["on_link"][:n].astype(np.int64).sum())
     assert c["moves"] == int(z["moves"][:n].astype(np.int64).sum())
+
+
+def test_oracle_congestion_counter_matches_reference():
+    from oracle.tick import OracleSim
+    from tickcheck import check_congestion_counter
+    z, flat = load_golden("grid5x")
+    sim = OracleSim(flat, seed=int(z["seed"]))
+    check_congestion_counter(sim, z)
+    sim.close()

@@ -64,3 +64,26 @@ def replay(sim, z, n_ticks=None, every=1, on_mismatch=None):
                     on_mismatch(t, s)
                 raise AssertionError(f"tick {t}: digest mismatch{detail}")
     return n
+
+
+def check_congestion_counter(sim, z, every=25):
+    """link.congested (reset every tick, run_traffic_simulation.py:80-82, 100-102) against the reference run: the sum
+    over links every `every` ticks, the per-link counts at the snapshot ticks.  Needs the shelter rule of the golden
+    (3 h) because sheltered vehicles leave the links."""
+    sim.set_shelter_after(3 * 3600)
+    sim.set_congest_after(1800)
+    n = int(z["n_ticks"])
+    snaps = set(int(t) for t in z["snapshot_ticks"])
+    events = route_events(z)
+    checked = 0
+    for t in range(n):
+        if t in events:
+            sim.set_routes(*events[t])
+        sim.step(t)
+        if t % every == 0 or t in snaps or t == n - 1:
+            c = sim.link_congested()
+            assert int(c.sum()) == int(z["congested_total"][t]), f"tick {t}"
+            if t in snaps:
+                assert (c == z[f"snap{t}_congested"]).all(), f"tick {t}"
+            checked += int(c.sum() > 0)
+    assert checked > 50      # the scenario really has vehicles stuck for more than half an hour
