@@ -137,6 +137,12 @@ int sq_set_shelter_after(SqSim* sim, int32_t seconds);
  * per-link counts of the last tick run. */
 int sq_set_congest_after(SqSim* sim, int32_t seconds);
 int sq_get_link_congested(SqSim* sim, int64_t* congested);
+/* Output cadence in one small read-back (the t_stats / link_stats lines of
+ * model/dta_meso_butte.py:291-348): out16 = [0..7] agents by status code (SQ_UNLOADED ... SQ_SHELTER_A1),
+ * [8] queued vehicles, [9] running vehicles, [10] congested vehicles (last tick), [11] closed links,
+ * [12] sum of node_move, [13] sum of total_vehicles_left over real links, [14] real links with a vehicle on them,
+ * [15] vehicles on closed links (Butte's in_fire_cnts for burning links). */
+int sq_get_summary(SqSim* sim, int64_t* out16);
 /* Per link: vehicles that sheltered on it (sum over a node's in-links = node.shelter_counts); per agent: the tick
  * at which it arrived or sheltered (-1 otherwise). */
 int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick);

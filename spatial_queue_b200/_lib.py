@@ -77,6 +77,7 @@ def _declare(L):
     L.sq_set_shelter_after.restype = ci; L.sq_set_shelter_after.argtypes = [vp, i32]
     L.sq_set_congest_after.restype = ci; L.sq_set_congest_after.argtypes = [vp, i32]
     L.sq_get_link_congested.restype = ci; L.sq_get_link_congested.argtypes = [vp, vp]
+    L.sq_get_summary.restype = ci; L.sq_get_summary.argtypes = [vp, vp]
     L.sq_get_shelter_state.restype = ci; L.sq_get_shelter_state.argtypes = [vp, vp, vp]
     L.sq_set_link_closed.restype = ci; L.sq_set_link_closed.argtypes = [vp, i32, vp, vp]
     L.sq_set_closure_schedule.restype = ci; L.sq_set_closure_schedule.argtypes = [vp, i32, vp, vp, vp]

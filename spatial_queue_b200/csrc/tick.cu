@@ -715,6 +715,35 @@ __global__ void __launch_bounds__(128) k_evacuate(const TickState s, int slot) {
   s.a_route_pos[a] = 0;
 }
 
+// Output cadence (row N4; the t_stats / link_stats reductions of model/dta_meso_butte.py:291-348): one pass over
+// agents, links and nodes into 16 counters, so a driver's periodic log line costs a 128-byte read-back instead of
+// a full state sync.  out: [0..7] agents by status code, [8] queued vehicles, [9] running vehicles, [10] congested
+// vehicles (last tick), [11] closed links, [12] sum of node_move, [13] sum of total_vehicles_left over real links,
+// [14] real links with any vehicle on them, [15] vehicles on closed links.
+__global__ void __launch_bounds__(256) k_summary(const TickState s, unsigned long long* out) {
+  __shared__ unsigned long long acc[16];
+  if (threadIdx.x < 16) acc[threadIdx.x] = 0ull;
+  __syncthreads();
+  const int stride = gridDim.x * blockDim.x;
+  for (int a = blockIdx.x * blockDim.x + threadIdx.x; a < s.A; a += stride)
+    atomicAdd(&acc[s.ag[a].rec.w & 7], 1ull);
+  for (int l = blockIdx.x * blockDim.x + threadIdx.x; l < s.L; l += stride) {
+    const unsigned q = s.qtail[l] - s.head[l], r = s.tail[l] - s.qtail[l];
+    if (q) atomicAdd(&acc[8], (unsigned long long)q);
+    if (r) atomicAdd(&acc[9], (unsigned long long)r);
+    if (s.l_congested[l]) atomicAdd(&acc[10], (unsigned long long)s.l_congested[l]);
+    if (s.l_closed[l]) { atomicAdd(&acc[11], 1ull); if (q + r) atomicAdd(&acc[15], (unsigned long long)(q + r)); }
+    if (!s.l_virtual[l]) {
+      if (s.total_left[l]) atomicAdd(&acc[13], (unsigned long long)s.total_left[l]);
+      if (q + r) atomicAdd(&acc[14], 1ull);
+    }
+  }
+  for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < s.N; n += stride)
+    if (s.node_move[n]) atomicAdd(&acc[12], (unsigned long long)s.node_move[n]);
+  __syncthreads();
+  if (threadIdx.x < 16 && acc[threadIdx.x]) atomicAdd(&out[threadIdx.x], acc[threadIdx.x]);
+}
+
 // Closure schedule (row N3): events [lo, hi) of the device event table take effect.  A closed link gets no
 // inflow from the next link phase on (queue_class.py:455) and weighs 1e8 for routing; a reopened one weighs its
 // free-flow time again (close_link_to_newcomers / open_link_to_newcomers, queue_class.py:467-474).  w_edge was
@@ -761,6 +790,7 @@ struct SqSim {
   size_t ev_cursor = 0;
   int* d_ev_link = nullptr;
   unsigned char* d_ev_closed = nullptr;
+  unsigned long long* d_summary = nullptr;
   std::vector<double> h_capacity, h_maxmph, h_fft;
   // route pool management
   int* d_pool = nullptr;
@@ -1138,7 +1168,7 @@ void sq_destroy(SqSim* sim) {
   if (sim->graph) cudaGraphExecDestroy(sim->graph);
   for (void* p : sim->allocs) cudaFree(p);
   cudaFree(sim->d_pool);
-  cudaFree(sim->d_ev_link); cudaFree(sim->d_ev_closed);
+  cudaFree(sim->d_ev_link); cudaFree(sim->d_ev_closed); cudaFree(sim->d_summary);
   if (sim->stream && sim->own_stream) cudaStreamDestroy(sim->stream);
   if (sim->cap_stream) cudaStreamDestroy(sim->cap_stream);
   delete sim;
@@ -1251,6 +1281,19 @@ int sq_set_congest_after(SqSim* sim, int32_t seconds) {
   sim->st.congest_after = seconds > 0 ? seconds : 0;
   if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel parameters changed
   return SQ_OK;
+}
+
+int sq_get_summary(SqSim* sim, int64_t* out16) {
+  if (!sim || !out16) return sq::set_error(SQ_ERR_ARG, "sq_get_summary: null argument");
+  if (!sim->d_summary) SQ_CUDA_TRY(cudaMalloc(&sim->d_summary, sizeof(unsigned long long) * 16));
+  SQ_CUDA_TRY(cudaMemsetAsync(sim->d_summary, 0, sizeof(unsigned long long) * 16, sim->stream));
+  const int work = std::max(sim->A, std::max(sim->L, sim->N));
+  const int grid = std::max(1, std::min((work + 255) / 256, 148 * 8));
+  k_summary<<<grid, 256, 0, sim->stream>>>(sim->st, sim->d_summary);
+  sq::count_launch(); sim->launches += 1;
+  SQ_CUDA_TRY(cudaGetLastError());
+  SQ_CUDA_TRY(cudaMemcpyAsync(out16, sim->d_summary, sizeof(unsigned long long) * 16, cudaMemcpyDeviceToHost, sim->stream));
+  return sq_sync(sim);
 }
 
 int sq_get_link_congested(SqSim* sim, int64_t* out) {

@@ -516,6 +516,12 @@ class Network:
                 self._reroute_due(t)
         sim.step(t)
 
+    def summary(self):
+        """Counts for the drivers' periodic log / t_stats line (model/dta_meso_butte.py:291-348) from one small
+        device reduction instead of a full sync_to_host: agents by status, vehicles queued / running / congested /
+        on closed links, closed links, node moves."""
+        return self.sim.summary()
+
     def schedule_closures(self, events):
         """Timed closures as a device event table: events = [(tick, link_id, closed)], the timed part of
         model/dta_meso_butte.py:88-115 without a host call per tick.  At the start of tick `tick` the link stops

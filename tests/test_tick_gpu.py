@@ -149,5 +149,13 @@ def test_config4_size_window_matches_oracle():
         assert (dev.link_congested() == orc.link_congested()).all()
     cd, co = dev.counters(), orc.counters()
     assert cd["agent_steps"] == co["agent_steps"] and cd["moves"] == co["moves"] and cd["arrivals"] == co["arrivals"]
+    # row N4: the one-read-back summary equals the same reductions over the oracle's full state
+    sm, ag, real = dev.summary(), orc.agent_state(), flat.link_is_virtual == 0
+    for code, name in enumerate(("unloaded", "enroute", "arrive", "shelter_p", "shelter_a1")):
+        assert sm[name] == int((ag["status"] == code).sum()), name
+    assert sm["queued"] == int(so["q"].sum()) and sm["running"] == int(so["r"].sum())
+    assert sm["congested"] == int(orc.link_congested().sum()) and sm["closed_links"] == 0
+    assert sm["node_moves"] == int(so["node_move"].sum()) and sm["vehicles_left"] == int(so["left"][real].sum())
+    assert sm["links_in_use"] == int(((so["q"] + so["r"])[real] > 0).sum())
     assert cd["moves"] > 500_000 and int(dev.link_congested().sum()) > 0
     dev.close(); orc.close()
