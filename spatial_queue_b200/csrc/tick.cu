@@ -147,7 +147,17 @@ __device__ __forceinline__ size_t tbl_index(const TickState& s, int epoch, int d
 }
 
 // ---- phase 1: load + link model, one thread per link ---------------------------------------------------
-__global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
+__device__ void reroute_slot(const TickState& s, int i);
+
+// The staggered reroute of this tick (k_reroute's work) rides in the same launch: blocks beyond `link_blocks`
+// re-point the agents of this tick's stagger slot.  The two halves touch different words of an agent record
+// (reroute: next link, epoch, route kind; load / give-up: enter time, status), both with word-sized stores, and a
+// reroute reads nothing the link half writes except the status, where either value gives the same decision.
+__global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_blocks) {
+  if ((int)blockIdx.x >= link_blocks) {
+    reroute_slot(s, ((int)blockIdx.x - link_blocks) * 256 + (int)threadIdx.x);
+    return;
+  }
   const int l = blockIdx.x * blockDim.x + threadIdx.x;
   const int t = *s.tick_link;
   if (l == 0) {
@@ -197,10 +207,9 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
       while (h != tl) {
         const int2 e = s.ring[base + (h & mask)];
         if (e.y != INT_MAX && (long long)t - e.y + dwell <= s.shelter_after) break;   // cannot be old enough yet
-        int4 rec = s.ag[e.x].rec;
+        const int4 rec = s.ag[e.x].rec;
         if (t - rec.z <= s.shelter_after) break;
-        rec.w = (rec.w & ~0xff) | SQ_SHELTER_A1;
-        s.ag[e.x].rec = rec;
+        s.ag[e.x].rec.w = (rec.w & ~0xff) | SQ_SHELTER_A1;
         s.a_arrive[e.x] = t;
         lo += (rec.w >> 8) & 0xff;
         ++h; ++sheltered;
@@ -218,11 +227,10 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s) {
       while (tl < cnt) {
         const int2 e = s.ring[base + tl];
         if (e.y - 1 > t) break;
-        int4 rec = s.ag[e.x].rec;
-        rec.z = e.y - 1;                                  // current_link_enter_time = departure tick
-        rec.w = (rec.w & ~0xff) | SQ_ENROUTE;
-        s.ag[e.x].rec = rec;
-        li += (rec.w >> 8) & 0xff;
+        const int w = s.ag[e.x].rec.w;
+        s.ag[e.x].rec.z = e.y - 1;                        // current_link_enter_time = departure tick
+        s.ag[e.x].rec.w = (w & ~0xff) | SQ_ENROUTE;
+        li += (w >> 8) & 0xff;
         ++tl; ++loaded;
       }
       if (loaded) { s.tail[l] = tl; s.len_in[l] = li; }
@@ -667,21 +675,8 @@ __global__ void __launch_bounds__(256) k_build_tables(const TickState s, int slo
 // Agent.get_path + find_next_link for the agents due this tick (t % freq == agent_id % freq,
 // run_traffic_simulation.py:107-109): adopt the newest tables unless the destination is out of reach
 // (distance > 1e8 keeps the old route, queue_class.py:511-513).  `all` != 0 routes every agent (t == 0).
-__global__ void __launch_bounds__(128) k_reroute(const TickState s, int all) {
-  const int i = blockIdx.x * 128 + threadIdx.x;
-  int a;
-  if (all) {
-    if (i >= s.A) return;
-    a = i;
-  } else {
-    const int t = *s.tick_link;
-    if (t <= 0) return;
-    const int b = t % s.freq;
-    const int k = s.bucket_ptr[b] + i;
-    if (k >= s.bucket_ptr[b + 1]) return;
-    a = s.bucket_agents[k];
-  }
-  int4 rec = s.ag[a].rec;
+__device__ __forceinline__ void reroute_agent(const TickState& s, int a) {
+  const int4 rec = s.ag[a].rec;
   const int st = rec.w & 0xff;
   if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
   const int node = s.l_end[rec.y];
@@ -690,8 +685,23 @@ __global__ void __launch_bounds__(128) k_reroute(const TickState s, int all) {
   if (s.dist_tbl[idx] > 1e8) return;
   s.ag[a].epoch = e;
   s.ag[a].route_len = -1;
-  rec.x = s.next_tbl[idx];
-  s.ag[a].rec = rec;
+  s.ag[a].rec.x = s.next_tbl[idx];
+}
+
+// i-th agent of this tick's stagger slot (t % freq == key % freq, run_traffic_simulation.py:107)
+__device__ void reroute_slot(const TickState& s, int i) {
+  if (!s.bucket_ptr) return;
+  const int t = *s.tick_link;
+  if (t <= 0) return;
+  const int b = t % s.freq;
+  const int k = s.bucket_ptr[b] + i;
+  if (k >= s.bucket_ptr[b + 1]) return;
+  reroute_agent(s, s.bucket_agents[k]);
+}
+
+__global__ void __launch_bounds__(128) k_reroute_all(const TickState s) {
+  const int a = blockIdx.x * 128 + threadIdx.x;
+  if (a < s.A) reroute_agent(s, a);
 }
 
 // Before table slot `slot` is overwritten: agents that still follow it (their reroutes kept failing) get
@@ -1031,9 +1041,9 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
 
 static int launch_tick(SqSim* sim, cudaStream_t st) {
   const int L = sim->L, N = sim->N;
-  if (sim->router_graph && sim->max_bucket > 0)
-    k_reroute<<<(sim->max_bucket + 127) / 128, 128, 0, st>>>(sim->st, 0);
-  k_link_phase<<<(L + 255) / 256, 256, 0, st>>>(sim->st);
+  const int link_blocks = (L + 255) / 256;
+  const int reroute_blocks = (sim->router_graph && sim->max_bucket > 0) ? (sim->max_bucket + 255) / 256 : 0;
+  k_link_phase<<<link_blocks + reroute_blocks, 256, 0, st>>>(sim->st, link_blocks);
   k_node_phase<<<(N + 63) / 64, 64, 0, st>>>(sim->st);
   return SQ_OK;
 }
@@ -1152,7 +1162,7 @@ static int next_event_tick(const SqSim* sim) {
   return sim->ev_cursor < sim->ev_tick.size() ? sim->ev_tick[sim->ev_cursor] : INT_MAX;
 }
 
-static int kernels_per_tick(const SqSim* sim) { return (sim->router_graph && sim->max_bucket > 0) ? 3 : 2; }
+static int kernels_per_tick(const SqSim*) { return 2; }
 
 extern "C" {
 
@@ -1405,7 +1415,7 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* r) {
   // t = 0: weights from the empty network, tables, and every agent routed (run_traffic_simulation.py:107)
   if ((rc = router_refresh(sim, 0))) return rc;
   if (A > 0) {
-    k_reroute<<<(A + 127) / 128, 128, 0, sim->stream>>>(s, 1);
+    k_reroute_all<<<(A + 127) / 128, 128, 0, sim->stream>>>(s);
     sq::count_launch(); sim->launches += 1;
   }
   SQ_CUDA_TRY(cudaGetLastError());
