@@ -1274,7 +1274,9 @@ static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t 
     case 64: sssp_ell_kernel<2><<<grid, 64, 0, st>>>(p); break;
     case 128: sssp_ell_kernel<4><<<grid, 128, 0, st>>>(p); break;
     case 256: sssp_ell_kernel<8><<<grid, 256, 0, st>>>(p); break;
-    default: return sq::set_error(SQ_ERR_ARG, "ELL kernel: threads must be 32, 64, 128 or 256 (got %d)", threads);
+    case 512: sssp_ell_kernel<16><<<grid, 512, 0, st>>>(p); break;
+    case 1024: sssp_ell_kernel<32><<<grid, 1024, 0, st>>>(p); break;
+    default: return sq::set_error(SQ_ERR_ARG, "ELL kernel: threads must be 32 ... 1024, a power of two (got %d)", threads);
   }
   sq::count_launch();
   SQ_CUDA_TRY(cudaGetLastError());
@@ -1365,7 +1367,10 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   // CTA-per-tree ELL kernel finishes a tree ~10x sooner (the router's 8 trees per weight refresh)
   const bool want_warp = g->algo == 2 || (g->algo == 3 && n >= 6 * n_sm);
   const bool use_warp = want_warp && vbits <= 24;   // >= 5 hash bits per queue entry
-  const int threads = use_warp ? 128 : std::min(g->threads, 256);
+  // a handful of trees (the device router's one per destination): the GPU is empty, so give each tree a whole
+  // SM's worth of threads; a round is then one or two passes over the wavefront instead of five
+  int threads = use_warp ? 128 : std::min(g->threads, 1024);
+  if (!use_warp && g->algo == 3) threads = n <= n_sm ? 1024 : n <= 2 * n_sm ? 512 : 256;
   int per_sm, grid, rows;   // rows = trees in flight (scratch distance rows in timing-only mode)
   size_t warp_smem = 0;
   if (use_warp) {
@@ -1653,7 +1658,7 @@ int sp_set_algo(Graph* g, int algo, double queue_factor) {
   if (algo < 0 || algo > 3) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL), 1 (bitmap), 2 (warp) or 3 (auto)");
   g->algo = algo;
   if (algo == 1 && g->threads < 128) g->threads = 256;
-  if ((algo == 0 || algo == 3) && g->threads > 256) g->threads = 256;
+  if (algo == 3 && g->threads > 256) g->threads = 256;
   if (queue_factor > 0.0) g->queue_factor = queue_factor;
   return SQ_OK;
 }

@@ -73,7 +73,7 @@ struct TickState {
   // nodes
   const long long* n_key; const unsigned char* n_type;
   const int* in_ptr; const int* in_links; const unsigned char* in_phase; const int* in_prio;
-  const int* out_ptr;
+  const int* out_ptr; const int* out_links;
   const long long* turn_ptr; const double* turn;
   long long* node_move;
   // agents
@@ -260,6 +260,13 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       if (sh) atomicAdd(&s.counters[7], (u64)sh);
     }
   }
+}
+
+// Fire-and-forget load: brings the sector into L1 without making the thread wait (the result is never used).  The
+// node phase is one thread's chain of dependent loads; whatever address is known early is touched early so that
+// the dependent part of the chain finds it in L1.
+__device__ __forceinline__ void touch(const void* p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
 
 // ---- phase 2: node model, one thread per node ---------------------------------------------------------------
@@ -493,6 +500,23 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
       active = 1;
       const long long key = s.n_key[n];
       const int type = s.n_type[n];
+      // everything whose address is known by now: the statics and in-side words of every candidate in-link (the
+      // primary and the opposite approach are among them), the out-side words of every out-link
+      for (int i = 0; i < indeg; ++i) {
+        if (!((cand >> i) & 1ull)) continue;
+        const int l = s.in_links[ib + i];
+        touch(&s.l_lanes[l]); touch(&s.l_ring_base[l]); touch(&s.l_ring_mask[l]); touch(&s.l_left_mask[l]);
+        touch(&s.l_rev[l]); touch(&s.out_c[l]); touch(&s.len_out[l]); touch(&s.total_left[l]);
+      }
+      {
+        const int ob = s.out_ptr[n], oe = s.out_ptr[n + 1];
+        touch(&s.turn_ptr[n]);
+        for (int j = ob; j < oe; ++j) {
+          const int ol = s.out_links[j];
+          touch(&s.in_c[ol]); touch(&s.storage_c[ol]); touch(&s.tail[ol]); touch(&s.l_ring_mask[ol]); touch(&s.head[ol]);
+          touch(&s.len_in[ol]); touch(&s.l_ring_base[ol]); touch(&s.l_fft[ol]); touch(&s.l_end[ol]); touch(&s.l_out_local[ol]);
+        }
+      }
       int primary = -1;  // local index of the primary in-link
       // `order` semantics: after the shuffle replacement the list is [c_r, rest in original order].
       int first = -1;    // local index moved to the front by the last shuffle (ties in :277 see it first)
@@ -932,7 +956,7 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
   UP(l_cap_s, d->link_cap_per_s, L); UP(l_storage, d->link_storage_cap, L); UP(l_fft, d->link_fft, L);
   UP(n_type, d->node_type, N); UP(in_ptr, d->node_in_ptr, N + 1); UP(in_links, d->node_in_links, d->node_in_ptr[N]);
   UP(in_phase, d->node_in_phase, d->node_in_ptr[N]); UP(in_prio, d->node_in_prio, d->node_in_ptr[N]);
-  UP(out_ptr, d->node_out_ptr, N + 1);
+  UP(out_ptr, d->node_out_ptr, N + 1); UP(out_links, d->node_out_links, d->node_out_ptr[N]);
   UP(turn, d->turn_angle, d->node_turn_ptr[N]);
 #undef UP
   {

@@ -63,7 +63,7 @@ def test_network_mtx_golden(spi):
 
 @pytest.mark.parametrize("directed", [True, False])
 @pytest.mark.parametrize("threads,smemq,algo,qfac", [(256, 0, 1, 0), (128, 32, 1, 0), (1024, 64, 1, 0),   # bitmap kernel
-                                                      (128, 0, 0, 0), (64, 0, 0, 0), (32, 0, 0, 0),       # ELL kernel
+                                                      (128, 0, 0, 0), (64, 0, 0, 0), (32, 0, 0, 0), (1024, 0, 0, 0), (512, 0, 0, 0),   # ELL kernel
                                                       (256, 0, 0, 4.0), (64, 0, 0, 0.02),                 # roomy / tight queues
                                                       (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0)])    # warp kernel: (ilp, ring)
 def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
