@@ -10,6 +10,13 @@ from spatial_queue_b200 import sp_interface as spi
 n = int(os.environ.get("GRID", 224))
 B = int(os.environ.get("BATCH", 4096))
 s, e, w = grid_graph(n, seed=1)
+TILE = int(os.environ.get("TILE", 0))     # experiment: renumber the grid into TILE x TILE tiles before building the graph
+if TILE:
+    ii, jj = np.divmod(np.arange(n * n), n)
+    nt = (n + TILE - 1) // TILE
+    key = ((ii // TILE) * nt + (jj // TILE)) * (TILE * TILE) + (ii % TILE) * TILE + (jj % TILE)
+    perm = np.argsort(np.argsort(key, kind="stable"), kind="stable").astype(np.int32)
+    s, e = perm[s], perm[e]
 g = spi.from_arrays(s, e, w)
 V = n * n
 origins = torch.from_numpy(np.random.default_rng(0).permutation(V)[:B].astype(np.int32)).cuda()
