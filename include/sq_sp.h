@@ -122,7 +122,8 @@ int sp_sync(Graph* graph);
 int sp_set_tuning(Graph* graph, int threads, int ctas_per_sm, double delta_factor, int smem_queue);
 
 /* Kernel choice: 3 (default) = auto: the warp kernel for batches of at least six trees per SM, the ELL kernel
- * below that (a lone tree finishes ~10x sooner on a whole CTA); 2 = warp kernel (one tree per warp, four-byte
+ * below that (a lone tree finishes ~10x sooner on a whole CTA); if more than 5 % of a batch's trees overflow the
+ * warp kernel's ring, the next batches use a 2048-entry ring and, failing that, the ELL kernel; 2 = warp kernel (one tree per warp, four-byte
  * hashed queue entries in a shared-memory ring), 0 = ELL kernel (one tree per CTA, four-edge vertex records, tagged queue entries, queues of
  * queue_factor x V entries), 1 = bitmap kernel only (CSR, per-vertex shared-memory bitmaps; also the fallback
  * that reruns trees whose queues overflowed in the other two).  All produce identical results.

@@ -1054,6 +1054,11 @@ struct SqGraph {
   int parent_format = 0;       // 0 = int32 vertex ids, 1 = one-byte in-edge codes (device batches only)
   int algo = 3;                // 3 = auto (default), 2 = warp kernel, 0 = ELL kernel, 1 = bitmap kernel (also everyone's fallback)
   int warp_ring = 1024, warp_ilp = 4, warp_ctas_per_sm = 0;
+  // auto mode learns from the overflow count of its last warp-kernel batch (read at the start of the next one)
+  int auto_ring = 0;           // ring capacity auto mode uses (0 = warp_ring)
+  bool auto_warp_unfit = false; // wavefronts of this graph do not fit the largest ring: auto stays on the ELL kernel
+  int auto_checks = 0;
+  int pending_check_n = 0;      // trees of the last auto warp batch whose overflow count has not been looked at yet
   unsigned* d_wfar = nullptr;
   int wfar_warps = 0, wfar_cap = 0;
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
@@ -1166,6 +1171,7 @@ static int g_build_and_upload(SqGraph* g) {
     if (!g->d_counter) SQ_CUDA_TRY(cudaMalloc(&g->d_counter, sizeof(int) * 1024));
     if (!g->d_stats) SQ_CUDA_TRY(cudaMalloc(&g->d_stats, sizeof(long long) * 5));
     g->topo_dirty = false;
+    g->auto_ring = 0; g->auto_warp_unfit = false; g->pending_check_n = 0; g->auto_checks = 0;
     g->w_dirty = true;
   } else if (g->w_dirty) {
     for (size_t i = 0; i < g->es.size(); ++i) {
@@ -1325,6 +1331,20 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     SQ_CUDA_TRY(cudaMalloc(&g->d_qscratch, sizeof(int) * (size_t)bm_grid * 4 * V));
     g->scratch_grid = bm_grid; g->scratch_V = V;
   }
+  if (g->pending_check_n > 0 && g->d_fail) {
+    // how did the wavefronts of this graph fit the warp kernel's ring last time?  More than 5 % of the trees handed
+    // to the fallback kernel: double the ring once (2048 entries, 12 warps per SM), then give the graph to the ELL
+    // kernel, whose queues spill to global memory
+    int nfail = 0;
+    SQ_CUDA_TRY(cudaMemcpyAsync(&nfail, g->d_fail, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SQ_CUDA_TRY(cudaStreamSynchronize(st));
+    if ((long long)nfail * 20 > g->pending_check_n) {
+      const int cur = g->auto_ring > 0 ? g->auto_ring : g->warp_ring;
+      if (cur < 2048) g->auto_ring = 2048; else g->auto_warp_unfit = true;
+    }
+    g->pending_check_n = 0;
+    g->auto_checks += 1;
+  }
   if (g->fail_cap < n + 2) {
     cudaFree(g->d_fail); g->d_fail = nullptr;
     SQ_CUDA_TRY(cudaMalloc(&g->d_fail, sizeof(int) * (size_t)(n + 2)));
@@ -1365,7 +1385,7 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   while ((1ll << vbits) < (long long)V) ++vbits;
   // auto (3): a warp per tree wins on throughput once every SM has several trees per scheduler; below that the
   // CTA-per-tree ELL kernel finishes a tree ~10x sooner (the router's 8 trees per weight refresh)
-  const bool want_warp = g->algo == 2 || (g->algo == 3 && n >= 6 * n_sm);
+  const bool want_warp = g->algo == 2 || (g->algo == 3 && n >= 6 * n_sm && !g->auto_warp_unfit);
   const bool use_warp = want_warp && vbits <= 24;   // >= 5 hash bits per queue entry
   // a handful of trees (the device router's one per destination): the GPU is empty, so give each tree a whole
   // SM's worth of threads; a round is then one or two passes over the wavefront instead of five
@@ -1375,7 +1395,8 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   size_t warp_smem = 0;
   if (use_warp) {
     int C = 64;
-    while (C < g->warp_ring) C <<= 1;
+    while (C < (g->algo == 3 && g->auto_ring > 0 ? g->auto_ring : g->warp_ring)) C <<= 1;
+    if (g->algo == 3 && g->auto_checks < 3) g->pending_check_n = n;   // the first batches after a topology change
     warp_smem = (size_t)4 * 2 * C * sizeof(unsigned);
     if (warp_smem > 200 * 1024) return sq::set_error(SQ_ERR_ARG, "warp kernel: ring capacity %d does not fit shared memory", C);
     per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (warp_smem + 1024));

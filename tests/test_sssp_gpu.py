@@ -276,3 +276,27 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse):
     dh, ph = g.sssp_batch(origins.cpu().numpy()[:5], reverse=reverse)
     assert (ph == p32[:5].cpu().numpy()).all()
     g.free()
+
+
+def test_auto_mode_learns_from_ring_overflows(spi):
+    """Auto kernel choice on a graph whose wavefronts outgrow the warp kernel's ring (a dense random graph, 1000
+    origins): the first batch hands trees to the fallback kernel, the following ones run with a larger ring or on the
+    ELL kernel; every batch is bit-exact."""
+    from oracle import sssp as osssp
+    rng = np.random.default_rng(8)
+    V, E = 6000, 60000
+    s = rng.integers(0, V, E).astype(np.int32)
+    e = rng.integers(0, V, E).astype(np.int32)
+    w = rng.random(E) * 10.0 + 0.01
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.set_warp_tuning(ring_cap=64)
+    og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1)
+    origins = rng.integers(0, V, 1000).astype(np.int32)
+    do, po = og.sssp_batch(origins)
+    overflows = []
+    for _ in range(4):
+        d, p = g.sssp_batch(origins)
+        overflows.append(g.last_stats()["overflows"])
+        assert d.tobytes() == do.tobytes() and (p == po).all()
+    assert overflows[0] > 50 and overflows[-1] < overflows[0]
+    g.free()
