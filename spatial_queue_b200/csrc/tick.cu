@@ -399,87 +399,170 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
   return false;
 }
 
-constexpr int GATHER = 16;  // vehicles whose records are gathered together (independent loads in flight)
+constexpr int GATHER = 8;   // vehicles whose records are gathered together (independent loads in flight)
 
-// Admit loop of run_node_model (:304-386) over the first k queued vehicles of in-link `il`; `secondary`
-// applies the "no more left turns from the opposite approach" skip of :289-292.  Everything a vehicle's
-// decision reads from its own records (ring entry -> agent record, destination, route kind -> next link's
-// start / local index / end -> next-next link from the router table) is gathered for GATHER vehicles at a
-// time, level by level, so the sequential part runs on local data.  For the primary link the same records
-// answer non_conflict_vehicles' question "does any of them turn left" (:248-263): *turns_left is set from the
-// next links the vehicles had before anything moved.
-__device__ void admit_from_link(const TickState& s, AdmitCtx& c, OutCache& oc, int il, int k, bool secondary,
-                                bool* turns_left) {
-  const long long base = s.l_ring_base[il];
-  const unsigned mask = s.l_ring_mask[il];
-  const unsigned h = s.head[il];
-  const u64 left = s.l_left_mask[il];
-  double out_c = s.out_c[il];
-  const long long len_out0 = s.len_out[il];
-  const int total_left0 = s.total_left[il];
-  u64 stay_lo = 0, stay_hi = 0;  // bit i = vehicle i stays in the queue
-  int moved = 0;
-  long long moved_len = 0;
-  bool any_left = false;
-  for (int i0 = 0; i0 < k; i0 += GATHER) {
-    Veh v[GATHER];
-    int st[GATHER], ep[GATHER], dl[GATHER], en[GATHER];
-    const int cnt = min(GATHER, k - i0);
+// The window of an in-link the node model works on this tick: its first k queued vehicles.
+struct Win {
+  long long base, len_out0;
+  u64 left;
+  double out_c;
+  unsigned mask, h;
+  int il, k, total_left0;
+};
+
+__device__ __forceinline__ void win_load(const TickState& s, Win& w, int il) {
+  w.il = il;
+  w.k = 0;
+  if (il < 0) return;
+  w.base = s.l_ring_base[il];
+  w.mask = s.l_ring_mask[il];
+  w.h = s.head[il];
+  w.left = s.l_left_mask[il];
+  w.out_c = s.out_c[il];
+  w.len_out0 = s.len_out[il];
+  w.total_left0 = s.total_left[il];
+  w.k = min(s.l_lanes[il], (int)(s.qtail[il] - w.h));
+}
+
+// Everything a vehicle's decision reads from its own records (ring entry -> agent record, destination, route
+// kind -> next link's start / local index / end -> next-next link from the router table) is gathered for
+// GATHER vehicles at a time, level by level, so the sequential part runs on local data.  The four levels are
+// separate functions so that the node kernel can interleave the gathers of two in-links (issue the loads of one
+// link's level, then consume the other's).
+struct VSet {
+  Veh v[GATHER];
+  int st[GATHER], ep[GATHER], dl[GATHER], en[GATHER];
+};
+
+__device__ __forceinline__ void lvl_ring(const TickState& s, const Win& w, int i0, VSet& g) {
+  const int cnt = w.k - i0;
 #pragma unroll
-    for (int j = 0; j < GATHER; ++j) v[j].agent = j < cnt ? s.ring[base + ((h + (unsigned)(i0 + j)) & mask)].x : -1;
+  for (int j = 0; j < GATHER; ++j) g.v[j].agent = j < cnt ? s.ring[w.base + ((w.h + (unsigned)(i0 + j)) & w.mask)].x : -1;
+}
+
+__device__ __forceinline__ void lvl_agent(const TickState& s, VSet& g) {
 #pragma unroll
-    for (int j = 0; j < GATHER; ++j) {
-      v[j].ol = -1; v[j].recw = 0; v[j].destin = -1; v[j].rlen = 0; ep[j] = 0; dl[j] = 0;
-      if (v[j].agent >= 0) {
-        const int a = v[j].agent;
-        const int4* q = reinterpret_cast<const int4*>(&s.ag[a]);
-        const int4 rec = q[0], aux = q[1];
-        v[j].ol = rec.x; v[j].recw = rec.w;
-        v[j].destin = aux.x; v[j].rlen = aux.y;
-        ep[j] = aux.z; dl[j] = aux.w;
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < GATHER; ++j) {
-      st[j] = c.node; v[j].lc = 0; en[j] = 0;
-      if (v[j].ol >= 0) { const int4 hop = s.l_hop[v[j].ol]; st[j] = hop.x; en[j] = hop.y; v[j].lc = hop.z; }
-    }
-#pragma unroll
-    for (int j = 0; j < GATHER; ++j) {
-      v[j].nxt = -1;
-      if (v[j].ol >= 0 && v[j].rlen < 0) v[j].nxt = s.next_tbl[tbl_index(s, ep[j], dl[j], en[j])];
-    }
-    for (int j = 0; j < cnt; ++j) {
-      const int i = i0 + j;
-      bool stay;
-      if (v[j].ol >= 0 && st[j] != c.node) {
-        raise_error(s, 2, v[j].agent, c.node, v[j].ol);                              // KeyError of :257-262 / :291
-        stay = true;
-      } else {
-        if (v[j].ol >= 0 && ((left >> v[j].lc) & 1ull)) any_left = true;
-        stay = admit_one(s, c, oc, il, secondary, left, v[j], out_c);
-      }
-      if (stay) { if (i < 64) stay_lo |= 1ull << i; else stay_hi |= 1ull << (i - 64); }
-      else { ++moved; moved_len += (v[j].recw >> 8) & 0xff; }
+  for (int j = 0; j < GATHER; ++j) {
+    Veh& v = g.v[j];
+    v.ol = -1; v.recw = 0; v.destin = -1; v.rlen = 0; g.ep[j] = 0; g.dl[j] = 0;
+    if (v.agent >= 0) {
+      const int4* q = reinterpret_cast<const int4*>(&s.ag[v.agent]);
+      const int4 rec = q[0], aux = q[1];
+      v.ol = rec.x; v.recw = rec.w;
+      v.destin = aux.x; v.rlen = aux.y;
+      g.ep[j] = aux.z; g.dl[j] = aux.w;
     }
   }
-  if (turns_left) *turns_left = any_left;
-  if (moved) {
+}
+
+__device__ __forceinline__ void lvl_hop(const TickState& s, int node, VSet& g) {
+#pragma unroll
+  for (int j = 0; j < GATHER; ++j) {
+    g.st[j] = node; g.v[j].lc = 0; g.en[j] = 0;
+    if (g.v[j].ol >= 0) { const int4 hop = s.l_hop[g.v[j].ol]; g.st[j] = hop.x; g.en[j] = hop.y; g.v[j].lc = hop.z; }
+  }
+}
+
+__device__ __forceinline__ void lvl_tbl(const TickState& s, VSet& g) {
+#pragma unroll
+  for (int j = 0; j < GATHER; ++j) {
+    g.v[j].nxt = -1;
+    if (g.v[j].ol >= 0 && g.v[j].rlen < 0) g.v[j].nxt = s.next_tbl[tbl_index(s, g.ep[j], g.dl[j], g.en[j])];
+  }
+}
+
+// What the admit loop accumulates for one in-link.
+struct LinkAcc {
+  u64 stay_lo = 0, stay_hi = 0;   // bit i = vehicle i stays in the queue
+  long long moved_len = 0;
+  int moved = 0;
+  bool any_left = false;
+};
+
+// Admit loop of run_node_model (:304-386) over the gathered vehicles [i0, i0 + GATHER) of the window; `secondary`
+// applies the "no more left turns from the opposite approach" skip of :289-292.  For the primary link the same
+// records answer non_conflict_vehicles' question "does any of them turn left" (:248-263): acc.any_left is set
+// from the next links the vehicles had before anything moved.
+__device__ __forceinline__ void admit_set(const TickState& s, AdmitCtx& c, OutCache& oc, Win& w, bool secondary, const VSet& g,
+                                          int i0, LinkAcc& acc) {
+  const int cnt = min(GATHER, w.k - i0);
+  for (int j = 0; j < cnt; ++j) {
+    const int i = i0 + j;
+    const Veh& v = g.v[j];
+    bool stay;
+    if (v.ol >= 0 && g.st[j] != c.node) {
+      raise_error(s, 2, v.agent, c.node, v.ol);                                    // KeyError of :257-262 / :291
+      stay = true;
+    } else {
+      if (v.ol >= 0 && ((w.left >> v.lc) & 1ull)) acc.any_left = true;
+      stay = admit_one(s, c, oc, w.il, secondary, w.left, v, w.out_c);
+    }
+    if (stay) { if (i < 64) acc.stay_lo |= 1ull << i; else acc.stay_hi |= 1ull << (i - 64); }
+    else { ++acc.moved; acc.moved_len += (v.recw >> 8) & 0xff; }
+  }
+}
+
+// The rest of a window beyond its first (pre-gathered) set, then the queue bookkeeping of the link.
+__device__ void admit_finish(const TickState& s, AdmitCtx& c, OutCache& oc, Win& w, bool secondary, LinkAcc& acc) {
+  for (int i0 = GATHER; i0 < w.k; i0 += GATHER) {
+    VSet g;
+    lvl_ring(s, w, i0, g);
+    lvl_agent(s, g);
+    lvl_hop(s, c.node, g);
+    lvl_tbl(s, g);
+    admit_set(s, c, oc, w, secondary, g, i0, acc);
+  }
+  if (acc.moved) {
     // close the gaps: stayers slide to the back of the window [h, h+k), preserving order
+    const int k = w.k;
     int j = k - 1;
     for (int i = k - 1; i >= 0; --i) {
-      const bool st = i < 64 ? ((stay_lo >> i) & 1ull) : ((stay_hi >> (i - 64)) & 1ull);
+      const bool st = i < 64 ? ((acc.stay_lo >> i) & 1ull) : ((acc.stay_hi >> (i - 64)) & 1ull);
       if (st) {
-        if (j != i) s.ring[base + ((h + (unsigned)j) & mask)] = s.ring[base + ((h + (unsigned)i) & mask)];
+        if (j != i) s.ring[w.base + ((w.h + (unsigned)j) & w.mask)] = s.ring[w.base + ((w.h + (unsigned)i) & w.mask)];
         --j;
       }
     }
-    s.head[il] = h + (unsigned)moved;
-    s.len_out[il] = len_out0 + moved_len;
-    s.total_left[il] = total_left0 + moved;
-    c.moves += moved;
+    s.head[w.il] = w.h + (unsigned)acc.moved;
+    s.len_out[w.il] = w.len_out0 + acc.moved_len;
+    s.total_left[w.il] = w.total_left0 + acc.moved;
+    c.moves += acc.moved;
   }
-  s.out_c[il] = out_c;
+  s.out_c[w.il] = w.out_c;
+}
+
+// Choice of the opposite approach (:267-293) among the remaining candidates `rest`, assuming the primary link
+// has no left turner: the in-link whose turn onto the primary's reverse link is the straightest.
+__device__ __forceinline__ int pick_secondary(const TickState& s, int n, int ib, int indeg, int type, u64 rest, int first,
+                                              int rcol) {
+  const int outdeg = s.out_ptr[n + 1] - s.out_ptr[n];
+  const double* tb = s.turn + s.turn_ptr[n];
+  int secondary = -1;
+  double best = 0.0;
+  // iteration order of the remaining list: [first (if any), others in original order]; the priority branch
+  // iterates in priority order
+  if (type == 2) {
+    int done_rank = -1;
+    for (;;) {
+      int br = INT_MAX, bi = -1;
+      for (int i = 0; i < indeg; ++i) {
+        const int r = s.in_prio[ib + i];
+        if (((rest >> i) & 1ull) && r > done_rank && r < br) { br = r; bi = i; }
+      }
+      if (bi < 0) break;
+      done_rank = br;
+      const double a = fabs(tb[bi * outdeg + rcol]);
+      if (secondary < 0 || a < best) { secondary = bi; best = a; }
+    }
+  } else {
+    if (first >= 0 && ((rest >> first) & 1ull)) { secondary = first; best = fabs(tb[first * outdeg + rcol]); }
+    for (int i = 0; i < indeg; ++i) {
+      if (!((rest >> i) & 1ull) || i == first) continue;
+      const double a = fabs(tb[i * outdeg + rcol]);
+      if (secondary < 0 || a < best) { secondary = i; best = a; }
+    }
+  }
+  return secondary;
 }
 
 __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
@@ -573,53 +656,39 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
 #pragma unroll
         for (int i = 0; i < MAXO; ++i) oc.link[i] = -1;
         const int lp = s.in_links[ib + primary];
-        const int qlen_p = (int)(s.qtail[lp] - s.head[lp]);
-        const int kp = min(s.l_lanes[lp], qlen_p);
-        // the primary link's vehicles go first (run_node_model walks the go-list in order); the same pass tells
-        // whether any of them turns left (:248-263), which is all the choice of the opposite approach needs.
-        // Nothing that choice reads (candidate set, angle table, the other links' queues) is touched by the
-        // primary admits, so doing them first gives the reference's result with one gather per vehicle.
-        bool left_phase = false;
-        admit_from_link(s, c, oc, lp, kp, false, &left_phase);
-        // opposite approach (:267-293)
-        int secondary = -1;
-        const u64 rest = cand & ~(1ull << primary);
+        // The primary link's vehicles go first (run_node_model walks the go-list in order); the same pass tells
+        // whether any of them turns left (:248-263), which decides if the opposite approach moves at all.
+        // Nothing the choice of that approach reads (candidate set, angle table, the other links' queues), and
+        // nothing its vehicles' decisions are gathered from (their ring entries, agent records, next-link
+        // table), is touched by the primary admits.  So the opposite approach is chosen and its vehicles'
+        // records are gathered *speculatively*, interleaved level by level with the primary's gather: one
+        // thread keeps both chains of dependent loads in flight, and the admits themselves stay in the
+        // reference's order.
+        Win wp, ws;
+        win_load(s, wp, lp);
         const int rev = s.l_rev[lp];
-        if (!left_phase && rest && rev >= 0) {
-          const int outdeg = s.out_ptr[n + 1] - s.out_ptr[n];
-          const double* tb = s.turn + s.turn_ptr[n];
-          const int rcol = s.l_out_local[rev];
-          double best = 0.0;
-          // iteration order of the remaining list: [first (if any), others in original order]; the priority
-          // branch iterates in priority order
-          if (type == 2) {
-            int done_rank = -1;
-            for (;;) {
-              int br = INT_MAX, bi = -1;
-              for (int i = 0; i < indeg; ++i) {
-                const int r = s.in_prio[ib + i];
-                if (((rest >> i) & 1ull) && r > done_rank && r < br) { br = r; bi = i; }
-              }
-              if (bi < 0) break;
-              done_rank = br;
-              const double a = fabs(tb[bi * outdeg + rcol]);
-              if (secondary < 0 || a < best) { secondary = bi; best = a; }
-            }
-          } else {
-            if (first >= 0 && ((rest >> first) & 1ull)) { secondary = first; best = fabs(tb[first * outdeg + rcol]); }
-            for (int i = 0; i < indeg; ++i) {
-              if (!((rest >> i) & 1ull) || i == first) continue;
-              const double a = fabs(tb[i * outdeg + rcol]);
-              if (secondary < 0 || a < best) { secondary = i; best = a; }
-            }
-          }
+        const u64 rest = cand & ~(1ull << primary);
+        VSet gp, gs;
+        lvl_ring(s, wp, 0, gp);
+        const int rcol = rev >= 0 ? s.l_out_local[rev] : 0;
+        lvl_agent(s, gp);
+        int secondary = -1;
+        if (rest && rev >= 0) secondary = pick_secondary(s, n, ib, indeg, type, rest, first, rcol);
+        win_load(s, ws, secondary >= 0 ? s.in_links[ib + secondary] : -1);
+        lvl_ring(s, ws, 0, gs);
+        lvl_hop(s, n, gp);
+        lvl_agent(s, gs);
+        lvl_tbl(s, gp);
+        lvl_hop(s, n, gs);
+        lvl_tbl(s, gs);
+        LinkAcc ap;
+        admit_set(s, c, oc, wp, false, gp, 0, ap);
+        admit_finish(s, c, oc, wp, false, ap);
+        if (!ap.any_left && ws.il >= 0) {                                         // opposite approach (:267-293)
+          LinkAcc as;
+          admit_set(s, c, oc, ws, true, gs, 0, as);
+          admit_finish(s, c, oc, ws, true, as);
         }
-        int ls = -1, ks = 0;
-        if (secondary >= 0) {
-          ls = s.in_links[ib + secondary];
-          ks = min(s.l_lanes[ls], (int)(s.qtail[ls] - s.head[ls]));
-        }
-        if (ls >= 0) admit_from_link(s, c, oc, ls, ks, true, nullptr);
         outcache_flush(s, oc);
         if (c.moves) s.node_move[n] += c.moves;
         moves = c.moves; arrivals = c.arrivals;
