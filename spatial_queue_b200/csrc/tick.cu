@@ -55,11 +55,20 @@ struct __align__(32) AgentRec {
   int dslot;       // destination slot of the router
 };
 
+// Static words of an in-link's window, one 32-byte sector: ring placement, left-turn mask over the end node's
+// out-links, whole lanes, and the local out-index (at the end node) of the reverse link (-1 = none).
+struct __align__(32) WinRec {
+  long long base;
+  u64 left;
+  unsigned mask;
+  int lanes, rcol, pad;
+};
+
 struct TickState {
   int N, L, A;
   u64 seed;
   // links, static
-  const int* l_start; const int* l_end; const int* l_lanes; const int* l_rev;
+  const int* l_start; const int* l_end; const int* l_lanes; const int* l_rev; const WinRec* l_win;
   const unsigned char* l_virtual; unsigned char* l_closed;
   const double* l_cap_s; const double* l_storage; const double* l_fft;
   const long long* l_ring_base; const unsigned* l_ring_mask; const int* l_vcount;
@@ -407,21 +416,24 @@ struct Win {
   u64 left;
   double out_c;
   unsigned mask, h;
-  int il, k, total_left0;
+  int il, k, total_left0, rcol;
 };
 
 __device__ __forceinline__ void win_load(const TickState& s, Win& w, int il) {
   w.il = il;
   w.k = 0;
   if (il < 0) return;
-  w.base = s.l_ring_base[il];
-  w.mask = s.l_ring_mask[il];
+  const int4* q = reinterpret_cast<const int4*>(&s.l_win[il]);
+  const int4 q0 = q[0], q1 = q[1];
+  w.base = ((long long)(unsigned)q0.y << 32) | (unsigned)q0.x;
+  w.left = ((u64)(unsigned)q0.w << 32) | (unsigned)q0.z;
+  w.mask = (unsigned)q1.x;
+  w.rcol = q1.z;
   w.h = s.head[il];
-  w.left = s.l_left_mask[il];
   w.out_c = s.out_c[il];
   w.len_out0 = s.len_out[il];
   w.total_left0 = s.total_left[il];
-  w.k = min(s.l_lanes[il], (int)(s.qtail[il] - w.h));
+  w.k = min(q1.y, (int)(s.qtail[il] - w.h));
 }
 
 // Everything a vehicle's decision reads from its own records (ring entry -> agent record, destination, route
@@ -588,12 +600,17 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
       for (int i = 0; i < indeg; ++i) {
         if (!((cand >> i) & 1ull)) continue;
         const int l = s.in_links[ib + i];
-        touch(&s.l_lanes[l]); touch(&s.l_ring_base[l]); touch(&s.l_ring_mask[l]); touch(&s.l_left_mask[l]);
-        touch(&s.l_rev[l]); touch(&s.out_c[l]); touch(&s.len_out[l]); touch(&s.total_left[l]);
+        touch(&s.l_win[l]); touch(&s.out_c[l]); touch(&s.len_out[l]); touch(&s.total_left[l]);
       }
       {
         const int ob = s.out_ptr[n], oe = s.out_ptr[n + 1];
-        touch(&s.turn_ptr[n]);
+        {
+          // the turn-angle rows of the node (the choice of the opposite approach reads one column of them)
+          const char* tb = reinterpret_cast<const char*>(s.turn + s.turn_ptr[n]);
+          const int bytes = indeg * (oe - ob) * 8;
+          for (int o = 0; o < bytes && o < 512; o += 128) touch(tb + o);
+          if (bytes > 0) touch(tb + min(bytes, 512) - 8);
+        }
         for (int j = ob; j < oe; ++j) {
           const int ol = s.out_links[j];
           touch(&s.in_c[ol]); touch(&s.storage_c[ol]); touch(&s.tail[ol]); touch(&s.l_ring_mask[ol]); touch(&s.head[ol]);
@@ -666,20 +683,18 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
         // reference's order.
         Win wp, ws;
         win_load(s, wp, lp);
-        const int rev = s.l_rev[lp];
         const u64 rest = cand & ~(1ull << primary);
         VSet gp, gs;
         lvl_ring(s, wp, 0, gp);
-        const int rcol = rev >= 0 ? s.l_out_local[rev] : 0;
-        lvl_agent(s, gp);
         int secondary = -1;
-        if (rest && rev >= 0) secondary = pick_secondary(s, n, ib, indeg, type, rest, first, rcol);
+        if (rest && wp.rcol >= 0) secondary = pick_secondary(s, n, ib, indeg, type, rest, first, wp.rcol);
         win_load(s, ws, secondary >= 0 ? s.in_links[ib + secondary] : -1);
         lvl_ring(s, ws, 0, gs);
-        lvl_hop(s, n, gp);
+        lvl_agent(s, gp);
         lvl_agent(s, gs);
-        lvl_tbl(s, gp);
+        lvl_hop(s, n, gp);
         lvl_hop(s, n, gs);
+        lvl_tbl(s, gp);
         lvl_tbl(s, gs);
         LinkAcc ap;
         admit_set(s, c, oc, wp, false, gp, 0, ap);
@@ -1049,6 +1064,15 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     if ((rc = dev_upload(sim, &s.l_hop, hop))) return rc;
   }
   if ((rc = dev_upload(sim, &s.l_left_mask, left_mask))) return rc;
+  {
+    std::vector<WinRec> win((size_t)L);
+    for (int l = 0; l < L; ++l) {
+      const int rev = d->link_reverse[l];
+      win[l].base = ring_base[l]; win[l].left = left_mask[l]; win[l].mask = ring_mask[l];
+      win[l].lanes = d->link_lanes_floor[l]; win[l].rcol = rev >= 0 ? (int)out_local[rev] : -1; win[l].pad = 0;
+    }
+    if ((rc = dev_upload(sim, &s.l_win, win))) return rc;
+  }
   if ((rc = dev_upload_rw(sim, &s.ring, ring))) return rc;
   {
     std::vector<unsigned> z(L, 0u);
