@@ -152,7 +152,8 @@ __device__ __forceinline__ int route_link_at(const TickState& s, int agent, int 
   return off >= 0 ? s.route_pool[off + pos] : s.mat_pool[-(off + 1) + pos];
 }
 __device__ __forceinline__ size_t tbl_index(const TickState& s, int epoch, int dslot, int node) {
-  return ((size_t)epoch * s.D + dslot) * (size_t)s.N + node;
+  // the row number (table slot x destination) fits 32 bits; one widening multiply-add for the rest
+  return (size_t)((u64)(unsigned)(epoch * s.D + dslot) * (u64)(unsigned)s.N + (u64)(unsigned)node);
 }
 
 // ---- phase 1: load + link model, one thread per link ---------------------------------------------------
@@ -271,13 +272,6 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
   }
 }
 
-// Fire-and-forget load: brings the sector into L1 without making the thread wait (the result is never used).  The
-// node phase is one thread's chain of dependent loads; whatever address is known early is touched early so that
-// the dependent part of the chain finds it in L1.
-__device__ __forceinline__ void touch(const void* p) {
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-}
-
 // ---- phase 2: node model, one thread per node ---------------------------------------------------------------
 struct AdmitCtx {
   int t, node, toss, moves, arrivals;
@@ -295,7 +289,7 @@ struct OutCache {
   unsigned tail[MAXO], room_end[MAXO], mask[MAXO];
   long long len_in[MAXO], base[MAXO];
   int ready[MAXO], end_node[MAXO];
-  bool dirty[MAXO];
+  unsigned dirty;           // bit lc = slot lc must be written back
 };
 
 __device__ __forceinline__ void outcache_fill(const TickState& s, OutCache& oc, int lc, int ol, int t) {
@@ -311,19 +305,16 @@ __device__ __forceinline__ void outcache_fill(const TickState& s, OutCache& oc, 
   oc.base[lc] = s.l_ring_base[ol];
   oc.ready[lc] = ready_tick(t, s.l_fft[ol]);
   oc.end_node[lc] = s.l_end[ol];
-  oc.dirty[lc] = false;
 }
 
 __device__ __forceinline__ void outcache_flush(const TickState& s, const OutCache& oc) {
-#pragma unroll
-  for (int lc = 0; lc < MAXO; ++lc) {
-    if (oc.link[lc] >= 0 && oc.dirty[lc]) {
-      const int ol = oc.link[lc];
-      s.in_c[ol] = oc.in_c[lc];
-      s.storage_c[ol] = oc.storage_c[lc];
-      s.tail[ol] = oc.tail[lc];
-      s.len_in[ol] = oc.len_in[lc];
-    }
+  for (unsigned m = oc.dirty; m; m &= m - 1) {
+    const int lc = __ffs((int)m) - 1;
+    const int ol = oc.link[lc];
+    s.in_c[ol] = oc.in_c[lc];
+    s.storage_c[ol] = oc.storage_c[lc];
+    s.tail[ol] = oc.tail[lc];
+    s.len_in[ol] = oc.len_in[lc];
   }
 }
 
@@ -370,7 +361,7 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
       else {
         if (!(out_c > in_c)) { out_c = out_c - 1.0; out_c = out_c > 0.0 ? out_c : 0.0; }
         in_c = in_c - 1.0; in_c = in_c > 0.0 ? in_c : 0.0;
-        if (cached) { oc.in_c[lc] = in_c; oc.dirty[lc] = true; } else s.in_c[ol] = in_c;
+        if (cached) { oc.in_c[lc] = in_c; oc.dirty |= 1u << lc; } else s.in_c[ol] = in_c;
       }
       return true;
     }
@@ -386,7 +377,7 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
     s.ring[oc.base[lc] + (tl & oc.mask[lc])] = make_int2(agent, oc.ready[lc]);   // append to the run list
     oc.tail[lc] = tl + 1u;
     oc.len_in[lc] += vlen;
-    oc.dirty[lc] = true;
+    oc.dirty |= 1u << lc;
   } else {
     s.in_c[ol] = in_c;
     s.storage_c[ol] = storage - (double)vlen;
@@ -408,7 +399,7 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
   return false;
 }
 
-constexpr int GATHER = 8;   // vehicles whose records are gathered together (independent loads in flight)
+constexpr int GATHER = 4;   // vehicles whose records are gathered together (independent loads in flight)
 
 // The window of an in-link the node model works on this tick: its first k queued vehicles.
 struct Win {
@@ -595,28 +586,6 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
       active = 1;
       const long long key = s.n_key[n];
       const int type = s.n_type[n];
-      // everything whose address is known by now: the statics and in-side words of every candidate in-link (the
-      // primary and the opposite approach are among them), the out-side words of every out-link
-      for (int i = 0; i < indeg; ++i) {
-        if (!((cand >> i) & 1ull)) continue;
-        const int l = s.in_links[ib + i];
-        touch(&s.l_win[l]); touch(&s.out_c[l]); touch(&s.len_out[l]); touch(&s.total_left[l]);
-      }
-      {
-        const int ob = s.out_ptr[n], oe = s.out_ptr[n + 1];
-        {
-          // the turn-angle rows of the node (the choice of the opposite approach reads one column of them)
-          const char* tb = reinterpret_cast<const char*>(s.turn + s.turn_ptr[n]);
-          const int bytes = indeg * (oe - ob) * 8;
-          for (int o = 0; o < bytes && o < 512; o += 128) touch(tb + o);
-          if (bytes > 0) touch(tb + min(bytes, 512) - 8);
-        }
-        for (int j = ob; j < oe; ++j) {
-          const int ol = s.out_links[j];
-          touch(&s.in_c[ol]); touch(&s.storage_c[ol]); touch(&s.tail[ol]); touch(&s.l_ring_mask[ol]); touch(&s.head[ol]);
-          touch(&s.len_in[ol]); touch(&s.l_ring_base[ol]); touch(&s.l_fft[ol]); touch(&s.l_end[ol]); touch(&s.l_out_local[ol]);
-        }
-      }
       int primary = -1;  // local index of the primary in-link
       // `order` semantics: after the shuffle replacement the list is [c_r, rest in original order].
       int first = -1;    // local index moved to the front by the last shuffle (ties in :277 see it first)
@@ -672,6 +641,7 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
         OutCache oc;
 #pragma unroll
         for (int i = 0; i < MAXO; ++i) oc.link[i] = -1;
+        oc.dirty = 0u;
         const int lp = s.in_links[ib + primary];
         // The primary link's vehicles go first (run_node_model walks the go-list in order); the same pass tells
         // whether any of them turns left (:248-263), which decides if the opposite approach moves at all.
@@ -705,7 +675,7 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
           admit_finish(s, c, oc, ws, true, as);
         }
         outcache_flush(s, oc);
-        if (c.moves) s.node_move[n] += c.moves;
+        if (c.moves) atomicAdd(reinterpret_cast<u64*>(&s.node_move[n]), (u64)c.moves);   // result unused: a fire-and-forget RED
         moves = c.moves; arrivals = c.arrivals;
       }
     }
