@@ -88,17 +88,18 @@ def _utm10n_np(lon, lat):
     return geo._FE + geo._K0 * geo._AHAT * x, geo._K0 * geo._AHAT * y
 
 
-def flat_grid(n, seed=1, arterial_every=8):
-    """FlatNetwork (without agents) of the n x n grid, built with array operations only but following the
-    loader's rules (queue_class.py:54-62, 137-176, 416): virtual source links first in node order, then the real
-    links in edge order; incoming order = that order filtered by end node; turn angles from the projected
-    two-point geometry with the reference's wrap rule."""
+def flat_from_edges(lon, lat, s, e, lanes, maxmph):
+    """FlatNetwork (without agents) of an arbitrary directed network given as arrays, built with array operations
+    only but following the loader's rules (queue_class.py:54-62, 137-176, 416): virtual source links first in node
+    order, then the real links in edge order; incoming order = that order filtered by end node; turn angles from the
+    projected two-point geometry with the reference's wrap rule.  Links need not have a reverse link and nodes need
+    not have out-links."""
     from .flatten import FlatNetwork
-    lon, lat = grid_coords(n, seed)
-    s, e = grid_edges(n)
-    length, lanes, maxmph = grid_attributes(n, s, e, lon, lat, arterial_every)
-    N, E = n * n, len(s)
+    s, e = np.asarray(s, np.int64), np.asarray(e, np.int64)
+    N, E = len(lon), len(s)
     L = N + E
+    x0, y0 = lon * M_PER_DEG_LON, lat * M_PER_DEG_LAT
+    length = np.hypot(x0[s] - x0[e], y0[s] - y0[e])
     fft = length / maxmph * 2.237
     capacity = (1900 * lanes).astype(np.float64)
     x, y = _utm10n_np(lon, lat)
@@ -117,11 +118,13 @@ def flat_grid(n, seed=1, arterial_every=8):
     f.link_fft = np.concatenate([np.zeros(N), fft])
     f.link_closed = np.zeros(L, np.uint8)
     f.link_maxmph = np.concatenate([np.full(N, 1e5), length / fft * 2.23694])
-    # reverse link: (e -> s) exists for every grid link
+    # reverse link (e -> s), where there is one
     key = s * N + e
     order = np.argsort(key, kind="stable")
-    pos = np.searchsorted(key[order], e * N + s)
-    f.link_reverse = np.concatenate([np.full(N, -1), N + order[pos]]).astype(np.int32)
+    skey = key[order]
+    pos = np.minimum(np.searchsorted(skey, e * N + s), E - 1)
+    rev = np.where(skey[pos] == e * N + s, N + order[pos], -1)
+    f.link_reverse = np.concatenate([np.full(N, -1), rev]).astype(np.int32)
 
     # CSR of incoming (virtual first, then real in edge order) and outgoing links
     in_order = np.argsort(e, kind="stable")
@@ -158,10 +161,19 @@ def flat_grid(n, seed=1, arterial_every=8):
     # (start, end) -> link table
     f.pair_start, f.pair_end, f.pair_link = s.astype(np.int32), e.astype(np.int32), (N + np.arange(E)).astype(np.int32)
     f.edge_start, f.edge_end, f.edge_fft = s.astype(np.int32), e.astype(np.int32), fft
-    f.n_grid = n
     # router arrays (flatten.router_arrays): node i is graph vertex i, real link N + k is edge k
     f.node_vertex = np.arange(N, dtype=np.int32)
     f.link_edge = np.concatenate([np.full(N, -1), np.arange(E)]).astype(np.int32)
+    return f
+
+
+def flat_grid(n, seed=1, arterial_every=8):
+    """FlatNetwork (without agents) of the n x n grid."""
+    lon, lat = grid_coords(n, seed)
+    s, e = grid_edges(n)
+    _, lanes, maxmph = grid_attributes(n, s, e, lon, lat, arterial_every)
+    f = flat_from_edges(lon, lat, s, e, lanes, maxmph)
+    f.n_grid = n
     return f
 
 
@@ -216,6 +228,32 @@ def add_agents(f, origin, destin, dept, vlen, next_link, dest_nodes):
     return f
 
 
+def next_link_tables(f, exits, router=None):
+    """next_link[d, v] = link to take at node v towards exit d (-1 at the exit and where there is no path), from one
+    tree per exit on the reversed graph.  Routing runs on the GPU through the product library unless `router`
+    supplies a callable (starts, ends, w, roots) -> parent[len(roots), V] (how the CPU tests inject the oracle)."""
+    s, e, w = f.edge_start, f.edge_end, f.edge_fft
+    N = len(f.node_key)
+    if router is None:
+        from . import sp_interface
+        g = sp_interface.from_arrays(e, s, w, max_vertex_id=N - 1)      # reversed graph
+        _, parent = g.sssp_batch(np.asarray(exits, np.int32), want_dist=False)
+        g.free()
+    else:
+        parent = router(e, s, w, exits)
+    # next link at node v towards exit d: the link (v -> parent[d, v])
+    key = s.astype(np.int64) * N + e
+    order = np.argsort(key)
+    v = np.arange(N, dtype=np.int64)
+    next_link = np.full((len(exits), N), -1, np.int32)
+    for d in range(len(exits)):
+        p = parent[d].astype(np.int64)
+        ok = p >= 0
+        pos = np.searchsorted(key[order], v[ok] * N + p[ok])
+        next_link[d, v[ok]] = N + order[pos]
+    return next_link
+
+
 def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=None, router=None, device_routes=False):
     """The C4-style workload: n x n grid, agents from uniform origins to the exit nodes with
     staggered departures, routed at t=0 on free-flow weights.
@@ -232,30 +270,85 @@ def grid_scenario(n, n_agents, horizon=7200, seed=1, arterial_every=8, exits=Non
     rng = np.random.default_rng(seed + 2)
     perm = rng.permutation(n_agents)            # add_demand shuffles the OD rows (queue_class.py:198)
     origin, destin, dept = origin[perm], destin[perm], od.dept_time.values[perm]
-    s, e, w = f.edge_start, f.edge_end, f.edge_fft
     if device_routes:
         # no host routing at all: DeviceSim(flat, routes_from_router=True) + attach_router(graph(flat), flat)
         add_agents(f, origin, destin, dept, np.full(n_agents, 8), None, exits)
         return f
-    if router is None:
-        from . import sp_interface
-        g = sp_interface.from_arrays(e, s, w, max_vertex_id=N - 1)      # reversed graph
-        _, parent = g.sssp_batch(exits.astype(np.int32), want_dist=False)
-        g.free()
-    else:
-        parent = router(e, s, w, exits)
-    # next link at node v towards exit d: the link (v -> parent[d, v])
-    key = s.astype(np.int64) * N + e
-    order = np.argsort(key)
-    v = np.arange(N, dtype=np.int64)
-    next_link = np.full((len(exits), N), -1, np.int32)
-    for d in range(len(exits)):
-        p = parent[d].astype(np.int64)
-        ok = p >= 0
-        pos = np.searchsorted(key[order], v[ok] * N + p[ok])
-        next_link[d, v[ok]] = N + order[pos]
+    next_link = next_link_tables(f, exits, router)
     f.next_link_table = next_link
     add_agents(f, origin, destin, dept, np.full(n_agents, 8), next_link, exits)
+    return f
+
+
+def town_edges(n, seed=1, drop=0.12, oneway=0.08, diag=0.06, hubs=2, hub_links=10):
+    """An irregular street network on the jittered n x n lattice (the stand-in for the Berkeley / Butte inputs the
+    reference does not ship): a share of the streets removed, a share one-way, diagonal shortcuts (node degrees from
+    0 to 8), a few hubs with `hub_links` extra two-way links to random nodes (more out-links than the node kernel
+    caches), links in shuffled order, 1-4 lanes, three speed classes."""
+    rng = np.random.default_rng(seed)
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    nid = ii * n + jj
+    und = [np.stack([nid[:-1, :].ravel(), nid[1:, :].ravel()], 1), np.stack([nid[:, :-1].ravel(), nid[:, 1:].ravel()], 1)]
+    und = np.concatenate(und)
+    und = und[rng.random(len(und)) >= drop]
+    d1 = np.stack([nid[:-1, :-1].ravel(), nid[1:, 1:].ravel()], 1)
+    d2 = np.stack([nid[1:, :-1].ravel(), nid[:-1, 1:].ravel()], 1)
+    dg = np.concatenate([d1[rng.random(len(d1)) < diag / 2], d2[rng.random(len(d2)) < diag / 2]])
+    und = np.concatenate([und, dg])
+    for h in rng.choice(n * n, hubs, replace=False):
+        far = rng.choice(np.setdiff1d(np.arange(n * n), [h]), hub_links, replace=False)
+        und = np.concatenate([und, np.stack([np.full(hub_links, h), far], 1)])
+    und = np.unique(np.sort(und, 1), axis=0)                         # no duplicate streets
+    und = und[rng.permutation(len(und))]
+    u = rng.random(len(und))
+    fwd, bwd = u >= oneway / 2, (u < oneway / 2) | (u >= oneway)     # one direction only below `oneway`
+    s = np.concatenate([und[fwd, 0], und[bwd, 1]])
+    e = np.concatenate([und[fwd, 1], und[bwd, 0]])
+    perm = rng.permutation(len(s))
+    s, e = s[perm], e[perm]
+    lanes = rng.choice([1, 1, 1, 2, 2, 3, 4], len(s))
+    maxmph = rng.choice([25, 25, 35, 45], len(s))
+    return s.astype(np.int64), e.astype(np.int64), lanes, maxmph
+
+
+def town_scenario(n, n_agents, horizon=600, seed=1, n_exits=8, signals=0.04, priority=0.03, router=None,
+                  device_routes=False):
+    """Irregular network + signal and priority nodes + demand from every node that can reach its exit.  Signal nodes
+    alternate between the roughly north-south and the roughly east-west approaches (the source link is always
+    green), priority nodes rank all their approaches in a random order."""
+    rng = np.random.default_rng(seed + 10)
+    lon, lat = grid_coords(n, seed)
+    s, e, lanes, maxmph = town_edges(n, seed)
+    f = flat_from_edges(lon, lat, s, e, lanes, maxmph)
+    N = n * n
+    indeg = np.diff(f.node_in_ptr)
+    pick = rng.random(N)
+    f.node_type = np.where((pick < signals) & (indeg >= 3), 1, np.where((pick > 1 - priority) & (indeg >= 3), 2, 0)).astype(np.uint8)
+    node_of = np.repeat(np.arange(N), indeg)
+    il = f.node_in_links
+    real = il >= N
+    dx = np.abs(lon[f.link_end_node[il]] - lon[np.maximum(f.link_start_node[il], 0)]) * M_PER_DEG_LON
+    dy = np.abs(lat[f.link_end_node[il]] - lat[np.maximum(f.link_start_node[il], 0)]) * M_PER_DEG_LAT
+    phase = np.where(real, np.where(dy >= dx, 1, 2), 3)
+    f.node_in_phase = np.where(f.node_type[node_of] == 1, phase, 0).astype(np.uint8)
+    # priority ranks: a random order of each node's approaches (rank = position among the node's sorted draws)
+    draw = rng.random(len(il))
+    o = np.lexsort((draw, node_of))
+    rank = np.empty(len(il), np.int64)
+    rank[o] = np.arange(len(il)) - f.node_in_ptr[node_of[o]]
+    f.node_in_prio = np.where(f.node_type[node_of] == 2, rank, -1).astype(np.int32)
+
+    exits = rng.choice(N, n_exits, replace=False).astype(np.int64)
+    next_link = next_link_tables(f, exits, router)
+    dslot = rng.integers(0, n_exits, n_agents)
+    origin = np.empty(n_agents, np.int64)
+    for d in range(n_exits):
+        ok = np.flatnonzero(next_link[d] >= 0)
+        m = dslot == d
+        origin[m] = rng.choice(ok, int(m.sum()))
+    dept = np.sort(rng.integers(0, horizon, n_agents))[rng.permutation(n_agents)]
+    f.next_link_table = next_link
+    add_agents(f, origin, exits[dslot], dept, rng.choice([6, 8, 8, 8, 12], n_agents), None if device_routes else next_link, exits)
     return f
 
 

@@ -159,3 +159,66 @@ def test_config4_size_window_matches_oracle():
     assert sm["links_in_use"] == int(((so["q"] + so["r"])[real] > 0).sum())
     assert cd["moves"] > 500_000 and int(dev.link_congested().sum()) > 0
     dev.close(); orc.close()
+
+
+def _town(device_routes=False):
+    from spatial_queue_b200 import synth
+    return synth.town_scenario(48, 40_000, horizon=300, seed=5, device_routes=device_routes)
+
+
+def test_town_network_matches_oracle():
+    """Irregular topology (stand-in for configs 2 / 3): streets removed, one-ways, diagonals, two hubs with more
+    out-links than the node kernel caches, 1-4 lanes, signal and priority nodes, mixed vehicle lengths, 40k agents
+    in five minutes (spill-back everywhere), links closed at tick 100 and half of them reopened at tick 250.
+    CUDA tick against the C oracle: bit-exact state and capacities at every stop."""
+    from oracle.tick import OracleSim
+    from spatial_queue_b200.tick import DeviceSim
+    flat = _town()
+    N = len(flat.node_key)
+    assert np.diff(flat.node_out_ptr).max() > 8 and (flat.node_type == 1).sum() > 20 and (flat.node_type == 2).sum() > 20
+    assert (flat.link_reverse[N:] < 0).sum() > 100
+    dev, orc = DeviceSim(flat, seed=11), OracleSim(flat, seed=11)
+    for s in (dev, orc):
+        s.set_shelter_after(400)
+        s.set_congest_after(90)
+    rng = np.random.default_rng(0)
+    shut = (N + rng.choice(len(flat.edge_start), 60, replace=False)).astype(np.int32)
+    t = 0
+    for stop in (1, 50, 100, 180, 250, 420, 700):
+        for s in (dev, orc):
+            if t == 100:
+                s.set_link_closed(shut, np.ones(len(shut), np.uint8))
+            if t == 250:
+                s.set_link_closed(shut[::2], np.zeros(len(shut[::2]), np.uint8))
+            s.run(t, stop - t)
+        t = stop
+        sd, so = dev.state(), orc.state()
+        assert state_digest(sd) == state_digest(so), f"tick {t - 1}"
+        for k in ("in_c", "out_c", "storage_c"):
+            assert sd[k].tobytes() == so[k].tobytes(), (k, t)
+        assert (dev.link_congested() == orc.link_congested()).all()
+    cd, co = dev.counters(), orc.counters()
+    assert cd["agent_steps"] == co["agent_steps"] and cd["moves"] == co["moves"] and cd["arrivals"] == co["arrivals"]
+    assert cd["moves"] > 100_000 and cd["arrivals"] > 1000
+    assert (dev.agent_state()["status"] == 4).sum() > 0          # some gave up (shelter_a1)
+    dev.close(); orc.close()
+
+
+def test_town_device_router_on_free_flow_weights_equals_fixed_routes():
+    """Rerouting every agent each 60 s on weights that never change must not change anything: the device router
+    (reverse trees on the irregular network -> next-link tables -> staggered reroute blocks) against the C oracle
+    walking the routes fixed at t=0."""
+    from oracle.tick import OracleSim
+    from spatial_queue_b200 import synth
+    from spatial_queue_b200.tick import DeviceSim
+    fixed, routed = _town(), _town(device_routes=True)
+    orc = OracleSim(fixed, seed=4)
+    dev = DeviceSim(routed, seed=4, routes_from_router=True)
+    dev.attach_router(synth.routing_graph(routed), routed, reroute_freq=60, weight_freq=10 ** 6)
+    t = 0
+    for stop in (1, 61, 200, 500):
+        dev.run(t, stop - t)
+        orc.run(t, stop - t)
+        t = stop
+        assert state_digest(dev.state()) == state_digest(orc.state()), f"tick {t - 1}"
+    dev.close(); orc.close()
