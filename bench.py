@@ -462,6 +462,29 @@ def main():
         e2e = {"value": e2e_val, "unit": "trees/s", "h2d_bytes_per_step": int(oh.nbytes),
                "d2h_bytes_per_step": int(dh.nbytes + ph.nbytes), "trees_per_call": eb}
 
+    # ---- e2e of the call the reference's agents make: get_path = distance(destin) + route(destin) per agent ----------
+    # (sp_route_batch: host origins + destinations in, host distances + paths out; one tree per origin on the device)
+    e2e_routes = None
+    if rank == 0 or world > 1:
+        rb = B
+        orr = origins_for(rank, rb, V, step=11)
+        drr = np.random.default_rng(100 + rank).integers(0, V, rb).astype(np.int32)
+        g.route_batch(orr[:512], drr[:512])
+        g.route_batch(orr, drr)                       # sizes the chunk buffers and the page-locked path pool
+        t0 = time.perf_counter()
+        reps = 2
+        for _ in range(reps):
+            rd, roff, rlen, rpool = g.route_batch(orr, drr)
+        wall = time.perf_counter() - t0
+        if world > 1:
+            tw = torch.tensor([wall], device="cuda")
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+            wall = float(tw.item())
+        e2e_routes = {"value": world * rb * reps / wall, "unit": "trees/s", "call": "sp_route_batch (one tree per agent, "
+                      "distance + path returned)", "h2d_bytes_per_step": int(orr.nbytes + drr.nbytes),
+                      "d2h_bytes_per_step": int(rd.nbytes + roff.nbytes + rlen.nbytes + rpool.nbytes),
+                      "trees_per_call": rb, "mean_path_vertices": float(rlen.mean())}
+
     clocks = sampler.stop() if rank == 0 else None
     line = None
     if rank == 0:
@@ -480,7 +503,7 @@ def main():
                              "traffic": SSSP_TRAFFIC_PER_TREE * B if SSSP_TRAFFIC_PER_TREE else None,
                              "kernel": "sssp_warp_kernel (+ sssp_parent_kernel, both inside kernel_ms)", "kernel_ms": kernel_ms,
                              "bytes_per_tree": bytes_per_tree, "peak_source": peak_src},
-                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+                "e2e": e2e, "e2e_routes": e2e_routes, "gpu_launches": int(launches), "clocks": clocks}
 
     # ---- HP-1 + CPU baselines: single GPU, rank 0 ----------------------------------------------------------------
     if rank == 0 and world == 1:

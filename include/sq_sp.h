@@ -74,6 +74,18 @@ int sp_sssp_batch(Graph* graph, const int* origins, int n, double* dist_out, int
 /* reverse != 0: trees on the reversed graph (distances to, and next vertex towards, each origin). */
 int sp_sssp_batch_ex(Graph* graph, const int* origins, int n, double* dist_out, int* parent_out, int reverse);
 
+/* Agent.get_path for a batch of agents (queue_class.py:491-512 / model/queue_class.py:491-512: g.dijkstra(origin,
+ * destin), sp.distance(destin), sp.route(destin)): for every pair k the distance origins[k] -> dests[k] (DBL_MAX
+ * when there is no path, like distance()) and the path as a vertex sequence origins[k], ..., dests[k] -- what
+ * route() returns as (start, end) pairs; empty when there is no path or origin == destination.  One full tree per
+ * DISTINCT origin is computed on the device and walked there, so only distances and paths cross PCIe (the full
+ * tables of sp_sssp_batch are 12 bytes per vertex per tree).  Host arrays: dist_out[n], route_off_out[n] (offset
+ * of path k in the pool), route_len_out[n] (vertices in path k).  The pool is page-locked memory owned by the graph,
+ * valid until the next sp_route_batch or sp_free_graph on it. */
+int sp_route_batch(Graph* graph, const int* origins, const int* dests, int n, double* dist_out,
+                   long long* route_off_out, int* route_len_out);
+const int* sp_route_pool(Graph* graph);
+
 /* Page-locked host memory for sp_sssp_batch outputs: with both destinations allocated here the device-to-host
  * copies overlap the computation of the next chunk of trees (PCIe-bound instead of staging-bound). */
 void* sp_alloc_host(size_t bytes);

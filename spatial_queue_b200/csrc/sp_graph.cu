@@ -25,6 +25,8 @@
 #include <sstream>
 #include <string>
 #include <unordered_map>
+#include <numeric>
+#include <cstring>
 #include <vector>
 
 #include "../../include/sq_sp.h"
@@ -1061,6 +1063,13 @@ struct SqGraph {
   int pending_check_n = 0;      // trees of the last auto warp batch whose overflow count has not been looked at yet
   unsigned* d_wfar = nullptr;
   int wfar_warps = 0, wfar_cap = 0;
+  // sp_route_batch: per-pair device arrays, path pool on both sides (the host pool is page-locked)
+  int* d_pair = nullptr;        // 3 x pair_cap: destination, tree, path length
+  long long* d_pair_off = nullptr;
+  double* d_pair_dist = nullptr;
+  size_t pair_cap = 0;
+  int* d_pool = nullptr; size_t d_pool_cap = 0;
+  int* h_pool = nullptr; size_t h_pool_cap = 0;
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
 
   // tuning
@@ -1077,6 +1086,47 @@ struct SqShortestPath {
   std::vector<double> distances;
   std::vector<int> parent;
 };
+
+// -------------------------------------------------------------------------------------------------
+// Route extraction (sp_route_batch): Agent.get_path needs distance(destin) and route(destin) of its tree, not the
+// tree.  One thread per (origin, destination) pair walks the predecessor row from the destination back to the
+// origin, once to count and once to write the path in forward order, so only paths cross PCIe.
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) route_len_kernel(const u64* __restrict__ dist, const int* __restrict__ parent,
+                                                        const int* __restrict__ origins, int V, int tree0, int n,
+                                                        const int* __restrict__ pdest, const int* __restrict__ ptree,
+                                                        int* __restrict__ plen, double* __restrict__ pdist) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int tl = ptree[k] - tree0;
+  const int dest = pdest[k];
+  const int src = origins[ptree[k]];
+  const size_t row = (size_t)tl * V;
+  const u64 d = (src >= 0 && src < V) ? dist[row + dest] : DIST_INF_BITS;
+  pdist[k] = __longlong_as_double((long long)d);
+  int len = 0;
+  if (d != DIST_INF_BITS && dest != src) {
+    int v = dest;
+    len = 1;
+    while (v != src && len <= V) { v = parent[row + v]; ++len; if (v < 0) { len = 0; break; } }
+    if (len > V) len = 0;
+  }
+  plen[k] = len;
+}
+
+__global__ void __launch_bounds__(128) route_write_kernel(const int* __restrict__ parent, int V, int tree0, int n,
+                                                          const int* __restrict__ pdest, const int* __restrict__ ptree,
+                                                          const int* __restrict__ plen, const long long* __restrict__ poff,
+                                                          long long pool0, int* __restrict__ pool) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int len = plen[k];
+  if (len == 0) return;
+  const size_t row = (size_t)(ptree[k] - tree0) * V;
+  int* out = pool + (poff[k] - pool0);
+  int v = pdest[k];
+  for (int i = len - 1; i >= 0; --i) { out[i] = v; if (i) v = parent[row + v]; }
+}
 
 static void g_add_edge(SqGraph* g, int v1, int v2, double w) {
   if (!g->directed && v1 > v2) std::swap(v1, v2);
@@ -1654,6 +1704,8 @@ void sp_free_graph(Graph* g) {
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
   cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail); cudaFree(g->d_wfar);
+  cudaFree(g->d_pair); cudaFree(g->d_pair_off); cudaFree(g->d_pair_dist); cudaFree(g->d_pool);
+  if (g->h_pool) cudaFreeHost(g->h_pool);
   if (g->s_compute) {
     cudaStreamDestroy(g->s_compute); cudaStreamDestroy(g->s_copy);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(g->ev_done[i]); cudaEventDestroy(g->ev_copied[i]); }
@@ -1784,6 +1836,17 @@ void sp_free_host(void* ptr) {
   if (ptr) cudaFreeHost(ptr);
 }
 
+static int g_ensure_streams(SqGraph* g) {
+  if (g->s_compute) return SQ_OK;
+  SQ_CUDA_TRY(cudaStreamCreateWithFlags(&g->s_compute, cudaStreamNonBlocking));
+  SQ_CUDA_TRY(cudaStreamCreateWithFlags(&g->s_copy, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) {
+    SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_done[i], cudaEventDisableTiming));
+    SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_copied[i], cudaEventDisableTiming));
+  }
+  return SQ_OK;
+}
+
 int sp_sssp_batch(Graph* g, const int* origins, int n, double* dist_out, int* parent_out) {
   return sp_sssp_batch_ex(g, origins, n, dist_out, parent_out, 0);
 }
@@ -1815,14 +1878,7 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
     SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * 2 * chunk * V));
     g->parent_buf_elems = 2 * chunk * V;
   }
-  if (!g->s_compute) {
-    SQ_CUDA_TRY(cudaStreamCreateWithFlags(&g->s_compute, cudaStreamNonBlocking));
-    SQ_CUDA_TRY(cudaStreamCreateWithFlags(&g->s_copy, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; ++i) {
-      SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_done[i], cudaEventDisableTiming));
-      SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_copied[i], cudaEventDisableTiming));
-    }
-  }
+  if (int rc = g_ensure_streams(g)) return rc;
   const bool pinned = is_pinned_host(dist_out) && is_pinned_host(parent_out);
   int k = 0;
   for (size_t off = 0; off < (size_t)n; off += chunk, ++k) {
@@ -1850,6 +1906,127 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
   g->last_stats[0] = n;
   return g_fetch_stats(g);
 }
+
+int sp_route_batch(Graph* g, const int* origins, const int* dests, int n, double* dist_out, long long* route_off_out,
+                   int* route_len_out) {
+  if (!g || ((!origins || !dests || !dist_out || !route_off_out || !route_len_out) && n > 0))
+    return sq::set_error(SQ_ERR_ARG, "sp_route_batch: null argument");
+  if (n <= 0) return SQ_OK;
+  if (int rc = g_build_and_upload(g)) return rc;
+  const int Vi = g->V;
+  const size_t V = (size_t)Vi;
+  for (int k = 0; k < n; ++k)
+    if (dests[k] < 0 || dests[k] >= Vi) return sq::set_error(SQ_ERR_ARG, "sp_route_batch: destination out of range");
+  // one tree per distinct origin; pairs sorted by tree so that a chunk of trees serves a contiguous run of pairs
+  std::vector<int> uo(origins, origins + n);
+  std::sort(uo.begin(), uo.end());
+  uo.erase(std::unique(uo.begin(), uo.end()), uo.end());
+  const int nt = (int)uo.size();
+  std::vector<int> order((size_t)n), ptree((size_t)n), pdest((size_t)n);
+  {
+    std::vector<int> tree_of((size_t)n);
+    for (int k = 0; k < n; ++k) tree_of[k] = (int)(std::lower_bound(uo.begin(), uo.end(), origins[k]) - uo.begin());
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return tree_of[a] < tree_of[b]; });
+    for (int i = 0; i < n; ++i) { ptree[i] = tree_of[order[i]]; pdest[i] = dests[order[i]]; }
+  }
+  if (int rc = g_ensure_streams(g)) return rc;
+  cudaStream_t st = g->s_compute;
+  if (g->origins_cap < nt) {
+    cudaFree(g->d_origins); g->d_origins = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_origins, sizeof(int) * (size_t)nt));
+    g->origins_cap = nt;
+  }
+  if (g->pair_cap < (size_t)n) {
+    cudaFree(g->d_pair); cudaFree(g->d_pair_off); cudaFree(g->d_pair_dist);
+    g->d_pair = nullptr; g->d_pair_off = nullptr; g->d_pair_dist = nullptr; g->pair_cap = 0;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_pair, sizeof(int) * 3 * (size_t)n));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_pair_off, sizeof(long long) * (size_t)n));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_pair_dist, sizeof(double) * (size_t)n));
+    g->pair_cap = (size_t)n;
+  }
+  int* d_pdest = g->d_pair;
+  int* d_ptree = g->d_pair + g->pair_cap;
+  int* d_plen = g->d_pair + 2 * g->pair_cap;
+  SQ_CUDA_TRY(cudaMemcpyAsync(g->d_origins, uo.data(), sizeof(int) * (size_t)nt, cudaMemcpyHostToDevice, st));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_pdest, pdest.data(), sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, st));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_ptree, ptree.data(), sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, st));
+  // trees per chunk: as many as a third of the free memory holds (the tree kernels want thousands per launch)
+  const size_t per_tree = V * (sizeof(u64) + sizeof(int));
+  size_t free_b = 0, total_b = 0;
+  SQ_CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
+  const size_t have = std::min(g->dist_buf_elems, g->parent_buf_elems) / std::max<size_t>(V, 1);   // trees the buffers hold already
+  size_t chunk = std::min<size_t>((size_t)nt, std::max(have, std::max<size_t>(64, (free_b / 3) / std::max<size_t>(per_tree, 1))));
+  if (const char* cap = getenv("SQB200_ROUTE_CHUNK")) chunk = std::min(chunk, (size_t)std::max(1, atoi(cap)));   // tests: force several chunks
+  if (g->dist_buf_elems < chunk * V) {
+    cudaFree(g->d_dist_buf); g->d_dist_buf = nullptr; g->dist_buf_elems = 0;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_dist_buf, sizeof(u64) * chunk * V));
+    g->dist_buf_elems = chunk * V;
+  }
+  if (g->parent_buf_elems < chunk * V) {
+    cudaFree(g->d_parent_buf); g->d_parent_buf = nullptr; g->parent_buf_elems = 0;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * chunk * V));
+    g->parent_buf_elems = chunk * V;
+  }
+  std::vector<int> len((size_t)n);
+  std::vector<long long> off((size_t)n);
+  std::vector<double> dist((size_t)n);
+  long long pool_used = 0;
+  int p0 = 0;
+  for (size_t t0 = 0; t0 < (size_t)nt; t0 += chunk) {
+    const int m = (int)std::min(chunk, (size_t)nt - t0);
+    int p1 = p0;
+    while (p1 < n && ptree[p1] < (int)t0 + m) ++p1;
+    const int np = p1 - p0;
+    const int fmt = g->parent_format;
+    g->parent_format = 0;
+    const int rc_run = g_run_batch_device(g, g->d_origins + t0, m, g->d_dist_buf, g->d_parent_buf, st, false);
+    g->parent_format = fmt;
+    if (rc_run) return rc_run;
+    if (np > 0) {
+      const int blocks = (np + 127) / 128;
+      route_len_kernel<<<blocks, 128, 0, st>>>(g->d_dist_buf, g->d_parent_buf, g->d_origins, Vi, (int)t0, np, d_pdest + p0,
+                                              d_ptree + p0, d_plen + p0, g->d_pair_dist + p0);
+      sq::count_launch();
+      SQ_CUDA_TRY(cudaMemcpyAsync(len.data() + p0, d_plen + p0, sizeof(int) * (size_t)np, cudaMemcpyDeviceToHost, st));
+      SQ_CUDA_TRY(cudaMemcpyAsync(dist.data() + p0, g->d_pair_dist + p0, sizeof(double) * (size_t)np, cudaMemcpyDeviceToHost, st));
+      SQ_CUDA_TRY(cudaStreamSynchronize(st));
+      const long long pool0 = pool_used;
+      for (int i = p0; i < p1; ++i) { off[i] = pool_used; pool_used += len[i]; }
+      const size_t need = (size_t)(pool_used - pool0);
+      if (need > 0) {
+        if (g->d_pool_cap < need) {
+          cudaFree(g->d_pool); g->d_pool = nullptr; g->d_pool_cap = 0;
+          SQ_CUDA_TRY(cudaMalloc(&g->d_pool, sizeof(int) * need));
+          g->d_pool_cap = need;
+        }
+        if (g->h_pool_cap < (size_t)pool_used) {
+          const size_t cap = std::max<size_t>((size_t)pool_used, std::max<size_t>(2 * g->h_pool_cap, 1 << 16));
+          int* nb = nullptr;
+          SQ_CUDA_TRY(cudaMallocHost(&nb, sizeof(int) * cap));
+          if (g->h_pool) { memcpy(nb, g->h_pool, sizeof(int) * (size_t)pool0); cudaFreeHost(g->h_pool); }
+          g->h_pool = nb; g->h_pool_cap = cap;
+        }
+        SQ_CUDA_TRY(cudaMemcpyAsync(g->d_pair_off + p0, off.data() + p0, sizeof(long long) * (size_t)np, cudaMemcpyHostToDevice, st));
+        route_write_kernel<<<blocks, 128, 0, st>>>(g->d_parent_buf, Vi, (int)t0, np, d_pdest + p0, d_ptree + p0, d_plen + p0,
+                                                  g->d_pair_off + p0, pool0, g->d_pool);
+        sq::count_launch();
+        SQ_CUDA_TRY(cudaMemcpyAsync(g->h_pool + pool0, g->d_pool, sizeof(int) * need, cudaMemcpyDeviceToHost, st));
+        SQ_CUDA_TRY(cudaStreamSynchronize(st));
+      }
+    }
+    p0 = p1;
+  }
+  SQ_CUDA_TRY(cudaStreamSynchronize(st));
+  for (int i = 0; i < n; ++i) {
+    const int k = order[i];
+    dist_out[k] = dist[i]; route_off_out[k] = off[i]; route_len_out[k] = len[i];
+  }
+  g->last_stats[0] = nt;
+  return g_fetch_stats(g);
+}
+
+const int* sp_route_pool(Graph* g) { return g ? g->h_pool : nullptr; }
 
 ShortestPath* dijkstra(Graph* g, int origin_v, int destination) {
   SqShortestPath* sp = new SqShortestPath();

@@ -373,26 +373,19 @@ class Network:
     # ---------------------------------------------------------------------------------------------------------
     def route_agents(self, t, agents=None):
         """`agent.get_path(t, g)` + `agent.find_next_link(...)` (run_traffic_simulation.py:107-109) for `agents`
-        (default: all), computed as one batch of full trees from the distinct start nodes.  Returns the agents
-        whose route changed."""
+        (default: all), computed as one `sp_route_batch` call.  Returns the agents whose route changed."""
         agents = list(self.agents.values()) if agents is None else list(agents)
         if not agents:
             return []
-        starts = sorted({a.current_link_end_nid for a in agents})
-        slot = {n: i for i, n in enumerate(starts)}
-        dist, parent = self.g.sssp_batch(np.array(starts, np.int32))
+        # one tree per distinct start node, computed and walked on the GPU: only distances and paths come back
+        dist, off, ln, pool = self.g.route_batch([a.current_link_end_nid for a in agents], [a.destin_nid for a in agents])
         changed = []
-        for a in agents:
-            row = slot[a.current_link_end_nid]
-            d = float(dist[row, a.destin_nid])
+        for i, a in enumerate(agents):
+            d = float(dist[i])
             hops = []
             if d <= 1e8:
-                node, par = a.destin_nid, parent[row]
-                while node != a.current_link_end_nid:
-                    p = int(par[node])
-                    hops.append((p, node))
-                    node = p
-                hops.reverse()
+                path = pool[off[i]: off[i] + ln[i]].tolist()
+                hops = list(zip(path[:-1], path[1:]))
             before = dict(a.route)
             a._adopt(t, d, hops)
             a.find_next_link(node2link_dict=self.node2link_dict)

@@ -156,6 +156,26 @@ class Graph:
                                      p.ctypes.data if want_parent else None, 1 if reverse else 0), "sp_sssp_batch")
         return d, p
 
+    def route_batch(self, origins, dests):
+        """`Agent.get_path` for many agents in one call (queue_class.py:491-512): for every pair the distance
+        origin -> destination (DBL_MAX if unreachable) and the path as a vertex sequence.  Returns
+        (dist f64[n], off i64[n], length i32[n], pool i32[total]): path k = pool[off[k] : off[k] + length[k]] =
+        origin, ..., destination (empty when unreachable or origin == destination).  One tree per distinct origin
+        is computed and walked on the GPU; only distances and paths come back."""
+        o = np.ascontiguousarray(origins, dtype=np.int32)
+        d = np.ascontiguousarray(dests, dtype=np.int32)
+        if o.shape != d.shape:
+            raise ValueError("origins and dests must have the same length")
+        n = len(o)
+        dist, off, ln = np.empty(n, np.float64), np.empty(n, np.int64), np.empty(n, np.int32)
+        check(lib().sp_route_batch(self._h, o.ctypes.data, d.ctypes.data, n, dist.ctypes.data, off.ctypes.data,
+                                   ln.ctypes.data), "sp_route_batch")
+        total = int((off + ln).max()) if n else 0
+        pool = np.empty(total, np.int32)
+        if total:
+            C.memmove(pool.ctypes.data, lib().sp_route_pool(self._h), 4 * total)
+        return dist, off, ln, pool
+
     def set_weights_device(self, weights_dev, stream=None):
         """Per-edge weights from a torch CUDA float64 tensor (creategraph order, NaN = keep)."""
         import torch

@@ -300,3 +300,76 @@ def test_auto_mode_learns_from_ring_overflows(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
     assert overflows[0] > 50 and overflows[-1] < overflows[0]
     g.free()
+
+
+def _walk(par, origin, dest):
+    path = [dest]
+    while path[-1] != origin:
+        path.append(int(par[path[-1]]))
+    return path[::-1]
+
+
+def test_route_batch_equals_get_path_of_the_oracle(spi):
+    """sp_route_batch (Agent.get_path for a batch: distance(destin) + route(destin), queue_class.py:491-512) against
+    the oracle's Dijkstra with the reference's early exit at the destination: distances bit for bit, paths equal to
+    the walk over the canonical predecessors, path cost re-summed forward == distance exactly; repeated origins,
+    origin == destination, unreachable pairs, an origin outside the graph; a call in several chunks of trees."""
+    from oracle import sssp as osssp
+    rng = np.random.default_rng(5)
+    for V, E, n in ((40, 60, 200), (2500, 9000, 3000)):
+        s = rng.integers(0, V, E).astype(np.int32)
+        e = rng.integers(0, V, E).astype(np.int32)
+        w = np.where(rng.random(E) < 0.3, np.round(rng.random(E) * 20) + 1.0, rng.random(E) * 100.0)
+        og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1)
+        g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+        o = rng.integers(0, V, n).astype(np.int32)
+        o[: n // 4] = o[0]                                # many agents at the same node
+        d = rng.integers(0, V, n).astype(np.int32)
+        d[5] = o[5]
+        o[7] = V + 3
+        dist, off, ln, pool = g.route_batch(o, d)
+        wmin = {}
+        for a, b, c in zip(s, e, w):
+            wmin[(int(a), int(b))] = min(c, wmin.get((int(a), int(b)), np.inf))
+        trees = {}
+        reached = 0
+        for k in range(n):
+            if k == 7:
+                assert dist[k] > 1e300 and ln[k] == 0
+                continue
+            do, _ = og.dijkstra(int(o[k]), int(d[k]))      # early exit at the destination, like the reference
+            assert dist[k].tobytes() == do[d[k]].tobytes(), k
+            path = pool[off[k]: off[k] + ln[k]].tolist()
+            if do[d[k]] > 1e300 or o[k] == d[k]:
+                assert path == []
+                continue
+            reached += 1
+            if int(o[k]) not in trees:
+                full, _ = og.dijkstra(int(o[k]))
+                trees[int(o[k])] = og.canonical_parents(int(o[k]), full)
+            assert path == _walk(trees[int(o[k])], int(o[k]), int(d[k])), k
+            acc = 0.0
+            for a, b in zip(path[:-1], path[1:]):
+                acc = acc + wmin[(a, b)]
+            assert acc == dist[k]
+        assert reached > n // 5
+        g.free()
+
+
+@pytest.mark.parametrize("chunk", [None, 97])
+def test_route_batch_on_the_grid_matches_full_tables(spi, chunk, monkeypatch):
+    if chunk:
+        monkeypatch.setenv("SQB200_ROUTE_CHUNK", str(chunk))      # 1500 trees in 16 chunks
+    s, e, w = grid_graph(64, seed=3)
+    V = 64 * 64
+    g = spi.from_arrays(s, e, w)
+    rng = np.random.default_rng(1)
+    o = rng.permutation(V)[:1500].astype(np.int32)
+    d = rng.integers(0, V, 1500).astype(np.int32)
+    dist, off, ln, pool = g.route_batch(o, d)
+    dd, pp = g.sssp_batch(o)
+    assert dist.tobytes() == dd[np.arange(1500), d].tobytes()
+    for k in range(0, 1500, 37):
+        assert pool[off[k]: off[k] + ln[k]].tolist() == (_walk(pp[k], int(o[k]), int(d[k])) if o[k] != d[k] else [])
+    assert int(ln.sum()) == len(pool) and ln.max() > 60
+    g.free()
