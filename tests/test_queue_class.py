@@ -228,3 +228,34 @@ def test_closure_schedule_equals_per_tick_calls(tmp_path):
         ds.append(state_digest(sched.sim.state()))
     assert dm == ds
     assert (manual.sim.agent_state()["arrive_tick"] == sched.sim.agent_state()["arrive_tick"]).all()
+
+
+@pytest.mark.gpu
+def test_get_partial_path_matches_the_reference_class():
+    """Agent.get_partial_path of the mirror (look-ahead re-plan + splice, model/queue_class.py:514-575) on the GPU
+    `sp` library against tests/golden/partial_path.json, which the unmodified reference class produced on its own
+    sp library: returned tuple, route dict (content and order), route distance and status, exactly."""
+    import types
+    from ctypes import c_double
+    from spatial_queue_b200 import sp_interface
+    z = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "partial_path.json")))
+    n = z["n"]
+    lon, lat = synth.grid_coords(n, seed=z["seed"])
+    s, e = synth.grid_edges(n)
+    length, _, maxmph = synth.grid_attributes(n, s, e, lon, lat, z["arterial_every"])
+    w = length / maxmph * 2.237
+    node2link = {(int(a), int(b)): i for i, (a, b) in enumerate(zip(s, e))}
+    for k, c in enumerate(z["cases"]):
+        g = sp_interface.from_arrays(s, e, w, max_vertex_id=n * n - 1)
+        links = {i: types.SimpleNamespace(travel_time=float(w[i])) for i in range(len(s))}
+        a = qc.Agent(k, c["origin"], c["destin"], 0, 8, 1, None)
+        a.get_path(0, g=g)
+        assert [[int(x), int(y)] for x, y in a.route.items()] == c["route_before"], k
+        cl = c["closed"]
+        g.update_edge(int(s[cl]), int(e[cl]), c_double(1e8))
+        links[cl].travel_time = 1e8
+        ret = a.get_partial_path(5, g=g, link_id_dict=links, node2link_dict=node2link)
+        assert (None if ret is None else [float(x) for x in ret]) == c["ret"], k
+        assert [[int(x), int(y)] for x, y in a.route.items()] == c["route_after"], k
+        assert float(a.route_distance) == c["route_distance"] and a.status == c["status"], k
+        g.free()
