@@ -131,6 +131,13 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* router);
  * `seconds` on one real link gives up (status SQ_SHELTER_A1) and leaves the link before the link model of that tick.
  * 0 (default) switches the rule off. */
 int sq_set_shelter_after(SqSim* sim, int32_t seconds);
+/* A driver rule took agents off the road (Butte's shelter_a2 detour rule, model/dta_meso_butte.py:199-263; the
+ * "remove passively sheltered vehicles immediately" step of both drivers, run_traffic_simulation.py:113-118): the
+ * listed ENROUTE agents get `status` (SQ_SHELTER_P or above; 5 = shelter_a2 in spatial_queue_b200/flatten.py) and
+ * stop tick `t`, and leave the queue / run list of their link at once, the other vehicles keeping their order.
+ * Call between ticks.  An agent that is not enroute makes the call fail (SQ_ERR_STATE). */
+int sq_stop_agents(SqSim* sim, int32_t n, const int32_t* agent_idx, int32_t status, int32_t t);
+
 /* The congestion counter of the same loop (run_traffic_simulation.py:100-102; model/dta_meso_butte.py:183-185 uses
  * max(1800, 10 fft)): link.congested is reset every tick (run_traffic_simulation.py:80-82) and then counts the vehicles that have
  * been on the (real) link for more than `seconds`.  0 (default) switches it off; sq_get_link_congested reads the

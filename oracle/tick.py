@@ -23,6 +23,7 @@ def _lib():
         L.oracle_tick_get_counters.argtypes = [vp, vp]
         L.oracle_tick_set_shelter_after.argtypes = [vp, ci]
         L.oracle_tick_set_congest_after.argtypes = [vp, ci]
+        L.oracle_tick_stop_agents.restype = ci; L.oracle_tick_stop_agents.argtypes = [vp, ci, vp, ci, ci]
         L.oracle_tick_get_link_congested.argtypes = [vp, vp]
         L.oracle_tick_get_shelter_state.argtypes = [vp, vp, vp]
         L.oracle_tick_error.restype = C.c_char_p; L.oracle_tick_error.argtypes = [vp]

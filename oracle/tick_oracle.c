@@ -371,6 +371,25 @@ int oracle_tick_step(OSim* s, int t) {
   return 0;
 }
 
+/* A driver rule stops agents between ticks (model/dta_meso_butte.py:199-263, run_traffic_simulation.py:113-118):
+ * status, stop tick, and [v for v in list if v != agent] on both lists of the agent's link. */
+int oracle_tick_stop_agents(OSim* s, int n, const int* agent_idx, int status, int t) {
+  int k;
+  if (status < 3) return fail(s, "stop_agents: not a stopped status", status, -1, -1);
+  for (k = 0; k < n; ++k) {
+    int i = agent_idx[k], cl;
+    if (i < 0 || i >= s->n_agents) return fail(s, "stop_agents: agent index out of range", i, -1, -1);
+    if (s->a_status[i] != SQ_ENROUTE) return fail(s, "stop_agents: agent is not on a link", i, -1, -1);
+    cl = s->a_cur[i];
+    s->a_status[i] = (uint8_t)status;
+    s->a_arrive[i] = t;
+    iv_remove_value(&s->queue[cl], i);
+    iv_remove_value(&s->run[cl], i);
+    s->l_shelter[cl] += 1;
+  }
+  return 0;
+}
+
 int oracle_tick_set_congest_after(OSim* s, int seconds) { s->congest_after = seconds > 0 ? seconds : 0; return 0; }
 int oracle_tick_get_link_congested(OSim* s, long long* out) {
   memcpy(out, s->l_congested, sizeof(long long) * (size_t)s->n_links);

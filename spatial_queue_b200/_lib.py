@@ -78,6 +78,7 @@ def _declare(L):
     L.sq_attach_router.restype = ci; L.sq_attach_router.argtypes = [vp, vp]
     L.sq_set_shelter_after.restype = ci; L.sq_set_shelter_after.argtypes = [vp, i32]
     L.sq_set_congest_after.restype = ci; L.sq_set_congest_after.argtypes = [vp, i32]
+    L.sq_stop_agents.restype = ci; L.sq_stop_agents.argtypes = [vp, i32, vp, i32, i32]
     L.sq_get_link_congested.restype = ci; L.sq_get_link_congested.argtypes = [vp, vp]
     L.sq_get_summary.restype = ci; L.sq_get_summary.argtypes = [vp, vp]
     L.sq_get_shelter_state.restype = ci; L.sq_get_shelter_state.argtypes = [vp, vp, vp]

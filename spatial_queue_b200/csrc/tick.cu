@@ -698,6 +698,53 @@ __global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
   }
 }
 
+// ---- host-ordered stops (sq_stop_agents): a driver rule took vehicles off the road ----------------------------
+// Drivers strip sheltering agents from their link's lists straight away (model/dta_meso_butte.py:256-263,
+// run_traffic_simulation.py:113-118).  Pass 1 marks the agents and their links, pass 2 lets one thread per
+// marked link close the gaps in its ring: the survivors slide towards the tail, in order, and the head and the
+// queue / run boundary move up by what was removed on their side.
+__global__ void k_stop_mark(const TickState s, int n, const int* __restrict__ agent_idx, int status, int t, int* tomb) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int a = agent_idx[i];
+  const int4 rec = s.ag[a].rec;
+  if ((rec.w & 0xff) != SQ_ENROUTE) { raise_error(s, 5, a, -1, rec.y); return; }
+  s.ag[a].rec.w = (rec.w & ~0xff) | (status & 0xff);
+  s.a_arrive[a] = t;
+  atomicAdd(&tomb[rec.y], 1);
+}
+
+__global__ void k_stop_compact(const TickState s, int n, const int* __restrict__ agent_idx, int* tomb) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int l = s.ag[agent_idx[i]].rec.y;
+  if (atomicExch(&tomb[l], 0) <= 0) return;          // another thread of this launch owns the link (or error above)
+  const long long base = s.l_ring_base[l];
+  const unsigned mask = s.l_ring_mask[l];
+  const unsigned h = s.head[l], qt = s.qtail[l], tl = s.tail[l];
+  unsigned j = tl;                                   // next free slot + 1, filling from the tail down
+  int removed = 0, removed_run = 0;
+  long long len = 0;
+  for (unsigned p = tl; p != h; --p) {
+    const int2 e = s.ring[base + ((p - 1u) & mask)];
+    const int w = s.ag[e.x].rec.w;
+    if ((w & 0xff) != SQ_ENROUTE) {
+      ++removed; len += (w >> 8) & 0xff;
+      if ((int)((p - 1u) - qt) >= 0) ++removed_run;
+    } else {
+      --j;
+      if (j != p - 1u) s.ring[base + (j & mask)] = e;
+    }
+  }
+  if (!removed) return;
+  s.head[l] = h + (unsigned)removed;
+  s.qtail[l] = qt + (unsigned)removed_run;
+  s.len_out[l] += len;
+  s.l_shelter[l] += removed;
+  if (s.cong_pos) s.cong_pos[l] = h + (unsigned)removed;   // the congested prefix is recounted by the next link phase
+  atomicAdd(&s.counters[7], (u64)removed);
+}
+
 // ---- route replacement (Agent.get_path + find_next_link) -----------------------------------------------
 __global__ void k_set_routes(const TickState s, int n, const int* agent_idx, const long long* new_off, const int* new_len) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1168,8 +1215,9 @@ static int check_device_error(SqSim* sim) {
   static const char* what[] = {"", "queued vehicle has no next link away from its destination (queue_class.py:312-314)",
                                "vehicle's next link does not leave this node (KeyError at queue_class.py:257-262)",
                                "vehicle ring overflow (link storage bound violated)",
-                               "device route pool exhausted while keeping the old route of an unroutable agent"};
-  return sq::set_error(SQ_ERR_STATE, "%s: agent %d, node %d, link %d", what[e[0] < 5 ? e[0] : 0], e[1], e[2], e[3]);
+                               "device route pool exhausted while keeping the old route of an unroutable agent",
+                               "sq_stop_agents: agent is not on a link (status != enroute)"};
+  return sq::set_error(SQ_ERR_STATE, "%s: agent %d, node %d, link %d", what[e[0] < 6 ? e[0] : 0], e[1], e[2], e[3]);
 }
 
 // Weight refresh + new routing tables (what the drivers do every `wfreq` ticks before the agent loop,
@@ -1370,6 +1418,26 @@ int sq_set_routes(SqSim* sim, int32_t n, const int32_t* agent_idx, const int64_t
   cudaFree(d_idx); cudaFree(d_off); cudaFree(d_len);
   sim->pool_used += add;
   return SQ_OK;
+}
+
+int sq_stop_agents(SqSim* sim, int32_t n, const int32_t* agent_idx, int32_t status, int32_t t) {
+  if (!sim || (n > 0 && !agent_idx)) return sq::set_error(SQ_ERR_ARG, "sq_stop_agents: null argument");
+  if (status < SQ_SHELTER_P || status > 255) return sq::set_error(SQ_ERR_ARG, "sq_stop_agents: status %d is not a stopped status", status);
+  if (n <= 0) return SQ_OK;
+  for (int i = 0; i < n; ++i)
+    if (agent_idx[i] < 0 || agent_idx[i] >= sim->A) return sq::set_error(SQ_ERR_ARG, "sq_stop_agents: agent index %d out of range", agent_idx[i]);
+  int* d_idx = nullptr; int* d_tomb = nullptr;
+  SQ_CUDA_TRY(cudaMalloc(&d_idx, sizeof(int) * (size_t)n));
+  SQ_CUDA_TRY(cudaMalloc(&d_tomb, sizeof(int) * (size_t)sim->L));
+  SQ_CUDA_TRY(cudaMemsetAsync(d_tomb, 0, sizeof(int) * (size_t)sim->L, sim->stream));
+  SQ_CUDA_TRY(cudaMemcpyAsync(d_idx, agent_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, sim->stream));
+  k_stop_mark<<<(n + 127) / 128, 128, 0, sim->stream>>>(sim->st, n, d_idx, status, t, d_tomb);
+  k_stop_compact<<<(n + 127) / 128, 128, 0, sim->stream>>>(sim->st, n, d_idx, d_tomb);
+  sq::count_launch(2); sim->launches += 2;
+  SQ_CUDA_TRY(cudaGetLastError());
+  const int rc = check_device_error(sim);
+  cudaFree(d_idx); cudaFree(d_tomb);
+  return rc;
 }
 
 int sq_set_congest_after(SqSim* sim, int32_t seconds) {

@@ -29,7 +29,7 @@ import pandas as pd
 from . import geo
 from . import sp_interface as interface
 from ._lib import B200LibraryError
-from .flatten import STATUS_NAMES, flatten_network, route_to_links
+from .flatten import STATUS_CODES, STATUS_NAMES, flatten_network, route_to_links
 
 abs_path = ""   # prefix of the Bolinas-style relative file names (queue_class.py:18 uses the module directory)
 
@@ -246,6 +246,8 @@ class Network:
         self.agents = {}
         self.agents_stopped = {}
         self.special_nodes = None
+        self.detour_factor = None      # host route mode: shelter_a2 when a reroute lengthens the trip this many times
+        self._detoured = []
         self._sim = None
         self._flat = None
         self.route_mode = "device"
@@ -386,18 +388,38 @@ class Network:
             if d <= 1e8:
                 path = pool[off[i]: off[i] + ln[i]].tolist()
                 hops = list(zip(path[:-1], path[1:]))
-            before = dict(a.route)
+            before, previous_distance = dict(a.route), a.route_distance
             a._adopt(t, d, hops)
             a.find_next_link(node2link_dict=self.node2link_dict)
             if a.route != before:
                 changed.append(a)
+            # Butte's detour rule (model/dta_meso_butte.py:199-204): the new route is more than `detour_factor`
+            # times the old one -> the agent shelters in place (shelter_a2); applied by _reroute_due
+            if self.detour_factor and a.status == "enroute" and a.route_distance > previous_distance * self.detour_factor:
+                self._detoured.append(a)
         return changed
+
+    def shelter_agents(self, agent_ids, status, t):
+        """What the drivers do when one of their rules stops an agent on the road (shelter_a2 after a detour,
+        model/dta_meso_butte.py:199-204, 256-263; shelter_park / shelter_a1, run_traffic_simulation.py:113-118):
+        the agent takes `status`, leaves its link's queue / run list at once and moves to `agents_stopped`."""
+        agent_ids = list(agent_ids)
+        if not agent_ids:
+            return
+        idx = [self._flat.agent_index[i] for i in agent_ids]
+        self.sim.stop_agents(idx, STATUS_CODES[status], t)
+        for i, aid in zip(idx, agent_ids):
+            a = self._agent_objs[i]
+            a.status = status
+            self._arrive_reported[i] = True
+            self.agents_stopped[aid] = (status, t, a.agent_type)
+            self.agents.pop(aid, None)
 
     # ---------------------------------------------------------------------------------------------------------
     # the device switch
     # ---------------------------------------------------------------------------------------------------------
     def use_gpu(self, seed=0, special_nodes=None, reroute_freq=300, weight_freq=100, route_at_start=True,
-                route_mode="device", shelter_after=3 * 3600, congest_after=1800):
+                route_mode="device", shelter_after=3 * 3600, congest_after=1800, detour_factor=None):
         """Move the simulation onto the GPU.  Call once after `add_demand` (and after any t=0 changes to
         `agent.departure_time`).
 
@@ -417,6 +439,9 @@ class Network:
             raise ValueError("route_mode must be 'device' or 'host'")
         self.route_mode = route_mode
         self._pending_status = {}
+        if detour_factor and route_mode != "host":
+            raise ValueError("detour_factor (Butte's shelter_a2 rule) needs route_mode='host'")
+        self.detour_factor = detour_factor
         if route_mode == "host":
             if route_at_start:
                 self.route_agents(0)
@@ -488,6 +513,9 @@ class Network:
                 links += seq
                 ptr.append(len(links))
             self.sim.set_routes(idx, ptr, links)
+        if self._detoured:
+            gone, self._detoured = self._detoured, []
+            self.shelter_agents([a.agent_id for a in gone], "shelter_a2", t)
 
     def _pull_agent_position(self, a, st, i):
         cur = int(st["cur"][i])

@@ -77,6 +77,12 @@ class _SimBase:
     def set_congest_after(self, seconds):
         self._check(self._fn("set_congest_after")(self._h, int(seconds)), "set_congest_after")
 
+    def stop_agents(self, agent_idx, status, t):
+        """A driver rule takes enroute agents off the road between ticks (status code >= 3, e.g. 5 = shelter_a2):
+        they leave their link's lists at once (model/dta_meso_butte.py:256-263)."""
+        a = np.ascontiguousarray(agent_idx, np.int32)
+        self._check(self._fn("stop_agents")(self._h, len(a), a.ctypes.data, int(status), int(t)), "stop_agents")
+
     def link_congested(self):
         out = np.empty(max(self.n_links, 1), np.int64)
         self._check(self._fn("get_link_congested")(self._h, out.ctypes.data), "get_link_congested")

@@ -259,3 +259,30 @@ def test_get_partial_path_matches_the_reference_class():
         assert [[int(x), int(y)] for x, y in a.route.items()] == c["route_after"], k
         assert float(a.route_distance) == c["route_distance"] and a.status == c["status"], k
         g.free()
+
+
+@pytest.mark.gpu
+def test_detour_rule_shelters_agents_on_the_device(tmp_path):
+    """Butte's shelter_a2 rule in host route mode (model/dta_meso_butte.py:199-204, 256-263): an enroute agent whose
+    new route is more than `detour_factor` times its previous one shelters in place -- status, stop tick, off its
+    link's lists at once (sq_stop_agents), into agents_stopped.  An exit is closed so that the reroutes lengthen."""
+    net, special = build_grid("grid8", tmp_path)
+    net.use_gpu(seed=5, special_nodes=special, reroute_freq=60, weight_freq=50, route_mode="host", detour_factor=1.25)
+    closing = [lid for lid, l in net.links.items() if l.link_type != "v" and l.end_nid == 0]
+    n0 = len(net.agents)
+    for t in range(500):
+        if t == 100:
+            for lid in closing:
+                net.links[lid].close_link_to_newcomers(g=net.g)
+                net.links[lid].status = "closed"
+        net.step(t)
+    net.sync_to_host()
+    a2 = {k: v for k, v in net.agents_stopped.items() if v[0] == "shelter_a2"}
+    assert len(a2) > 5 and all(60 < v[1] < 500 for v in a2.values())
+    on_links = {v for l in net.links.values() for v in l.queue_vehicles + l.run_vehicles}
+    assert not (set(a2) & on_links) and not (set(a2) & set(net.agents))
+    st = net.sim.agent_state()["status"]
+    assert int((st == 5).sum()) == len(a2)
+    assert len(net.agents) + len(net.agents_stopped) == n0
+    with pytest.raises(ValueError):
+        build_grid("grid8", tmp_path)[0].use_gpu(route_mode="device", detour_factor=2)

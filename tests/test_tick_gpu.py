@@ -222,3 +222,45 @@ def test_town_device_router_on_free_flow_weights_equals_fixed_routes():
         t = stop
         assert state_digest(dev.state()) == state_digest(orc.state()), f"tick {t - 1}"
     dev.close(); orc.close()
+
+
+def test_stop_agents_matches_oracle():
+    """sq_stop_agents (a driver rule shelters enroute agents between ticks: they leave their link's queue / run list
+    at once, model/dta_meso_butte.py:256-263) against the oracle's list filtering: random agents anywhere in the
+    rings (queue part, run part, source links, several on one link), every 40 ticks, on the irregular network."""
+    from oracle.tick import OracleSim
+    from spatial_queue_b200.tick import DeviceSim
+    flat = _town()
+    dev, orc = DeviceSim(flat, seed=2), OracleSim(flat, seed=2)
+    for s in (dev, orc):
+        s.set_congest_after(60)
+    rng = np.random.default_rng(7)
+    t, stopped = 0, 0
+    for stop in range(40, 601, 40):
+        dev.run(t, stop - t)
+        orc.run(t, stop - t)
+        t = stop
+        ag = orc.agent_state()
+        on = np.flatnonzero(ag["status"] == 1)
+        pick = rng.choice(on, min(len(on), 400), replace=False).astype(np.int32)
+        # several victims on the same links: everyone on the 3 fullest links as well
+        ptr, order = orc.link_vehicles()
+        full = np.argsort(np.diff(ptr))[-3:]
+        pick = np.unique(np.concatenate([pick] + [order[ptr[l]:ptr[l + 1]] for l in full])).astype(np.int32)
+        for s in (dev, orc):
+            s.stop_agents(pick, 5, t)
+        stopped += len(pick)
+        sd, so = dev.state(), orc.state()
+        assert state_digest(sd) == state_digest(so), f"after stops at {t}"
+    dev.run(t, 100); orc.run(t, 100)
+    sd, so = dev.state(), orc.state()
+    assert state_digest(sd) == state_digest(so)
+    for k in ("in_c", "out_c", "storage_c"):
+        assert sd[k].tobytes() == so[k].tobytes(), k
+    assert (dev.link_congested() == orc.link_congested()).all()
+    cd, co = dev.counters(), orc.counters()
+    assert cd["agent_steps"] == co["agent_steps"] and cd["moves"] == co["moves"]
+    assert int((dev.agent_state()["status"] == 5).sum()) == stopped > 3000
+    with pytest.raises(Exception):
+        dev.stop_agents(pick[:1], 5, t)          # already stopped: not enroute
+    dev.close(); orc.close()
