@@ -247,7 +247,9 @@ class Network:
         self.agents_stopped = {}
         self.special_nodes = None
         self.detour_factor = None      # host route mode: shelter_a2 when a reroute lengthens the trip this many times
+        self.closure_reroute_freq = None   # host route mode: reroute agents about to enter a closed link, staggered
         self._detoured = []
+        self._closed_idx = set()
         self._sim = None
         self._flat = None
         self.route_mode = "device"
@@ -419,7 +421,8 @@ class Network:
     # the device switch
     # ---------------------------------------------------------------------------------------------------------
     def use_gpu(self, seed=0, special_nodes=None, reroute_freq=300, weight_freq=100, route_at_start=True,
-                route_mode="device", shelter_after=3 * 3600, congest_after=1800, detour_factor=None):
+                route_mode="device", shelter_after=3 * 3600, congest_after=1800, detour_factor=None,
+                closure_reroute_freq=None):
         """Move the simulation onto the GPU.  Call once after `add_demand` (and after any t=0 changes to
         `agent.departure_time`).
 
@@ -441,7 +444,9 @@ class Network:
         self._pending_status = {}
         if detour_factor and route_mode != "host":
             raise ValueError("detour_factor (Butte's shelter_a2 rule) needs route_mode='host'")
-        self.detour_factor = detour_factor
+        if closure_reroute_freq and route_mode != "host":
+            raise ValueError("closure_reroute_freq (Butte's reroute-upon-closure rule) needs route_mode='host'")
+        self.detour_factor, self.closure_reroute_freq = detour_factor, closure_reroute_freq
         if route_mode == "host":
             if route_at_start:
                 self.route_agents(0)
@@ -491,14 +496,18 @@ class Network:
     def _reroute_due(self, t):
         """Agents with t % reroute_freq == agent_id % reroute_freq that are still travelling or waiting to
         depart (run_traffic_simulation.py:95-98, 107)."""
-        f = self.reroute_freq
-        if not f:
+        f, cf = self.reroute_freq, self.closure_reroute_freq if self._closed_idx else None
+        if not f and not cf:
             return
-        due = [i for i, a in enumerate(self._agent_objs) if a.agent_id % f == t % f]
-        if not due:
+        due = [i for i, a in enumerate(self._agent_objs) if f and a.agent_id % f == t % f]
+        # reroute upon closure (model/dta_meso_butte.py:205-209): the agent's next link is closed, staggered by id
+        near = [i for i, a in enumerate(self._agent_objs) if cf and a.agent_id % cf == t % cf]
+        if not due and not near:
             return
         st = self.sim.agent_state()
         live = [i for i in due if st["status"][i] in (0, 1)]
+        seen = set(live)
+        live += [i for i in near if i not in seen and st["status"][i] in (0, 1) and int(st["nxt"][i]) in self._closed_idx]
         if not live:
             return
         for i in live:
@@ -561,6 +570,8 @@ class Network:
             idx = [self._flat.link_index[lid] for lid in self._pending_status]
             sim = self.sim
             sim.set_link_closed(idx, [1 if c else 0 for c in self._pending_status.values()])
+            for i, c in zip(idx, self._pending_status.values()):
+                (self._closed_idx.add if c else self._closed_idx.discard)(i)
             self._pending_status.clear()
 
     def run(self, t0, n):

@@ -286,3 +286,38 @@ def test_detour_rule_shelters_agents_on_the_device(tmp_path):
     assert len(net.agents) + len(net.agents_stopped) == n0
     with pytest.raises(ValueError):
         build_grid("grid8", tmp_path)[0].use_gpu(route_mode="device", detour_factor=2)
+
+
+@pytest.mark.gpu
+def test_reroute_upon_closure_rule(tmp_path):
+    """Butte's reroute-upon-closure rule in host route mode (model/dta_meso_butte.py:205-209): an agent whose next
+    link is closed is rerouted when t % 10 == agent_id % 10, so twelve ticks after a closure the only agents still
+    heading into it are those that reached the link before it less than ten ticks ago (there is a way round);
+    without the rule the regular 300 s stagger leaves several times as many waiting at the closed link."""
+    waiting = {}
+    for freq in (10, None):
+        net, special = build_grid("grid8", tmp_path)
+        net.use_gpu(seed=5, special_nodes=special, reroute_freq=300, weight_freq=100, route_mode="host",
+                    closure_reroute_freq=freq)
+        for t in range(60):
+            net.step(t)
+        # close the street most agents are about to turn into (not one that ends at an exit: there must be a way round)
+        st = net.sim.agent_state()
+        exits = set(int(x) for x in net._flat.agent_destin)
+        nxt = st["nxt"][(st["status"] <= 1) & (st["nxt"] >= 0)]
+        cnt = np.bincount(nxt, minlength=len(net._link_objs))
+        cnt[[i for i, l in enumerate(net._link_objs) if l.link_type == "v" or net._flat.node_index[l.end_nid] in exits]] = 0
+        busiest = int(cnt.argmax())
+        assert cnt[busiest] > 5
+        link = net._link_objs[busiest]
+        link.close_link_to_newcomers(g=net.g)
+        link.status = "closed"
+        for t in range(60, 72):
+            net.step(t)
+        st = net.sim.agent_state()
+        head_in = (st["status"] <= 1) & (st["nxt"] == busiest)
+        waiting[freq] = int(head_in.sum())
+        if freq:
+            # whoever still heads into it only just got there: moved onto the link before it within the last ten ticks
+            assert ((st["status"][head_in] == 1) & (st["enter"][head_in] > 71 - 10)).all()
+    assert waiting[10] * 3 < waiting[None], waiting
