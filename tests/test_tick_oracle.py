@@ -28,3 +28,43 @@ def test_oracle_congestion_counter_matches_reference():
     sim = OracleSim(flat, seed=int(z["seed"]))
     check_congestion_counter(sim, z)
     sim.close()
+
+
+def test_oracle_on_irregular_network_conserves_vehicles():
+    """Host logic of the irregular-network generator (synth.flat_from_edges / town_scenario, routed here by the C
+    SSSP oracle) + the oracle's stop_agents: CSR consistency of the flat network, and vehicle conservation through
+    closures, give-ups and driver-ordered stops."""
+    from oracle import sssp as osssp
+    from spatial_queue_b200 import synth
+
+    def router(starts, ends, w, roots):
+        og = osssp.OracleGraph(starts, ends, w, max_vertex_id=int(max(starts.max(), ends.max())))
+        return og.sssp_batch(np.asarray(roots, np.int32), want_dist=False)[1]
+
+    flat = synth.town_scenario(24, 6000, horizon=200, seed=5, router=router)
+    N, L = len(flat.node_key), len(flat.link_start_node)
+    assert (flat.link_end_node[flat.node_in_links] == np.repeat(np.arange(N), np.diff(flat.node_in_ptr))).all()
+    assert (flat.link_start_node[flat.node_out_links] == np.repeat(np.arange(N), np.diff(flat.node_out_ptr))).all()
+    rev = flat.link_reverse
+    has = rev >= 0
+    assert (flat.link_start_node[rev[has]] == flat.link_end_node[has]).all() and (flat.link_end_node[rev[has]] == flat.link_start_node[has]).all()
+    assert (~has[N:]).sum() > 10 and np.diff(flat.node_out_ptr).max() > 8
+    sim = OracleSim(flat, seed=1)
+    sim.set_shelter_after(150)
+    rng = np.random.default_rng(0)
+    t, stopped = 0, 0
+    for stop in (50, 100, 150, 200, 300, 400):
+        sim.run(t, stop - t)
+        t = stop
+        on = np.flatnonzero(sim.agent_state()["status"] == 1)
+        pick = rng.choice(on, min(50, len(on)), replace=False).astype(np.int32)
+        sim.stop_agents(pick, 5, t)
+        stopped += len(pick)
+        if stop == 100:
+            sim.set_link_closed(N + rng.choice(L - N, 40, replace=False).astype(np.int32), np.ones(40, np.uint8))
+        st, ls = sim.agent_state()["status"], sim.link_state()
+        assert int((st == 1).sum()) == int(ls["q"].sum() + ls["r"].sum())          # enroute <=> on exactly one link list
+        ptr, order = sim.link_vehicles()
+        assert len(np.unique(order)) == len(order) and (st[order] == 1).all()
+    assert int((st == 5).sum()) == stopped and (st == 4).sum() > 0 and (st == 2).sum() > 500
+    sim.close()
