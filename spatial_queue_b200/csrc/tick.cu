@@ -1733,7 +1733,9 @@ int sq_get_counters(SqSim* sim, int64_t* out6) {
   if (int rc = sq_sync(sim)) return rc;
   sim->sheltered = (long long)c[7];
   out6[0] = (int64_t)c[0];
-  out6[1] = (int64_t)(c[1] + (c[0] > 0 ? c[5] - c[4] - c[7] : 0));  // + vehicles on links after the last tick
+  // + vehicles on links after the last tick: loaded - arrived - taken off the road, as frozen by its node phase
+  // (c[8]; c[7] may already include sq_stop_agents calls made since)
+  out6[1] = (int64_t)(c[1] + (c[0] > 0 ? c[6] - c[4] - c[8] : 0));
   out6[2] = (int64_t)c[2]; out6[3] = (int64_t)c[3]; out6[4] = (int64_t)c[4];
   out6[5] = sim->launches;
   return SQ_OK;

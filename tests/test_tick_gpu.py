@@ -264,3 +264,50 @@ def test_stop_agents_matches_oracle():
     with pytest.raises(Exception):
         dev.stop_agents(pick[:1], 5, t)          # already stopped: not enroute
     dev.close(); orc.close()
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_small_towns_match_oracle(seed):
+    """Differential fuzz: small irregular networks with random shape parameters (dead ends, isolated nodes, hubs,
+    dense signals / priority nodes), short horizons (everything jams), random closures, reopenings and driver stops,
+    a random give-up limit.  CUDA tick == C oracle at every stop, digest and capacities."""
+    from oracle.tick import OracleSim
+    from spatial_queue_b200 import synth
+    from spatial_queue_b200.tick import DeviceSim
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(6, 15))
+    lon, lat = synth.grid_coords(n, seed)
+    s, e, lanes, maxmph = synth.town_edges(n, seed, drop=float(rng.uniform(0.05, 0.4)), oneway=float(rng.uniform(0, 0.3)),
+                                           diag=float(rng.uniform(0, 0.3)), hubs=int(rng.integers(0, 3)),
+                                           hub_links=int(rng.integers(3, min(14, n * n - 2))))
+    flat = synth.town_scenario(n, int(rng.integers(300, 4000)), horizon=int(rng.integers(20, 200)), seed=seed,
+                               n_exits=int(rng.integers(1, 6)), signals=float(rng.uniform(0, 0.3)),
+                               priority=float(rng.uniform(0, 0.3)))
+    N, E = len(flat.node_key), len(flat.edge_start)
+    dev, orc = DeviceSim(flat, seed=seed), OracleSim(flat, seed=seed)
+    give_up = int(rng.integers(50, 400))
+    for sim in (dev, orc):
+        sim.set_shelter_after(give_up)
+        sim.set_congest_after(int(give_up // 3))
+    t = 0
+    for _ in range(8):
+        stop = t + int(rng.integers(1, 90))
+        dev.run(t, stop - t)
+        orc.run(t, stop - t)
+        t = stop
+        sd, so = dev.state(), orc.state()
+        assert state_digest(sd) == state_digest(so), f"seed {seed} tick {t - 1}"
+        for k in ("in_c", "out_c", "storage_c"):
+            assert sd[k].tobytes() == so[k].tobytes(), (seed, k, t)
+        assert (dev.link_congested() == orc.link_congested()).all()
+        links = (N + rng.choice(E, min(E, 5), replace=False)).astype(np.int32)
+        flags = rng.integers(0, 2, len(links)).astype(np.uint8)
+        on = np.flatnonzero(so["status"] == 1)
+        pick = rng.choice(on, min(len(on), int(rng.integers(0, 30))), replace=False).astype(np.int32)
+        for sim in (dev, orc):
+            sim.set_link_closed(links, flags)
+            if len(pick):
+                sim.stop_agents(pick, 5, t)
+    cd, co = dev.counters(), orc.counters()
+    assert cd["agent_steps"] == co["agent_steps"] and cd["moves"] == co["moves"] and cd["arrivals"] == co["arrivals"]
+    dev.close(); orc.close()
