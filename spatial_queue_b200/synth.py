@@ -311,6 +311,19 @@ def town_edges(n, seed=1, drop=0.12, oneway=0.08, diag=0.06, hubs=2, hub_links=1
     return s.astype(np.int64), e.astype(np.int64), lanes, maxmph
 
 
+def town_frames(n, seed=1, **shape):
+    """The irregular network of `town_edges` as the loader's CSV frames (edges, nodes), like `grid_frames`."""
+    lon, lat = grid_coords(n, seed)
+    s, e, lanes, maxmph = town_edges(n, seed, **shape)
+    x, y = lon * M_PER_DEG_LON, lat * M_PER_DEG_LAT
+    length = np.hypot(x[s] - x[e], y[s] - y[e])
+    geom = [f"LINESTRING ({lon[a]!r} {lat[a]!r}, {lon[b]!r} {lat[b]!r})" for a, b in zip(s, e)]
+    edges = pd.DataFrame({"eid": np.arange(len(s)), "nid_s": s, "nid_e": e, "length": length, "lanes": lanes,
+                          "maxmph": maxmph, "type": "residential", "geometry": geom})
+    nodes = pd.DataFrame({"nid": np.arange(n * n), "osmid": 10_000_000 + np.arange(n * n), "lon": lon, "lat": lat})
+    return edges, nodes
+
+
 def town_scenario(n, n_agents, horizon=600, seed=1, n_exits=8, signals=0.04, priority=0.03, router=None,
                   device_routes=False):
     """Irregular network + signal and priority nodes + demand from every node that can reach its exit.  Signal nodes

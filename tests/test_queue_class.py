@@ -9,6 +9,7 @@ import json
 import os
 
 import numpy as np
+import pandas as pd
 import pytest
 
 from tickcheck import load_golden, state_digest
@@ -321,3 +322,63 @@ def test_reroute_upon_closure_rule(tmp_path):
             # whoever still heads into it only just got there: moved onto the link before it within the last ten ticks
             assert ((st["status"][head_in] == 1) & (st["enter"][head_in] > 71 - 10)).all()
     assert waiting[10] * 3 < waiting[None], waiting
+
+
+def build_town(seed, tmp_path, n=9, agents=900):
+    """Irregular network through the mirror's CSV loader; origins anywhere (some cannot reach their exit: shelter_p at
+    t=0, queue_class.py:494-499), origins only at nodes that have a way out (the reference crashes otherwise)."""
+    edges, nodes = synth.town_frames(n, seed, hubs=1, hub_links=6)
+    rng = np.random.default_rng(seed)
+    has_out = np.unique(edges.nid_s.values)
+    exits = rng.choice(np.unique(edges.nid_e.values), 3, replace=False)
+    origin = rng.choice(has_out, agents)
+    destin = exits[rng.integers(0, 3, agents)]
+    clash = origin == destin
+    origin[clash] = has_out[(np.searchsorted(has_out, origin[clash]) + 1) % len(has_out)]
+    origin[origin == destin] = has_out[0] if has_out[0] not in exits else has_out[1]
+    od = pd.DataFrame({"origin_osmid": 10_000_000 + origin, "destin_osmid": 10_000_000 + destin,
+                       "dept_time": 1 + (np.arange(agents) * 50) // agents, "type": "local"})
+    wp = str(tmp_path)
+    edges.to_csv(wp + "/edges.csv", index=False)
+    nodes.to_csv(wp + "/nodes.csv", index=False)
+    od.to_csv(wp + "/od.csv", index=False)
+    np.random.seed(seed)
+    net = qc.Network()
+    net.dataframe_to_network(project_location="", network_file_edges=wp + "/edges.csv",
+                             network_file_nodes=wp + "/nodes.csv", special_nodes=EMPTY, scen_nm="town")
+    net.add_connectivity()
+    net.add_demand(demand_files=["/od.csv"], write_path=wp)
+    return net
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_host_and_device_routing_agree_on_irregular_networks(seed, tmp_path):
+    """The two routing modes of the mirror on irregular networks (one-ways, dead ends, unreachable exits -> shelter_p
+    at t=0): per-agent forward paths from `sp_route_batch` on the host side vs reverse-tree next-link tables on the
+    device, rerouting every 40 s on weights refreshed every 25 s, one street closed for a while."""
+    runs = []
+    for mode in ("host", "device"):
+        (tmp_path / mode).mkdir()
+        net = build_town(seed, tmp_path / mode)
+        net.use_gpu(seed=seed, special_nodes=EMPTY, reroute_freq=40, weight_freq=25, route_mode=mode, shelter_after=200)
+        runs.append(net)
+    digests = [[], []]
+    for k, net in enumerate(runs):
+        closing = sorted(lid for lid, l in net.links.items() if l.link_type != "v")[5::40]
+        for t in range(330):
+            if t in (60, 200):
+                for lid in closing:
+                    if t == 60:
+                        net.links[lid].close_link_to_newcomers(g=net.g)
+                        net.links[lid].status = "closed"
+                    else:
+                        net.links[lid].open_link_to_newcomers(g=net.g)
+                        net.links[lid].status = "open"
+            net.step(t)
+            if t % 10 == 0:
+                digests[k].append(state_digest(net.sim.state()))
+    bad = [i for i, (a, b) in enumerate(zip(*digests)) if a != b]
+    assert not bad, f"first difference at tick {bad[0] * 10}"
+    assert (runs[0].sim.agent_state()["arrive_tick"] == runs[1].sim.agent_state()["arrive_tick"]).all()
+    assert (runs[0].sim.agent_state()["status"] == 2).sum() > 100
