@@ -368,18 +368,22 @@ constexpr int QS = 384;  // shared-memory entries per queue
 // Queue entry = (vertex, vertex it was reached from, distance when pushed).  The 'from' vertex lets the
 // relaxation skip the edge straight back (it can never improve: weights are >= 0), a quarter of all atomics
 // on a grid.  Stored as int2 {v, from} + u64.
+// The global parts are reached through a small table in shared memory (six pointers per array, filled once per
+// CTA): building them per round cost ~100 dependent 64-bit multiply-adds on the path of every relaxation round,
+// and they are only needed when a queue outgrows its shared part.
 struct HQ2 {
   int2* sv;  // shared part
   u64* sd;
-  int2* gv;  // global part
-  u64* gd;
+  int2* const* gvt;  // tables of the global parts, indexed by qi
+  u64* const* gdt;
+  int qi;
   __device__ __forceinline__ void get(int pos, int2& v, u64& d) const {
     if (pos < QS) { v = sv[pos]; d = sd[pos]; }
-    else { v = ld_cg_int2(&gv[pos - QS]); d = sq::ld_cg_u64(&gd[pos - QS]); }
+    else { v = ld_cg_int2(&gvt[qi][pos - QS]); d = sq::ld_cg_u64(&gdt[qi][pos - QS]); }
   }
   __device__ __forceinline__ void put(int pos, int2 v, u64 d, int gcap, int* fail) const {
     if (pos < QS) { sv[pos] = v; sd[pos] = d; }
-    else if (pos - QS < gcap) { gv[pos - QS] = v; gd[pos - QS] = d; }
+    else if (pos - QS < gcap) { gvt[qi][pos - QS] = v; gdt[qi][pos - QS] = d; }
     else *fail = 1;
   }
 };
@@ -418,9 +422,16 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
   const size_t per_cta = 4 * (size_t)gcap + 2 * (size_t)fcap;
   u64* gd_base = reinterpret_cast<u64*>(p.q2scratch) + (size_t)blockIdx.x * per_cta;
   int2* gv_base = reinterpret_cast<int2*>(p.q2v) + (size_t)blockIdx.x * per_cta;
-  auto Q = [&](int i) -> HQ2 { return HQ2{s_qv[i], s_qd[i], gv_base + (size_t)i * gcap, gd_base + (size_t)i * gcap}; };
-  auto FARV = [&](int i) -> int2* { return gv_base + 4 * (size_t)gcap + (size_t)i * fcap; };
-  auto FARD = [&](int i) -> u64* { return gd_base + 4 * (size_t)gcap + (size_t)i * fcap; };
+  __shared__ int2* s_gv[6];   // global parts: queues 0..3, far piles 4..5
+  __shared__ u64* s_gd[6];
+  if (tid < 6) {
+    const size_t off = tid < 4 ? (size_t)tid * gcap : 4 * (size_t)gcap + (size_t)(tid - 4) * fcap;
+    s_gv[tid] = gv_base + off;
+    s_gd[tid] = gd_base + off;
+  }
+  __syncthreads();
+  auto Q = [&](int i) -> HQ2 { return HQ2{s_qv[i], s_qd[i], s_gv, s_gd, i}; };
+  auto FARQ = [&](int i) -> HQ2 { return HQ2{nullptr, nullptr, s_gv, s_gd, 4 + i}; };  // global only: positions start at QS
 
   int st_rounds = 0, st_relax = 0, st_trans = 0;  // per launch; 32 bits are plenty per thread
 
@@ -482,10 +493,10 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
             __syncthreads();
             const double T2 = T + p.delta;
             u64 lmin = DIST_INF_BITS;
-            const int2* fiv = FARV(fcur);
-            const u64* fid = FARD(fcur);
+            const int2* fiv = s_gv[4 + fcur];
+            const u64* fid = s_gd[4 + fcur];
             const HQ2 qb = Q(bkt);
-            const HQ2 qf{nullptr, nullptr, FARV(fcur ^ 1), FARD(fcur ^ 1)};  // global only: positions start at QS
+            const HQ2 qf = FARQ(fcur ^ 1);
             for (int i0 = 0; i0 < nf; i0 += THREADS) {
               const int i = i0 + tid;
               bool to_b = false, to_f = false;
@@ -534,7 +545,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
 
       // ---- one relaxation round: 4 lanes per frontier vertex, 16 vertices per warp iteration -------
       const HQ2 qin = Q(cur), qn = Q(nxt), qb = Q(bkt);
-      const HQ2 qf{nullptr, nullptr, FARV(fcur), FARD(fcur)};
+      const HQ2 qf = FARQ(fcur);
       const double T2 = T + p.delta;
       for (int base = warp * 16; base < n; base += NW * 16) {
         int u[2], from[2];
