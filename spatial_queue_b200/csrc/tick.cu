@@ -568,7 +568,7 @@ __device__ __forceinline__ int pick_secondary(const TickState& s, int n, int ib,
   return secondary;
 }
 
-__global__ void __launch_bounds__(64) k_node_phase(const TickState s) {
+__global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   const int t = *s.tick_node;
   if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; s.counters[8] = s.counters[7]; }
@@ -1178,7 +1178,9 @@ static int launch_tick(SqSim* sim, cudaStream_t st) {
   const int link_blocks = (L + 255) / 256;
   const int reroute_blocks = (sim->router_graph && sim->max_bucket > 0) ? (sim->max_bucket + 255) / 256 : 0;
   k_link_phase<<<link_blocks + reroute_blocks, 256, 0, st>>>(sim->st, link_blocks);
-  k_node_phase<<<(N + 63) / 64, 64, 0, st>>>(sim->st);
+  // one warp per CTA: the warps are independent chains, the finer grain spreads them evenly over the SMs (measured:
+  // 31.7 / 32.1 / 32.5 us per tick with 32 / 64 / 128 threads)
+  k_node_phase<<<(N + 31) / 32, 32, 0, st>>>(sim->st);
   return SQ_OK;
 }
 
