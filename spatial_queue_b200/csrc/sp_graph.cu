@@ -1452,6 +1452,9 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   // SM's worth of threads; a round is then one or two passes over the wavefront instead of five
   int threads = use_warp ? 128 : std::min(g->threads, 1024);
   if (!use_warp && g->algo == 3) threads = n <= n_sm ? 1024 : n <= 2 * n_sm ? 512 : 256;
+  // a lone tree per SM is bound by the number of rounds, not by work: four times wider buckets save the rounds spent
+  // on bucket transitions (8 trees on the config-4 graph: 0.57 -> 0.52 ms, 7 % more relaxations)
+  if (!use_warp && g->algo == 3 && n <= n_sm) p.delta = g->delta * 4.0;
   int per_sm, grid, rows;   // rows = trees in flight (scratch distance rows in timing-only mode)
   size_t warp_smem = 0;
   if (use_warp) {

@@ -7,6 +7,8 @@ from spatial_queue_b200 import sp_interface as spi
 n = int(os.environ.get("GRID", 159)); B = int(os.environ.get("BATCH", 8))
 s, e, w = grid_graph(n, seed=1)
 g = spi.from_arrays(s, e, w); V = n * n
+if os.environ.get("DELTA"):
+    g.set_tuning(delta_factor=float(os.environ["DELTA"]))
 origins = np.random.default_rng(0).permutation(V)[:B].astype(np.int32)
 o = torch.from_numpy(origins).cuda()
 dist = torch.empty((B, V), dtype=torch.float64, device="cuda"); par = torch.empty((B, V), dtype=torch.int32, device="cuda")
