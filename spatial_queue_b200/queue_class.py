@@ -433,7 +433,12 @@ class Network:
         `congest_after` seconds on their link (run_traffic_simulation.py:80-118).  `network.step(t)` is one C call.
         route_mode="host": routes are Python dicts on the agents like in the reference (`agent.route`), recomputed
         in batches of forward trees and pushed to the device; use it when a driver edits routes itself
-        (e.g. get_partial_path)."""
+        (e.g. get_partial_path).  Host mode also carries Butte's two extra rules (model/dta_meso_butte.py:199-209):
+        `detour_factor=2` shelters an enroute agent whose rerouted trip is more than twice its previous one
+        (shelter_a2, `shelter_agents`), `closure_reroute_freq=10` reroutes agents whose next link is closed when
+        t % 10 == agent_id % 10.  Both run before the device tick, i.e. before the give-up test of the same second
+        (the reference tests give-up first; the two only meet when an agent's stagger slot falls on the very second
+        it gives up)."""
         from .flatten import router_arrays
         from .tick import DeviceSim
         if special_nodes is not None:
