@@ -107,6 +107,7 @@ struct TickState {
   int* l_shelter;            // vehicles that gave up on this link (shelter_a1)
   int shelter_after;         // seconds on one link before a vehicle shelters (run_traffic_simulation.py:103), 0 = off
   int congest_after;         // seconds on one link before a vehicle counts as congested (run_traffic_simulation.py:101), 0 = off
+  u64* n_cand;               // [N] bit i = in-link i of the node has a non-empty queue (written by k_link_phase)
   unsigned* cong_pos;        // [L] ring index of the first vehicle not yet congested (lags behind head when the queue moves)
   long long* l_congested;    // [L] link.congested of the last tick: vehicles on the link for longer than congest_after
   // run control
@@ -250,6 +251,13 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       const unsigned qt0 = qt;
       while (qt != tl && s.ring[base + (qt & mask)].y <= t) ++qt;
       if (qt != qt0) s.qtail[l] = qt;
+    }
+    // candidate bit of the end node: k_node_phase reads one word per node instead of walking its in-links' queue
+    // bounds (three dependent loads at the head of every node's chain); fire-and-forget REDs (updating only on change, via a per-link byte, measured slower)
+    {
+      const u64 bit = 1ull << s.l_in_local[l];
+      u64* w = &s.n_cand[s.l_end[l]];
+      if (qt != s.head[l]) atomicOr(w, bit); else atomicAnd(w, ~bit);
     }
     // capacities (:453-455)
     s.storage_c[l] = s.l_storage[l] - (double)(li - s.len_out[l]);
@@ -576,12 +584,8 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
   if (n < s.N) {
     const int ib = s.in_ptr[n];
     const int indeg = s.in_ptr[n + 1] - ib;
-    // candidate in-links: non-empty queue, incoming_links order (:230)
-    u64 cand = 0;
-    for (int i = 0; i < indeg; ++i) {
-      const int l = s.in_links[ib + i];
-      if (s.qtail[l] != s.head[l]) cand |= 1ull << i;
-    }
+    // candidate in-links: non-empty queue, incoming_links order (:230); the link phase keeps the mask
+    u64 cand = s.n_cand[n];
     if (cand) {
       active = 1;
       const long long key = s.n_key[n];
@@ -1124,6 +1128,8 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
       std::vector<unsigned> zu((size_t)std::max(L, 1), 0u);
       std::vector<long long> zl((size_t)std::max(L, 1), 0ll);
       if ((rc = dev_upload_rw(sim, &s.cong_pos, zu))) return rc;
+      std::vector<u64> zc64(N, 0);
+      if ((rc = dev_upload_rw(sim, &s.n_cand, zc64))) return rc;
       if ((rc = dev_upload_rw(sim, &s.l_congested, zl))) return rc;
     }
     s.D = 0; s.K = 0; s.freq = 1;
