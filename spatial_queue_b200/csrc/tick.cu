@@ -586,10 +586,10 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
     const int indeg = s.in_ptr[n + 1] - ib;
     // candidate in-links: non-empty queue, incoming_links order (:230); the link phase keeps the mask
     u64 cand = s.n_cand[n];
+    const long long key = s.n_key[n];     // issued with the mask: coalesced, and off the active nodes' chain
+    const int type = s.n_type[n];
     if (cand) {
       active = 1;
-      const long long key = s.n_key[n];
-      const int type = s.n_type[n];
       int primary = -1;  // local index of the primary in-link
       // `order` semantics: after the shuffle replacement the list is [c_r, rest in original order].
       int first = -1;    // local index moved to the front by the last shuffle (ties in :277 see it first)
