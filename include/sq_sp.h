@@ -133,14 +133,23 @@ int sp_sync(Graph* graph);
  * current), shared-memory queue slots per queue of the bitmap kernel (0 = default). */
 int sp_set_tuning(Graph* graph, int threads, int ctas_per_sm, double delta_factor, int smem_queue);
 
-/* Kernel choice: 3 (default) = auto: the warp kernel for batches of at least six trees per SM, the ELL kernel
+/* Kernel choice: 3 (default) = auto: the group kernel (4) for large batches of origins that lie close together (see
+ * sp_set_group_tuning), else the warp kernel for batches of at least six trees per SM, the ELL kernel
  * below that (a lone tree finishes ~10x sooner on a whole CTA); if more than 5 % of a batch's trees overflow the
  * warp kernel's ring, the next batches use a 2048-entry ring and, failing that, the ELL kernel; 2 = warp kernel (one tree per warp, four-byte
  * hashed queue entries in a shared-memory ring), 0 = ELL kernel (one tree per CTA, four-edge vertex records, tagged queue entries, queues of
  * queue_factor x V entries), 1 = bitmap kernel only (CSR, per-vertex shared-memory bitmaps; also the fallback
- * that reruns trees whose queues overflowed in the other two).  All produce identical results.
+ * that reruns trees whose queues overflowed in the other two), 4 = group kernel (eight trees per warp on interleaved
+ * distance rows, no atomics, no overflow path).  All produce identical results.
  * queue_factor <= 0 keeps the current value. */
 int sp_set_algo(Graph* graph, int algo, double queue_factor);
+
+/* Group-kernel knobs (algo 4, and auto mode on dense batches): eight trees of neighbouring origins share one
+ * frontier and one warp (csrc/sp_group.cuh).  warps_per_sm: resident groups per SM (multiple of 4, 0 keeps; default
+ * 16); batch: pops decided per batch, 8 / 16 / 32 (0 keeps; default 16); prefetch: 1 = prefetch a batch's rows
+ * into L1 (< 0 keeps; default 1); auto mode picks the group kernel for batches of at least min_trees origins
+ * (0 keeps; default 2048) that hold at least V / min_density origins (0 keeps; default 8). */
+int sp_set_group_tuning(Graph* graph, int warps_per_sm, int batch, int prefetch, int min_trees, int min_density);
 
 /* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps; default 1024), frontier
  * vertices per step = 8 x ilp (1, 2 or 4; 0 keeps; default 4), CTAs of four warps per SM (0 = default 4, at most

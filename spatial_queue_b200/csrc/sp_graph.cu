@@ -909,6 +909,8 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
   }
 }
 
+#include "sp_group.cuh"
+
 // Canonical predecessors for a batch of finished trees: parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]}, -1 for
 // the origin and for unreached vertices.  One thread per vertex; its (up to four) in-edges come from a
 // slot-major copy of the reverse ELL (coalesced) and stay in registers while blockIdx.y strides over trees, so
@@ -987,10 +989,12 @@ __global__ void __launch_bounds__(256) decode_parents_kernel(int V, int n_trees,
 struct WeightSlots {
   const int* adj; const int* radj;    // CSR / CSC record index, -1 = edge not in the graph
   const int* ell; const int* rell;    // >= 0: index into the ELL array; < 0: -(overflow index + 1)
+  const int* gell; const int* grell;  // same for the group kernel's ELL pair (internal numbering)
 };
 __global__ void __launch_bounds__(256) scatter_weights_kernel(int n, int V, const double* __restrict__ w, WeightSlots ws,
                                                               EdgeRec* adj, EdgeRec* radj, EdgeRec* ell, EdgeRec* ovf,
-                                                              EdgeRec* rell, EdgeRec* rovf, double* fs_w, double* rs_w) {
+                                                              EdgeRec* rell, EdgeRec* rovf, double* fs_w, double* rs_w,
+                                                              EdgeRec* gell, EdgeRec* govf, EdgeRec* grell, EdgeRec* grovf) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
   const double x = w[i];
@@ -1005,6 +1009,10 @@ __global__ void __launch_bounds__(256) scatter_weights_kernel(int n, int V, cons
   const int r = ws.rell[i];
   if (r >= 0) { rell[r].w = x; rs_w[(size_t)(r & 3) * V + (r >> 2)] = x; }
   else rovf[-(r + 1)].w = x;
+  const int ge = ws.gell[i];
+  if (ge >= 0) gell[ge].w = x; else govf[-(ge + 1)].w = x;
+  const int gr = ws.grell[i];
+  if (gr >= 0) grell[gr].w = x; else grovf[-(gr + 1)].w = x;
 }
 
 // =================================================================================================
@@ -1082,6 +1090,22 @@ struct SqGraph {
   int* d_pool = nullptr; size_t d_pool_cap = 0;
   int* h_pool = nullptr; size_t h_pool_cap = 0;
   double queue_factor = 1.0;   // queue capacities of the ELL kernel: near = factor*V, far = 2*factor*V
+  // group kernel (sp_group.cuh): internal numbering along a Hilbert curve over landmark pseudo-coordinates
+  std::vector<int> h_perm, h_iperm;      // caller id -> internal id and back
+  int* d_perm = nullptr; int* d_iperm = nullptr;
+  std::vector<EdgeRec> h_gell[2], h_govf[2];   // [0] forward, [1] reverse; internal numbering
+  EdgeRec* d_gell[2] = {nullptr, nullptr}; EdgeRec* d_govf[2] = {nullptr, nullptr};
+  size_t govf_cap[2] = {0, 0};
+  int4* d_gheads[2] = {nullptr, nullptr};
+  int* d_gkey = nullptr; int* d_tord = nullptr; size_t gkey_cap = 0;
+  int* d_ghist = nullptr; size_t ghist_cap = 0;
+  u64* d_gdist = nullptr; size_t gdist_groups = 0;
+  unsigned* d_gring = nullptr; unsigned* d_gpend = nullptr; unsigned* d_ginp = nullptr;
+  int g_warps = 0, g_ring_cap = 0, g_pend_cap = 0, g_words = 0;
+  int group_warps_per_sm = 16, group_pb = 16, group_pf = 1;
+  int group_min_trees = 2048;            // auto mode: batches at least this large ...
+  int group_min_density = 8;             // ... with at least V / this many origins go to the group kernel
+  size_t group_scratch_bytes = (size_t)24 << 30;   // upper bound of the interleaved distance scratch per chunk
 
   // tuning
   int threads = 256;
@@ -1159,6 +1183,76 @@ static void g_free_device(SqGraph* g) {
   g->d_row_ptr = g->d_rrow_ptr = nullptr; g->d_adj = g->d_radj = nullptr;
   g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
   g->ovf_cap = g->rovf_cap = 0;
+  cudaFree(g->d_perm); cudaFree(g->d_iperm); g->d_perm = g->d_iperm = nullptr;
+  for (int d = 0; d < 2; ++d) {
+    cudaFree(g->d_gell[d]); cudaFree(g->d_govf[d]); cudaFree(g->d_gheads[d]);
+    g->d_gell[d] = g->d_govf[d] = nullptr; g->d_gheads[d] = nullptr; g->govf_cap[d] = 0;
+  }
+}
+
+// Locality order for the group kernel.  Road networks come without usable coordinates at this level (the ABI takes
+// an edge list), so the order is built from the graph alone: hop distances from two landmarks a, c (a = a peripheral
+// vertex, c = the vertex farthest from both a and the vertex b farthest from a) are pseudo-coordinates; their sum and
+// difference are roughly orthogonal on a planar network; vertices are sorted along a Hilbert curve over those two.
+static unsigned hilbert_key(unsigned n, unsigned x, unsigned y) {
+  unsigned d = 0;
+  for (unsigned s = n / 2; s > 0; s /= 2) {
+    const unsigned rx = (x & s) ? 1u : 0u, ry = (y & s) ? 1u : 0u;
+    d += s * s * ((3u * rx) ^ ry);
+    if (ry == 0) {
+      if (rx == 1) { x = s - 1 - x; y = s - 1 - y; }
+      std::swap(x, y);
+    }
+  }
+  return d;
+}
+
+static void locality_order(int V, const std::vector<int>& rp, const std::vector<EdgeRec>& adj, const std::vector<int>& rrp,
+                           const std::vector<EdgeRec>& radj, std::vector<int>& perm, std::vector<int>& iperm) {
+  perm.assign(V, 0); iperm.assign(V, 0);
+  if (V == 0) return;
+  std::vector<int> q(V), da(V), db(V), dc(V);
+  auto bfs = [&](int src, std::vector<int>& d) {   // hops on the undirected graph; unreached vertices keep -1
+    std::fill(d.begin(), d.end(), -1);
+    int h = 0, tl = 0;
+    q[tl++] = src; d[src] = 0;
+    while (h < tl) {
+      const int x = q[h++];
+      for (int i = rp[x]; i < rp[x + 1]; ++i) { const int y = adj[i].v; if (d[y] < 0) { d[y] = d[x] + 1; q[tl++] = y; } }
+      for (int i = rrp[x]; i < rrp[x + 1]; ++i) { const int y = radj[i].v; if (d[y] < 0) { d[y] = d[x] + 1; q[tl++] = y; } }
+    }
+  };
+  // start from the vertex of largest degree's component: vertex 0 may be isolated (ids need not be dense)
+  int start = 0;
+  for (int v = 0; v < V; ++v)
+    if (rp[v + 1] - rp[v] + rrp[v + 1] - rrp[v] > rp[start + 1] - rp[start] + rrp[start + 1] - rrp[start]) start = v;
+  bfs(start, db);
+  int a = start;
+  for (int v = 0; v < V; ++v) if (db[v] > db[a]) a = v;
+  bfs(a, da);
+  int b = a;
+  for (int v = 0; v < V; ++v) if (da[v] > da[b]) b = v;
+  bfs(b, db);
+  int c = a; long best = -1;
+  for (int v = 0; v < V; ++v) { const long m = std::min(da[v], db[v]); if (m > best) { best = m; c = v; } }
+  bfs(c, dc);
+  int pmin = INT_MAX, qmin = INT_MAX, pmax = INT_MIN, qmax = INT_MIN;
+  for (int v = 0; v < V; ++v) {
+    if (da[v] < 0 || dc[v] < 0) continue;
+    const int pp = da[v] + dc[v], qq = da[v] - dc[v];
+    pmin = std::min(pmin, pp); pmax = std::max(pmax, pp); qmin = std::min(qmin, qq); qmax = std::max(qmax, qq);
+  }
+  if (pmin > pmax) { pmin = pmax = qmin = qmax = 0; }
+  unsigned side = 2;
+  while ((int)side <= std::max(pmax - pmin, qmax - qmin) / 2 + 1) side <<= 1;
+  std::vector<std::pair<unsigned long long, int>> keyed(V);
+  for (int v = 0; v < V; ++v) {
+    unsigned long long kx = ~0ull >> 1;   // other components: after the main one, in id order
+    if (da[v] >= 0 && dc[v] >= 0) kx = hilbert_key(side, (unsigned)(da[v] + dc[v] - pmin) / 2, (unsigned)(da[v] - dc[v] - qmin) / 2);
+    keyed[v] = std::make_pair(kx, v);
+  }
+  std::sort(keyed.begin(), keyed.end());
+  for (int x = 0; x < V; ++x) { iperm[x] = keyed[x].second; perm[keyed[x].second] = x; }
 }
 
 // CSR -> four-wide ELL + overflow list.  .pad of every record: low 3 bits = the slot, in the head vertex's own
@@ -1182,6 +1276,37 @@ static void build_ell(const std::vector<int>& rp, const std::vector<EdgeRec>& ad
       ell[(size_t)4 * v + 0].pad |= (int)ovf.size() << 3;
       ell[(size_t)4 * v + 1].pad |= (deg - 4) << 3;
       for (int j = 4; j < deg; ++j) ovf.push_back(adj[b + j]);
+    }
+  }
+}
+
+// The group kernel's ELL pair: the CSR / CSC in internal numbering (per-vertex edge order kept, so slot numbers and
+// one-byte predecessor codes mean the same as in the caller's numbering), four edges per record + overflow.  The
+// record's slot-0 pad carries the "sequential path" flag in bit 0.
+static void build_group_ell(int V, const std::vector<int>& rp, const std::vector<EdgeRec>& adj, const std::vector<int>& perm,
+                            const std::vector<int>& iperm, std::vector<EdgeRec>& gell, std::vector<EdgeRec>& govf,
+                            std::vector<int4>& heads) {
+  std::vector<int> rpn(V + 1, 0);
+  std::vector<EdgeRec> adjn(adj.size());
+  for (int x = 0; x < V; ++x) rpn[x + 1] = rpn[x] + (rp[iperm[x] + 1] - rp[iperm[x]]);
+  for (int x = 0; x < V; ++x) {
+    const int v = iperm[x];
+    for (int i = rp[v], o = rpn[x]; i < rp[v + 1]; ++i, ++o) adjn[o] = EdgeRec{adj[i].w, perm[adj[i].v], 0};
+  }
+  build_ell(rpn, adjn, V, gell, govf);
+  heads.assign(std::max(V, 1), make_int4(-1, -1, -1, -1));
+  for (int x = 0; x < V; ++x) {
+    EdgeRec* r = &gell[(size_t)4 * x];
+    bool slow = rpn[x + 1] - rpn[x] > 4;
+    for (int a = 0; a < 4; ++a) {
+      if (r[a].v == x) slow = true;
+      for (int b = a + 1; b < 4; ++b) if (r[a].v >= 0 && r[a].v == r[b].v) slow = true;
+    }
+    heads[x] = make_int4(r[0].v, r[1].v, r[2].v, r[3].v);
+    for (int a = 0; a < 4; ++a) {
+      const bool empty = r[a].v < 0;
+      r[a].pad = (r[a].pad & ~7) | (slow ? 1 : 0) | (empty ? 2 : 0);
+      if (empty) { r[a].v = x; r[a].w = 0.0; }   // never improves: the fast path needs no "has edge" test
     }
   }
 }
@@ -1231,6 +1356,18 @@ static int g_build_and_upload(SqGraph* g) {
     SQ_CUDA_TRY(cudaMemcpy(g->d_rrow_ptr, rrp.data(), sizeof(int) * (size_t)(V + 1), cudaMemcpyHostToDevice));
     if (!g->d_counter) SQ_CUDA_TRY(cudaMalloc(&g->d_counter, sizeof(int) * 1024));
     if (!g->d_stats) SQ_CUDA_TRY(cudaMalloc(&g->d_stats, sizeof(long long) * 5));
+    // group kernel: internal numbering and its device arrays
+    locality_order(V, rp, g->h_adj, rrp, g->h_radj, g->h_perm, g->h_iperm);
+    SQ_CUDA_TRY(cudaMalloc(&g->d_perm, sizeof(int) * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_iperm, sizeof(int) * (size_t)std::max(V, 1)));
+    if (V > 0) {
+      SQ_CUDA_TRY(cudaMemcpy(g->d_perm, g->h_perm.data(), sizeof(int) * (size_t)V, cudaMemcpyHostToDevice));
+      SQ_CUDA_TRY(cudaMemcpy(g->d_iperm, g->h_iperm.data(), sizeof(int) * (size_t)V, cudaMemcpyHostToDevice));
+    }
+    for (int d = 0; d < 2; ++d) {
+      SQ_CUDA_TRY(cudaMalloc(&g->d_gell[d], sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
+      SQ_CUDA_TRY(cudaMalloc(&g->d_gheads[d], sizeof(int4) * (size_t)std::max(V, 1)));
+    }
     g->topo_dirty = false;
     g->auto_ring = 0; g->auto_warp_unfit = false; g->pending_check_n = 0; g->auto_checks = 0;
     g->w_dirty = true;
@@ -1276,10 +1413,23 @@ static int g_build_and_upload(SqGraph* g) {
         SQ_CUDA_TRY(cudaMemcpy(dir ? g->d_fs_w : g->d_rs_w, sw.data(), sizeof(double) * sw.size(), cudaMemcpyHostToDevice));
       }
     }
+    for (int d = 0; d < 2; ++d) {
+      std::vector<int4> heads;
+      build_group_ell(g->V, d ? g->h_rrp : g->h_rp, d ? g->h_radj : g->h_adj, g->h_perm, g->h_iperm, g->h_gell[d], g->h_govf[d], heads);
+      if (g->h_govf[d].size() + 1 > g->govf_cap[d]) {
+        cudaFree(g->d_govf[d]); g->d_govf[d] = nullptr;
+        g->govf_cap[d] = g->h_govf[d].size() + 1;
+        SQ_CUDA_TRY(cudaMalloc(&g->d_govf[d], sizeof(EdgeRec) * g->govf_cap[d]));
+      }
+      SQ_CUDA_TRY(cudaMemcpy(g->d_gell[d], g->h_gell[d].data(), sizeof(EdgeRec) * g->h_gell[d].size(), cudaMemcpyHostToDevice));
+      SQ_CUDA_TRY(cudaMemcpy(g->d_gheads[d], heads.data(), sizeof(int4) * heads.size(), cudaMemcpyHostToDevice));
+      if (!g->h_govf[d].empty())
+        SQ_CUDA_TRY(cudaMemcpy(g->d_govf[d], g->h_govf[d].data(), sizeof(EdgeRec) * g->h_govf[d].size(), cudaMemcpyHostToDevice));
+    }
     if (g->wslots_n != g->es.size()) {
       // where each logged edge's weight lives on the device (for sp_set_weights_device)
       const size_t n = g->es.size();
-      std::vector<int> slots(4 * std::max<size_t>(n, 1), -1);
+      std::vector<int> slots(6 * std::max<size_t>(n, 1), -1);
       for (size_t i = 0; i < n; ++i) {
         const int a = g->edge_slot[i], r = g->edge_rslot[i];
         if (a < 0) continue;
@@ -1289,6 +1439,9 @@ static int g_build_and_upload(SqGraph* g) {
         slots[2 * n + i] = ja < 4 ? 4 * v + ja : -((g->h_ell[(size_t)4 * v].pad >> 3) + (ja - 4) + 1);
         const int u = g->ee[i], jr = r - g->h_rrp[u];
         slots[3 * n + i] = jr < 4 ? 4 * u + jr : -((g->h_rell[(size_t)4 * u].pad >> 3) + (jr - 4) + 1);
+        const int xv = g->h_perm[v], xu = g->h_perm[u];
+        slots[4 * n + i] = ja < 4 ? 4 * xv + ja : -((g->h_gell[0][(size_t)4 * xv].pad >> 3) + (ja - 4) + 1);
+        slots[5 * n + i] = jr < 4 ? 4 * xu + jr : -((g->h_gell[1][(size_t)4 * xu].pad >> 3) + (jr - 4) + 1);
       }
       cudaFree(g->d_wslots); g->d_wslots = nullptr;
       SQ_CUDA_TRY(cudaMalloc(&g->d_wslots, sizeof(int) * slots.size()));
@@ -1347,6 +1500,107 @@ static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t 
   }
   sq::count_launch();
   SQ_CUDA_TRY(cudaGetLastError());
+  return SQ_OK;
+}
+
+// Group kernel path (sp_group.cuh): trees sorted by the internal id of their origin, eight per group, one warp per
+// group; then one pass un-interleaves the distances into the caller's tables and writes the canonical predecessors.
+static int g_run_group(SqGraph* g, const int* origins_dev, int n, u64* dist_dev, int* parent_dev, cudaStream_t st, bool reverse,
+                       int n_sm) {
+  const int V = g->V;
+  const int dir = reverse ? 1 : 0;
+  const int n_groups = (n + 7) / 8, n_pad = n_groups * 8;
+  if (parent_dev && g->parent_format) {
+    size_t worst = 0;
+    const std::vector<int>& rp = reverse ? g->h_rp : g->h_rrp;
+    for (int v = 0; v < V; ++v) worst = std::max<size_t>(worst, (size_t)(rp[v + 1] - rp[v]));
+    if (worst > 254) return sq::set_error(SQ_ERR_LIMIT, "one-byte predecessor codes need in-degree <= 254 (found %zu)", worst);
+  }
+  // ---- sort the trees by origin (counting sort on the internal ids) ----
+  if (g->gkey_cap < (size_t)n_pad) {
+    cudaFree(g->d_gkey); cudaFree(g->d_tord); g->d_gkey = g->d_tord = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_gkey, sizeof(int) * (size_t)n_pad));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_tord, sizeof(int) * (size_t)n_pad));
+    g->gkey_cap = (size_t)n_pad;
+  }
+  if (g->ghist_cap < (size_t)V + 1) {
+    cudaFree(g->d_ghist); g->d_ghist = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_ghist, sizeof(int) * ((size_t)V + 1)));
+    g->ghist_cap = (size_t)V + 1;
+  }
+  SQ_CUDA_TRY(cudaMemsetAsync(g->d_ghist, 0, sizeof(int) * ((size_t)V + 1), st));
+  group_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, V, origins_dev, g->d_perm, g->d_gkey, g->d_ghist);
+  group_scan_kernel<<<1, 1024, 0, st>>>(V + 1, g->d_ghist);
+  group_scatter_kernel<<<(n_pad + 255) / 256, 256, 0, st>>>(n, n_pad, g->d_gkey, g->d_ghist, g->d_tord);
+  sq::count_launch(3);
+  SQ_CUDA_TRY(cudaGetLastError());
+
+  // ---- scratch: interleaved distance rows for a chunk of groups, queues per resident warp ----
+  const size_t row_bytes = (size_t)V * 64;
+  size_t chunk = std::max<size_t>(1, std::min<size_t>((size_t)n_groups, g->group_scratch_bytes / std::max<size_t>(row_bytes, 1)));
+  if (g->gdist_groups < chunk) {
+    cudaFree(g->d_gdist); g->d_gdist = nullptr; g->gdist_groups = 0;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_gdist, row_bytes * chunk));
+    g->gdist_groups = chunk;
+  }
+  const int wps = std::max(4, std::min(g->group_warps_per_sm, 32)) / 4 * 4;
+  const int warps = (int)std::min<size_t>(chunk, (size_t)n_sm * wps);
+  const int grid = (warps + 3) / 4;
+  int ring_cap = 64;
+  while (ring_cap < V) ring_cap <<= 1;
+  const int pend_cap = V + 32, words = (V + 31) / 32;
+  if (g->g_warps < grid * 4 || g->g_ring_cap != ring_cap || g->g_pend_cap != pend_cap) {
+    cudaFree(g->d_gring); cudaFree(g->d_gpend); cudaFree(g->d_ginp);
+    g->d_gring = g->d_gpend = g->d_ginp = nullptr; g->g_warps = 0;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_gring, sizeof(unsigned) * (size_t)grid * 4 * ring_cap));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_gpend, sizeof(unsigned) * (size_t)grid * 4 * 2 * pend_cap));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_ginp, sizeof(unsigned) * (size_t)grid * 4 * words));
+    g->g_warps = grid * 4; g->g_ring_cap = ring_cap; g->g_pend_cap = pend_cap; g->g_words = words;
+  }
+  typedef void (*GroupKernel)(const GroupParams);
+  static const GroupKernel kernels[3][2] = {{sssp_group_kernel<8, 0>, sssp_group_kernel<8, 1>},
+                                            {sssp_group_kernel<16, 0>, sssp_group_kernel<16, 1>},
+                                            {sssp_group_kernel<32, 0>, sssp_group_kernel<32, 1>}};
+  {
+    // no shared memory at all: give every byte of the SM's array to L1 (the in-order pops live on L1 hits)
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    SQ_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 64 && !attr_set[dev]) {
+      for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < 2; ++b)
+          SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[a][b], cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+      attr_set[dev] = true;
+    }
+  }
+  const GroupKernel kern = kernels[g->group_pb <= 8 ? 0 : g->group_pb <= 16 ? 1 : 2][g->group_pf ? 1 : 0];
+  for (size_t g0 = 0; g0 < (size_t)n_groups; g0 += chunk) {
+    const int m = (int)std::min(chunk, (size_t)n_groups - g0);
+    GroupParams gp;
+    memset(&gp, 0, sizeof(gp));
+    gp.V = V; gp.n_groups = m;
+    gp.gell = g->d_gell[dir]; gp.govf = g->d_govf[dir]; gp.gheads = g->d_gheads[dir];
+    gp.perm = g->d_perm; gp.origins = origins_dev; gp.tord = g->d_tord + g0 * 8;
+    gp.gdist = g->d_gdist; gp.ring = g->d_gring; gp.pend = g->d_gpend; gp.inp = g->d_ginp;
+    gp.ring_cap = ring_cap; gp.pend_cap = pend_cap; gp.words = words;
+    gp.counter = g->d_counter + 8 + (int)((g0 / chunk) & 127);   // d_counter[0..7] belong to the other kernels; zeroed per batch
+    gp.delta = g->delta;
+#ifdef SQ_SSSP_STATS
+    gp.stats = g->d_stats;
+#endif
+    const int wm = std::min(m, warps);
+    kern<<<(wm + 3) / 4, 128, 0, st>>>(gp);
+    sq::count_launch();
+    SQ_CUDA_TRY(cudaGetLastError());
+    if (dist_dev || parent_dev) {
+      dim3 fgrid((unsigned)(((size_t)V + 255) / 256), (unsigned)std::max(1, std::min(m, 2048)));
+      group_finalize_kernel<<<fgrid, 256, 0, st>>>(V, m, g->d_gell[dir ^ 1], g->d_govf[dir ^ 1], g->d_iperm, origins_dev,
+                                                  g->d_tord + g0 * 8, g->d_gdist, dist_dev, parent_dev, g->parent_format);
+      sq::count_launch();
+      SQ_CUDA_TRY(cudaGetLastError());
+    }
+  }
+  g->last_stats[0] = n;
   return SQ_OK;
 }
 
@@ -1440,6 +1694,10 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     g->last_stats[0] = n;
     return SQ_OK;
   }
+
+  // ---- group kernel: large batches whose origins lie close together (algo 4, or auto on dense batches) ----
+  if (g->algo == 4 || (g->algo == 3 && n >= g->group_min_trees && (long long)n * g->group_min_density >= (long long)V))
+    return g_run_group(g, origins_dev, n, dist_dev, parent_dev, st, reverse, n_sm);
 
   // ---- warp kernel (algo 2, default) or ELL kernel (algo 0) -------------------------------------------
   int vbits = 1;
@@ -1719,6 +1977,8 @@ void sp_free_graph(Graph* g) {
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
   cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail); cudaFree(g->d_wfar);
   cudaFree(g->d_pair); cudaFree(g->d_pair_off); cudaFree(g->d_pair_dist); cudaFree(g->d_pool);
+  cudaFree(g->d_gkey); cudaFree(g->d_tord); cudaFree(g->d_ghist); cudaFree(g->d_gdist);
+  cudaFree(g->d_gring); cudaFree(g->d_gpend); cudaFree(g->d_ginp);
   if (g->h_pool) cudaFreeHost(g->h_pool);
   if (g->s_compute) {
     cudaStreamDestroy(g->s_compute); cudaStreamDestroy(g->s_copy);
@@ -1742,7 +2002,8 @@ int sp_set_tuning(Graph* g, int threads, int ctas_per_sm, double delta_factor, i
 
 int sp_set_algo(Graph* g, int algo, double queue_factor) {
   if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: null graph");
-  if (algo < 0 || algo > 3) return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL), 1 (bitmap), 2 (warp) or 3 (auto)");
+  if (algo < 0 || algo > 4)
+    return sq::set_error(SQ_ERR_ARG, "sp_set_algo: algo must be 0 (ELL), 1 (bitmap), 2 (warp), 3 (auto) or 4 (group)");
   g->algo = algo;
   if (algo == 1 && g->threads < 128) g->threads = 256;
   if (algo == 3 && g->threads > 256) g->threads = 256;
@@ -1756,6 +2017,17 @@ int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
   if (ring_cap > 0) g->warp_ring = ring_cap;
   if (ilp > 0) g->warp_ilp = ilp;
   if (ctas_per_sm >= 0) g->warp_ctas_per_sm = ctas_per_sm;
+  return SQ_OK;
+}
+
+int sp_set_group_tuning(Graph* g, int warps_per_sm, int batch, int prefetch, int min_trees, int min_density) {
+  if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_group_tuning: null graph");
+  if (batch != 0 && batch != 8 && batch != 16 && batch != 32) return sq::set_error(SQ_ERR_ARG, "sp_set_group_tuning: batch must be 8, 16 or 32");
+  if (warps_per_sm > 0) g->group_warps_per_sm = warps_per_sm;
+  if (batch > 0) g->group_pb = batch;
+  if (prefetch >= 0) g->group_pf = prefetch;
+  if (min_trees > 0) g->group_min_trees = min_trees;
+  if (min_density > 0) g->group_min_density = min_density;
   return SQ_OK;
 }
 
@@ -1802,9 +2074,10 @@ int sp_set_weights_device(Graph* g, const double* weights_dev, int nedges, void*
   if (nedges == 0) return SQ_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const size_t n = (size_t)nedges;
-  WeightSlots ws{g->d_wslots, g->d_wslots + n, g->d_wslots + 2 * n, g->d_wslots + 3 * n};
+  WeightSlots ws{g->d_wslots, g->d_wslots + n, g->d_wslots + 2 * n, g->d_wslots + 3 * n, g->d_wslots + 4 * n, g->d_wslots + 5 * n};
   scatter_weights_kernel<<<(nedges + 255) / 256, 256, 0, st>>>(nedges, g->V, weights_dev, ws, g->d_adj, g->d_radj, g->d_ell,
-                                                             g->d_ovf, g->d_rell, g->d_rovf, g->d_fs_w, g->d_rs_w);
+                                                             g->d_ovf, g->d_rell, g->d_rovf, g->d_fs_w, g->d_rs_w,
+                                                             g->d_gell[0], g->d_govf[0], g->d_gell[1], g->d_govf[1]);
   sq::count_launch();
   SQ_CUDA_TRY(cudaGetLastError());
   // keep the host log in step (it is what update_edge / writegraph / the next structural rebuild start from)

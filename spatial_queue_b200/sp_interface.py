@@ -128,11 +128,16 @@ class Graph:
               "sp_decode_parents_device")
 
     def set_algo(self, algo=3, queue_factor=0.0):
-        """3 = auto (default), 2 = warp kernel, 0 = ELL kernel, 1 = bitmap kernel; see include/sq_sp.h."""
+        """3 = auto (default), 4 = group kernel, 2 = warp kernel, 0 = ELL kernel, 1 = bitmap kernel; see include/sq_sp.h."""
         check(lib().sp_set_algo(self._h, int(algo), float(queue_factor)), "sp_set_algo")
 
     def set_warp_tuning(self, ring_cap=0, ilp=0, ctas_per_sm=-1):
         check(lib().sp_set_warp_tuning(self._h, int(ring_cap), int(ilp), int(ctas_per_sm)), "sp_set_warp_tuning")
+
+    def set_group_tuning(self, warps_per_sm=0, batch=0, prefetch=-1, min_trees=0, min_density=0):
+        """Group kernel (algo 4 / auto on dense batches): see include/sq_sp.h."""
+        check(lib().sp_set_group_tuning(self._h, int(warps_per_sm), int(batch), int(prefetch), int(min_trees),
+                                        int(min_density)), "sp_set_group_tuning")
 
     def sync(self):
         check(lib().sp_sync(self._h), "sp_sync")

@@ -65,7 +65,8 @@ def test_network_mtx_golden(spi):
 @pytest.mark.parametrize("threads,smemq,algo,qfac", [(256, 0, 1, 0), (128, 32, 1, 0), (1024, 64, 1, 0),   # bitmap kernel
                                                       (128, 0, 0, 0), (64, 0, 0, 0), (32, 0, 0, 0), (1024, 0, 0, 0), (512, 0, 0, 0),   # ELL kernel
                                                       (256, 0, 0, 4.0), (64, 0, 0, 0.02),                 # roomy / tight queues
-                                                      (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0)])    # warp kernel: (ilp, ring)
+                                                      (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0),    # warp kernel: (ilp, ring)
+                                                      (8, 0, 4, 0), (16, 1, 4, 0), (32, 1, 4, 0)])         # group kernel: (batch, prefetch)
 def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
     from oracle import sssp as osssp
     rng = np.random.default_rng(11 + threads)
@@ -82,9 +83,13 @@ def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
         if algo == 2:
             g.set_warp_tuning(ring_cap=smemq, ilp=threads)
             g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
+        elif algo == 4:
+            # parallel edges, self loops, out-degrees beyond four (sequential path), closed links (threshold jumps)
+            g.set_group_tuning(batch=threads, prefetch=smemq)
+            g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
         else:
             g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
-        origins = np.concatenate([rng.integers(0, V, 7), [-1, V, V + 5]]).astype(np.int32)
+        origins = np.concatenate([rng.integers(0, V, 7 if algo != 4 else 29), [-1, V, V + 5]]).astype(np.int32)
         d, p = g.sssp_batch(origins)
         do, po = og.sssp_batch(origins)
         assert d.tobytes() == do.tobytes()
@@ -160,7 +165,7 @@ def test_weight_updates_reach_the_device(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
 
 
-@pytest.mark.parametrize("algo", [0, 1, 2, 3])
+@pytest.mark.parametrize("algo", [0, 1, 2, 3, 4])
 def test_grid_batch_and_device_api(spi, algo):
     import torch
     from oracle import sssp as osssp
@@ -251,8 +256,9 @@ def test_reverse_trees_and_device_weight_refresh(spi):
     g.free()
 
 
+@pytest.mark.parametrize("algo", [3, 4])
 @pytest.mark.parametrize("reverse", [False, True])
-def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse):
+def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo):
     """The compact table the multi-GPU path all-gathers (one byte per vertex) expands to exactly the int32 tree."""
     import torch
     rng = np.random.default_rng(31)
@@ -261,6 +267,7 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse):
     e = rng.integers(0, V, E).astype(np.int32)
     w = np.round(rng.random(E) * 20.0) + 1.0   # many exact ties
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.set_algo(algo)
     origins = torch.from_numpy(rng.integers(0, V, 40).astype(np.int32)).cuda()
     d = torch.empty((40, V), dtype=torch.float64, device="cuda")
     p32 = torch.empty((40, V), dtype=torch.int32, device="cuda")
@@ -275,6 +282,14 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse):
     g.set_parent_format(0)
     dh, ph = g.sssp_batch(origins.cpu().numpy()[:5], reverse=reverse)
     assert (ph == p32[:5].cpu().numpy()).all()
+    if algo == 4:
+        # and the group kernel's tables are the other kernels' tables
+        g.set_algo(0)
+        d0 = torch.empty_like(d)
+        p0 = torch.empty_like(p32)
+        g.sssp_batch_device(origins, d0, p0, reverse=reverse)
+        torch.cuda.synchronize()
+        assert torch.equal(d0.view(torch.int64), d.view(torch.int64)) and torch.equal(p0, p32)
     g.free()
 
 
@@ -372,4 +387,121 @@ def test_route_batch_on_the_grid_matches_full_tables(spi, chunk, monkeypatch):
     for k in range(0, 1500, 37):
         assert pool[off[k]: off[k] + ln[k]].tolist() == (_walk(pp[k], int(o[k]), int(d[k])) if o[k] != d[k] else [])
     assert int(ln.sum()) == len(pool) and ln.max() > 60
+    g.free()
+
+
+# ---- the benchmarked configuration, at its size (VERDICT r1 parity hole 1a) -------------------------------------------
+
+def _config5():
+    import bench
+    s, e, w, V = bench.sssp_workload(224)
+    return np.asarray(s, np.int32), np.asarray(e, np.int32), np.asarray(w, np.float64), V, bench
+
+
+def _congested_weights(s, e, w, seed=2):
+    """second weight set, w = q / (cap + 0.1) * 3600 * 25 / maxmph + fft with q ~ Poisson(3)
+    (queue_class.py:463-466 on one-lane 1900 veh/h links at 25 mph)."""
+    q = np.random.default_rng(seed).poisson(3.0, len(w)).astype(np.float64)
+    return q / (1900.0 + 0.1) * 3600 * 25 / 25.0 + w
+
+
+@pytest.mark.parametrize("algo,n", [(3, 2368), (4, 2368), (3, 18944)])
+def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
+    """bench.py's HP-2 workload itself: 224x224 grid, bench.origins_for origins, through sp_sssp_batch_device in auto
+    mode (2,368 origins: sssp_warp_kernel; 18,944 origins, the benchmarked batch: sssp_group_kernel) and with the group
+    kernel forced; distances bit for bit and canonical predecessors equal to the C oracle for every tree of the small
+    batch and for a 1,024-tree sample of the large one; eight trees also against the reference library itself."""
+    import torch
+    from oracle import sssp as osssp
+    s, e, w, V, bench = _config5()
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.set_algo(algo)
+    origins = bench.origins_for(0, n, V, step=0)
+    o_dev = torch.from_numpy(origins).cuda()
+    d_dev = torch.empty((n, V), dtype=torch.float64, device="cuda")
+    p_dev = torch.empty((n, V), dtype=torch.int32, device="cuda")
+    g.sssp_batch_device(o_dev, d_dev, p_dev)
+    torch.cuda.synchronize()
+    st = g.last_stats()
+    sample = np.arange(n) if n <= 4096 else np.random.default_rng(0).choice(n, 1024, replace=False)
+    og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1)
+    do, po = og.sssp_batch(origins[sample])
+    idx = torch.from_numpy(sample).cuda()
+    assert d_dev[idx].cpu().numpy().tobytes() == do.tobytes()
+    assert (p_dev[idx].cpu().numpy() == po).all()
+    # size-independent properties over the whole batch: origin rows, reachability, no edge can still relax
+    assert bool((d_dev[torch.arange(n, device="cuda"), o_dev.long()] == 0).all())
+    assert bool((d_dev < 1e300).all())
+    sd, ed, wd = (torch.from_numpy(x).cuda() for x in (s.astype(np.int64), e.astype(np.int64), w))
+    for lo in range(0, n, 1024):
+        blk = d_dev[lo:lo + 1024]
+        assert bool((blk[:, ed] <= blk[:, sd] + wd).all())
+    if osssp.ref_available():
+        rg = osssp.RefGraph(s, e, w, max_vertex_id=V - 1)
+        for i in sample[:8]:
+            dr, _ = rg.dijkstra(int(origins[i]), -1)
+            assert d_dev[int(i)].cpu().numpy().tobytes() == dr.tobytes()
+    # the one-byte code path of the same batch decodes to the same tables
+    g.set_parent_format(1)
+    codes = torch.empty((n, V), dtype=torch.uint8, device="cuda")
+    g.sssp_batch_device(o_dev, None, codes)
+    out = torch.empty((min(n, 2368), V), dtype=torch.int32, device="cuda")
+    g.decode_parents_device(codes[:len(out)], out)
+    torch.cuda.synchronize()
+    assert torch.equal(out, p_dev[:len(out)])
+    g.set_parent_format(0)
+    del st
+    g.free()
+
+
+@pytest.mark.parametrize("algo", [3, 4])
+def test_config5_congested_weight_set(spi, algo):
+    """Same graph with the second, congested weight set of SURVEY.md 8(d) (queues ~ Poisson(3)) pushed through
+    sp_set_weights_device, 1,024 origins (auto mode: the warp kernel; forced: the group kernel)."""
+    import torch
+    from oracle import sssp as osssp
+    s, e, w, V, bench = _config5()
+    w2 = _congested_weights(s, e, w)
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.set_algo(algo)
+    g.set_weights_device(torch.from_numpy(w2).cuda())
+    origins = bench.origins_for(0, 1024, V, step=3)
+    o_dev = torch.from_numpy(origins).cuda()
+    d_dev = torch.empty((1024, V), dtype=torch.float64, device="cuda")
+    p_dev = torch.empty((1024, V), dtype=torch.int32, device="cuda")
+    g.sssp_batch_device(o_dev, d_dev, p_dev)
+    torch.cuda.synchronize()
+    do, po = osssp.OracleGraph(s, e, w2, max_vertex_id=V - 1).sssp_batch(origins)
+    assert d_dev.cpu().numpy().tobytes() == do.tobytes()
+    assert (p_dev.cpu().numpy() == po).all()
+    g.free()
+
+
+def test_group_kernel_on_an_irregular_network_with_closures(spi):
+    """The group kernel where its assumptions are weakest: a town-like network (streets removed, one-ways, hubs with
+    more than four out-links), 3 % of the links closed at 1e8 (threshold jumps, pending-list rescans), origins
+    clustered AND scattered, duplicates and out-of-range origins in the batch; forward and reverse trees."""
+    import torch
+    from oracle import sssp as osssp
+    from spatial_queue_b200 import synth
+    rng = np.random.default_rng(4)
+    s, e, _, _ = synth.town_edges(40, seed=3)
+    s, e = np.asarray(s, np.int32), np.asarray(e, np.int32)
+    V = 40 * 40
+    w = rng.random(len(s)) * 30.0 + 2.0
+    w[rng.random(len(s)) < 0.03] = 1e8
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    g.set_algo(4)
+    origins = np.concatenate([rng.integers(0, V, 300), np.arange(100, 140), [5, 5, 5, -1, V + 7]]).astype(np.int32)
+    n = len(origins)
+    for reverse in (False, True):
+        o_dev = torch.from_numpy(origins).cuda()
+        d_dev = torch.empty((n, V), dtype=torch.float64, device="cuda")
+        p_dev = torch.empty((n, V), dtype=torch.int32, device="cuda")
+        g.sssp_batch_device(o_dev, d_dev, p_dev, reverse=reverse)
+        torch.cuda.synchronize()
+        og = osssp.OracleGraph(e, s, w, max_vertex_id=V - 1) if reverse else osssp.OracleGraph(s, e, w, max_vertex_id=V - 1)
+        do, po = og.sssp_batch(origins)
+        assert d_dev.cpu().numpy().tobytes() == do.tobytes()
+        assert (p_dev.cpu().numpy() == po).all()
     g.free()
