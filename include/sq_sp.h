@@ -150,6 +150,11 @@ int sp_set_algo(Graph* graph, int algo, double queue_factor);
  * into L1 (< 0 keeps; default 1); auto mode picks the group kernel for batches of at least min_trees origins
  * (0 keeps; default 2048) that hold at least V / min_density origins (0 keeps; default 8). */
 int sp_set_group_tuning(Graph* graph, int warps_per_sm, int batch, int prefetch, int min_trees, int min_density);
+/* Which tree kernel works on the group layout: 0 (default) = the warp kernel, a CTA of eight warps per group and one
+ * tree per warp (ring_cap entries per tree, 0 keeps; default 1024; trees that outgrow it are rerun by the bitmap
+ * kernel); 1 = sssp_group_kernel, one warp per group, no atomics and no capacity limits (also what mode 0 falls back
+ * to when the graph is too large for the bitmap kernel). */
+int sp_set_group_mode(Graph* graph, int mode, int ring_cap);
 
 /* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps; default 1024), frontier
  * vertices per step = 8 x ilp (1, 2 or 4; 0 keeps; default 4), CTAs of four warps per SM (0 = default 4, at most

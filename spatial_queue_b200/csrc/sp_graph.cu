@@ -84,6 +84,11 @@ struct TreeParams {
   int wfar_cap;
   int ring_cap;           // entries per shared-memory ring (power of two)
   int vbits;              // bits of a queue entry that hold the vertex id
+  // grouped variant of the warp kernel (eight sibling trees per CTA on interleaved rows)
+  u64* gdist;             // [groups][V][8]
+  const int* tord;        // [groups * 8] tree at each sorted position, -1 = padding
+  const int* perm;        // caller id -> internal id
+  int parent_codes;       // bitmap kernel's own predecessor pass: 1 = one-byte in-edge codes
 };
 
 #define DIST_INF_BITS 0x7FEFFFFFFFFFFFFFull  // DBL_MAX, what the reference leaves in unreached slots
@@ -300,8 +305,9 @@ __global__ void __launch_bounds__(THREADS) sssp_nearfar_kernel(const TreeParams 
     // ---- canonical predecessor pass: parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]} -----------
     if (p.parent_out) {
       int* parent = p.parent_out + (size_t)tree * V;
+      unsigned char* pcode = reinterpret_cast<unsigned char*>(p.parent_out) + (size_t)tree * V;
       for (int v = tid; v < V; v += THREADS) {
-        int best = -1;
+        int best = -1, bslot = 255;
         if (valid && v != src) {
           const u64 dvb = sq::ld_cg_u64(&dist[v]);
           if (dvb != DIST_INF_BITS) {
@@ -313,12 +319,13 @@ __global__ void __launch_bounds__(THREADS) sssp_nearfar_kernel(const TreeParams 
               const u64 dub = sq::ld_cg_u64(&dist[er.v]);
               if (dub == DIST_INF_BITS) continue;
               const double cand = __longlong_as_double((long long)dub) + er.w;
-              if ((u64)__double_as_longlong(cand) == dvb && er.v < best) best = er.v;
+              if ((u64)__double_as_longlong(cand) == dvb && er.v < best) { best = er.v; bslot = min(idx - b, 254); }
             }
-            if (best == INT_MAX) best = -1;
+            if (best == INT_MAX) { best = -1; bslot = 255; }
           }
         }
-        parent[v] = best;
+        if (p.parent_codes) pcode[v] = (unsigned char)bslot;
+        else parent[v] = best;
       }
     }
     __syncthreads();
@@ -692,9 +699,15 @@ __device__ __forceinline__ unsigned dist_hash(u64 d) {
   return ((unsigned)d * 0x9E3779B1u) ^ ((unsigned)(d >> 32) * 0x85EBCA6Bu);
 }
 
-template <int ILP>
-__global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
+// GROUPED: the eight warps of a CTA run the eight trees of one group of neighbouring origins (sorted by the host along
+// the locality order) on INTERLEAVED distance rows, dist[v][8] in internal numbering (p.gdist), so that the sectors
+// and lines the sibling trees touch are the same ones: a quarter of the L2 footprint per tree, and the two rows of a
+// 128-byte line belong to adjacent vertices.  group_finalize_kernel un-interleaves the rows afterwards.  The ELL is the
+// group form (sp_group.cuh): pad bit 1 = empty slot, bits 3..5 = slot of the edge straight back, bits 6.. = overflow.
+template <int ILP, bool GROUPED>
+__global__ void __launch_bounds__(GROUPED ? 256 : 128) sssp_warp_kernel(const TreeParams p) {
   extern __shared__ unsigned s_rings[];
+  __shared__ int s_grp;
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = lane & 3, grp = lane >> 2;
@@ -713,26 +726,51 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
   int st_steps = 0, st_relax = 0, st_trans = 0;
 
   for (;;) {
-    int tree = 0;
-    if (lane == 0) tree = atomicAdd(p.tree_counter, 1);
-    tree = __shfl_sync(FULL, tree, 0);
-    if (tree >= p.n_trees) break;
-
-    u64* dist = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)gwarp * V;
-    const int src = p.origins[tree];
-    const bool valid_src = (src >= 0 && src < V);
-    {  // distance row = DBL_MAX (graph.cc:178); rows are 8-byte aligned, 16-byte stores on the aligned middle
-      const int head = (int)(((uintptr_t)dist >> 3) & 1);
-      if (lane == 0 && head && V > 0) dist[0] = DIST_INF_BITS;
-      const int pairs = (V - head) >> 1;
-      ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dist + head);
-      const ulonglong2 inf2 = make_ulonglong2(DIST_INF_BITS, DIST_INF_BITS);
+    int tree = 0, src = -1;
+    u64* dist;
+    if (GROUPED) {
+      __syncthreads();                       // every warp is done with the previous group
+      if (threadIdx.x == 0) s_grp = atomicAdd(p.tree_counter, 1);
+      __syncthreads();
+      const int gidx = s_grp;
+      if (gidx >= p.n_trees) break;          // n_trees = number of groups here
+      dist = p.gdist + (size_t)gidx * V * 8;
+      {  // rows = DBL_MAX (graph.cc:178), all eight warps together
+        ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dist);
+        const ulonglong2 inf2 = make_ulonglong2(DIST_INF_BITS, DIST_INF_BITS);
+        const int n2 = V * 4;
 #pragma unroll 4
-      for (int i = lane; i < pairs; i += 32) d2[i] = inf2;
-      if (lane == 0 && ((V - head) & 1)) dist[V - 1] = DIST_INF_BITS;
+        for (int i = threadIdx.x; i < n2; i += 256) d2[i] = inf2;
+      }
+      tree = __ldg(&p.tord[gidx * 8 + warp]);
+      if (tree >= 0) {
+        const int o = __ldg(&p.origins[tree]);
+        if (o >= 0 && o < V) src = __ldg(&p.perm[o]);
+      }
+      dist += warp;                          // this warp's column
+      __syncthreads();
+    } else {
+      if (lane == 0) tree = atomicAdd(p.tree_counter, 1);
+      tree = __shfl_sync(FULL, tree, 0);
+      if (tree >= p.n_trees) break;
+      dist = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)gwarp * V;
+      src = p.origins[tree];
+      {  // distance row = DBL_MAX (graph.cc:178); rows are 8-byte aligned, 16-byte stores on the aligned middle
+        const int head = (int)(((uintptr_t)dist >> 3) & 1);
+        if (lane == 0 && head && V > 0) dist[0] = DIST_INF_BITS;
+        const int pairs = (V - head) >> 1;
+        ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dist + head);
+        const ulonglong2 inf2 = make_ulonglong2(DIST_INF_BITS, DIST_INF_BITS);
+#pragma unroll 4
+        for (int i = lane; i < pairs; i += 32) d2[i] = inf2;
+        if (lane == 0 && ((V - head) & 1)) dist[V - 1] = DIST_INF_BITS;
+      }
+      __syncwarp();
     }
-    __syncwarp();
+    const bool valid_src = (src >= 0 && src < V);
     if (!valid_src) continue;
+    // element v of this tree's distance column
+    auto DA = [&](unsigned v) -> u64* { return GROUPED ? dist + ((size_t)v << 3) : dist + v; };
 
     unsigned* cur = ring_a;
     unsigned* bkt = ring_a + C;
@@ -740,7 +778,7 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
     int nf = 0, fcur = 0;          // far pile
     bool fail = false;
     if (lane == 0) {
-      dist[src] = 0ull;
+      *DA((unsigned)src) = 0ull;
       cur[0] = (unsigned)src | (7u << vbits) | (dist_hash(0ull) & himask);
     }
     __syncwarp();
@@ -778,7 +816,7 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
           const unsigned* fp = far_base + (size_t)fcur * fcap;
           for (int i = lane; i < nf; i += 32) {
             const unsigned e = (unsigned)sq::ld_cg_s32(reinterpret_cast<const int*>(fp + i));
-            const u64 d = sq::ld_cg_u64(&dist[e & vmask]);
+            const u64 d = sq::ld_cg_u64(DA(e & vmask));
             if (((dist_hash(d) ^ e) & himask) == 0 && d < lmin) lmin = d;
           }
 #pragma unroll
@@ -805,7 +843,7 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
             double d = 0.0;
             if (i < nf) {
               e = (unsigned)sq::ld_cg_s32(reinterpret_cast<const int*>(fp + i));
-              const u64 db = sq::ld_cg_u64(&dist[e & vmask]);
+              const u64 db = sq::ld_cg_u64(DA(e & vmask));
               live = ((dist_hash(db) ^ e) & himask) == 0;
               d = __longlong_as_double((long long)db);
             }
@@ -846,8 +884,8 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
         raw[j] = make_int4(0, 0, -1, 7);
         if (act[j]) {
           const unsigned u = ent[j] & vmask;
-          dnow[j] = sq::ld_cg_u64(&dist[u]);
-          raw[j] = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u * 4 + slot]));
+          dnow[j] = sq::ld_cg_u64(DA(u));
+          raw[j] = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u * 4 + slot]));   // GROUPED: p.ell = the group ELL
         }
       }
       bool ok[ILP], has[ILP];
@@ -855,23 +893,24 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
 #pragma unroll
       for (int j = 0; j < ILP; ++j) {
         ok[j] = act[j] && ((dist_hash(dnow[j]) ^ ent[j]) & himask) == 0;
-        has[j] = ok[j] && raw[j].z >= 0 && slot != (int)((ent[j] >> vbits) & 7u);
+        has[j] = ok[j] && (GROUPED ? !(raw[j].w & 2) : raw[j].z >= 0) && slot != (int)((ent[j] >> vbits) & 7u);
         ndb[j] = (u64)__double_as_longlong(__longlong_as_double((long long)dnow[j]) + __hiloint2double(raw[j].y, raw[j].x));
         old[j] = 0ull;
       }
 #pragma unroll
       for (int j = 0; j < ILP; ++j)
-        if (has[j]) old[j] = atomicMin(&dist[raw[j].z], ndb[j]);
+        if (has[j]) old[j] = atomicMin(DA((unsigned)raw[j].z), ndb[j]);
 #pragma unroll
       for (int j = 0; j < ILP; ++j) {
         st_relax += has[j];
-        const unsigned ne = (unsigned)raw[j].z | ((unsigned)(raw[j].w & 7) << vbits) | (dist_hash(ndb[j]) & himask);
+        const unsigned back = GROUPED ? (unsigned)(raw[j].w >> 3) & 7u : (unsigned)(raw[j].w & 7);
+        const unsigned ne = (unsigned)raw[j].z | (back << vbits) | (dist_hash(ndb[j]) & himask);
         push(has[j] && ndb[j] < old[j], ndb[j], ne);
       }
       // edges beyond the fourth of a vertex (rare on road networks)
 #pragma unroll
       for (int j = 0; j < ILP; ++j) {
-        const int my = ok[j] ? (raw[j].w >> 3) : 0;
+        const int my = ok[j] ? (raw[j].w >> (GROUPED ? 6 : 3)) : 0;
         if (!__any_sync(FULL, slot == 1 && my != 0)) continue;
         const int ovf_b = __shfl_sync(FULL, my, lane & ~3);
         const int ovf_n = __shfl_sync(FULL, my, (lane & ~3) + 1);
@@ -883,7 +922,7 @@ __global__ void __launch_bounds__(128) sssp_warp_kernel(const TreeParams p) {
           if (h2) {
             const EdgeRec er = ld_edge(&p.ovf[ovf_b + k]);
             nb2 = (u64)__double_as_longlong(__longlong_as_double((long long)dnow[j]) + er.w);
-            old2 = atomicMin(&dist[er.v], nb2);
+            old2 = atomicMin(DA((unsigned)er.v), nb2);
             ne = (unsigned)er.v | (7u << vbits) | (dist_hash(nb2) & himask);
           }
           st_relax += h2;
@@ -1103,6 +1142,8 @@ struct SqGraph {
   unsigned* d_gring = nullptr; unsigned* d_gpend = nullptr; unsigned* d_ginp = nullptr;
   int g_warps = 0, g_ring_cap = 0, g_pend_cap = 0, g_words = 0;
   int group_warps_per_sm = 16, group_pb = 16, group_pf = 1;
+  int group_mode = 0;                    // 0 = grouped warp kernel (a CTA of eight warps per group), 1 = sssp_group_kernel
+  int group_ring = 1024;                 // ring entries per tree of the grouped warp kernel
   int group_min_trees = 2048;            // auto mode: batches at least this large ...
   int group_min_density = 8;             // ... with at least V / this many origins go to the group kernel
   size_t group_scratch_bytes = (size_t)24 << 30;   // upper bound of the interleaved distance scratch per chunk
@@ -1305,7 +1346,8 @@ static void build_group_ell(int V, const std::vector<int>& rp, const std::vector
     heads[x] = make_int4(r[0].v, r[1].v, r[2].v, r[3].v);
     for (int a = 0; a < 4; ++a) {
       const bool empty = r[a].v < 0;
-      r[a].pad = (r[a].pad & ~7) | (slow ? 1 : 0) | (empty ? 2 : 0);
+      // bit 0: sequential path, bit 1: empty slot, bits 3..5: slot of the edge straight back (7 = none), bits 6..: overflow
+      r[a].pad = (slow ? 1 : 0) | (empty ? 2 : 0) | ((r[a].pad & 7) << 3) | ((r[a].pad >> 3) << 6);
       if (empty) { r[a].v = x; r[a].w = 0.0; }   // never improves: the fast path needs no "has edge" test
     }
   }
@@ -1440,8 +1482,8 @@ static int g_build_and_upload(SqGraph* g) {
         const int u = g->ee[i], jr = r - g->h_rrp[u];
         slots[3 * n + i] = jr < 4 ? 4 * u + jr : -((g->h_rell[(size_t)4 * u].pad >> 3) + (jr - 4) + 1);
         const int xv = g->h_perm[v], xu = g->h_perm[u];
-        slots[4 * n + i] = ja < 4 ? 4 * xv + ja : -((g->h_gell[0][(size_t)4 * xv].pad >> 3) + (ja - 4) + 1);
-        slots[5 * n + i] = jr < 4 ? 4 * xu + jr : -((g->h_gell[1][(size_t)4 * xu].pad >> 3) + (jr - 4) + 1);
+        slots[4 * n + i] = ja < 4 ? 4 * xv + ja : -((g->h_gell[0][(size_t)4 * xv].pad >> 6) + (ja - 4) + 1);
+        slots[5 * n + i] = jr < 4 ? 4 * xu + jr : -((g->h_gell[1][(size_t)4 * xu].pad >> 6) + (jr - 4) + 1);
       }
       cudaFree(g->d_wslots); g->d_wslots = nullptr;
       SQ_CUDA_TRY(cudaMalloc(&g->d_wslots, sizeof(int) * slots.size()));
@@ -1503,11 +1545,17 @@ static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t 
   return SQ_OK;
 }
 
-// Group kernel path (sp_group.cuh): trees sorted by the internal id of their origin, eight per group, one warp per
-// group; then one pass un-interleaves the distances into the caller's tables and writes the canonical predecessors.
-static int g_run_group(SqGraph* g, const int* origins_dev, int n, u64* dist_dev, int* parent_dev, cudaStream_t st, bool reverse,
-                       int n_sm) {
+// Group path: the trees are sorted by the internal id of their origin (a Hilbert order over the network) and cut into
+// groups of eight; a group's distances live interleaved, dist[v][8], in library scratch.  Two tree kernels work on that
+// layout: the grouped variant of sssp_warp_kernel (group_mode 0: one CTA of eight warps per group, one tree per warp)
+// and sssp_group_kernel (group_mode 1: one warp per group, no atomics, no capacity limits).  group_finalize_kernel then
+// un-interleaves the rows into the caller's tables and writes the canonical predecessors in the same pass.
+struct BitmapGeom { int grid, threads; size_t smem; bool fits; };
+
+static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm, const cudaDeviceProp& prop, const int* origins_dev,
+                       int n, u64* dist_dev, int* parent_dev, cudaStream_t st, bool reverse) {
   const int V = g->V;
+  const int n_sm = prop.multiProcessorCount;
   const int dir = reverse ? 1 : 0;
   const int n_groups = (n + 7) / 8, n_pad = n_groups * 8;
   if (parent_dev && g->parent_format) {
@@ -1516,6 +1564,12 @@ static int g_run_group(SqGraph* g, const int* origins_dev, int n, u64* dist_dev,
     for (int v = 0; v < V; ++v) worst = std::max<size_t>(worst, (size_t)(rp[v + 1] - rp[v]));
     if (worst > 254) return sq::set_error(SQ_ERR_LIMIT, "one-byte predecessor codes need in-degree <= 254 (found %zu)", worst);
   }
+  int vbits = 1;
+  while ((1ll << vbits) < (long long)V) ++vbits;
+  // the warp kernel needs a fallback for trees whose wavefront outgrows its ring; without one (graph too large for the
+  // bitmap kernel, or ids too wide for the hashed queue entries) the group runs on the kernel that cannot overflow
+  const bool warp_mode = g->group_mode == 0 && vbits <= 24 && bm.fits;
+
   // ---- sort the trees by origin (counting sort on the internal ids) ----
   if (g->gkey_cap < (size_t)n_pad) {
     cudaFree(g->d_gkey); cudaFree(g->d_tord); g->d_gkey = g->d_tord = nullptr;
@@ -1535,7 +1589,7 @@ static int g_run_group(SqGraph* g, const int* origins_dev, int n, u64* dist_dev,
   sq::count_launch(3);
   SQ_CUDA_TRY(cudaGetLastError());
 
-  // ---- scratch: interleaved distance rows for a chunk of groups, queues per resident warp ----
+  // ---- scratch: interleaved distance rows for a chunk of groups ----
   const size_t row_bytes = (size_t)V * 64;
   size_t chunk = std::max<size_t>(1, std::min<size_t>((size_t)n_groups, g->group_scratch_bytes / std::max<size_t>(row_bytes, 1)));
   if (g->gdist_groups < chunk) {
@@ -1543,53 +1597,101 @@ static int g_run_group(SqGraph* g, const int* origins_dev, int n, u64* dist_dev,
     SQ_CUDA_TRY(cudaMalloc(&g->d_gdist, row_bytes * chunk));
     g->gdist_groups = chunk;
   }
-  const int wps = std::max(4, std::min(g->group_warps_per_sm, 32)) / 4 * 4;
-  const int warps = (int)std::min<size_t>(chunk, (size_t)n_sm * wps);
-  const int grid = (warps + 3) / 4;
+
+  // ---- kernel geometry ----
+  int grid = 0;
+  size_t warp_smem = 0;
+  int C = 64, fcap = 0;
   int ring_cap = 64;
-  while (ring_cap < V) ring_cap <<= 1;
   const int pend_cap = V + 32, words = (V + 31) / 32;
-  if (g->g_warps < grid * 4 || g->g_ring_cap != ring_cap || g->g_pend_cap != pend_cap) {
-    cudaFree(g->d_gring); cudaFree(g->d_gpend); cudaFree(g->d_ginp);
-    g->d_gring = g->d_gpend = g->d_ginp = nullptr; g->g_warps = 0;
-    SQ_CUDA_TRY(cudaMalloc(&g->d_gring, sizeof(unsigned) * (size_t)grid * 4 * ring_cap));
-    SQ_CUDA_TRY(cudaMalloc(&g->d_gpend, sizeof(unsigned) * (size_t)grid * 4 * 2 * pend_cap));
-    SQ_CUDA_TRY(cudaMalloc(&g->d_ginp, sizeof(unsigned) * (size_t)grid * 4 * words));
-    g->g_warps = grid * 4; g->g_ring_cap = ring_cap; g->g_pend_cap = pend_cap; g->g_words = words;
-  }
+  typedef void (*WarpKernel)(const TreeParams);
   typedef void (*GroupKernel)(const GroupParams);
-  static const GroupKernel kernels[3][2] = {{sssp_group_kernel<8, 0>, sssp_group_kernel<8, 1>},
-                                            {sssp_group_kernel<16, 0>, sssp_group_kernel<16, 1>},
-                                            {sssp_group_kernel<32, 0>, sssp_group_kernel<32, 1>}};
-  {
-    // no shared memory at all: give every byte of the SM's array to L1 (the in-order pops live on L1 hits)
+  static const WarpKernel wkernels[4] = {sssp_warp_kernel<1, true>, sssp_warp_kernel<2, true>, sssp_warp_kernel<4, true>,
+                                         sssp_warp_kernel<8, true>};
+  static const GroupKernel gkernels[3][2] = {{sssp_group_kernel<8, 0>, sssp_group_kernel<8, 1>},
+                                             {sssp_group_kernel<16, 0>, sssp_group_kernel<16, 1>},
+                                             {sssp_group_kernel<32, 0>, sssp_group_kernel<32, 1>}};
+  int dev = 0;
+  SQ_CUDA_TRY(cudaGetDevice(&dev));
+  if (warp_mode) {
+    while (C < g->group_ring) C <<= 1;
+    warp_smem = (size_t)8 * 2 * C * sizeof(unsigned);
+    if (warp_smem > 200 * 1024) return sq::set_error(SQ_ERR_ARG, "group path: ring capacity %d does not fit shared memory", C);
+    int per_sm = (int)((size_t)prop.sharedMemPerMultiprocessor / (warp_smem + 1024));
+    per_sm = std::max(1, std::min(per_sm, std::max(1, g->group_warps_per_sm / 8)));
+    per_sm = std::min(per_sm, 2048 / 256);
+    grid = (int)std::min<size_t>(chunk, (size_t)n_sm * per_sm);
+    fcap = std::min(std::max(V, 32), std::max(1024, V / 8));
+    if (g->wfar_warps < grid * 8 || g->wfar_cap != fcap) {
+      cudaFree(g->d_wfar); g->d_wfar = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_wfar, sizeof(unsigned) * (size_t)grid * 8 * 2 * fcap));
+      g->wfar_warps = grid * 8; g->wfar_cap = fcap;
+    }
     static bool attr_set[64] = {false};
-    int dev = 0;
-    SQ_CUDA_TRY(cudaGetDevice(&dev));
+    static int last_pct[64];
+    if (dev < 64) {
+      if (!attr_set[dev]) {
+        for (int i = 0; i < 4; ++i)
+          SQ_CUDA_TRY(cudaFuncSetAttribute(wkernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set[dev] = true;
+        last_pct[dev] = -1;
+      }
+      int pct = (int)((100 * (size_t)per_sm * (warp_smem + 1024) + prop.sharedMemPerMultiprocessor - 1) / prop.sharedMemPerMultiprocessor);
+      pct = std::max(0, std::min(100, pct));
+      if (pct != last_pct[dev]) {
+        for (int i = 0; i < 4; ++i)
+          SQ_CUDA_TRY(cudaFuncSetAttribute(wkernels[i], cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        last_pct[dev] = pct;
+      }
+    }
+  } else {
+    const int wps = std::max(4, std::min(g->group_warps_per_sm, 32)) / 4 * 4;
+    const int warps = (int)std::min<size_t>(chunk, (size_t)n_sm * wps);
+    grid = (warps + 3) / 4;
+    while (ring_cap < V) ring_cap <<= 1;
+    if (g->g_warps < grid * 4 || g->g_ring_cap != ring_cap || g->g_pend_cap != pend_cap) {
+      cudaFree(g->d_gring); cudaFree(g->d_gpend); cudaFree(g->d_ginp);
+      g->d_gring = g->d_gpend = g->d_ginp = nullptr; g->g_warps = 0;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_gring, sizeof(unsigned) * (size_t)grid * 4 * ring_cap));
+      SQ_CUDA_TRY(cudaMalloc(&g->d_gpend, sizeof(unsigned) * (size_t)grid * 4 * 2 * pend_cap));
+      SQ_CUDA_TRY(cudaMalloc(&g->d_ginp, sizeof(unsigned) * (size_t)grid * 4 * words));
+      g->g_warps = grid * 4; g->g_ring_cap = ring_cap; g->g_pend_cap = pend_cap; g->g_words = words;
+    }
+    // no shared memory at all: give every byte of the SM's array to L1
+    static bool attr_set[64] = {false};
     if (dev < 64 && !attr_set[dev]) {
-      for (int a = 0; a < 3; ++a)
-        for (int b = 0; b < 2; ++b)
-          SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[a][b], cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+      for (int a2 = 0; a2 < 3; ++a2)
+        for (int b2 = 0; b2 < 2; ++b2)
+          SQ_CUDA_TRY(cudaFuncSetAttribute(gkernels[a2][b2], cudaFuncAttributePreferredSharedMemoryCarveout, 0));
       attr_set[dev] = true;
     }
   }
-  const GroupKernel kern = kernels[g->group_pb <= 8 ? 0 : g->group_pb <= 16 ? 1 : 2][g->group_pf ? 1 : 0];
+
   for (size_t g0 = 0; g0 < (size_t)n_groups; g0 += chunk) {
     const int m = (int)std::min(chunk, (size_t)n_groups - g0);
-    GroupParams gp;
-    memset(&gp, 0, sizeof(gp));
-    gp.V = V; gp.n_groups = m;
-    gp.gell = g->d_gell[dir]; gp.govf = g->d_govf[dir]; gp.gheads = g->d_gheads[dir];
-    gp.perm = g->d_perm; gp.origins = origins_dev; gp.tord = g->d_tord + g0 * 8;
-    gp.gdist = g->d_gdist; gp.ring = g->d_gring; gp.pend = g->d_gpend; gp.inp = g->d_ginp;
-    gp.ring_cap = ring_cap; gp.pend_cap = pend_cap; gp.words = words;
-    gp.counter = g->d_counter + 8 + (int)((g0 / chunk) & 127);   // d_counter[0..7] belong to the other kernels; zeroed per batch
-    gp.delta = g->delta;
-#ifdef SQ_SSSP_STATS
-    gp.stats = g->d_stats;
-#endif
-    const int wm = std::min(m, warps);
-    kern<<<(wm + 3) / 4, 128, 0, st>>>(gp);
+    int* counter = g->d_counter + 8 + (int)((g0 / chunk) & 127);   // [0..7] belong to the other kernels; zeroed per batch
+    if (warp_mode) {
+      TreeParams p = base;
+      p.n_trees = m;                      // groups
+      p.origins = origins_dev; p.dist_out = nullptr; p.parent_out = nullptr;
+      p.tord = g->d_tord + g0 * 8; p.perm = g->d_perm; p.gdist = g->d_gdist;
+      p.ell = g->d_gell[dir]; p.ovf = g->d_govf[dir];
+      p.tree_counter = counter;
+      p.wfar = g->d_wfar; p.wfar_cap = fcap; p.ring_cap = C; p.vbits = vbits;
+      wkernels[g->warp_ilp == 1 ? 0 : g->warp_ilp == 2 ? 1 : g->warp_ilp == 8 ? 3 : 2]<<<std::min(m, grid), 256, warp_smem, st>>>(p);
+    } else {
+      GroupParams gp;
+      memset(&gp, 0, sizeof(gp));
+      gp.V = V; gp.n_groups = m;
+      gp.gell = g->d_gell[dir]; gp.govf = g->d_govf[dir]; gp.gheads = g->d_gheads[dir];
+      gp.perm = g->d_perm; gp.origins = origins_dev; gp.tord = g->d_tord + g0 * 8;
+      gp.gdist = g->d_gdist; gp.ring = g->d_gring; gp.pend = g->d_gpend; gp.inp = g->d_ginp;
+      gp.ring_cap = ring_cap; gp.pend_cap = pend_cap; gp.words = words;
+      gp.counter = counter;
+      gp.delta = g->delta;
+      gp.stats = base.stats;
+      gkernels[g->group_pb <= 8 ? 0 : g->group_pb <= 16 ? 1 : 2][g->group_pf ? 1 : 0]<<<(std::min(m, grid * 4) + 3) / 4, 128, 0, st>>>(gp);
+    }
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
     if (dist_dev || parent_dev) {
@@ -1599,6 +1701,17 @@ static int g_run_group(SqGraph* g, const int* origins_dev, int n, u64* dist_dev,
       sq::count_launch();
       SQ_CUDA_TRY(cudaGetLastError());
     }
+  }
+  if (warp_mode) {
+    // trees whose wavefront outgrew the ring (normally none: these CTAs exit at once): the bitmap kernel recomputes
+    // them in the caller's numbering, straight into the caller's tables, predecessors included
+    TreeParams pf = base;
+    pf.origins = origins_dev; pf.dist_out = dist_dev; pf.parent_out = parent_dev; pf.parent_codes = g->parent_format;
+    pf.tree_counter = g->d_fail + 1;
+    pf.tree_list = g->d_fail + 2;
+    pf.n_list = g->d_fail;
+    pf.stats = nullptr;
+    if (int rc = launch_bitmap_kernel(g, pf, bm.grid, bm.smem, bm.threads, st)) return rc;
   }
   g->last_stats[0] = n;
   return SQ_OK;
@@ -1696,8 +1809,10 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   }
 
   // ---- group kernel: large batches whose origins lie close together (algo 4, or auto on dense batches) ----
-  if (g->algo == 4 || (g->algo == 3 && n >= g->group_min_trees && (long long)n * g->group_min_density >= (long long)V))
-    return g_run_group(g, origins_dev, n, dist_dev, parent_dev, st, reverse, n_sm);
+  if (g->algo == 4 || (g->algo == 3 && n >= g->group_min_trees && (long long)n * g->group_min_density >= (long long)V)) {
+    const BitmapGeom bm{bm_grid, bm_threads, smem, bitmap_fits};
+    return g_run_group(g, p, bm, prop, origins_dev, n, dist_dev, parent_dev, st, reverse);
+  }
 
   // ---- warp kernel (algo 2, default) or ELL kernel (algo 0) -------------------------------------------
   int vbits = 1;
@@ -1781,7 +1896,8 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   p.parent_out = nullptr;  // predecessors come from sssp_parent_kernel below
   if (use_warp) {
     typedef void (*WarpKernel)(const TreeParams);
-    static const WarpKernel kernels[4] = {sssp_warp_kernel<1>, sssp_warp_kernel<2>, sssp_warp_kernel<4>, sssp_warp_kernel<8>};
+    static const WarpKernel kernels[4] = {sssp_warp_kernel<1, false>, sssp_warp_kernel<2, false>, sssp_warp_kernel<4, false>,
+                                          sssp_warp_kernel<8, false>};
     static bool attr_set = false;
     if (!attr_set) {
       for (int i = 0; i < 4; ++i)
@@ -2017,6 +2133,13 @@ int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
   if (ring_cap > 0) g->warp_ring = ring_cap;
   if (ilp > 0) g->warp_ilp = ilp;
   if (ctas_per_sm >= 0) g->warp_ctas_per_sm = ctas_per_sm;
+  return SQ_OK;
+}
+
+int sp_set_group_mode(Graph* g, int mode, int ring_cap) {
+  if (!g || mode < 0 || mode > 1) return sq::set_error(SQ_ERR_ARG, "sp_set_group_mode: mode must be 0 or 1");
+  g->group_mode = mode;
+  if (ring_cap > 0) g->group_ring = ring_cap;
   return SQ_OK;
 }
 

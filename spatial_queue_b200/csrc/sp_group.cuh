@@ -36,7 +36,8 @@ struct GroupParams {
   const EdgeRec* gell;   // [V][4], internal numbering.  .pad bit 0 (all four slots) = record needs the sequential path
                          // (more than four edges, two edges to one head, or a self loop); bit 1 = empty slot (its
                          // head is the vertex itself with weight 0, so the fast path needs no "has edge" test);
-                         // slot 0 bits 3.. = overflow start; slot 1 bits 3.. = overflow count
+                         // bits 3..5 = slot of the edge straight back (warp kernel); slot 0 bits 6.. = overflow
+                         // start; slot 1 bits 6.. = overflow count
   const EdgeRec* govf;
   const int4* gheads;    // [V] the four heads of a record (-1 = none), for prefetching
   const int* perm;       // caller id -> internal id
@@ -224,8 +225,8 @@ __global__ void __launch_bounds__(128) sssp_group_kernel(const GroupParams p) {
           // ---- sequential path: parallel edges, self loops, more than four out-edges.  Lanes 0..7 relax one edge at
           // a time and push at once (the batch decode sees no ballots for this pop).
           __syncwarp();
-          const int ovf_b = __shfl_sync(FULL, rc.w, 0) >> 3;
-          const int ovf_n = __shfl_sync(FULL, rc.w, 8) >> 3;
+          const int ovf_b = __shfl_sync(FULL, rc.w, 0) >> 6;
+          const int ovf_n = __shfl_sync(FULL, rc.w, 8) >> 6;
           for (int e = 0; e < 4 + ovf_n; ++e) {
             int v, pd = 0;
             double w;
@@ -360,8 +361,8 @@ __global__ void __launch_bounds__(256) group_finalize_kernel(int V, int n_groups
       nw[q] = __hiloint2double(raw.y, raw.x);
       nx[q] = (raw.w & 2) ? -1 : raw.z;            // empty slots point at the vertex itself
       nv[q] = nx[q] >= 0 ? __ldg(&iperm[nx[q]]) : -1;
-      if (q == 0) ovf_b = raw.w >> 3;
-      if (q == 1) ovf_n = raw.w >> 3;
+      if (q == 0) ovf_b = raw.w >> 6;
+      if (q == 1) ovf_n = raw.w >> 6;
     }
   }
   for (int g = blockIdx.y; g < n_groups; g += gridDim.y) {

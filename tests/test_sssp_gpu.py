@@ -66,7 +66,8 @@ def test_network_mtx_golden(spi):
                                                       (128, 0, 0, 0), (64, 0, 0, 0), (32, 0, 0, 0), (1024, 0, 0, 0), (512, 0, 0, 0),   # ELL kernel
                                                       (256, 0, 0, 4.0), (64, 0, 0, 0.02),                 # roomy / tight queues
                                                       (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0),    # warp kernel: (ilp, ring)
-                                                      (8, 0, 4, 0), (16, 1, 4, 0), (32, 1, 4, 0)])         # group kernel: (batch, prefetch)
+                                                      (8, 0, 4, 0), (16, 1, 4, 0), (32, 1, 4, 0),         # group kernel: (batch, prefetch)
+                                                      (2, 64, 5, 0), (4, 1024, 5, 0)])                    # grouped warp kernel: (ilp, ring)
 def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
     from oracle import sssp as osssp
     rng = np.random.default_rng(11 + threads)
@@ -79,17 +80,24 @@ def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
         w = np.where(rng.random(E) < 0.3, np.round(w) + 1.0, w)  # ties, strictly positive
         og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1, directed=directed)
         g = spi.from_arrays(s, e, w, max_vertex_id=V - 1, directed=directed)
-        g.set_algo(algo, qfac)
+        g.set_algo(min(algo, 4), qfac)
         if algo == 2:
             g.set_warp_tuning(ring_cap=smemq, ilp=threads)
             g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
         elif algo == 4:
             # parallel edges, self loops, out-degrees beyond four (sequential path), closed links (threshold jumps)
+            g.set_group_mode(1)
             g.set_group_tuning(batch=threads, prefetch=smemq)
+            g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
+        elif algo == 5:
+            # the warp kernel on the group layout; the 64-entry ring overflows on these graphs (bitmap-kernel rerun)
+            g.set_algo(4)
+            g.set_group_mode(0, smemq)
+            g.set_warp_tuning(ilp=threads)
             g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
         else:
             g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
-        origins = np.concatenate([rng.integers(0, V, 7 if algo != 4 else 29), [-1, V, V + 5]]).astype(np.int32)
+        origins = np.concatenate([rng.integers(0, V, 7 if algo < 4 else 29), [-1, V, V + 5]]).astype(np.int32)
         d, p = g.sssp_batch(origins)
         do, po = og.sssp_batch(origins)
         assert d.tobytes() == do.tobytes()
@@ -165,14 +173,15 @@ def test_weight_updates_reach_the_device(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
 
 
-@pytest.mark.parametrize("algo", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("algo", [0, 1, 2, 3, 4, 5])
 def test_grid_batch_and_device_api(spi, algo):
     import torch
     from oracle import sssp as osssp
     n = 64
     s, e, w = grid_graph(n, seed=1)
     g = spi.from_arrays(s, e, w)
-    g.set_algo(algo)
+    g.set_algo(min(algo, 4))
+    g.set_group_mode(1 if algo == 4 else 0)
     og = osssp.OracleGraph(s, e, w)
     # 1000 origins: above the auto switch-over (six trees per SM), so algo 3 runs the warp kernel here
     origins = np.random.default_rng(2).permutation(n * n)[:1000].astype(np.int32)
@@ -256,7 +265,7 @@ def test_reverse_trees_and_device_weight_refresh(spi):
     g.free()
 
 
-@pytest.mark.parametrize("algo", [3, 4])
+@pytest.mark.parametrize("algo", [3, 4, 5])
 @pytest.mark.parametrize("reverse", [False, True])
 def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo):
     """The compact table the multi-GPU path all-gathers (one byte per vertex) expands to exactly the int32 tree."""
@@ -267,7 +276,8 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo)
     e = rng.integers(0, V, E).astype(np.int32)
     w = np.round(rng.random(E) * 20.0) + 1.0   # many exact ties
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
-    g.set_algo(algo)
+    g.set_algo(min(algo, 4))
+    g.set_group_mode(1 if algo == 4 else 0, 64 if algo == 5 else 0)   # 5: tiny ring, some trees rerun by the bitmap kernel
     origins = torch.from_numpy(rng.integers(0, V, 40).astype(np.int32)).cuda()
     d = torch.empty((40, V), dtype=torch.float64, device="cuda")
     p32 = torch.empty((40, V), dtype=torch.int32, device="cuda")
@@ -282,8 +292,8 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo)
     g.set_parent_format(0)
     dh, ph = g.sssp_batch(origins.cpu().numpy()[:5], reverse=reverse)
     assert (ph == p32[:5].cpu().numpy()).all()
-    if algo == 4:
-        # and the group kernel's tables are the other kernels' tables
+    if algo >= 4:
+        # and the group path's tables are the other kernels' tables
         g.set_algo(0)
         d0 = torch.empty_like(d)
         p0 = torch.empty_like(p32)
@@ -405,7 +415,7 @@ def _congested_weights(s, e, w, seed=2):
     return q / (1900.0 + 0.1) * 3600 * 25 / 25.0 + w
 
 
-@pytest.mark.parametrize("algo,n", [(3, 2368), (4, 2368), (3, 18944)])
+@pytest.mark.parametrize("algo,n", [(3, 2368), (4, 2368), (5, 2368), (3, 18944)])
 def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     """bench.py's HP-2 workload itself: 224x224 grid, bench.origins_for origins, through sp_sssp_batch_device in auto
     mode (2,368 origins: sssp_warp_kernel; 18,944 origins, the benchmarked batch: sssp_group_kernel) and with the group
@@ -415,7 +425,8 @@ def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     from oracle import sssp as osssp
     s, e, w, V, bench = _config5()
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
-    g.set_algo(algo)
+    g.set_algo(min(algo, 4))
+    g.set_group_mode(1 if algo == 4 else 0)
     origins = bench.origins_for(0, n, V, step=0)
     o_dev = torch.from_numpy(origins).cuda()
     d_dev = torch.empty((n, V), dtype=torch.float64, device="cuda")
@@ -454,7 +465,7 @@ def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     g.free()
 
 
-@pytest.mark.parametrize("algo", [3, 4])
+@pytest.mark.parametrize("algo", [3, 4, 5])
 def test_config5_congested_weight_set(spi, algo):
     """Same graph with the second, congested weight set of SURVEY.md 8(d) (queues ~ Poisson(3)) pushed through
     sp_set_weights_device, 1,024 origins (auto mode: the warp kernel; forced: the group kernel)."""
@@ -463,7 +474,8 @@ def test_config5_congested_weight_set(spi, algo):
     s, e, w, V, bench = _config5()
     w2 = _congested_weights(s, e, w)
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
-    g.set_algo(algo)
+    g.set_algo(min(algo, 4))
+    g.set_group_mode(1 if algo == 4 else 0)
     g.set_weights_device(torch.from_numpy(w2).cuda())
     origins = bench.origins_for(0, 1024, V, step=3)
     o_dev = torch.from_numpy(origins).cuda()
@@ -477,7 +489,8 @@ def test_config5_congested_weight_set(spi, algo):
     g.free()
 
 
-def test_group_kernel_on_an_irregular_network_with_closures(spi):
+@pytest.mark.parametrize("mode", [0, 1])
+def test_group_kernel_on_an_irregular_network_with_closures(spi, mode):
     """The group kernel where its assumptions are weakest: a town-like network (streets removed, one-ways, hubs with
     more than four out-links), 3 % of the links closed at 1e8 (threshold jumps, pending-list rescans), origins
     clustered AND scattered, duplicates and out-of-range origins in the batch; forward and reverse trees."""
@@ -492,6 +505,7 @@ def test_group_kernel_on_an_irregular_network_with_closures(spi):
     w[rng.random(len(s)) < 0.03] = 1e8
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
     g.set_algo(4)
+    g.set_group_mode(mode)
     origins = np.concatenate([rng.integers(0, V, 300), np.arange(100, 140), [5, 5, 5, -1, V + 7]]).astype(np.int32)
     n = len(origins)
     for reverse in (False, True):

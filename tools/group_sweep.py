@@ -45,22 +45,31 @@ print(json.dumps({"algo": "warp", "ms": round(ms_warp, 2), "trees_per_s": round(
                   "frac": round(B / ms_warp * 1e3 * btree / (peak * 1e9), 4)}), flush=True)
 
 g.set_algo(4)
+# (mode, warps per SM, a, b, delta factor): mode 0 = grouped warp kernel, a = ILP, b = ring entries per tree;
+#                                           mode 1 = sssp_group_kernel, a = pops per batch, b = prefetch
 configs = json.loads(os.environ.get("CONFIGS", "null")) or [
-    (16, 16, 1, 4.0), (16, 16, 0, 4.0), (16, 32, 1, 4.0), (16, 8, 1, 4.0), (8, 32, 1, 4.0), (8, 16, 1, 4.0), (12, 16, 1, 4.0),
-    (24, 16, 1, 4.0), (32, 16, 1, 4.0), (32, 8, 1, 4.0), (16, 16, 1, 2.0), (16, 16, 1, 8.0), (16, 32, 0, 4.0), (32, 32, 0, 4.0)]
-for wps, pb, pf, df in configs:
+    (0, 16, 4, 1024, 4.0), (0, 24, 4, 1024, 4.0), (0, 16, 2, 1024, 4.0), (0, 16, 8, 1024, 4.0), (0, 24, 2, 1024, 4.0),
+    (0, 32, 2, 512, 4.0), (0, 32, 4, 512, 4.0), (0, 8, 8, 1024, 4.0), (0, 16, 4, 1024, 2.0), (0, 16, 4, 1024, 8.0),
+    (0, 24, 4, 1024, 2.0), (0, 48, 2, 512, 4.0), (0, 48, 4, 512, 4.0), (1, 16, 32, 1, 4.0)]
+for mode, wps, a, b, df in configs:
     try:
-        g.set_group_tuning(warps_per_sm=wps, batch=pb, prefetch=pf)
+        if mode == 0:
+            g.set_group_mode(0, b)
+            g.set_warp_tuning(ilp=a)
+            g.set_group_tuning(warps_per_sm=wps)
+        else:
+            g.set_group_mode(1)
+            g.set_group_tuning(warps_per_sm=wps, batch=a, prefetch=b)
         g.set_tuning(delta_factor=df)
         dist.zero_(); par.zero_()
         ms = timed(lambda: g.sssp_batch_device(o, dist, par))
         ok = bool(torch.equal(dist[:chk].view(torch.int64), dref.view(torch.int64))) and bool(torch.equal(par[:chk], pref))
         ms_tree = timed(lambda: g.sssp_batch_device(o, None, None), reps=2)
-        g.sssp_batch_device(o[:2048], None, None); torch.cuda.synchronize()
-        st = g.last_stats() if False else None
+        g.sssp_batch(origins[:64], want_dist=False)
+        st = g.last_stats()
         tps = B / ms * 1e3
-        print(json.dumps({"algo": "group", "warps_per_sm": wps, "batch": pb, "prefetch": pf, "delta": df, "ms": round(ms, 2),
+        print(json.dumps({"algo": "group", "mode": mode, "warps_per_sm": wps, "a": a, "b": b, "delta": df, "ms": round(ms, 2),
                           "ms_trees_only": round(ms_tree, 2), "trees_per_s": round(tps), "frac": round(tps * btree / (peak * 1e9), 4),
-                          "bit_exact_vs_warp": ok}), flush=True)
+                          "bit_exact_vs_warp": ok, "overflows": st["overflows"]}), flush=True)
     except Exception as ex:
-        print("ERR", wps, pb, pf, df, ex, flush=True)
+        print("ERR", mode, wps, a, b, df, ex, flush=True)
