@@ -93,6 +93,14 @@ struct TreeParams {
 
 #define DIST_INF_BITS 0x7FEFFFFFFFFFFFFFull  // DBL_MAX, what the reference leaves in unreached slots
 
+// Bucket thresholds must move: with delta below half an ulp of T (distances of 1e8 behind a closed link next to
+// sub-nanosecond weights) T + delta == T and a bucket transition would find the same empty window for ever.
+__device__ __forceinline__ double next_up(double x) { return __longlong_as_double(__double_as_longlong(x) + 1); }
+__device__ __forceinline__ double advance(double T, double delta) {
+  const double n = T + delta;
+  return n > T ? n : next_up(T);
+}
+
 // A queue whose first `cap_s` slots live in shared memory and the rest in a per-CTA global scratch
 // row of V ints.  Entries are unique (guarded by a shared-memory bit per vertex), so V slots suffice.
 struct HQ {
@@ -201,7 +209,7 @@ __global__ void __launch_bounds__(THREADS) sssp_nearfar_kernel(const TreeParams 
           if (tid == 0) { s_min = DIST_INF_BITS; s_cnt[2 + (fcur ^ 1)] = 0; }
           __syncthreads();
           const double Told = T;
-          T = Told + p.delta;
+          T = advance(Told, p.delta);
           u64 lmin = DIST_INF_BITS;
           const HQ qfar_in = Q(2 + fcur), qfar_out = Q(2 + (fcur ^ 1)), qnear_out = Q(cur);
           for (int i0 = 0; i0 < nf; i0 += THREADS) {
@@ -489,7 +497,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
           if (nb == 0 && nf == 0) { done = true; break; }
           bool advanced = false;
           if (nb > 0) {  // the next bucket becomes the current queue as it is
-            T += p.delta;
+            T = advance(T, p.delta);
             const int t = cur; cur = bkt; bkt = t;
             advanced = true;
           }
@@ -498,7 +506,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
             __syncthreads();
             if (tid == 0) { s_min = DIST_INF_BITS; s_fcnt[fcur ^ 1] = 0; }
             __syncthreads();
-            const double T2 = T + p.delta;
+            const double T2 = advance(T, p.delta);
             u64 lmin = DIST_INF_BITS;
             const int2* fiv = s_gv[4 + fcur];
             const u64* fid = s_gd[4 + fcur];
@@ -553,7 +561,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
       // ---- one relaxation round: 4 lanes per frontier vertex, 16 vertices per warp iteration -------
       const HQ2 qin = Q(cur), qn = Q(nxt), qb = Q(bkt);
       const HQ2 qf = FARQ(fcur);
-      const double T2 = T + p.delta;
+      const double T2 = advance(T, p.delta);
       for (int base = warp * 16; base < n; base += NW * 16) {
         int u[2], from[2];
         u64 dub[2];
@@ -782,7 +790,7 @@ __global__ void __launch_bounds__(GROUPED ? 256 : 128) sssp_warp_kernel(const Tr
       cur[0] = (unsigned)src | (7u << vbits) | (dist_hash(0ull) & himask);
     }
     __syncwarp();
-    double T = delta, T2 = delta + delta;
+    double T = delta, T2 = advance(delta, delta);
     // Classifies one candidate per lane and appends it to the ring / next bucket / far pile.  Convergent.
     auto push = [&](bool imp, u64 ndb, unsigned ent) {
       const double nd = __longlong_as_double((long long)ndb);
@@ -829,7 +837,7 @@ __global__ void __launch_bounds__(GROUPED ? 256 : 128) sssp_warp_kernel(const Tr
         }
         { unsigned* t = cur; cur = bkt; bkt = t; }
         ch = 0; ct = bt; bt = 0;
-        T = T2; T2 = T + delta;
+        T = T2; T2 = advance(T, delta);
         ++st_trans;
         if (nf > 0) {
           // split the far pile against the new next-bucket range [T, T2)

@@ -69,8 +69,6 @@ __device__ __forceinline__ unsigned ld_u32(const unsigned* p) {
 __device__ __forceinline__ void st_u32(unsigned* p, unsigned v) { asm volatile("st.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
-__device__ __forceinline__ double next_up(double x) { return __longlong_as_double(__double_as_longlong(x) + 1); }
-
 // PB = pops per batch (8, 16 or 32); PF = 1: prefetch a batch's rows into L1 when it is read
 template <int PB, int PF>
 __global__ void __launch_bounds__(128) sssp_group_kernel(const GroupParams p) {
@@ -139,8 +137,7 @@ __global__ void __launch_bounds__(128) sssp_group_kernel(const GroupParams p) {
         // ---- bucket transition: scan the pending list, four entries per step (eight lanes read one row) ----------
         if (np == 0) break;
         ++st_trans;
-        double T_new = T + delta;
-        if (!(T_new > T)) T_new = next_up(T);
+        double T_new = advance(T, delta);
         for (;;) {
           const unsigned* P = pend0 + (size_t)pcur * p.pend_cap;
           unsigned* Pn = pend0 + (size_t)(pcur ^ 1) * p.pend_cap;
@@ -183,8 +180,7 @@ __global__ void __launch_bounds__(128) sssp_group_kernel(const GroupParams p) {
           if (rt > 0 || nn == 0) break;
           // nothing within reach: open the next bucket at the smallest marked distance
           const double Tg = __longlong_as_double((long long)gmin);
-          T_new = Tg + delta;
-          if (!(T_new > Tg)) T_new = next_up(Tg);
+          T_new = advance(Tg, delta);
         }
         T = T_new;
         continue;
