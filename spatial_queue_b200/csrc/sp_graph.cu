@@ -22,6 +22,7 @@
 #include <fstream>
 #include <iostream>
 #include <map>
+#include <mutex>
 #include <sstream>
 #include <string>
 #include <unordered_map>
@@ -38,6 +39,9 @@ using sq::SQ_ERR_LIMIT;
 using sq::SQ_OK;
 
 typedef unsigned long long u64;
+
+#define SQ_MAX_DEVICES 64
+static std::mutex g_attr_mutex;   // kernel attributes are set once per device
 
 // =================================================================================================
 // Device side
@@ -1150,6 +1154,7 @@ struct SqGraph {
   unsigned* d_gring = nullptr; unsigned* d_gpend = nullptr; unsigned* d_ginp = nullptr;
   int g_warps = 0, g_ring_cap = 0, g_pend_cap = 0, g_words = 0;
   int group_warps_per_sm = 16, group_pb = 16, group_pf = 1;
+  cudaDeviceProp prop; int prop_dev = -1;
   int group_mode = 0;                    // 0 = grouped warp kernel (a CTA of eight warps per group), 1 = sssp_group_kernel
   int group_ring = 1024;                 // ring entries per tree of the grouped warp kernel
   int group_min_trees = 2048;            // auto mode: batches at least this large ...
@@ -1517,10 +1522,16 @@ static int g_build_and_upload(SqGraph* g) {
 
 template <int THREADS>
 static int launch_trees(SqGraph* g, TreeParams& p, int grid, size_t smem, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    SQ_CUDA_TRY(cudaFuncSetAttribute(sssp_nearfar_kernel<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
+  // function attributes belong to a device's context: one flag per device, set under a lock
+  static bool attr_set[SQ_MAX_DEVICES] = {false};
+  int dev = 0;
+  SQ_CUDA_TRY(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> lock(g_attr_mutex);
+    if (dev < 0 || dev >= SQ_MAX_DEVICES || !attr_set[dev]) {
+      SQ_CUDA_TRY(cudaFuncSetAttribute(sssp_nearfar_kernel<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      if (dev >= 0 && dev < SQ_MAX_DEVICES) attr_set[dev] = true;
+    }
   }
   sssp_nearfar_kernel<THREADS><<<grid, THREADS, smem, st>>>(p);
   sq::count_launch();
@@ -1560,12 +1571,15 @@ static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t 
 // un-interleaves the rows into the caller's tables and writes the canonical predecessors in the same pass.
 struct BitmapGeom { int grid, threads; size_t smem; bool fits; };
 
+// host_list != nullptr: run only the trees listed there (the rerun of trees another kernel gave up on, on graphs too
+// large for the bitmap kernel), in list order, on sssp_group_kernel.
 static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm, const cudaDeviceProp& prop, const int* origins_dev,
-                       int n, u64* dist_dev, int* parent_dev, cudaStream_t st, bool reverse) {
+                       int n, u64* dist_dev, int* parent_dev, cudaStream_t st, bool reverse, const int* host_list = nullptr,
+                       int n_list = 0) {
   const int V = g->V;
   const int n_sm = prop.multiProcessorCount;
   const int dir = reverse ? 1 : 0;
-  const int n_groups = (n + 7) / 8, n_pad = n_groups * 8;
+  const int n_groups = ((host_list ? n_list : n) + 7) / 8, n_pad = n_groups * 8;
   if (parent_dev && g->parent_format) {
     size_t worst = 0;
     const std::vector<int>& rp = reverse ? g->h_rp : g->h_rrp;
@@ -1576,7 +1590,7 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
   while ((1ll << vbits) < (long long)V) ++vbits;
   // the warp kernel needs a fallback for trees whose wavefront outgrows its ring; without one (graph too large for the
   // bitmap kernel, or ids too wide for the hashed queue entries) the group runs on the kernel that cannot overflow
-  const bool warp_mode = g->group_mode == 0 && vbits <= 24 && bm.fits;
+  const bool warp_mode = g->group_mode == 0 && vbits <= 24 && bm.fits && !host_list;
 
   // ---- sort the trees by origin (counting sort on the internal ids) ----
   if (g->gkey_cap < (size_t)n_pad) {
@@ -1590,12 +1604,20 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
     SQ_CUDA_TRY(cudaMalloc(&g->d_ghist, sizeof(int) * ((size_t)V + 1)));
     g->ghist_cap = (size_t)V + 1;
   }
-  SQ_CUDA_TRY(cudaMemsetAsync(g->d_ghist, 0, sizeof(int) * ((size_t)V + 1), st));
-  group_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, V, origins_dev, g->d_perm, g->d_gkey, g->d_ghist);
-  group_scan_kernel<<<1, 1024, 0, st>>>(V + 1, g->d_ghist);
-  group_scatter_kernel<<<(n_pad + 255) / 256, 256, 0, st>>>(n, n_pad, g->d_gkey, g->d_ghist, g->d_tord);
-  sq::count_launch(3);
-  SQ_CUDA_TRY(cudaGetLastError());
+  if (host_list) {
+    std::vector<int> tl((size_t)n_pad, -1);
+    std::copy(host_list, host_list + n_list, tl.begin());
+    SQ_CUDA_TRY(cudaMemcpyAsync(g->d_tord, tl.data(), sizeof(int) * (size_t)n_pad, cudaMemcpyHostToDevice, st));
+    SQ_CUDA_TRY(cudaStreamSynchronize(st));   // tl goes out of scope
+    SQ_CUDA_TRY(cudaMemsetAsync(g->d_counter + 8, 0, sizeof(int) * 128, st));
+  } else {
+    SQ_CUDA_TRY(cudaMemsetAsync(g->d_ghist, 0, sizeof(int) * ((size_t)V + 1), st));
+    group_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, V, origins_dev, g->d_perm, g->d_gkey, g->d_ghist);
+    group_scan_kernel<<<1, 1024, 0, st>>>(V + 1, g->d_ghist);
+    group_scatter_kernel<<<(n_pad + 255) / 256, 256, 0, st>>>(n, n_pad, g->d_gkey, g->d_ghist, g->d_tord);
+    sq::count_launch(3);
+    SQ_CUDA_TRY(cudaGetLastError());
+  }
 
   // ---- scratch: interleaved distance rows for a chunk of groups ----
   const size_t row_bytes = (size_t)V * 64;
@@ -1635,9 +1657,10 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
       SQ_CUDA_TRY(cudaMalloc(&g->d_wfar, sizeof(unsigned) * (size_t)grid * 8 * 2 * fcap));
       g->wfar_warps = grid * 8; g->wfar_cap = fcap;
     }
-    static bool attr_set[64] = {false};
-    static int last_pct[64];
-    if (dev < 64) {
+    static bool attr_set[SQ_MAX_DEVICES] = {false};
+    static int last_pct[SQ_MAX_DEVICES];
+    std::lock_guard<std::mutex> lock(g_attr_mutex);
+    if (dev >= 0 && dev < SQ_MAX_DEVICES) {
       if (!attr_set[dev]) {
         for (int i = 0; i < 4; ++i)
           SQ_CUDA_TRY(cudaFuncSetAttribute(wkernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -1666,8 +1689,9 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
       g->g_warps = grid * 4; g->g_ring_cap = ring_cap; g->g_pend_cap = pend_cap; g->g_words = words;
     }
     // no shared memory at all: give every byte of the SM's array to L1
-    static bool attr_set[64] = {false};
-    if (dev < 64 && !attr_set[dev]) {
+    static bool attr_set[SQ_MAX_DEVICES] = {false};
+    std::lock_guard<std::mutex> lock(g_attr_mutex);
+    if (dev >= 0 && dev < SQ_MAX_DEVICES && !attr_set[dev]) {
       for (int a2 = 0; a2 < 3; ++a2)
         for (int b2 = 0; b2 < 2; ++b2)
           SQ_CUDA_TRY(cudaFuncSetAttribute(gkernels[a2][b2], cudaFuncAttributePreferredSharedMemoryCarveout, 0));
@@ -1721,7 +1745,7 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
     pf.stats = nullptr;
     if (int rc = launch_bitmap_kernel(g, pf, bm.grid, bm.smem, bm.threads, st)) return rc;
   }
-  g->last_stats[0] = n;
+  if (!host_list) g->last_stats[0] = n;
   return SQ_OK;
 }
 
@@ -1732,14 +1756,13 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   if (int rc = g_build_and_upload(g)) return rc;
   const int V = g->V;
   if (V <= 0) return sq::set_error(SQ_ERR_ARG, "graph has no vertices");
-  static cudaDeviceProp prop;
-  static int prop_dev = -1;
   int dev = 0;
   SQ_CUDA_TRY(cudaGetDevice(&dev));
-  if (prop_dev != dev) {
-    SQ_CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
-    prop_dev = dev;
+  if (g->prop_dev != dev) {     // cached per graph (a graph lives on one device), not per process
+    SQ_CUDA_TRY(cudaGetDeviceProperties(&g->prop, dev));
+    g->prop_dev = dev;
   }
+  const cudaDeviceProp& prop = g->prop;
   const int n_sm = prop.multiProcessorCount;
 
   // ---- bitmap kernel geometry (main kernel when algo == 1, else the fallback of the ELL kernel) ----
@@ -1906,22 +1929,25 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     typedef void (*WarpKernel)(const TreeParams);
     static const WarpKernel kernels[4] = {sssp_warp_kernel<1, false>, sssp_warp_kernel<2, false>, sssp_warp_kernel<4, false>,
                                           sssp_warp_kernel<8, false>};
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[SQ_MAX_DEVICES] = {false};
+    static int last_pct[SQ_MAX_DEVICES];
+    std::lock_guard<std::mutex> lock(g_attr_mutex);
+    const int di = (dev >= 0 && dev < SQ_MAX_DEVICES) ? dev : 0;
+    if (!attr_set[di]) {
       for (int i = 0; i < 4; ++i)
         SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr_set = true;
+      attr_set[di] = true;
+      last_pct[di] = -1;
     }
     {
       // shared-memory carve-out = what the resident CTAs need and no more: with the default (largest) carve-out
       // L1 shrinks to ~28 KB and the kernel loses a quarter of its throughput (measured)
       int pct = (int)((100 * (size_t)per_sm * (warp_smem + 1024) + prop.sharedMemPerMultiprocessor - 1) / prop.sharedMemPerMultiprocessor);
       pct = std::max(0, std::min(100, pct));
-      static int last_pct = -1;
-      if (pct != last_pct) {
+      if (pct != last_pct[di]) {
         for (int i = 0; i < 4; ++i)
           SQ_CUDA_TRY(cudaFuncSetAttribute(kernels[i], cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        last_pct = pct;
+        last_pct[di] = pct;
       }
     }
     kernels[g->warp_ilp == 1 ? 0 : g->warp_ilp == 2 ? 1 : g->warp_ilp == 8 ? 3 : 2]<<<grid, 128, warp_smem, st>>>(p);
@@ -1938,6 +1964,18 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     pf.n_list = g->d_fail;
     pf.stats = nullptr;
     if (int rc = launch_bitmap_kernel(g, pf, bm_grid, smem, bm_threads, st)) return rc;
+  }
+  std::vector<int> redo;
+  if (!bitmap_fits) {
+    // the graph is too large for the bitmap kernel's shared-memory bitmaps (V > ~436k): look at the overflow list now
+    // and rerun those trees on the group kernel, whose queues are bounded by V and cannot overflow
+    int nfail = 0;
+    SQ_CUDA_TRY(cudaMemcpyAsync(&nfail, g->d_fail, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SQ_CUDA_TRY(cudaStreamSynchronize(st));
+    if (nfail > 0) {
+      redo.resize((size_t)nfail);
+      SQ_CUDA_TRY(cudaMemcpy(redo.data(), g->d_fail + 2, sizeof(int) * (size_t)nfail, cudaMemcpyDeviceToHost));
+    }
   }
   if (parent_dev) {
     const int codes = g->parent_format;
@@ -1957,6 +1995,11 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
                                                 origins_dev, p.dist_out, parent_dev, codes);
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
+  }
+  if (!redo.empty()) {
+    const BitmapGeom bm{bm_grid, bm_threads, smem, bitmap_fits};
+    if (int rc = g_run_group(g, p, bm, prop, origins_dev, n, dist_dev, parent_dev, st, reverse, redo.data(), (int)redo.size()))
+      return rc;
   }
   g->last_stats[0] = n;
   return SQ_OK;

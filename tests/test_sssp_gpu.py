@@ -519,3 +519,21 @@ def test_group_kernel_on_an_irregular_network_with_closures(spi, mode):
         assert d_dev.cpu().numpy().tobytes() == do.tobytes()
         assert (p_dev.cpu().numpy() == po).all()
     g.free()
+
+
+def test_large_graph_overflow_is_rerun_not_dropped(spi):
+    """beyond ~436k vertices the bitmap kernel cannot be the fallback.  A 700 x 700 grid (490k vertices), the
+    warp kernel forced with a 64-entry ring: every tree overflows, is listed, and must come back complete (rerun on
+    sssp_group_kernel, whose queues are bounded by V)."""
+    from oracle import sssp as osssp
+    n = 700
+    s, e, w = grid_graph(n, seed=2)
+    g = spi.from_arrays(s, e, w)
+    g.set_algo(2)
+    g.set_warp_tuning(ring_cap=64, ilp=2)
+    origins = np.array([0, n * n // 2 + 17, n * n - 1, 123456, 7], np.int32)
+    d, p = g.sssp_batch(origins)
+    assert g.last_stats()["overflows"] == len(origins)
+    do, po = osssp.OracleGraph(s, e, w).sssp_batch(origins)
+    assert d.tobytes() == do.tobytes() and (p == po).all()
+    g.free()
