@@ -150,6 +150,14 @@ int sq_get_link_congested(SqSim* sim, int64_t* congested);
  * [12] sum of node_move, [13] sum of total_vehicles_left over real links, [14] real links with a vehicle on them,
  * [15] vehicles on closed links (Butte's in_fire_cnts for burning links). */
 int sq_get_summary(SqSim* sim, int64_t* out16);
+/* The second return value of Node.run_node_model (model/queue_class.py:287-383: node_move_link_pairs, one (in_link,
+ * out_link) pair per vehicle moved) as counters: after sq_enable_pair_moves every move from in-link i to out-link j of
+ * a node adds one to entry node_turn_ptr[node] + i_local * outdeg + j_local of a table shaped like the turn-angle table
+ * (SqNetDesc.turn_angle); sq_get_pair_moves reads it back (out holds node_turn_ptr[n_nodes] entries).  Butte's
+ * check_traffic_flow_links_dict (model/dta_meso_butte.py:124-131) is a lookup in that table.  Arrivals, which the
+ * reference records as (in_link, None), are total_vehicles_left[in_link] minus the row sum. */
+int sq_enable_pair_moves(SqSim* sim);
+int sq_get_pair_moves(SqSim* sim, int64_t* out);
 /* Per link: vehicles that sheltered on it (sum over a node's in-links = node.shelter_counts); per agent: the tick
  * at which it arrived or sheltered (-1 otherwise). */
 int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick);

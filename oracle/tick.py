@@ -21,6 +21,7 @@ def _lib():
         L.oracle_tick_get_node_state.argtypes = [vp, vp]
         L.oracle_tick_get_link_weights.argtypes = [vp, vp]
         L.oracle_tick_get_counters.argtypes = [vp, vp]
+        L.oracle_tick_get_pair_moves.argtypes = [vp, vp]
         L.oracle_tick_set_shelter_after.argtypes = [vp, ci]
         L.oracle_tick_set_congest_after.argtypes = [vp, ci]
         L.oracle_tick_stop_agents.restype = ci; L.oracle_tick_stop_agents.argtypes = [vp, ci, vp, ci, ci]

@@ -56,6 +56,7 @@ typedef struct {
   IVec* a_route; int* a_pos;
   int* virt_of_node;
   int64_t* node_move;
+  int64_t* pair_moves;   /* [turn table shape] moves per (in_link, out_link): node_move_link_pairs, model/queue_class.py:291-383 */
   int64_t counters[6];
   int shelter_after; /* run_traffic_simulation.py:103: seconds on one real link before status shelter_a1; 0 = rule off */
   int* l_shelter;
@@ -131,6 +132,7 @@ OSim* oracle_tick_create(const SqNetDesc* d) {
     s->a_enter[i] = -1; s->a_arrive[i] = -1;
   }
   s->node_move = (int64_t*)calloc((size_t)(N ? N : 1), sizeof(int64_t));
+  s->pair_moves = (int64_t*)calloc((size_t)(s->turn_ptr[N] ? s->turn_ptr[N] : 1), sizeof(int64_t));
   return s;
 }
 
@@ -146,7 +148,7 @@ void oracle_tick_destroy(OSim* s) {
   free(s->a_origin); free(s->a_destin); free(s->a_dept); free(s->a_vlen);
   free(s->queue); free(s->run); free(s->in_c); free(s->out_c); free(s->storage_c); free(s->total_left);
   free(s->a_status); free(s->a_cur); free(s->a_next); free(s->a_enter); free(s->a_arrive); free(s->a_route);
-  free(s->a_pos); free(s->virt_of_node); free(s->node_move); free(s->l_shelter); free(s->l_congested); free(s);
+  free(s->a_pos); free(s->virt_of_node); free(s->node_move); free(s->pair_moves); free(s->l_shelter); free(s->l_congested); free(s);
 }
 
 static int fail(OSim* s, const char* msg, int a, int b, int c) {
@@ -238,6 +240,14 @@ static int non_conflict_vehicles(OSim* s, int t, int node, GoVeh* go, int* n_go)
 
 static double max0(double x) { return x > 0 ? x : 0; } /* max(0, x) */
 
+/* node_move_link_pairs.append((in_link, out_link)) of model/queue_class.py:327, :352, counted per pair */
+static void count_pair(OSim* s, int node, int il, int ol) {
+  int ib = s->in_ptr[node], ie = s->in_ptr[node + 1], ob = s->out_ptr[node], oe = s->out_ptr[node + 1], i, j;
+  for (i = ib; i < ie && s->in_links[i] != il; ++i) {}
+  for (j = ob; j < oe && s->out_links[j] != ol; ++j) {}
+  if (i < ie && j < oe) s->pair_moves[s->turn_ptr[node] + (int64_t)(i - ib) * (oe - ob) + (j - ob)] += 1;
+}
+
 static void move_agent(OSim* s, int agent, int t) { /* :610-615 + :598-608 */
   s->a_enter[agent] = t;
   s->a_cur[agent] = s->a_next[agent];
@@ -271,6 +281,7 @@ static int run_node_model(OSim* s, int t, int node) {
       iv_push(&s->run[ol], agent);
       s->in_c[ol] = max0(s->in_c[ol] - 1);
       s->storage_c[ol] -= s->a_vlen[agent];
+      count_pair(s, node, il, ol);
       move_agent(s, agent, t);
     } else {                                                                               /* :358-386 */
       double cc = s->out_c[il] < s->in_c[ol] ? s->out_c[il] : s->in_c[ol]; /* min(out, in): first minimal */
@@ -285,6 +296,7 @@ static int run_node_model(OSim* s, int t, int node) {
         iv_push(&s->run[ol], agent);
         s->in_c[ol] = max0(s->in_c[ol] - 1);
         s->storage_c[ol] -= s->a_vlen[agent];
+        count_pair(s, node, il, ol);
         move_agent(s, agent, t);
       } else {
         if (s->out_c[il] < s->in_c[ol]) s->out_c[il] = max0(s->out_c[il] - 1);
@@ -481,5 +493,9 @@ int oracle_tick_get_link_weights(OSim* s, double* w) {
   return 0;
 }
 
+int oracle_tick_get_pair_moves(OSim* s, int64_t* out) {
+  memcpy(out, s->pair_moves, sizeof(int64_t) * (size_t)s->turn_ptr[s->n_nodes]);
+  return 0;
+}
 int oracle_tick_get_counters(OSim* s, int64_t* out6) { memcpy(out6, s->counters, sizeof(s->counters)); return 0; }
 const char* oracle_tick_error(OSim* s) { return s->err; }

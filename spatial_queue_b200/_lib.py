@@ -91,6 +91,8 @@ def _declare(L):
     L.sq_get_agent_state.restype = ci; L.sq_get_agent_state.argtypes = [vp] * 6
     L.sq_get_node_state.restype = ci; L.sq_get_node_state.argtypes = [vp, vp]
     L.sq_get_link_weights.restype = ci; L.sq_get_link_weights.argtypes = [vp, vp]
+    L.sq_enable_pair_moves.restype = ci; L.sq_enable_pair_moves.argtypes = [vp]
+    L.sq_get_pair_moves.restype = ci; L.sq_get_pair_moves.argtypes = [vp, vp]
     L.sq_get_counters.restype = ci; L.sq_get_counters.argtypes = [vp, vp]
     L.sq_last_error.restype = C.c_char_p; L.sq_last_error.argtypes = []
     L.sq_kernel_launches.restype = C.c_longlong; L.sq_kernel_launches.argtypes = []

@@ -107,6 +107,8 @@ struct TickState {
   int* l_shelter;            // vehicles that gave up on this link (shelter_a1)
   int shelter_after;         // seconds on one link before a vehicle shelters (run_traffic_simulation.py:103), 0 = off
   int congest_after;         // seconds on one link before a vehicle counts as congested (run_traffic_simulation.py:101), 0 = off
+  unsigned* pair_moves;      // [turn table shape] vehicles moved from in-link i to out-link j of a node, or nullptr (off):
+                             // the (in_link, out_link) pairs run_node_model returns (model/queue_class.py:377-383)
   u64* n_cand;               // [N] bit i = in-link i of the node has a non-empty queue (written by k_link_phase)
   unsigned* cong_pos;        // [L] ring index of the first vehicle not yet congested (lags behind head when the queue moves)
   long long* l_congested;    // [L] link.congested of the last tick: vehicles on the link for longer than congest_after
@@ -284,6 +286,7 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
 struct AdmitCtx {
   int t, node, toss, moves, arrivals;
   long long key;
+  long long pair_row;   // index of (this in-link, out-link 0) in the pair-move table, when it is kept
 };
 
 // The in-side words of a node's out-links (remaining inflow / storage, run-list tail, length sum) are written by
@@ -396,6 +399,7 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
     s.tail[ol] = tl + 1u;
     s.len_in[ol] += vlen;
   }
+  if (s.pair_moves) atomicAdd(&s.pair_moves[c.pair_row + lc], 1u);   // result unused: a RED
   // move_agent_to_next_link + find_next_link (:610-615, :598-608)
   int nxt = v.nxt;
   if (v.rlen >= 0) {
@@ -671,10 +675,15 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
         lvl_tbl(s, gp);
         lvl_tbl(s, gs);
         LinkAcc ap;
+        long long pair0 = 0;
+        int outdeg = 0;
+        if (s.pair_moves) { pair0 = s.turn_ptr[n]; outdeg = s.out_ptr[n + 1] - s.out_ptr[n]; }
+        c.pair_row = pair0 + (long long)primary * outdeg;
         admit_set(s, c, oc, wp, false, gp, 0, ap);
         admit_finish(s, c, oc, wp, false, ap);
         if (!ap.any_left && ws.il >= 0) {                                         // opposite approach (:267-293)
           LinkAcc as;
+          c.pair_row = pair0 + (long long)secondary * outdeg;
           admit_set(s, c, oc, ws, true, gs, 0, as);
           admit_finish(s, c, oc, ws, true, as);
         }
@@ -919,6 +928,7 @@ struct SqSim {
   std::vector<void*> allocs;
   int N = 0, L = 0, A = 0;
   long long ring_slots = 0;
+  size_t n_turn = 0;   // entries of the turn table (sum over nodes of in-degree x out-degree)
   // host copies needed by getters
   std::vector<long long> h_ring_base;
   std::vector<unsigned> h_ring_mask;
@@ -981,6 +991,7 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
   const int N = d->n_nodes, L = d->n_links, A = d->n_agents;
   if (N <= 0 || L <= 0 || A < 0) return sq::set_error(SQ_ERR_ARG, "sq_create: empty network (N=%d L=%d A=%d)", N, L, A);
   sim->N = N; sim->L = L; sim->A = A;
+  sim->n_turn = (size_t)d->node_turn_ptr[N];
   TickState& s = sim->st;
   s.N = N; s.L = L; s.A = A; s.seed = d->seed;
   SQ_CUDA_TRY(cudaStreamCreateWithFlags(&sim->stream, cudaStreamNonBlocking));
@@ -1132,6 +1143,7 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
       if ((rc = dev_upload_rw(sim, &s.n_cand, zc64))) return rc;
       if ((rc = dev_upload_rw(sim, &s.l_congested, zl))) return rc;
     }
+    s.pair_moves = nullptr;
     s.D = 0; s.K = 0; s.freq = 1;
     s.n_vertex = nullptr; s.next_tbl = nullptr; s.dist_tbl = nullptr;
     s.cur_epoch = nullptr; s.bucket_ptr = nullptr; s.bucket_agents = nullptr; s.l_edge = nullptr; s.w_edge = nullptr;
@@ -1474,6 +1486,28 @@ int sq_get_link_congested(SqSim* sim, int64_t* out) {
   if (!sim || !out) return sq::set_error(SQ_ERR_ARG, "sq_get_link_congested: null argument");
   SQ_CUDA_TRY(cudaMemcpyAsync(out, sim->st.l_congested, sizeof(long long) * (size_t)sim->L, cudaMemcpyDeviceToHost, sim->stream));
   return sq_sync(sim);
+}
+
+int sq_enable_pair_moves(SqSim* sim) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_enable_pair_moves: null sim");
+  if (sim->st.pair_moves) return SQ_OK;
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  const size_t n = std::max<size_t>(sim->n_turn, 1);
+  SQ_CUDA_TRY(cudaMalloc(&sim->st.pair_moves, sizeof(unsigned) * n));
+  sim->allocs.push_back(sim->st.pair_moves);
+  SQ_CUDA_TRY(cudaMemset(sim->st.pair_moves, 0, sizeof(unsigned) * n));
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel parameters changed
+  return SQ_OK;
+}
+
+int sq_get_pair_moves(SqSim* sim, int64_t* out) {
+  if (!sim || !out) return sq::set_error(SQ_ERR_ARG, "sq_get_pair_moves: null argument");
+  if (!sim->st.pair_moves) return sq::set_error(SQ_ERR_ARG, "sq_get_pair_moves: call sq_enable_pair_moves first");
+  std::vector<unsigned> h(sim->n_turn);
+  SQ_CUDA_TRY(cudaMemcpyAsync(h.data(), sim->st.pair_moves, sizeof(unsigned) * sim->n_turn, cudaMemcpyDeviceToHost, sim->stream));
+  if (int rc = sq_sync(sim)) return rc;
+  for (size_t i = 0; i < sim->n_turn; ++i) out[i] = (int64_t)h[i];
+  return SQ_OK;
 }
 
 int sq_set_shelter_after(SqSim* sim, int32_t seconds) {

@@ -551,6 +551,23 @@ class Network:
                 self._reroute_due(t)
         sim.step(t)
 
+    def count_link_pair_flows(self):
+        """Start counting vehicles per (in_link, out_link) pair on the device: the second return value of
+        Node.run_node_model (model/queue_class.py:377-383) that Butte's node_model accumulates into
+        check_traffic_flow_links_dict (model/dta_meso_butte.py:124-131).  Call after use_gpu, before the first step."""
+        self.sim.enable_pair_moves()
+        return self
+
+    def link_pair_flows(self, pairs=None):
+        """{(in_link_id, out_link_id): vehicles moved so far}; `pairs` restricts the result to the given keys (the
+        reference's check_traffic_flow_links_dict), with 0 for pairs nobody crossed."""
+        il, ol, cnt = self.sim.pair_moves(self._flat)
+        ids = self._flat.link_ids
+        flows = {(ids[a], ids[b]): int(c) for a, b, c in zip(il, ol, cnt)}
+        if pairs is not None:
+            return {k: flows.get(k, 0) for k in pairs}
+        return flows
+
     def summary(self):
         """Counts for the drivers' periodic log / t_stats line (model/dta_meso_butte.py:291-348) from one small
         device reduction instead of a full sync_to_host: agents by status, vehicles queued / running / congested /

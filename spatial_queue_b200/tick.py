@@ -136,6 +136,22 @@ class _SimBase:
         self._check(self._fn("get_link_weights")(self._h, w.ctypes.data), "get_link_weights")
         return w
 
+    def pair_moves(self, flat):
+        """Vehicles moved per (in_link, out_link) pair -- what Node.run_node_model returns as node_move_link_pairs
+        (model/queue_class.py:377-383), counted: -> (in_link i32[], out_link i32[], count i64[]) over the pairs with at
+        least one move.  `flat` supplies the node CSR the table is shaped after.  DeviceSim: enable_pair_moves first."""
+        n_turn = int(flat.node_turn_ptr[-1])
+        tbl = np.zeros(max(n_turn, 1), np.int64)
+        self._check(self._fn("get_pair_moves")(self._h, tbl.ctypes.data), "get_pair_moves")
+        tbl = tbl[:n_turn]
+        idx = np.flatnonzero(tbl)
+        node = np.searchsorted(np.asarray(flat.node_turn_ptr), idx, side="right") - 1
+        outdeg = (np.asarray(flat.node_out_ptr)[node + 1] - np.asarray(flat.node_out_ptr)[node]).astype(np.int64)
+        rel = idx - np.asarray(flat.node_turn_ptr)[node]
+        il = np.asarray(flat.node_in_links)[np.asarray(flat.node_in_ptr)[node] + rel // outdeg]
+        ol = np.asarray(flat.node_out_links)[np.asarray(flat.node_out_ptr)[node] + rel % outdeg]
+        return il.astype(np.int32), ol.astype(np.int32), tbl[idx]
+
     def counters(self):
         out = np.zeros(6, np.int64)
         self._check(self._fn("get_counters")(self._h, out.ctypes.data), "get_counters")
@@ -217,6 +233,10 @@ class DeviceSim(_SimBase):
         r.reroute_freq, r.weight_freq = int(reroute_freq), int(weight_freq)
         self._check(self._L.sq_attach_router(self._h, C.byref(r)), "attach_router")
         self._router_graph = graph   # keep the graph alive as long as the sim uses it
+
+    def enable_pair_moves(self):
+        """Start counting moves per (in_link, out_link) pair (include/sq_tick.h sq_enable_pair_moves)."""
+        self._check(self._L.sq_enable_pair_moves(self._h), "enable_pair_moves")
 
     def set_shelter_after(self, seconds):
         self._check(self._L.sq_set_shelter_after(self._h, int(seconds)), "set_shelter_after")

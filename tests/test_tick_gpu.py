@@ -311,3 +311,25 @@ def test_random_small_towns_match_oracle(seed):
     cd, co = dev.counters(), orc.counters()
     assert cd["agent_steps"] == co["agent_steps"] and cd["moves"] == co["moves"] and cd["arrivals"] == co["arrivals"]
     dev.close(); orc.close()
+
+
+def test_link_pair_flow_counters_match_oracle():
+    """Row A6: run_node_model's second return value, (in_link, out_link) per moved vehicle (model/queue_class.py:
+    377-383), as per-pair counters on the device; equal to the oracle's pair list after 600 ticks on the irregular
+    network, and consistent with total_vehicles_left (row sum + arrivals)."""
+    from oracle.tick import OracleSim
+    from spatial_queue_b200.tick import DeviceSim
+    flat = _town()
+    dev, orc = DeviceSim(flat, seed=4), OracleSim(flat, seed=4)
+    dev.enable_pair_moves()
+    dev.run(0, 600)
+    orc.run(0, 600)
+    di, do_, dc = dev.pair_moves(flat)
+    oi, oo, oc = orc.pair_moves(flat)
+    assert len(dc) > 2000 and (di == oi).all() and (do_ == oo).all() and (dc == oc).all()
+    cd = dev.counters()
+    assert int(dc.sum()) == cd["moves"] - cd["arrivals"]
+    left = dev.link_state()["left"].astype(np.int64)
+    per_in = np.bincount(di, weights=dc, minlength=len(left)).astype(np.int64)
+    assert (per_in <= left).all() and int((left - per_in).sum()) == cd["arrivals"]
+    dev.close(); orc.close()

@@ -67,4 +67,8 @@ def test_oracle_on_irregular_network_conserves_vehicles():
         ptr, order = sim.link_vehicles()
         assert len(np.unique(order)) == len(order) and (st[order] == 1).all()
     assert int((st == 5).sum()) == stopped and (st == 4).sum() > 0 and (st == 2).sum() > 500
+    # node_move_link_pairs (model/queue_class.py:377-383) as counters: one pair per move that is not an arrival
+    il, ol, cnt = sim.pair_moves(flat)
+    c = sim.counters()
+    assert int(cnt.sum()) == c["moves"] - c["arrivals"] and (flat.link_end_node[il] == flat.link_start_node[ol]).all()
     sim.close()
