@@ -69,7 +69,7 @@ typedef struct SqNetDesc {
 typedef struct SqSim SqSim;
 
 /* Agent status codes (spatial_queue_b200/flatten.py STATUS_CODES). */
-enum { SQ_UNLOADED = 0, SQ_ENROUTE = 1, SQ_ARRIVE = 2, SQ_SHELTER_P = 3, SQ_SHELTER_A1 = 4 };
+enum { SQ_UNLOADED = 0, SQ_ENROUTE = 1, SQ_ARRIVE = 2, SQ_SHELTER_P = 3, SQ_SHELTER_A1 = 4, SQ_SHELTER_A2 = 5 };
 
 /* Build device state from a network that has not ticked yet.  NULL on failure (sq_last_error). */
 SqSim* sq_create(const SqNetDesc* desc);
@@ -126,6 +126,18 @@ typedef struct SqRouterDesc {
   int32_t reroute_freq, weight_freq;
 } SqRouterDesc;
 int sq_attach_router(SqSim* sim, const SqRouterDesc* router);
+
+/* Butte's additions to the agent loop (model/dta_meso_butte.py:193-209, 256-263), inside the device router:
+ *   detour_factor > 0:        whenever an agent is rerouted, its new route distance is compared with the one it had
+ *                             (Agent.route_distance, 5e7 before the first route); an ENROUTE agent whose trip grew by
+ *                             more than the factor (the reference uses 2) gets status SQ_SHELTER_A2 and leaves its
+ *                             link's queue / run list before the link model of the same tick;
+ *   closure_reroute_freq > 0: an agent whose next link is closed (sq_set_link_closed / closure schedule) reroutes when
+ *                             t % closure_reroute_freq == agent_key % closure_reroute_freq (the reference uses 10),
+ *                             after its regular reroute if both fall on the same tick.
+ * The reroutes then run as a launch of their own before the link phase (three kernels per tick instead of two).
+ * Call once, after sq_attach_router and before the first tick. */
+int sq_set_reroute_rules(SqSim* sim, double detour_factor, int32_t closure_reroute_freq);
 
 /* Agent-loop rule of the drivers (run_traffic_simulation.py:100-104, 113-118): a vehicle that has spent more than
  * `seconds` on one real link gives up (status SQ_SHELTER_A1) and leaves the link before the link model of that tick.

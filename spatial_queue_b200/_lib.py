@@ -63,6 +63,7 @@ def _declare(L):
     L.sp_set_warp_tuning.restype = ci; L.sp_set_warp_tuning.argtypes = [vp, ci, ci, ci]
     L.sp_set_group_tuning.restype = ci; L.sp_set_group_tuning.argtypes = [vp, ci, ci, ci, ci, ci]
     L.sp_set_group_mode.restype = ci; L.sp_set_group_mode.argtypes = [vp, ci, ci]
+    L.sp_set_relax_mode.restype = ci; L.sp_set_relax_mode.argtypes = [vp, ci]
     L.sp_last_stats.restype = ci; L.sp_last_stats.argtypes = [vp, vp]
     L.sp_last_error.restype = C.c_char_p; L.sp_last_error.argtypes = []
     L.sp_kernel_launches.restype = C.c_longlong; L.sp_kernel_launches.argtypes = []
@@ -91,6 +92,7 @@ def _declare(L):
     L.sq_get_agent_state.restype = ci; L.sq_get_agent_state.argtypes = [vp] * 6
     L.sq_get_node_state.restype = ci; L.sq_get_node_state.argtypes = [vp, vp]
     L.sq_get_link_weights.restype = ci; L.sq_get_link_weights.argtypes = [vp, vp]
+    L.sq_set_reroute_rules.restype = ci; L.sq_set_reroute_rules.argtypes = [vp, cd, i32]
     L.sq_enable_pair_moves.restype = ci; L.sq_enable_pair_moves.argtypes = [vp]
     L.sq_get_pair_moves.restype = ci; L.sq_get_pair_moves.argtypes = [vp, vp]
     L.sq_get_counters.restype = ci; L.sq_get_counters.argtypes = [vp, vp]

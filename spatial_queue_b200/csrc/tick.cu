@@ -102,6 +102,14 @@ struct TickState {
   double* w_edge;            // [graph edges] staging for sp_set_weights_device
   int* mat_pool;             // routes materialised on the device (agents that could not be rerouted)
   long long* mat_used; long long mat_cap;
+  // Butte's rules inside the router (model/dta_meso_butte.py:193-209, 256-263), off unless sq_set_reroute_rules
+  double* a_rdist;           // [A] Agent.route_distance: distance of the route last adopted (5e7 before the first)
+  double detour_factor;      // > 0: an enroute agent whose new route is longer than factor x the old one shelters (shelter_a2)
+  int cfreq;                 // > 0: agents whose next link is closed reroute when t % cfreq == key % cfreq
+  const int* cbucket_ptr; const int* cbucket_agents;   // agents by key % cfreq
+  const int* a_rslot; const int* a_cslot;              // key % freq, key % cfreq per agent
+  int max_cbucket;
+  int* l_tomb;               // [L] > 0: vehicles on this link stopped during this tick's agent loop; the link phase strips them
   // agent-loop rules of the drivers
   const int* l_dwell;        // floor(fft) + 2: upper bound of ready_tick - enter_time
   int* l_shelter;            // vehicles that gave up on this link (shelter_a1)
@@ -159,6 +167,36 @@ __device__ __forceinline__ size_t tbl_index(const TickState& s, int epoch, int d
   return (size_t)((u64)(unsigned)(epoch * s.D + dslot) * (u64)(unsigned)s.N + (u64)(unsigned)node);
 }
 
+// Vehicles that stopped on link l since the last tick (status no longer enroute) leave its lists at once, wherever they
+// stand (model/dta_meso_butte.py:256-263): the survivors slide towards the tail in order, the head and the queue / run
+// boundary move up by what was removed on their side.  Returns the number removed.
+__device__ int strip_stopped(const TickState& s, int l) {
+  const long long base = s.l_ring_base[l];
+  const unsigned mask = s.l_ring_mask[l];
+  const unsigned h = s.head[l], qt = s.qtail[l], tl = s.tail[l];
+  unsigned j = tl;                                   // next free slot + 1, filling from the tail down
+  int removed = 0, removed_run = 0;
+  long long len = 0;
+  for (unsigned p = tl; p != h; --p) {
+    const int2 e = s.ring[base + ((p - 1u) & mask)];
+    const int w = s.ag[e.x].rec.w;
+    if ((w & 0xff) != SQ_ENROUTE) {
+      ++removed; len += (w >> 8) & 0xff;
+      if ((int)((p - 1u) - qt) >= 0) ++removed_run;
+    } else {
+      --j;
+      if (j != p - 1u) s.ring[base + (j & mask)] = e;
+    }
+  }
+  if (!removed) return 0;
+  s.head[l] = h + (unsigned)removed;
+  s.qtail[l] = qt + (unsigned)removed_run;
+  s.len_out[l] += len;
+  s.l_shelter[l] += removed;
+  if (s.cong_pos) s.cong_pos[l] = h + (unsigned)removed;   // the congested prefix is recounted by the next link phase
+  return removed;
+}
+
 // ---- phase 1: load + link model, one thread per link ---------------------------------------------------
 __device__ void reroute_slot(const TickState& s, int i);
 
@@ -183,6 +221,10 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
   }
   int loaded = 0, sheltered = 0;
   if (l < s.L) {
+    if (s.l_tomb && s.l_tomb[l] > 0) {     // shelter_a2 vehicles of this tick's reroutes (k_reroute_rules ran before)
+      sheltered += strip_stopped(s, l);
+      s.l_tomb[l] = 0;
+    }
     unsigned tl = s.tail[l];
     unsigned qt = s.qtail[l];
     const long long base = s.l_ring_base[l];
@@ -217,6 +259,7 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       unsigned h = s.head[l];
       const int dwell = s.l_dwell[l];
       long long lo = 0;
+      int gave_up = 0;
       while (h != tl) {
         const int2 e = s.ring[base + (h & mask)];
         if (e.y != INT_MAX && (long long)t - e.y + dwell <= s.shelter_after) break;   // cannot be old enough yet
@@ -225,13 +268,14 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
         s.ag[e.x].rec.w = (rec.w & ~0xff) | SQ_SHELTER_A1;
         s.a_arrive[e.x] = t;
         lo += (rec.w >> 8) & 0xff;
-        ++h; ++sheltered;
+        ++h; ++gave_up;
       }
-      if (sheltered) {
+      if (gave_up) {
         s.head[l] = h;
         s.len_out[l] += lo;
-        s.l_shelter[l] += sheltered;
+        s.l_shelter[l] += gave_up;
         if ((int)(qt - h) < 0) { qt = h; s.qtail[l] = qt; }   // they were still in the run part
+        sheltered += gave_up;
       }
     }
     if (s.l_virtual[l]) {
@@ -732,30 +776,8 @@ __global__ void k_stop_compact(const TickState s, int n, const int* __restrict__
   if (i >= n) return;
   const int l = s.ag[agent_idx[i]].rec.y;
   if (atomicExch(&tomb[l], 0) <= 0) return;          // another thread of this launch owns the link (or error above)
-  const long long base = s.l_ring_base[l];
-  const unsigned mask = s.l_ring_mask[l];
-  const unsigned h = s.head[l], qt = s.qtail[l], tl = s.tail[l];
-  unsigned j = tl;                                   // next free slot + 1, filling from the tail down
-  int removed = 0, removed_run = 0;
-  long long len = 0;
-  for (unsigned p = tl; p != h; --p) {
-    const int2 e = s.ring[base + ((p - 1u) & mask)];
-    const int w = s.ag[e.x].rec.w;
-    if ((w & 0xff) != SQ_ENROUTE) {
-      ++removed; len += (w >> 8) & 0xff;
-      if ((int)((p - 1u) - qt) >= 0) ++removed_run;
-    } else {
-      --j;
-      if (j != p - 1u) s.ring[base + (j & mask)] = e;
-    }
-  }
-  if (!removed) return;
-  s.head[l] = h + (unsigned)removed;
-  s.qtail[l] = qt + (unsigned)removed_run;
-  s.len_out[l] += len;
-  s.l_shelter[l] += removed;
-  if (s.cong_pos) s.cong_pos[l] = h + (unsigned)removed;   // the congested prefix is recounted by the next link phase
-  atomicAdd(&s.counters[7], (u64)removed);
+  const int removed = strip_stopped(s, l);
+  if (removed) atomicAdd(&s.counters[7], (u64)removed);
 }
 
 // ---- route replacement (Agent.get_path + find_next_link) -----------------------------------------------
@@ -813,17 +835,29 @@ __global__ void __launch_bounds__(256) k_build_tables(const TickState s, int slo
 // Agent.get_path + find_next_link for the agents due this tick (t % freq == agent_id % freq,
 // run_traffic_simulation.py:107-109): adopt the newest tables unless the destination is out of reach
 // (distance > 1e8 keeps the old route, queue_class.py:511-513).  `all` != 0 routes every agent (t == 0).
-__device__ __forceinline__ void reroute_agent(const TickState& s, int a) {
+__device__ __forceinline__ void reroute_agent(const TickState& s, int a, int t) {
   const int4 rec = s.ag[a].rec;
   const int st = rec.w & 0xff;
   if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
   const int node = s.l_end[rec.y];
   const int e = *s.cur_epoch;
   const size_t idx = tbl_index(s, e, s.ag[a].dslot, node);
-  if (s.dist_tbl[idx] > 1e8) return;
+  const double d = s.dist_tbl[idx];
+  if (d > 1e8) return;
   s.ag[a].epoch = e;
   s.ag[a].route_len = -1;
   s.ag[a].rec.x = s.next_tbl[idx];
+  if (s.a_rdist) {
+    // previous_distance = agent.route_distance; get_path; shelter_a2 if the trip more than doubled
+    // (model/dta_meso_butte.py:195-198, 201-204)
+    const double prev = s.a_rdist[a];
+    s.a_rdist[a] = d;
+    if (s.detour_factor > 0.0 && st == SQ_ENROUTE && d > prev * s.detour_factor) {
+      s.ag[a].rec.w = (rec.w & ~0xff) | SQ_SHELTER_A2;
+      s.a_arrive[a] = t;
+      atomicAdd(&s.l_tomb[rec.y], 1);      // the link phase of this tick takes the vehicle off the link
+    }
+  }
 }
 
 // i-th agent of this tick's stagger slot (t % freq == key % freq, run_traffic_simulation.py:107)
@@ -834,12 +868,40 @@ __device__ void reroute_slot(const TickState& s, int i) {
   const int b = t % s.freq;
   const int k = s.bucket_ptr[b] + i;
   if (k >= s.bucket_ptr[b + 1]) return;
-  reroute_agent(s, s.bucket_agents[k]);
+  reroute_agent(s, s.bucket_agents[k], t);
 }
 
 __global__ void __launch_bounds__(128) k_reroute_all(const TickState s) {
   const int a = blockIdx.x * 128 + threadIdx.x;
-  if (a < s.A) reroute_agent(s, a);
+  if (a < s.A) reroute_agent(s, a, 0);
+}
+
+// The agent loop's reroute rules with Butte's additions (model/dta_meso_butte.py:193-209), one launch BEFORE the link
+// phase (a sheltering vehicle must be off its link before the link model of the same second, :256-263):
+//   regular stagger slot  t % freq  == key % freq   -> get_path (+ the detour test in reroute_agent);
+//   closure stagger slot  t % cfreq == key % cfreq  -> get_path again if the agent's next link is closed.
+// An agent due in both slots is handled by its closure-slot thread, in the reference's order.
+__global__ void __launch_bounds__(128) k_reroute_rules(const TickState s) {
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  const int t = *s.tick_link;
+  if (t <= 0) return;
+  if (s.cfreq > 0) {
+    const int b2 = t % s.cfreq;
+    const int k2 = s.cbucket_ptr[b2] + i;
+    if (k2 < s.cbucket_ptr[b2 + 1]) {
+      const int a = s.cbucket_agents[k2];
+      if (s.a_rslot[a] == t % s.freq) reroute_agent(s, a, t);
+      const int4 rec = s.ag[a].rec;
+      const int st = rec.w & 0xff;
+      if ((st == SQ_UNLOADED || st == SQ_ENROUTE) && rec.x >= 0 && s.l_closed[rec.x]) reroute_agent(s, a, t);
+    }
+  }
+  const int b = t % s.freq;
+  const int k = s.bucket_ptr[b] + i;
+  if (k < s.bucket_ptr[b + 1]) {
+    const int a = s.bucket_agents[k];
+    if (!(s.cfreq > 0 && s.a_cslot[a] == t % s.cfreq)) reroute_agent(s, a, t);
+  }
 }
 
 // Before table slot `slot` is overwritten: agents that still follow it (their reroutes kept failing) get
@@ -958,6 +1020,7 @@ struct SqSim {
   double* d_tdist = nullptr;        // [D][V] reverse-tree scratch
   int* d_tnext = nullptr;
   int* d_pair_ptr = nullptr; int* d_pair_endv = nullptr; int* d_pair_link = nullptr;
+  std::vector<long long> agent_key;   // router: agent ids (stagger slots)
   long long launches = 0;
   cudaGraphExec_t graph = nullptr;
   int graph_ticks = 0;
@@ -1144,6 +1207,8 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
       if ((rc = dev_upload_rw(sim, &s.l_congested, zl))) return rc;
     }
     s.pair_moves = nullptr;
+    s.a_rdist = nullptr; s.detour_factor = 0.0; s.cfreq = 0; s.cbucket_ptr = nullptr; s.cbucket_agents = nullptr;
+    s.a_rslot = nullptr; s.a_cslot = nullptr; s.max_cbucket = 0; s.l_tomb = nullptr;
     s.D = 0; s.K = 0; s.freq = 1;
     s.n_vertex = nullptr; s.next_tbl = nullptr; s.dist_tbl = nullptr;
     s.cur_epoch = nullptr; s.bucket_ptr = nullptr; s.bucket_agents = nullptr; s.l_edge = nullptr; s.w_edge = nullptr;
@@ -1195,7 +1260,13 @@ static int launch_tick(SqSim* sim, cudaStream_t st) {
   const int L = sim->L, N = sim->N;
   const int lb = 128;   // measured: 31.5 / 31.5 / 32.1 us per tick with 64 / 128 / 256 threads
   const int link_blocks = (L + lb - 1) / lb;
-  const int reroute_blocks = (sim->router_graph && sim->max_bucket > 0) ? (sim->max_bucket + lb - 1) / lb : 0;
+  int reroute_blocks = (sim->router_graph && sim->max_bucket > 0) ? (sim->max_bucket + lb - 1) / lb : 0;
+  if (sim->st.a_rdist) {
+    // Butte's rules: the reroutes run as their own launch before the link phase
+    const int work = std::max(sim->max_bucket, sim->st.max_cbucket);
+    if (work > 0) k_reroute_rules<<<(work + 127) / 128, 128, 0, st>>>(sim->st);
+    reroute_blocks = 0;
+  }
   k_link_phase<<<link_blocks + reroute_blocks, lb, 0, st>>>(sim->st, link_blocks);
   // one warp per CTA: the warps are independent chains, the finer grain spreads them evenly over the SMs (measured:
   // 31.7 / 32.1 / 32.5 us per tick with 32 / 64 / 128 threads)
@@ -1318,7 +1389,7 @@ static int next_event_tick(const SqSim* sim) {
   return sim->ev_cursor < sim->ev_tick.size() ? sim->ev_tick[sim->ev_cursor] : INT_MAX;
 }
 
-static int kernels_per_tick(const SqSim*) { return 2; }
+static int kernels_per_tick(const SqSim* sim) { return sim->st.a_rdist ? 3 : 2; }
 
 extern "C" {
 
@@ -1537,8 +1608,11 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* r) {
   SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
   TickState& s = sim->st;
   int rc;
-  // epochs kept: a route is at most reroute_freq ticks old when it is renewed; +2 for the slot being built
-  const int K = r->reroute_freq / r->weight_freq + 3;
+  // epochs kept: a route is at most reroute_freq ticks old when it is renewed, so reroute_freq / weight_freq + 1 regular
+  // refreshes can be live, + the slot being built, + 8 for refreshes off the weight grid (closure events, host edits of
+  // the graph) inside one reroute period.  Beyond that the oldest slot is recycled early and k_evacuate writes its
+  // followers' remaining routes out (correct, but it eats the materialisation pool).
+  const int K = r->reroute_freq / r->weight_freq + 3 + 8;
   s.D = D; s.K = K; s.freq = r->reroute_freq;
   if ((rc = dev_upload_ptr(sim, &s.n_vertex, r->node_vertex, (size_t)N))) return rc;
   {  // destination slots go into the agents' records (one-time round trip)
@@ -1604,6 +1678,7 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* r) {
     if ((rc = dev_upload(sim, &s.bucket_ptr, ptr))) return rc;
     if ((rc = dev_upload(sim, &s.bucket_agents, ag))) return rc;
   }
+  sim->agent_key.assign(r->agent_key, r->agent_key + A);
   sim->router_graph = g;
   sim->wfreq = r->weight_freq;
   sim->graph_V = V; sim->graph_E = E;
@@ -1612,6 +1687,51 @@ int sq_attach_router(SqSim* sim, const SqRouterDesc* r) {
   if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }
   // t = 0: weights from the empty network, tables, and every agent routed (run_traffic_simulation.py:107)
   if ((rc = router_refresh(sim, 0))) return rc;
+  if (A > 0) {
+    k_reroute_all<<<(A + 127) / 128, 128, 0, sim->stream>>>(s);
+    sq::count_launch(); sim->launches += 1;
+  }
+  SQ_CUDA_TRY(cudaGetLastError());
+  return sq_sync(sim);
+}
+
+int sq_set_reroute_rules(SqSim* sim, double detour_factor, int32_t closure_reroute_freq) {
+  if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_set_reroute_rules: null sim");
+  if (!sim->router_graph) return sq::set_error(SQ_ERR_ARG, "sq_set_reroute_rules: attach a router first");
+  if (detour_factor < 0.0 || closure_reroute_freq < 0) return sq::set_error(SQ_ERR_ARG, "sq_set_reroute_rules: negative argument");
+  if (sim->st.a_rdist) return sq::set_error(SQ_ERR_ARG, "sq_set_reroute_rules: rules are already set");
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  TickState& s = sim->st;
+  const int A = sim->A, L = sim->L, F = s.freq, CF = closure_reroute_freq;
+  int rc;
+  {
+    // route_distance of the t = 0 routes: the distance table entry of each agent's origin
+    std::vector<double> rd((size_t)std::max(A, 1), 5e7);
+    if ((rc = dev_upload_rw(sim, &s.a_rdist, rd))) return rc;
+    std::vector<int> zl((size_t)L, 0);
+    if ((rc = dev_upload_rw(sim, &s.l_tomb, zl))) return rc;
+  }
+  {
+    std::vector<int> rs((size_t)std::max(A, 1), 0), cs((size_t)std::max(A, 1), 0);
+    auto slot = [&](int a, int m) { long long k = sim->agent_key[a] % m; return (int)(k < 0 ? k + m : k); };
+    for (int a = 0; a < A; ++a) { rs[a] = slot(a, F); cs[a] = CF > 0 ? slot(a, CF) : 0; }
+    if ((rc = dev_upload(sim, &s.a_rslot, rs))) return rc;
+    if ((rc = dev_upload(sim, &s.a_cslot, cs))) return rc;
+    if (CF > 0) {
+      std::vector<int> ptr((size_t)CF + 1, 0), ag((size_t)std::max(A, 1));
+      for (int a = 0; a < A; ++a) ++ptr[(size_t)cs[a] + 1];
+      s.max_cbucket = 0;
+      for (int b = 0; b < CF; ++b) { s.max_cbucket = std::max(s.max_cbucket, ptr[(size_t)b + 1]); ptr[(size_t)b + 1] += ptr[b]; }
+      std::vector<int> fill(ptr.begin(), ptr.end() - 1);
+      for (int a = 0; a < A; ++a) ag[fill[cs[a]]++] = a;
+      if ((rc = dev_upload(sim, &s.cbucket_ptr, ptr))) return rc;
+      if ((rc = dev_upload(sim, &s.cbucket_agents, ag))) return rc;
+    }
+  }
+  s.detour_factor = detour_factor;
+  s.cfreq = CF;
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }   // kernel parameters and launches changed
+  // the routes given at attach time: route_distance = distance from the origin (never a detour: previous = 5e7)
   if (A > 0) {
     k_reroute_all<<<(A + 127) / 128, 128, 0, sim->stream>>>(s);
     sq::count_launch(); sim->launches += 1;

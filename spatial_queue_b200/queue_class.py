@@ -433,12 +433,13 @@ class Network:
         `congest_after` seconds on their link (run_traffic_simulation.py:80-118).  `network.step(t)` is one C call.
         route_mode="host": routes are Python dicts on the agents like in the reference (`agent.route`), recomputed
         in batches of forward trees and pushed to the device; use it when a driver edits routes itself
-        (e.g. get_partial_path).  Host mode also carries Butte's two extra rules (model/dta_meso_butte.py:199-209):
+        (e.g. get_partial_path).  Butte's two extra rules (model/dta_meso_butte.py:199-209) work in both modes:
         `detour_factor=2` shelters an enroute agent whose rerouted trip is more than twice its previous one
-        (shelter_a2, `shelter_agents`), `closure_reroute_freq=10` reroutes agents whose next link is closed when
-        t % 10 == agent_id % 10.  Both run before the device tick, i.e. before the give-up test of the same second
-        (the reference tests give-up first; the two only meet when an agent's stagger slot falls on the very second
-        it gives up)."""
+        (shelter_a2), `closure_reroute_freq=10` reroutes agents whose next link is closed when
+        t % 10 == agent_id % 10.  In device mode they run inside the router (sq_set_reroute_rules), in host mode in
+        Python (`route_agents`, `shelter_agents`); either way before the link model of the tick, i.e. before the
+        give-up test of the same second (the reference tests give-up first; the two only meet when an agent's
+        stagger slot falls on the very second it gives up)."""
         from .flatten import router_arrays
         from .tick import DeviceSim
         if special_nodes is not None:
@@ -447,10 +448,6 @@ class Network:
             raise ValueError("route_mode must be 'device' or 'host'")
         self.route_mode = route_mode
         self._pending_status = {}
-        if detour_factor and route_mode != "host":
-            raise ValueError("detour_factor (Butte's shelter_a2 rule) needs route_mode='host'")
-        if closure_reroute_freq and route_mode != "host":
-            raise ValueError("closure_reroute_freq (Butte's reroute-upon-closure rule) needs route_mode='host'")
         self.detour_factor, self.closure_reroute_freq = detour_factor, closure_reroute_freq
         if route_mode == "host":
             if route_at_start:
@@ -468,6 +465,9 @@ class Network:
             self._flat = router_arrays(flatten_network(self, self.special_nodes), self)
             self._sim = DeviceSim(self._flat, seed=seed, routes_from_router=True)
             self._sim.attach_router(self.g, self._flat, reroute_freq=reroute_freq, weight_freq=weight_freq)
+            if detour_factor or closure_reroute_freq:
+                # Butte's two rules inside the device router (sq_set_reroute_rules): no per-tick host work
+                self._sim.set_reroute_rules(detour_factor or 0.0, closure_reroute_freq or 0)
         if shelter_after:
             self._sim.set_shelter_after(shelter_after)
         if congest_after:
@@ -630,7 +630,7 @@ class Network:
             a.this_link = self._flat.link_ids[cur] if cur >= 0 else None
             a.next_link = self._flat.link_ids[nxt] if nxt >= 0 else None
             a.next_link_end_nid = self._end_node_of_link[nxt] if nxt >= 0 else None
-            if a.status in ("arrive", "shelter_a1") and not self._arrive_reported[i]:
+            if a.status in ("arrive", "shelter_a1", "shelter_a2") and not self._arrive_reported[i]:
                 self._arrive_reported[i] = True
                 # the reference's agent loop notices an arrival one tick later, a give-up in the same tick
                 when = int(sh["stop_tick"][i]) + (1 if a.status == "arrive" else 0)

@@ -234,6 +234,11 @@ class DeviceSim(_SimBase):
         self._check(self._L.sq_attach_router(self._h, C.byref(r)), "attach_router")
         self._router_graph = graph   # keep the graph alive as long as the sim uses it
 
+    def set_reroute_rules(self, detour_factor=0.0, closure_reroute_freq=0):
+        """Butte's shelter_a2 detour rule and reroute-upon-closure inside the device router (include/sq_tick.h)."""
+        self._check(self._L.sq_set_reroute_rules(self._h, float(detour_factor or 0.0), int(closure_reroute_freq or 0)),
+                    "set_reroute_rules")
+
     def enable_pair_moves(self):
         """Start counting moves per (in_link, out_link) pair (include/sq_tick.h sq_enable_pair_moves)."""
         self._check(self._L.sq_enable_pair_moves(self._h), "enable_pair_moves")

@@ -285,8 +285,6 @@ def test_detour_rule_shelters_agents_on_the_device(tmp_path):
     st = net.sim.agent_state()["status"]
     assert int((st == 5).sum()) == len(a2)
     assert len(net.agents) + len(net.agents_stopped) == n0
-    with pytest.raises(ValueError):
-        build_grid("grid8", tmp_path)[0].use_gpu(route_mode="device", detour_factor=2)
 
 
 @pytest.mark.gpu
@@ -382,3 +380,49 @@ def test_host_and_device_routing_agree_on_irregular_networks(seed, tmp_path):
     assert not bad, f"first difference at tick {bad[0] * 10}"
     assert (runs[0].sim.agent_state()["arrive_tick"] == runs[1].sim.agent_state()["arrive_tick"]).all()
     assert (runs[0].sim.agent_state()["status"] == 2).sum() > 100
+
+
+@pytest.mark.gpu
+def test_butte_rules_inside_the_device_router_equal_host_mode(tmp_path):
+    """Rows N1 / N2: Butte's shelter_a2 detour rule and reroute-upon-closure (model/dta_meso_butte.py:193-209, 256-263)
+    inside the device router (sq_set_reroute_rules: per-agent route distance, closure stagger slot, the sheltering
+    vehicle stripped from the middle of its ring by the link phase of the same tick) against the same rules in host
+    route mode (Python over sp_route_batch + sq_stop_agents), tick for tick, on four irregular networks with streets
+    closed at t = 60 and reopened at t = 200.  A low detour factor makes the rule fire."""
+    total_a2 = 0
+    for seed in (1, 2, 3, 4):
+        runs = []
+        for mode in ("host", "device"):
+            d = tmp_path / f"{mode}{seed}"
+            d.mkdir()
+            net = build_town(seed, d)
+            net.use_gpu(seed=seed, special_nodes=EMPTY, reroute_freq=40, weight_freq=25, route_mode=mode, shelter_after=200,
+                        detour_factor=1.2, closure_reroute_freq=10)
+            runs.append(net)
+        digests = [[], []]
+        for k, net in enumerate(runs):
+            closing = sorted(lid for lid, l in net.links.items() if l.link_type != "v")[5::12]
+            for t in range(330):
+                if t in (60, 200):
+                    for lid in closing:
+                        if t == 60:
+                            net.links[lid].close_link_to_newcomers(g=net.g)
+                            net.links[lid].status = "closed"
+                        else:
+                            net.links[lid].open_link_to_newcomers(g=net.g)
+                            net.links[lid].status = "open"
+                net.step(t)
+                if t % 5 == 0:
+                    digests[k].append(state_digest(net.sim.state()))
+        bad = [i for i, (a, b) in enumerate(zip(*digests)) if a != b]
+        assert not bad, f"seed {seed}: first difference at tick {bad[0] * 5}"
+        sa, sb = runs[0].sim.agent_state(), runs[1].sim.agent_state()
+        assert (sa["status"] == sb["status"]).all() and (sa["arrive_tick"] == sb["arrive_tick"]).all()
+        sh0, sh1 = runs[0].sim.shelter_state(), runs[1].sim.shelter_state()
+        assert (sh0["stop_tick"] == sh1["stop_tick"]).all() and (sh0["link_shelter"] == sh1["link_shelter"]).all()
+        total_a2 += int((sb["status"] == 5).sum())
+        # the device run made no per-tick host call beyond step(): its mirror objects only move at sync_to_host
+        runs[1].sync_to_host()
+        a2 = {k for k, v in runs[1].agents_stopped.items() if v[0] == "shelter_a2"}
+        assert len(a2) == int((sb["status"] == 5).sum())
+    assert total_a2 > 10

@@ -68,5 +68,6 @@ def test_config4_device_router_matches_forward_dijkstra_host_path():
     assert (dev.agent_state()["arrive_tick"] == orc.agent_state()["arrive_tick"]).all()
     # the case is what it claims to be: everyone rerouted about 20 times, queues long enough to change the weights
     assert rerouted > 150_000 * (TICKS // REROUTE) * 0.8 and fr.trees_computed > 100_000
-    assert cd["moves"] > 1_000_000 and float(np.nanmax(orc.link_weights())) > 100.0
+    # (free-flow weights are 9 - 24 s on this grid; queued links weigh more than twice that)
+    assert cd["moves"] > 1_000_000 and float(np.nanmax(orc.link_weights())) > 50.0
     dev.close(); orc.close()
