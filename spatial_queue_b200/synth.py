@@ -325,14 +325,15 @@ def town_frames(n, seed=1, **shape):
 
 
 def town_scenario(n, n_agents, horizon=600, seed=1, n_exits=8, signals=0.04, priority=0.03, router=None,
-                  device_routes=False):
+                  device_routes=False, exits_on_rim=False, **shape):
     """Irregular network + signal and priority nodes + demand from every node that can reach its exit.  Signal nodes
     alternate between the roughly north-south and the roughly east-west approaches (the source link is always
     green), priority nodes rank all their approaches in a random order."""
     rng = np.random.default_rng(seed + 10)
     lon, lat = grid_coords(n, seed)
-    s, e, lanes, maxmph = town_edges(n, seed)
+    s, e, lanes, maxmph = town_edges(n, seed, **shape)
     f = flat_from_edges(lon, lat, s, e, lanes, maxmph)
+    f.edge_lanes, f.edge_maxmph = np.asarray(lanes), np.asarray(maxmph)
     N = n * n
     indeg = np.diff(f.node_in_ptr)
     pick = rng.random(N)
@@ -351,7 +352,13 @@ def town_scenario(n, n_agents, horizon=600, seed=1, n_exits=8, signals=0.04, pri
     rank[o] = np.arange(len(il)) - f.node_in_ptr[node_of[o]]
     f.node_in_prio = np.where(f.node_type[node_of] == 2, rank, -1).astype(np.int32)
 
-    exits = rng.choice(N, n_exits, replace=False).astype(np.int64)
+    if exits_on_rim:
+        # an evacuation: the exits are nodes on the rim of the network that most of it can reach
+        ii, jj = np.divmod(np.arange(N), n)
+        rim = np.flatnonzero(((ii == 0) | (ii == n - 1) | (jj == 0) | (jj == n - 1)) & (indeg >= 2))
+        exits = rng.choice(rim, n_exits, replace=False).astype(np.int64)
+    else:
+        exits = rng.choice(N, n_exits, replace=False).astype(np.int64)
     next_link = next_link_tables(f, exits, router)
     dslot = rng.integers(0, n_exits, n_agents)
     origin = np.empty(n_agents, np.int64)
@@ -370,3 +377,68 @@ def routing_graph(f):
     links, queue_class.py:123): edge k = real link N + k, weight = fft."""
     from . import sp_interface
     return sp_interface.from_arrays(f.edge_start, f.edge_end, f.edge_fft, max_vertex_id=len(f.node_key) - 1)
+
+
+# ---- stand-ins for the two configurations whose inputs the reference does not ship (SURVEY.md 8d) -------------------
+
+def berkeley_standin(router=None, device_routes=False, n_agents=50_000):
+    """BASELINE config 2 (benchmark/profile_berkeley.py: 1,401 ticks, no rerouting; link ids up to 37,806 at
+    model/dta_meso_berkeley.py:92; the OD and network files are not shipped): an OSM-like network of ~38k links on
+    ~15k nodes -- the jittered lattice with 36 % of its streets removed, 8 % one-way, diagonals, hubs, 1-4 lanes --
+    and 50,000 agents leaving over twenty minutes."""
+    return town_scenario(122, n_agents, horizon=1200, seed=21, n_exits=12, router=router, device_routes=device_routes,
+                         drop=0.36, oneway=0.08, diag=0.06, hubs=4, hub_links=8)
+
+
+def butte_standin(router=None, device_routes=True, n_agents=100_000):
+    """BASELINE config 3 (model/dta_meso_butte.py: 18,001 ticks, link ids up to 30,175 at :99; inputs not shipped):
+    ~31k links on ~12k nodes, 100,000 evacuees leaving over two hours for six exits on the rim."""
+    return town_scenario(110, n_agents, horizon=7200, seed=31, n_exits=6, router=router, device_routes=device_routes,
+                         exits_on_rim=True, drop=0.36, oneway=0.08, diag=0.06, hubs=3, hub_links=8)
+
+
+def butte_closure_schedule(f, seed=7, last_fire_tick=340 * 60, fire_share=0.005, p_close=0.15, reopen_after=3600):
+    """The closure schedule of model/dta_meso_butte.py:56-115 with the fire raster replaced by host draws (SURVEY.md
+    8d): every 300 s until t = 20,400 the fire reaches 0.5 % of the residential links (here: one-lane links); a link
+    it reaches for the first time burns, and with probability 0.15 it is closed to newcomers together with its
+    opposite link, to reopen 3,600 s later (:111-115; the reopening acts on the link model of the following second);
+    three timed closures of arterials (two, two and eight links with three or more lanes) at 1,800 / 3,600 / 10,800 s
+    stay for good (:88-101).  Returns [(tick, link index, closed)] sorted by tick -- the input of
+    sq_set_closure_schedule and of the host paths it is compared with."""
+    rng = np.random.default_rng(seed)
+    N = len(f.node_key)
+    real = np.arange(N, len(f.link_end_node))
+    lanes = np.asarray(f.link_lanes_floor)
+    residential = real[lanes[real] == 1]
+    arterial = real[lanes[real] >= 3]
+    rev = np.asarray(f.link_reverse)
+    burnt = np.zeros(len(f.link_end_node), bool)
+    forever = np.zeros(len(f.link_end_node), bool)
+    ev = []
+    timed = {1800: 2, 3600: 2, 10800: 8}
+    picks = rng.choice(arterial, sum(timed.values()), replace=False)
+    k = 0
+    timed_links = {}
+    for t, cnt in timed.items():
+        timed_links[t] = picks[k:k + cnt]
+        k += cnt
+    for t in range(0, last_fire_tick + 1, 300):
+        for l in rng.choice(residential, max(1, int(fire_share * len(residential))), replace=False):
+            if burnt[l]:
+                continue
+            burnt[l] = True
+            opp = rev[l]
+            if opp >= 0:
+                burnt[opp] = True
+            if rng.random() < p_close:
+                for x in ([l] if opp < 0 else [l, opp]):
+                    if not forever[x]:
+                        ev.append((t, int(x), 1))
+                        ev.append((t + reopen_after + 1, int(x), 0))
+        if t in timed_links:
+            for x in timed_links[t]:
+                forever[x] = True
+                ev.append((t, int(x), 1))
+    # a timed closure wins over a later reopening of the same link
+    ev = [e for e in ev if not (e[2] == 0 and forever[e[1]])]
+    return sorted(ev, key=lambda e: e[0])
