@@ -35,9 +35,22 @@ TICK_HORIZON = 7_200
 REROUTE_FREQ = 60          # BASELINE.json config 4 / north_star: reroute every 60 s
 WEIGHT_FREQ = 100          # run_traffic_simulation.py:83
 SHELTER_AFTER = 3 * 3600   # run_traffic_simulation.py:103
-# dram__bytes_read.sum + dram__bytes_write.sum of sssp_warp_kernel per tree, from the committed ncu --set full capture
-# (profiles/); None until measured for the current kernel
-SSSP_TRAFFIC_PER_TREE = 2_147_000   # profiles/r1c_sssp_warp_full_ncu.txt: (1.032 + 3.365) GB over 2048 trees
+# roofline.traffic comes from this round's own `ncu --set full` capture: tools/make_profile_summary.py writes
+# dram__bytes_read.sum + dram__bytes_write.sum per launch (per tree / per tick) and the file they came from into
+# profiles/traffic.json; with no capture the field is null.
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "traffic.json")
+
+
+def measured_traffic(kind):
+    try:
+        return json.load(open(TRAFFIC_FILE)).get(kind)
+    except Exception:
+        return None
+
+
+def sssp_workload_name(n, E, V):
+    """The same string in both arms (the driver compares config.workload of `ours` and `reference`)."""
+    return f"config 5: batched SSSP reroute sweep, {n}x{n} grid ({E} links, {V} nodes), full trees + canonical predecessors"
 
 
 def measured_peaks():
@@ -154,60 +167,99 @@ def flat_nbytes(f):
     return int(sum(v.nbytes for v in f.as_dict().values()))
 
 
-def make_tick_sim(flat, stream=None):
-    """Config 4 as the drivers run it: every agent rerouted each REROUTE_FREQ s (staggered by id) on edge weights
-    refreshed from the queue lengths every WEIGHT_FREQ s, give-up rule after 3 h on a link -- all on the device."""
+def tick_cases(args):
+    """The three tick workloads: BASELINE.json configs 4 (headline), 2 and 3 (stand-ins of SURVEY.md 8d: the reference
+    ships neither the Berkeley nor the Butte inputs)."""
+    c4 = {"key": "tick", "name": f"config 4: {args.tick_grid}x{args.tick_grid} grid", "ticks": args.tick_ticks,
+          "flat": lambda: synth.grid_scenario(args.tick_grid, args.tick_agents, horizon=TICK_HORIZON, seed=1, device_routes=True),
+          "flat_cpu": lambda: synth.grid_scenario(args.tick_grid, args.tick_agents, horizon=TICK_HORIZON, seed=1),
+          "router": (REROUTE_FREQ, WEIGHT_FREQ), "rules": None, "closures": False, "shelter": SHELTER_AFTER,
+          "window": args.cpu_window,
+          "what": f"every agent rerouted each {REROUTE_FREQ} s on weights refreshed every {WEIGHT_FREQ} s (8 reverse trees per "
+                  f"refresh), give-up after {SHELTER_AFTER} s on a link; all on the device",
+          "cpu_note": "routes fixed at t=0, no rerouting"}
+    c2 = {"key": "tick_c2", "name": "config 2: Berkeley stand-in (OSM-like network, signal + priority nodes)", "ticks": 1401,
+          "flat": lambda: synth.berkeley_standin(), "flat_cpu": None,
+          "router": None, "rules": None, "closures": False, "shelter": SHELTER_AFTER, "window": 1401,
+          "what": "benchmark/profile_berkeley.py:144: ticks 0..1400, routes fixed at t=0, no rerouting",
+          "cpu_note": "the same run (no rerouting in this configuration)"}
+    c3 = {"key": "tick_c3", "name": "config 3: Butte stand-in (evacuation to six exits)", "ticks": 18001,
+          "flat": lambda: synth.butte_standin(device_routes=True), "flat_cpu": lambda: synth.butte_standin(device_routes=False),
+          "router": (REROUTE_FREQ, WEIGHT_FREQ), "rules": (2.0, 10), "closures": True, "shelter": 9000, "window": 1800,
+          "what": f"model/dta_meso_butte.py: rerouting every {REROUTE_FREQ} s on weights refreshed every {WEIGHT_FREQ} s, shelter_a2 "
+                  "when a reroute more than doubles the trip, reroute upon closure (stagger 10), closure schedule of :56-115 "
+                  "(fire closures every 300 s with p = 0.15, reopening after 3,600 s, three timed arterial closures) as a device "
+                  "event table, give-up after 9,000 s; all on the device, no host call per tick",
+          "cpu_note": "routes fixed at t=0, no rerouting, no closures"}
+    return [c4] if args.no_configs23 else [c4, c2, c3]
+
+
+def make_tick_sim(flat, case, stream=None):
+    """A workload as the drivers run it, all on the device (see tick_cases)."""
     from spatial_queue_b200.tick import DeviceSim
-    sim = DeviceSim(flat, seed=7, routes_from_router=True)
+    sim = DeviceSim(flat, seed=7, routes_from_router=case["router"] is not None)
     if stream is not None:
         sim.set_stream(stream)
-    sim.attach_router(synth.routing_graph(flat), flat, reroute_freq=REROUTE_FREQ, weight_freq=WEIGHT_FREQ)
-    sim.set_shelter_after(SHELTER_AFTER)
+    if case["router"]:
+        sim.attach_router(synth.routing_graph(flat), flat, reroute_freq=case["router"][0], weight_freq=case["router"][1])
+    if case["rules"]:
+        sim.set_reroute_rules(*case["rules"])
+    if case["closures"]:
+        ev = synth.butte_closure_schedule(flat)
+        sim.set_closure_schedule([e[0] for e in ev], [e[1] for e in ev], [e[2] for e in ev])
+    sim.set_shelter_after(case["shelter"])
     return sim
 
 
-def run_tick_gpu(args, torch, peak):
+def run_tick_gpu(case, args, torch, peak):
     t0 = time.perf_counter()
-    flat = synth.grid_scenario(args.tick_grid, args.tick_agents, horizon=TICK_HORIZON, seed=1, device_routes=True)
+    flat = case["flat"]()
     build_s = time.perf_counter() - t0
     L = len(flat.link_end_node)
+    ticks, window = case["ticks"], min(case["window"], case["ticks"])
     stream = torch.cuda.current_stream().cuda_stream
     res = {}
     # device-resident run: state already in HBM when the clock starts
-    warm = make_tick_sim(flat, stream)                   # throwaway instance: first-launch costs, cold caches
+    warm = make_tick_sim(flat, case, stream)             # throwaway instance: first-launch costs, cold caches
     warm.run(0, 256); warm.sync(); warm.close()
     best = None
     for rep in range(max(1, args.tick_reps)):
-        sim = make_tick_sim(flat, stream)
+        sim = make_tick_sim(flat, case, stream)
         sim.sync()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        evw = torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        sim.run(0, args.cpu_window)
-        evw.record()
-        sim.run(args.cpu_window, args.tick_ticks - args.cpu_window)
-        ev1.record()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record()
+        sim.run(0, window)
+        ev[1].record()
+        cw = sim.counters()                              # the device's own counters at the window boundary (syncs)
+        ev[2].record()
+        if ticks > window:
+            sim.run(window, ticks - window)
+        ev[3].record()
         sim.sync()
-        ms = ev0.elapsed_time(ev1)
+        ms_window = ev[0].elapsed_time(ev[1])
+        ms = ms_window + ev[2].elapsed_time(ev[3])
         c = sim.counters()
         if best is None or ms < best[0]:
-            best = (ms, ev0.elapsed_time(evw), c)
+            best = (ms, ms_window, c, cw)
         if rep + 1 < max(1, args.tick_reps):
             sim.close()
-    ms, ms_window, c = best
+    ms, ms_window, c, cw = best
     res["value"] = c["agent_steps"] / (ms / 1e3)
-    res["ms_per_tick"] = ms / args.tick_ticks
+    res["ms_per_tick"] = ms / ticks
     res["counters"] = c
     nbytes = tick_bytes(c, L)
+    tr = measured_traffic(case["key"])
     res["roofline"] = {"bound": "hbm", "achieved": nbytes / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
-                       "traffic": None, "bytes_per_tick": nbytes / max(c["ticks"], 1)}
+                       "traffic": tr["bytes_per_tick"] if tr else None, "traffic_source": tr["source"] if tr else None,
+                       "bytes_per_tick": nbytes / max(c["ticks"], 1)}
     res["roofline"]["frac"] = res["roofline"]["achieved"] / peak
     arrive = sim.agent_state()["arrive_tick"]
+    res["stopped"] = {k: v for k, v in sim.summary().items() if k in ("arrive", "shelter_p", "shelter_a1", "shelter_a2", "closed_links")}
     sim.close()
     # end to end: host arrays in, full run, arrival ticks + link state out
     t0 = time.perf_counter()
-    sim = make_tick_sim(flat)
-    sim.run(0, args.tick_ticks)
+    sim = make_tick_sim(flat, case)
+    sim.run(0, ticks)
     ag = sim.agent_state()
     ls = sim.link_state()
     wall = time.perf_counter() - t0
@@ -217,11 +269,25 @@ def run_tick_gpu(args, torch, peak):
     res["e2e"] = {"value": c2["agent_steps"] / wall, "unit": "agent-steps/s", "wall_s": wall,
                   "h2d_bytes_per_step": flat_nbytes(flat),
                   "d2h_bytes_per_step": int(sum(v.nbytes for v in ag.values()) + sum(v.nbytes for v in ls.values()))}
-    res["window_ticks"] = args.cpu_window
+    res["window_ticks"] = window
     res["window_ms"] = ms_window
+    res["window_agent_steps"] = cw["agent_steps"]
     res["build_s"] = build_s
     res["arrived"] = int((arrive >= 0).sum())
     return res, flat
+
+
+def python_reference_note():
+    """The Python reference itself, timed in the build container (tools/time_reference_tick.py; it cannot travel to the
+    GPU box): one line for the cpu_baseline sample text."""
+    try:
+        rows = [json.loads(l) for l in open(os.path.join(ROOT, "profiles", "r2_reference_tick_timing.jsonl")) if l.startswith("{")]
+        g = [r for r in rows if r["case"].startswith("50x50")][0]
+        return (f"; the unmodified Python reference on one core of the build container: {g['on_link_agent_steps_per_s']:.3g} "
+                f"on-link agent-steps/s ({g['s_per_tick']:.3f} s/tick) on a 50x50 grid with 20k agents "
+                f"(profiles/r2_reference_tick_timing.jsonl)")
+    except Exception:
+        return ""
 
 
 def run_tick_cpu(flat, ticks):
@@ -264,8 +330,7 @@ def reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": "sssp_trees_per_s", "value": value, "unit": "trees/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * cores * per_core / value,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid",
-                       "sample": sample},
+            "config": {"workload": sssp_workload_name(args.sssp_grid, len(s), V), "sample": sample},
             "cpu_baseline": {"value": value, "unit": "trees/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "trees/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -279,6 +344,65 @@ def reference_arm(args, rank, world):
                         "cpu_baseline": {"value": rate, "unit": "agent-steps/s", "cores": 1, "kind": "port",
                                          "sample": f"ticks 0..{args.cpu_window - 1} of config 4 ({wall:.1f} s)"}}
     print(json.dumps(line), flush=True)
+
+
+def run_sweep(args, torch, dist, g, V, E, rank, world, peak):
+    """BASELINE config 5 as the sweep it is named as: B = 1k ... 64k TOTAL origins, split over the ranks (strong scaling:
+    rank r computes shard_bounds(B, r, world)), full trees + predecessors per step, tables gathered (every rank, or
+    --gather-to).  One point per B: trees/s over all ranks (max over ranks of the device time), which kernel ran."""
+    from spatial_queue_b200 import shard
+    points = []
+    bytes_per_tree = 20 * E + 24 * V
+    compact = world > 1 and not args.no_gather
+    g.set_parent_format(1 if compact else 0)
+    pdt = torch.uint8 if compact else torch.int32
+    for Btot in (1024, 2048, 4096, 8192, 16384, 32768, 65536):
+        lo, hi = shard.shard_bounds(Btot, rank, world)
+        n = hi - lo
+        rows = max(shard.shard_bounds(Btot, r, world)[1] - shard.shard_bounds(Btot, r, world)[0] for r in range(world))
+        perm = np.random.default_rng(4321).permutation(V)
+        o_dev = torch.from_numpy(perm[(np.arange(lo, hi)) % V].astype(np.int32)).cuda()
+        dist_dev = torch.empty((n, V), dtype=torch.float64, device="cuda")
+        par_dev = torch.empty((rows, V), dtype=pdt, device="cuda")
+        gathered = None
+        if compact:
+            gathered = torch.empty((world * rows, V), dtype=pdt, device="cuda") if (args.gather_to < 0 or rank == args.gather_to) else None
+
+        def step():
+            g.sssp_batch_device(o_dev, dist_dev, par_dev[:n])
+            if compact:
+                if args.gather_to < 0:
+                    dist.all_gather_into_tensor(gathered, par_dev)
+                else:
+                    parts = list(gathered.split(rows)) if rank == args.gather_to else None
+                    dist.gather(par_dev, parts, dst=args.gather_to)
+
+        for _ in range(max(3, args.warmup)):
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.steps
+        if world > 1:
+            tm = torch.tensor([ms], device="cuda")
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            ms = float(tm.item())
+        tps = Btot / (ms / 1e3)
+        n_sm = torch.cuda.get_device_properties(0).multi_processor_count
+        kernel = "group layout (sssp_warp_kernel<grouped>)" if (n >= 2048 and n * 8 >= V) else \
+            ("sssp_warp_kernel" if n >= 6 * n_sm else "sssp_ell_kernel")
+        points.append({"total_origins": Btot, "origins_per_gpu": n, "ms_per_step": ms, "trees_per_s": tps,
+                       "frac_of_one_gpu_roofline": tps * bytes_per_tree / (peak * 1e9) / world, "kernel": kernel})
+        del dist_dev, par_dev, gathered
+        torch.cuda.empty_cache()
+    g.set_parent_format(0)
+    return points
 
 
 def main():
@@ -300,6 +424,9 @@ def main():
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--nccl-gather", action="store_true", help="N > 1: NCCL all-gather instead of copy-engine pushes")
     ap.add_argument("--chunks", type=int, default=4, help="N > 1: pieces the batch is cut into (gather of one overlaps the trees of the next)")
+    ap.add_argument("--gather-to", type=int, default=-1, help="N > 1: push the tables to this rank only (the simulating GPU) instead of to every rank")
+    ap.add_argument("--sweep", action="store_true", help="config 5 as a sweep: 1k..64k total origins split over the ranks (strong scaling)")
+    ap.add_argument("--no-configs23", action="store_true", help="skip the config 2 / 3 tick objects")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0))
@@ -328,6 +455,17 @@ def main():
     g.sync()
     B = args.batch
     bytes_per_tree = 20 * E + 24 * V
+    if args.sweep:
+        pts = run_sweep(args, torch, dist, g, V, E, rank, world, peak)
+        if rank == 0:
+            print(json.dumps({"metric": "sssp_trees_per_s", "unit": "trees/s", "n_gpus": world, "scaling": "strong",
+                              "config": {"workload": sssp_workload_name(args.sssp_grid, E, V),
+                                         "gather": "none" if world == 1 or args.no_gather else
+                                         ("NCCL gather to rank %d" % args.gather_to if args.gather_to >= 0 else "NCCL all-gather on every rank")},
+                              "steps": args.steps, "sweep": pts}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     dist_dev = torch.empty((B, V), dtype=torch.float64, device="cuda")
     # N > 1: the int32 predecessor (next-hop) tables of every rank are all-gathered to every rank.  The batch is
     # cut into chunks; the gather of chunk k runs on a side stream while chunk k+1 is computed, and the tables
@@ -351,7 +489,7 @@ def main():
             try:
                 from spatial_queue_b200.shard import PeerTables
                 peer = PeerTables(n_chunks, cb, V, pdt)
-                gather_kind = "copy-engine pushes into symmetric memory"
+                gather_kind = "copy-engine pushes into symmetric memory" + (f", to rank {args.gather_to} only" if args.gather_to >= 0 else "")
             except Exception as ex:       # no symmetric memory on this box: NCCL collective instead
                 if rank == 0:
                     print(f"symmetric memory unavailable ({type(ex).__name__}: {ex}); using the NCCL all-gather", file=sys.stderr)
@@ -379,7 +517,7 @@ def main():
                 done = torch.cuda.Event()
                 done.record(cur)
                 if peer is not None:
-                    peer.push(c, par_dev[sl], after=done)
+                    peer.push(c, par_dev[sl], after=done, to=args.gather_to if args.gather_to >= 0 else None)
                 else:
                     comm_stream.wait_event(done)
                     with torch.cuda.stream(comm_stream):
@@ -432,35 +570,58 @@ def main():
         sums = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(sums, mine)
         ok = True
-        for c in range(n_chunks):
-            tbl = peer.table(c) if peer is not None else gathered[c]
-            for r in range(world):
-                ok = ok and int(tbl[r * cb:(r + 1) * cb].to(torch.int64).sum().item()) == int(sums[r][c].item())
+        if args.gather_to < 0 or peer is None or rank == args.gather_to:
+            for c in range(n_chunks):
+                tbl = peer.table(c) if peer is not None else gathered[c]
+                for r in range(world):
+                    ok = ok and int(tbl[r * cb:(r + 1) * cb].to(torch.int64).sum().item()) == int(sums[r][c].item())
         flag = torch.tensor([1 if ok else 0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         gather_ok = bool(flag.item())
     if compact:
         g.set_parent_format(0)
-    # ---- e2e through the host-buffer C ABI (origins in host memory -> dist + parent in host memory) -------------
-    e2e = None
+    # ---- e2e through the host-buffer C ABI: host origins in, host next-hop tables out ---------------------------------
+    # `e2e` = sp_sssp_batch_codes: the whole batch, predecessors as one-byte in-edge codes in page-locked host memory
+    # (50 KB per tree; a consumer holding the graph follows the codes directly, sp_decode_parents_host gives vertex ids).
+    # `e2e_full` = sp_sssp_batch: f64 distances + int32 predecessors (602 KB per tree: PCIe-bound), 4,096 trees.
+    e2e = e2e_full = None
     if rank == 0 or world > 1:
-        # host origins in, page-locked host distance + predecessor arrays out (the copies are inside the call)
-        eb = min(B, 4096)
-        oh = origins_for(rank, eb, V, step=7)
-        dh, ph = spi.pinned_empty((eb, V), np.float64), spi.pinned_empty((eb, V), np.int32)
-        g.sssp_batch(oh[:256], out=(dh[:256], ph[:256]))
+        oh = origins_for(rank, B, V, step=7)
+        ch = spi.pinned_empty((B, V), np.uint8)
+        g.sssp_batch_codes(oh[:2368], out=(None, ch[:2368]))
+        g.sssp_batch_codes(oh, out=(None, ch))
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
         reps = 2
         for _ in range(reps):
-            g.sssp_batch(oh, out=(dh, ph))
+            g.sssp_batch_codes(oh, out=(None, ch))
         wall = time.perf_counter() - t0
-        e2e_val = world * eb * reps / wall
         if world > 1:
             tw = torch.tensor([wall], device="cuda")
             dist.all_reduce(tw, op=dist.ReduceOp.MAX)
-            e2e_val = world * eb * reps / float(tw.item())
-        e2e = {"value": e2e_val, "unit": "trees/s", "h2d_bytes_per_step": int(oh.nbytes),
-               "d2h_bytes_per_step": int(dh.nbytes + ph.nbytes), "trees_per_call": eb}
+            wall = float(tw.item())
+        e2e = {"value": world * B * reps / wall, "unit": "trees/s", "h2d_bytes_per_step": int(oh.nbytes),
+               "d2h_bytes_per_step": int(ch.nbytes), "trees_per_call": B,
+               "call": "sp_sssp_batch_codes (host origins in, one-byte predecessor codes in page-locked host memory out)"}
+        del ch
+        eb = min(B, 4096)
+        dh, ph = spi.pinned_empty((eb, V), np.float64), spi.pinned_empty((eb, V), np.int32)
+        g.sssp_batch(oh[:256], out=(dh[:256], ph[:256]))
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            g.sssp_batch(oh[:eb], out=(dh, ph))
+        wall = time.perf_counter() - t0
+        if world > 1:
+            tw = torch.tensor([wall], device="cuda")
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+            wall = float(tw.item())
+        e2e_full = {"value": world * eb * reps / wall, "unit": "trees/s", "h2d_bytes_per_step": int(oh[:eb].nbytes),
+                    "d2h_bytes_per_step": int(dh.nbytes + ph.nbytes), "trees_per_call": eb,
+                    "call": "sp_sssp_batch (f64 distances + int32 predecessors, 602 KB per tree over PCIe)"}
+        del dh, ph
 
     # ---- e2e of the call the reference's agents make: get_path = distance(destin) + route(destin) per agent ----------
     # (sp_route_batch: host origins + destinations in, host distances + paths out; one tree per origin on the device)
@@ -489,21 +650,25 @@ def main():
     line = None
     if rank == 0:
         achieved = bytes_per_tree * B / (kernel_ms / 1e3) / 1e9
+        tr = measured_traffic("sssp")
         line = {"metric": "sssp_trees_per_s", "value": value, "unit": "trees/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"config 5: batched SSSP reroute sweep, {args.sssp_grid}x{args.sssp_grid} grid "
-                                       f"({E} links, {V} nodes), {B} origins per GPU per step, full trees + canonical "
-                                       f"predecessors" + (f", one-byte next-hop tables gathered on every rank in {n_chunks} chunks ({gather_kind}) "
-                                                          f"overlapped with the next chunk's trees" if gather_kind else ""),
+                "config": {"workload": sssp_workload_name(args.sssp_grid, E, V),
+                           "batch_per_gpu": B,
+                           "gather": (f"one-byte next-hop tables in {n_chunks} chunks ({gather_kind}), overlapped with the next "
+                                      f"chunk's trees") if gather_kind else None,
                            "gather_verified": gather_ok,
+                           "e2e_call": "sp_sssp_batch_codes: host origins in, one-byte predecessor codes (50 KB per tree) in "
+                                       "page-locked host memory out; e2e_full = f64 distances + int32 predecessors",
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": SSSP_TRAFFIC_PER_TREE * B if SSSP_TRAFFIC_PER_TREE else None,
-                             "kernel": "sssp_warp_kernel (+ sssp_parent_kernel, both inside kernel_ms)", "kernel_ms": kernel_ms,
+                             "traffic": tr["bytes_per_tree"] * B if tr else None,
+                             "traffic_source": tr["source"] if tr else None,
+                             "kernel": "tree kernel + predecessor / un-interleave pass, both inside kernel_ms", "kernel_ms": kernel_ms,
                              "bytes_per_tree": bytes_per_tree, "peak_source": peak_src},
-                "e2e": e2e, "e2e_routes": e2e_routes, "gpu_launches": int(launches), "clocks": clocks}
+                "e2e": e2e, "e2e_full": e2e_full, "e2e_routes": e2e_routes, "gpu_launches": int(launches), "clocks": clocks}
 
     # ---- HP-1 + CPU baselines: single GPU, rank 0 ----------------------------------------------------------------
     if rank == 0 and world == 1:
@@ -525,30 +690,29 @@ def main():
                 line["cpu_baseline"] = {"value": 256 / (time.perf_counter() - t1), "unit": "trees/s", "cores": 1,
                                         "kind": "port", "sample": "256 full trees, oracle/sssp_oracle.c"}
         if not args.no_tick:
-            l0 = _lib.lib().sq_kernel_launches()
-            tick, flat = run_tick_gpu(args, torch, peak)
-            tick_line = {"metric": "agent_steps_per_s", "value": tick["value"], "unit": "agent-steps/s",
-                         "ms_per_tick": tick["ms_per_tick"], "dtype": "i32 state + f64 capacities",
-                         "config": {"workload": f"config 4: {args.tick_grid}x{args.tick_grid} grid, "
-                                                f"{len(flat.link_end_node)} links, {args.tick_agents} agents over "
-                                                f"{TICK_HORIZON} s, {args.tick_ticks} ticks, every agent rerouted each {REROUTE_FREQ} s on "
-                                                f"weights refreshed every {WEIGHT_FREQ} s (8 reverse trees per refresh), "
-                                                f"give-up after {SHELTER_AFTER} s on a link; all on the device"},
-                         "counters": tick["counters"], "arrived": tick["arrived"], "roofline": tick["roofline"],
-                         "e2e": tick["e2e"], "gpu_launches": int(_lib.lib().sq_kernel_launches() - l0)}
-            if not args.no_cpu:
-                # the C port replays the tick only: routes fixed at t = 0 (the reference's per-agent Dijkstra
-                # would come on top: 16.7k reroutes per tick at this size)
-                flat_cpu = synth.grid_scenario(args.tick_grid, args.tick_agents, horizon=TICK_HORIZON, seed=1)
-                rate, wall, c = run_tick_cpu(flat_cpu, args.cpu_window)
-                gpu_same = c["agent_steps"] / ((tick["window_ms"]) / 1e3)
-                tick_line["cpu_baseline"] = {"value": rate, "unit": "agent-steps/s", "cores": 1, "kind": "port",
-                                             "sample": f"ticks 0..{args.cpu_window - 1} of the same network and demand, "
-                                                       f"routes fixed at t=0, no rerouting ({wall:.1f} s, "
-                                                       f"oracle/tick_oracle.c)",
-                                             "gpu_same_window": gpu_same}
-            line["tick"] = tick_line
-            line["gpu_launches"] += tick_line["gpu_launches"]
+            for case in tick_cases(args):
+                l0 = _lib.lib().sq_kernel_launches()
+                tick, flat = run_tick_gpu(case, args, torch, peak)
+                tick_line = {"metric": "agent_steps_per_s", "value": tick["value"], "unit": "agent-steps/s",
+                             "ms_per_tick": tick["ms_per_tick"], "dtype": "i32 state + f64 capacities",
+                             "config": {"workload": f"{case['name']}, {len(flat.link_end_node)} links (source links included), "
+                                                    f"{len(flat.agent_key)} agents, {case['ticks']} ticks; {case['what']}"},
+                             "counters": tick["counters"], "arrived": tick["arrived"], "stopped": tick["stopped"],
+                             "roofline": tick["roofline"], "e2e": tick["e2e"],
+                             "gpu_launches": int(_lib.lib().sq_kernel_launches() - l0)}
+                if not args.no_cpu:
+                    # the C port replays the tick only (the reference's per-agent Dijkstra would come on top)
+                    flat_cpu = case["flat_cpu"]() if case["flat_cpu"] else flat
+                    rate, wall, c = run_tick_cpu(flat_cpu, tick["window_ticks"])
+                    tick_line["cpu_baseline"] = {
+                        "value": rate, "unit": "agent-steps/s", "cores": 1, "kind": "port",
+                        "sample": f"ticks 0..{tick['window_ticks'] - 1} of the same network and demand, {case['cpu_note']} "
+                                  f"({wall:.1f} s, oracle/tick_oracle.c){python_reference_note()}",
+                        # the device's own agent-steps over the same ticks / its own time for them
+                        "gpu_same_window": tick["window_agent_steps"] / (tick["window_ms"] / 1e3),
+                        "gpu_window_agent_steps": tick["window_agent_steps"], "cpu_window_agent_steps": c["agent_steps"]}
+                line[case["key"]] = tick_line
+                line["gpu_launches"] += tick_line["gpu_launches"]
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

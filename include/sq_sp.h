@@ -74,6 +74,14 @@ int sp_sssp_batch(Graph* graph, const int* origins, int n, double* dist_out, int
 /* reverse != 0: trees on the reversed graph (distances to, and next vertex towards, each origin). */
 int sp_sssp_batch_ex(Graph* graph, const int* origins, int n, double* dist_out, int* parent_out, int reverse);
 
+/* sp_sssp_batch_ex with the predecessors in the compact form of sp_set_parent_format 1: codes_out[n][V], one byte per
+ * vertex = the index of the in-edge (creation order at that vertex; out-edge for reverse trees) that attains the
+ * distance, 255 = none; dist_out may be NULL.  Every consumer that holds the graph can follow the codes directly
+ * (sp_decode_parents_host turns them into vertex ids: parent_out[n][V]).  On config 5 a tree is 50 KB over PCIe instead
+ * of 602 KB, so the call is bound by the tree kernel, not by the link. */
+int sp_sssp_batch_codes(Graph* graph, const int* origins, int n, double* dist_out, unsigned char* codes_out, int reverse);
+int sp_decode_parents_host(Graph* graph, const unsigned char* codes, int n, int* parent_out, int reverse);
+
 /* Agent.get_path for a batch of agents (queue_class.py:491-512 / model/queue_class.py:491-512: g.dijkstra(origin,
  * destin), sp.distance(destin), sp.route(destin)): for every pair k the distance origins[k] -> dests[k] (DBL_MAX
  * when there is no path, like distance()) and the path as a vertex sequence origins[k], ..., dests[k] -- what

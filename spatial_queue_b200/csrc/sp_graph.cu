@@ -2340,7 +2340,12 @@ int sp_sssp_batch(Graph* g, const int* origins, int n, double* dist_out, int* pa
   return sp_sssp_batch_ex(g, origins, n, dist_out, parent_out, 0);
 }
 
-int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int* parent_out, int reverse) {
+// Host-buffer batches: trees are produced in chunks into two device buffers; while chunk i is computed on one stream,
+// chunk i-1 travels to the host on another.  With page-locked destinations (sp_alloc_host) the copies are asynchronous
+// and the call runs at PCIe speed; pageable destinations still work, the driver then stages every copy.
+// codes != 0: predecessors leave as one-byte in-edge codes (parent_out is then unsigned char[n][V]): 50 KB per tree on
+// config 5 instead of 200 KB, and with dist_out == NULL nothing else crosses PCIe.
+static int g_batch_host(SqGraph* g, const int* origins, int n, double* dist_out, void* parent_out, int reverse, int codes) {
   if (!g || (!origins && n > 0)) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch: null argument");
   if (n <= 0) return SQ_OK;
   if (int rc = g_build_and_upload(g)) return rc;
@@ -2351,21 +2356,23 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
     g->origins_cap = n;
   }
   SQ_CUDA_TRY(cudaMemcpy(g->d_origins, origins, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
-  // Trees are produced in chunks into two device buffers; while chunk i is computed on one stream, chunk i-1
-  // travels to the host on another.  With page-locked destinations (sp_alloc_host) the copies are asynchronous
-  // and the call runs at PCIe speed; pageable destinations still work, the driver then stages every copy.
-  const size_t per_tree = V * (sizeof(u64) + sizeof(int));
+  const size_t psize = codes ? 1 : sizeof(int);
+  const size_t per_tree = V * ((dist_out ? sizeof(u64) : 0) + (parent_out ? psize : 0));
   size_t chunk = std::max<size_t>(1, std::min<size_t>((size_t)n, ((size_t)1 << 29) / std::max<size_t>(per_tree, 1)));
+  // at least four chunks on large batches (the copy of one hides behind the trees of the next), but never so small that
+  // a chunk leaves SMs idle
+  chunk = std::min(chunk, std::max<size_t>(((size_t)n + 3) / 4, 2368));
   if ((size_t)n > chunk) chunk = std::max<size_t>(chunk, 64);
   if (dist_out && g->dist_buf_elems < 2 * chunk * V) {
     cudaFree(g->d_dist_buf); g->d_dist_buf = nullptr;
     SQ_CUDA_TRY(cudaMalloc(&g->d_dist_buf, sizeof(u64) * 2 * chunk * V));
     g->dist_buf_elems = 2 * chunk * V;
   }
-  if (parent_out && g->parent_buf_elems < 2 * chunk * V) {
+  const size_t pelems = (2 * chunk * V * psize + sizeof(int) - 1) / sizeof(int);   // in ints
+  if (parent_out && g->parent_buf_elems < pelems) {
     cudaFree(g->d_parent_buf); g->d_parent_buf = nullptr;
-    SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * 2 * chunk * V));
-    g->parent_buf_elems = 2 * chunk * V;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * pelems));
+    g->parent_buf_elems = pelems;
   }
   if (int rc = g_ensure_streams(g)) return rc;
   const bool pinned = is_pinned_host(dist_out) && is_pinned_host(parent_out);
@@ -2374,11 +2381,11 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
     const int m = (int)std::min(chunk, (size_t)n - off);
     const int b = k & 1;
     u64* dbuf = dist_out ? g->d_dist_buf + (size_t)b * chunk * V : nullptr;
-    int* pbuf = parent_out ? g->d_parent_buf + (size_t)b * chunk * V : nullptr;
+    unsigned char* pbuf = parent_out ? reinterpret_cast<unsigned char*>(g->d_parent_buf) + (size_t)b * chunk * V * psize : nullptr;
     if (k >= 2) SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_compute, g->ev_copied[b], 0));  // buffer b is free again
     const int fmt = g->parent_format;
-    g->parent_format = 0;  // host batches always return vertex ids
-    const int rc_run = g_run_batch_device(g, g->d_origins + off, m, dbuf, pbuf, g->s_compute, reverse != 0);
+    g->parent_format = codes ? 1 : 0;
+    const int rc_run = g_run_batch_device(g, g->d_origins + off, m, dbuf, reinterpret_cast<int*>(pbuf), g->s_compute, reverse != 0);
     g->parent_format = fmt;
     if (rc_run) return rc_run;
     SQ_CUDA_TRY(cudaEventRecord(g->ev_done[b], g->s_compute));
@@ -2387,13 +2394,42 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
     if (dist_out)
       SQ_CUDA_TRY(cudaMemcpyAsync(dist_out + off * V, dbuf, sizeof(u64) * (size_t)m * V, cudaMemcpyDeviceToHost, g->s_copy));
     if (parent_out)
-      SQ_CUDA_TRY(cudaMemcpyAsync(parent_out + off * V, pbuf, sizeof(int) * (size_t)m * V, cudaMemcpyDeviceToHost, g->s_copy));
+      SQ_CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<unsigned char*>(parent_out) + off * V * psize, pbuf, psize * (size_t)m * V,
+                                  cudaMemcpyDeviceToHost, g->s_copy));
     SQ_CUDA_TRY(cudaEventRecord(g->ev_copied[b], g->s_copy));
   }
   SQ_CUDA_TRY(cudaStreamSynchronize(g->s_compute));
   SQ_CUDA_TRY(cudaStreamSynchronize(g->s_copy));
   g->last_stats[0] = n;
   return g_fetch_stats(g);
+}
+
+int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int* parent_out, int reverse) {
+  return g_batch_host(g, origins, n, dist_out, parent_out, reverse, 0);
+}
+
+int sp_sssp_batch_codes(Graph* g, const int* origins, int n, double* dist_out, unsigned char* codes_out, int reverse) {
+  if (!codes_out) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch_codes: null codes_out");
+  return g_batch_host(g, origins, n, dist_out, codes_out, reverse, 1);
+}
+
+// One-byte in-edge codes -> vertex ids on the host (what sp_decode_parents_device does on the GPU): code c of vertex v
+// is the c-th in-edge of v in creation order (for reverse trees: the c-th out-edge), 255 = none.
+int sp_decode_parents_host(Graph* g, const unsigned char* codes, int n, int* parent_out, int reverse) {
+  if (!g || !codes || !parent_out) return sq::set_error(SQ_ERR_ARG, "sp_decode_parents_host: null argument");
+  if (int rc = g_build_and_upload(g)) return rc;
+  const std::vector<int>& rp = reverse ? g->h_rp : g->h_rrp;
+  const std::vector<EdgeRec>& adj = reverse ? g->h_adj : g->h_radj;
+  const size_t V = (size_t)g->V;
+  for (int i = 0; i < n; ++i) {
+    const unsigned char* c = codes + (size_t)i * V;
+    int* p = parent_out + (size_t)i * V;
+    for (size_t v = 0; v < V; ++v) {
+      const int code = c[v];
+      p[v] = (code == 255 || rp[v] + code >= rp[v + 1]) ? -1 : adj[(size_t)rp[v] + code].v;
+    }
+  }
+  return SQ_OK;
 }
 
 int sp_route_batch(Graph* g, const int* origins, const int* dests, int n, double* dist_out, long long* route_off_out,

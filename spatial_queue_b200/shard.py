@@ -47,6 +47,33 @@ def all_gather_tables(local, n_total, dist=None, group=None):
     return torch.cat(parts, 0)
 
 
+def gather_tables_to(local, n_total, dst=0, dist=None, group=None):
+    """The north-star form of the exchange: the tables go to the SIMULATING rank only (`dst`), which gets the
+    [n_total, V] table in rank order; every other rank gets None.  Same padding rule as all_gather_tables."""
+    import torch
+    import torch.distributed as tdist
+    dist = dist or tdist
+    world = dist.get_world_size(group)
+    if world == 1:
+        return local
+    rank = dist.get_rank(group)
+    V = local.shape[1]
+    rows = max(shard_bounds(n_total, r, world)[1] - shard_bounds(n_total, r, world)[0] for r in range(world))
+    send = local
+    if local.shape[0] != rows:
+        send = torch.empty((rows, V), dtype=local.dtype, device=local.device)
+        send[: local.shape[0]] = local
+    parts = [torch.empty((rows, V), dtype=local.dtype, device=local.device) for _ in range(world)] if rank == dst else None
+    dist.gather(send.contiguous(), parts, dst=dst, group=group)
+    if rank != dst:
+        return None
+    out = []
+    for r in range(world):
+        lo, hi = shard_bounds(n_total, r, world)
+        out.append(parts[r][: hi - lo])
+    return torch.cat(out, 0)
+
+
 class PeerTables:
     """All-gather of next-hop tables without SMs: every rank owns a [slots, world * rows, V] buffer in symmetric
     memory (torch.distributed._symmetric_memory: the peers' buffers are mapped into this process over
@@ -72,13 +99,17 @@ class PeerTables:
                       for r in range(self.world)]
         self.stream = torch.cuda.Stream()
 
-    def push(self, slot, src, after=None):
-        """Copy `src` ([rows, V], this rank's finished chunk) into row block `rank` of slot `slot` on every rank."""
+    def push(self, slot, src, after=None, to=None):
+        """Copy `src` ([rows, V], this rank's finished chunk) into row block `rank` of slot `slot` on every rank, or,
+        with `to` = a rank, into that rank's table only (the tables are needed where the simulation runs)."""
         import torch
         if after is not None:
             self.stream.wait_event(after)
         lo = self.rank * self.rows
         with torch.cuda.stream(self.stream):
+            if to is not None:
+                self.peers[to][slot, lo: lo + src.shape[0]].copy_(src, non_blocking=True)
+                return
             for k in range(self.world):
                 r = (self.rank + k) % self.world          # start with the own copy, then walk the ring
                 self.peers[r][slot, lo: lo + src.shape[0]].copy_(src, non_blocking=True)

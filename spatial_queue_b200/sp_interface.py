@@ -169,6 +169,28 @@ class Graph:
                                      p.ctypes.data if want_parent else None, 1 if reverse else 0), "sp_sssp_batch")
         return d, p
 
+    def sssp_batch_codes(self, origins, want_dist=False, out=None, reverse=False):
+        """Full trees for `origins` with the predecessors as one-byte in-edge codes (sp_sssp_batch_codes):
+        -> (dist f64[n,V] or None, codes u8[n,V]) in page-locked host memory; `out=(dist or None, codes)` reuses arrays."""
+        o = np.ascontiguousarray(origins, dtype=np.int32)
+        V = self.nvertices
+        if out is not None:
+            d, c = out
+        else:
+            d = pinned_empty((len(o), V), np.float64) if want_dist else None
+            c = pinned_empty((len(o), V), np.uint8)
+        check(lib().sp_sssp_batch_codes(self._h, o.ctypes.data, len(o), d.ctypes.data if d is not None else None,
+                                        c.ctypes.data, 1 if reverse else 0), "sp_sssp_batch_codes")
+        return d, c
+
+    def decode_parents_host(self, codes, reverse=False):
+        """codes u8[n,V] -> parent i32[n,V] on the host (sp_decode_parents_host)."""
+        c = np.ascontiguousarray(codes, dtype=np.uint8)
+        p = np.empty(c.shape, np.int32)
+        check(lib().sp_decode_parents_host(self._h, c.ctypes.data, int(c.shape[0]), p.ctypes.data, 1 if reverse else 0),
+              "sp_decode_parents_host")
+        return p
+
     def route_batch(self, origins, dests):
         """`Agent.get_path` for many agents in one call (queue_class.py:491-512): for every pair the distance
         origin -> destination (DBL_MAX if unreachable) and the path as a vertex sequence.  Returns

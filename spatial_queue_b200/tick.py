@@ -190,7 +190,7 @@ class DeviceSim(_SimBase):
         """include/sq_tick.h sq_get_summary: the drivers' periodic statistics from one 128-byte read-back."""
         o = np.zeros(16, np.int64)
         self._check(self._L.sq_get_summary(self._h, o.ctypes.data), "get_summary")
-        names = ("unloaded", "enroute", "arrive", "shelter_p", "shelter_a1")
+        names = ("unloaded", "enroute", "arrive", "shelter_p", "shelter_a1", "shelter_a2")
         d = {k: int(o[i]) for i, k in enumerate(names)}
         d.update(queued=int(o[8]), running=int(o[9]), congested=int(o[10]), closed_links=int(o[11]), node_moves=int(o[12]),
                  vehicles_left=int(o[13]), links_in_use=int(o[14]), on_closed_links=int(o[15]))

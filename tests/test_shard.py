@@ -33,6 +33,10 @@ def _worker(rank, world, port, n_origins, q):
     mine = shard.shard_origins(origins, rank, world)
     _, parent = osssp.OracleGraph(s, e, w).sssp_batch(mine)
     full = shard.all_gather_tables(torch.from_numpy(parent), len(origins))
+    only0 = shard.gather_tables_to(torch.from_numpy(parent), len(origins), dst=0)
+    assert (only0 is None) == (rank != 0)
+    if rank == 0:
+        assert torch.equal(only0, full)
     q.put((rank, full.numpy().copy()))
     dist.barrier()
     dist.destroy_process_group()

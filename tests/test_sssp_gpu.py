@@ -537,3 +537,23 @@ def test_large_graph_overflow_is_rerun_not_dropped(spi):
     do, po = osssp.OracleGraph(s, e, w).sssp_batch(origins)
     assert d.tobytes() == do.tobytes() and (p == po).all()
     g.free()
+
+
+@pytest.mark.parametrize("reverse", [False, True])
+def test_host_batch_with_one_byte_codes_decodes_to_the_int32_tables(spi, reverse):
+    """sp_sssp_batch_codes (host buffers, 1 byte per vertex over PCIe) + sp_decode_parents_host == sp_sssp_batch's int32
+    predecessor table; distances optional; in-degrees beyond four and exact ties; several chunks."""
+    rng = np.random.default_rng(41)
+    V, E = 2500, 13000
+    s = rng.integers(0, V, E).astype(np.int32)
+    e = rng.integers(0, V, E).astype(np.int32)
+    w = np.round(rng.random(E) * 20.0) + 1.0
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    origins = np.concatenate([rng.integers(0, V, 5000), [-1, V + 3]]).astype(np.int32)
+    d0, p0 = g.sssp_batch(origins, reverse=reverse)
+    d1, c1 = g.sssp_batch_codes(origins, want_dist=True, reverse=reverse)
+    assert d1.tobytes() == d0.tobytes()
+    assert (g.decode_parents_host(c1, reverse=reverse) == p0).all()
+    _, c2 = g.sssp_batch_codes(origins, reverse=reverse)
+    assert (c2 == c1).all()
+    g.free()
