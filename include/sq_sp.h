@@ -163,11 +163,6 @@ int sp_set_group_tuning(Graph* graph, int warps_per_sm, int batch, int prefetch,
  * kernel); 1 = sssp_group_kernel, one warp per group, no atomics and no capacity limits (also what mode 0 falls back
  * to when the graph is too large for the bitmap kernel). */
 int sp_set_group_mode(Graph* graph, int mode, int ring_cap);
-/* How the warp kernel relaxes an edge: 0 = one 64-bit atomicMin whose return value decides the push; 1 = read the
- * head's distance, and only where the candidate is smaller send a RED.MIN without return value (the push follows the
- * value read; a candidate that lost the race leaves a queue entry its hash marks as stale); 2 = read, then atomicMin
- * with return where smaller.  All give identical results. */
-int sp_set_relax_mode(Graph* graph, int mode);
 
 /* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps; default 1024), frontier
  * vertices per step = 8 x ilp (1, 2 or 4; 0 keeps; default 4), CTAs of four warps per SM (0 = default 4, at most

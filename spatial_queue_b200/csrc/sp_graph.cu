@@ -93,7 +93,6 @@ struct TreeParams {
   const int* tord;        // [groups * 8] tree at each sorted position, -1 = padding
   const int* perm;        // caller id -> internal id
   int parent_codes;       // bitmap kernel's own predecessor pass: 1 = one-byte in-edge codes
-  int relax_mode;         // warp kernel: 0 = atomicMin with return, 1 = load + RED.MIN, 2 = load, then atomicMin if better
 };
 
 #define DIST_INF_BITS 0x7FEFFFFFFFFFFFFFull  // DBL_MAX, what the reference leaves in unreached slots
@@ -910,28 +909,12 @@ __global__ void __launch_bounds__(GROUPED ? 256 : 128) sssp_warp_kernel(const Tr
         ndb[j] = (u64)__double_as_longlong(__longlong_as_double((long long)dnow[j]) + __hiloint2double(raw[j].y, raw[j].x));
         old[j] = 0ull;
       }
-      if (p.relax_mode == 0) {
+      // (measured and dropped, profiles/r2c_group_sweep.jsonl: reading the head's distance first and sending a RED.MIN
+      //  without return value only where the candidate is smaller -- 46 % of the relaxations -- is 14 % SLOWER than the
+      //  atomic with return; read + atomicMin where smaller is 5 % slower.  The kernel is not bound by the L2 atomic units.)
 #pragma unroll
-        for (int j = 0; j < ILP; ++j)
-          if (has[j]) old[j] = atomicMin(DA((unsigned)raw[j].z), ndb[j]);
-      } else {
-        // read first, then a fire-and-forget RED.MIN only where the candidate looks better: less than half of the
-        // relaxations improve anything, and a reduction without a return value does not hold the warp.  The value read
-        // may be stale (another lane's RED of this step is still on its way): the RED keeps the minimum regardless, and
-        // an entry pushed for a candidate that lost is recognised as stale by its hash when popped.
-#pragma unroll
-        for (int j = 0; j < ILP; ++j)
-          if (has[j]) old[j] = sq::ld_cg_u64(DA((unsigned)raw[j].z));
-        if (p.relax_mode == 1) {
-#pragma unroll
-          for (int j = 0; j < ILP; ++j)
-            if (has[j] && ndb[j] < old[j]) atomicMin(DA((unsigned)raw[j].z), ndb[j]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < ILP; ++j)
-            if (has[j] && ndb[j] < old[j]) old[j] = atomicMin(DA((unsigned)raw[j].z), ndb[j]);
-        }
-      }
+      for (int j = 0; j < ILP; ++j)
+        if (has[j]) old[j] = atomicMin(DA((unsigned)raw[j].z), ndb[j]);
 #pragma unroll
       for (int j = 0; j < ILP; ++j) {
         st_relax += has[j];
@@ -1177,7 +1160,6 @@ struct SqGraph {
   cudaDeviceProp prop; int prop_dev = -1;
   int group_mode = 0;                    // 0 = grouped warp kernel (a CTA of eight warps per group), 1 = sssp_group_kernel
   int group_ring = 1024;                 // ring entries per tree of the grouped warp kernel
-  int relax_mode = 0;                    // warp kernel relaxation: see TreeParams::relax_mode
   int group_min_trees = 2048;            // auto mode: batches at least this large ...
   int group_min_density = 8;             // ... with at least V / this many origins go to the group kernel
   size_t group_scratch_bytes = (size_t)24 << 30;   // upper bound of the interleaved distance scratch per chunk
@@ -1849,7 +1831,6 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   p.delta = g->delta; p.nq = nq; p.words = words;
   p.ell = g->d_ell; p.ovf = g->d_ovf; p.rell = g->d_rell; p.rovf = g->d_rovf;
   p.fail_count = g->d_fail; p.fail_list = g->d_fail + 2;
-  p.relax_mode = g->relax_mode;
   if (reverse) {  // trees on the reversed graph: distances *to* the origin, parent = next vertex towards it
     std::swap(p.row_ptr, p.rrow_ptr); std::swap(p.adj, p.radj);
     std::swap(p.ell, p.rell); std::swap(p.ovf, p.rovf);
@@ -2206,12 +2187,6 @@ int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
   if (ring_cap > 0) g->warp_ring = ring_cap;
   if (ilp > 0) g->warp_ilp = ilp;
   if (ctas_per_sm >= 0) g->warp_ctas_per_sm = ctas_per_sm;
-  return SQ_OK;
-}
-
-int sp_set_relax_mode(Graph* g, int mode) {
-  if (!g || mode < 0 || mode > 2) return sq::set_error(SQ_ERR_ARG, "sp_set_relax_mode: mode must be 0, 1 or 2");
-  g->relax_mode = mode;
   return SQ_OK;
 }
 

@@ -139,10 +139,6 @@ class Graph:
         check(lib().sp_set_group_tuning(self._h, int(warps_per_sm), int(batch), int(prefetch), int(min_trees),
                                         int(min_density)), "sp_set_group_tuning")
 
-    def set_relax_mode(self, mode=0):
-        """Warp kernel relaxation: 0 atomicMin, 1 load + RED.MIN, 2 load then atomicMin; see include/sq_sp.h."""
-        check(lib().sp_set_relax_mode(self._h, int(mode)), "sp_set_relax_mode")
-
     def set_group_mode(self, mode=0, ring_cap=0):
         """0 = grouped warp kernel (default), 1 = sssp_group_kernel; see include/sq_sp.h."""
         check(lib().sp_set_group_mode(self._h, int(mode), int(ring_cap)), "sp_set_group_mode")

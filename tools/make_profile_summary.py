@@ -95,6 +95,26 @@ for f in sorted(os.listdir(src)):
             out.write("`ncu --set full --clock-control none --import-source on`, one launch (tools/gpu_round.sh); exported with\n"
                       "`ncu -i <rep> --page raw --csv` / `--page source --csv` (tools/make_profile_summary.py).\n\n")
             full(os.path.join(src, f), out)
+# roofline.traffic of bench.py: DRAM bytes of the captured launches, per tree / per tick
+import json
+traffic = {}
+for f, kind, unit, per in (("sssp_warp_full.ncu-rep", "sssp", "bytes_per_tree", int(os.environ.get("BATCH", 2368))),
+                           ("tick_node_full.ncu-rep", "tick", "bytes_per_tick", 1)):
+    rep = os.path.join(src, f)
+    if not os.path.exists(rep):
+        continue
+    raw = list(csv.reader(io.StringIO(export(rep, "raw"))))
+    hdr, units, vals = raw[0], raw[1], raw[2]
+
+    def val(name):
+        i = hdr.index(name)
+        x = float(vals[i].replace(",", ""))
+        return x * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(units[i], 1)
+    tot = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
+    traffic[kind] = {unit: tot / per, "source": f"profiles/{tag}_{f[:-8]}_ncu.txt (dram__bytes_read.sum + dram__bytes_write.sum of "
+                     f"one launch{' of %d trees' % per if per > 1 else ': k_node_phase of one tick'})"}
+if traffic:
+    json.dump(traffic, open(os.path.join(dst, "traffic.json"), "w"), indent=1)
 if os.path.exists(os.path.join(src, "bench.json")):
     open(os.path.join(dst, f"{tag}_bench.json"), "w").write(open(os.path.join(src, "bench.json")).read())
 print("wrote", [f for f in os.listdir(dst) if f.startswith(tag)])
