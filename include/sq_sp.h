@@ -154,14 +154,16 @@ int sp_set_algo(Graph* graph, int algo, double queue_factor);
 
 /* Group-kernel knobs (algo 4, and auto mode on dense batches): eight trees of neighbouring origins share one
  * frontier and one warp (csrc/sp_group.cuh).  warps_per_sm: resident groups per SM (multiple of 4, 0 keeps; default
- * 16); batch: pops decided per batch, 8 / 16 / 32 (0 keeps; default 16); prefetch: 1 = prefetch a batch's rows
+ * 16); batch: pops decided per batch, 8 / 16 / 32 (mode 2: pops in flight, 4 / 8 / 16) (0 keeps; default 16); prefetch: 1 = prefetch a batch's rows
  * into L1 (< 0 keeps; default 1); auto mode picks the group kernel for batches of at least min_trees origins
  * (0 keeps; default 2048) that hold at least V / min_density origins (0 keeps; default 8). */
 int sp_set_group_tuning(Graph* graph, int warps_per_sm, int batch, int prefetch, int min_trees, int min_density);
 /* Which tree kernel works on the group layout: 0 (default) = the warp kernel, a CTA of eight warps per group and one
  * tree per warp (ring_cap entries per tree, 0 keeps; default 1024; trees that outgrow it are rerun by the bitmap
  * kernel); 1 = sssp_group_kernel, one warp per group, no atomics and no capacity limits (also what mode 0 falls back
- * to when the graph is too large for the bitmap kernel). */
+ * to when the graph is too large for the bitmap kernel); 2 = sssp_union_kernel, one warp per group with a shared
+ * frontier, 64-bit atomics on the interleaved rows and `batch` (sp_set_group_tuning: 4, 8 or 16) pops in flight; two
+ * bits per vertex per warp in shared memory bound it to about 400k vertices (larger graphs run mode 1). */
 int sp_set_group_mode(Graph* graph, int mode, int ring_cap);
 
 /* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps; default 1024), frontier

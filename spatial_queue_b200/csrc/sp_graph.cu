@@ -1594,6 +1594,9 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
   // the warp kernel needs a fallback for trees whose wavefront outgrows its ring; without one (graph too large for the
   // bitmap kernel, or ids too wide for the hashed queue entries) the group runs on the kernel that cannot overflow
   const bool warp_mode = g->group_mode == 0 && vbits <= 24 && bm.fits && !host_list;
+  // union kernel: two bits per vertex per warp in shared memory
+  const size_t union_smem = (size_t)4 * 2 * ((V + 31) / 32) * sizeof(unsigned);
+  const bool union_mode = g->group_mode == 2 && !host_list && bm.fits && union_smem <= 200 * 1024;
 
   // ---- sort the trees by origin (counting sort on the internal ids) ----
   if (g->gkey_cap < (size_t)n_pad) {
@@ -1641,6 +1644,7 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
   typedef void (*GroupKernel)(const GroupParams);
   static const WarpKernel wkernels[4] = {sssp_warp_kernel<1, true>, sssp_warp_kernel<2, true>, sssp_warp_kernel<4, true>,
                                          sssp_warp_kernel<8, true>};
+  static const GroupKernel ukernels[3] = {sssp_union_kernel<4>, sssp_union_kernel<8>, sssp_union_kernel<16>};
   static const GroupKernel gkernels[3][2] = {{sssp_group_kernel<8, 0>, sssp_group_kernel<8, 1>},
                                              {sssp_group_kernel<16, 0>, sssp_group_kernel<16, 1>},
                                              {sssp_group_kernel<32, 0>, sssp_group_kernel<32, 1>}};
@@ -1679,7 +1683,8 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
       }
     }
   } else {
-    const int wps = std::max(4, std::min(g->group_warps_per_sm, 32)) / 4 * 4;
+    int wps = std::max(4, std::min(g->group_warps_per_sm, 32)) / 4 * 4;
+    if (union_mode) wps = std::max(4, std::min(wps, 4 * (int)(prop.sharedMemPerMultiprocessor / (union_smem + 1024))));
     const int warps = (int)std::min<size_t>(chunk, (size_t)n_sm * wps);
     grid = (warps + 3) / 4;
     while (ring_cap < V) ring_cap <<= 1;
@@ -1691,14 +1696,29 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
       SQ_CUDA_TRY(cudaMalloc(&g->d_ginp, sizeof(unsigned) * (size_t)grid * 4 * words));
       g->g_warps = grid * 4; g->g_ring_cap = ring_cap; g->g_pend_cap = pend_cap; g->g_words = words;
     }
-    // no shared memory at all: give every byte of the SM's array to L1
+    // sssp_group_kernel: no shared memory at all, give every byte of the SM's array to L1; union kernel: its bitmaps
     static bool attr_set[SQ_MAX_DEVICES] = {false};
+    static int u_pct[SQ_MAX_DEVICES];
     std::lock_guard<std::mutex> lock(g_attr_mutex);
-    if (dev >= 0 && dev < SQ_MAX_DEVICES && !attr_set[dev]) {
-      for (int a2 = 0; a2 < 3; ++a2)
-        for (int b2 = 0; b2 < 2; ++b2)
-          SQ_CUDA_TRY(cudaFuncSetAttribute(gkernels[a2][b2], cudaFuncAttributePreferredSharedMemoryCarveout, 0));
-      attr_set[dev] = true;
+    if (dev >= 0 && dev < SQ_MAX_DEVICES) {
+      if (!attr_set[dev]) {
+        for (int a2 = 0; a2 < 3; ++a2) {
+          for (int b2 = 0; b2 < 2; ++b2)
+            SQ_CUDA_TRY(cudaFuncSetAttribute(gkernels[a2][b2], cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+          SQ_CUDA_TRY(cudaFuncSetAttribute(ukernels[a2], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        }
+        attr_set[dev] = true;
+        u_pct[dev] = -1;
+      }
+      if (union_mode) {
+        int pct = (int)((100 * (size_t)(wps / 4) * (union_smem + 1024) + prop.sharedMemPerMultiprocessor - 1) / prop.sharedMemPerMultiprocessor);
+        pct = std::max(0, std::min(100, pct));
+        if (pct != u_pct[dev]) {
+          for (int a2 = 0; a2 < 3; ++a2)
+            SQ_CUDA_TRY(cudaFuncSetAttribute(ukernels[a2], cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+          u_pct[dev] = pct;
+        }
+      }
     }
   }
 
@@ -1725,7 +1745,11 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
       gp.counter = counter;
       gp.delta = g->delta;
       gp.stats = base.stats;
-      gkernels[g->group_pb <= 8 ? 0 : g->group_pb <= 16 ? 1 : 2][g->group_pf ? 1 : 0]<<<(std::min(m, grid * 4) + 3) / 4, 128, 0, st>>>(gp);
+      gp.fail_list = base.fail_list; gp.fail_count = base.fail_count;
+      if (union_mode)
+        ukernels[g->group_pb <= 4 ? 0 : g->group_pb <= 8 ? 1 : 2]<<<(std::min(m, grid * 4) + 3) / 4, 128, union_smem, st>>>(gp);
+      else
+        gkernels[g->group_pb <= 8 ? 0 : g->group_pb <= 16 ? 1 : 2][g->group_pf ? 1 : 0]<<<(std::min(m, grid * 4) + 3) / 4, 128, 0, st>>>(gp);
     }
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
@@ -1737,7 +1761,7 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
       SQ_CUDA_TRY(cudaGetLastError());
     }
   }
-  if (warp_mode) {
+  if (warp_mode || union_mode) {
     // trees whose wavefront outgrew the ring (normally none: these CTAs exit at once): the bitmap kernel recomputes
     // them in the caller's numbering, straight into the caller's tables, predecessors included
     TreeParams pf = base;
@@ -2191,7 +2215,7 @@ int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
 }
 
 int sp_set_group_mode(Graph* g, int mode, int ring_cap) {
-  if (!g || mode < 0 || mode > 1) return sq::set_error(SQ_ERR_ARG, "sp_set_group_mode: mode must be 0 or 1");
+  if (!g || mode < 0 || mode > 2) return sq::set_error(SQ_ERR_ARG, "sp_set_group_mode: mode must be 0, 1 or 2");
   g->group_mode = mode;
   if (ring_cap > 0) g->group_ring = ring_cap;
   return SQ_OK;
@@ -2199,7 +2223,8 @@ int sp_set_group_mode(Graph* g, int mode, int ring_cap) {
 
 int sp_set_group_tuning(Graph* g, int warps_per_sm, int batch, int prefetch, int min_trees, int min_density) {
   if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_group_tuning: null graph");
-  if (batch != 0 && batch != 8 && batch != 16 && batch != 32) return sq::set_error(SQ_ERR_ARG, "sp_set_group_tuning: batch must be 8, 16 or 32");
+  if (batch != 0 && batch != 4 && batch != 8 && batch != 16 && batch != 32)
+    return sq::set_error(SQ_ERR_ARG, "sp_set_group_tuning: batch must be 4, 8, 16 or 32");
   if (warps_per_sm > 0) g->group_warps_per_sm = warps_per_sm;
   if (batch > 0) g->group_pb = batch;
   if (prefetch >= 0) g->group_pf = prefetch;

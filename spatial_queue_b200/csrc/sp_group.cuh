@@ -53,6 +53,8 @@ struct GroupParams {
   int* counter;
   long long* stats;      // [1] pops, [2] edge relaxations (per group, not per tree), [3] transitions
   double delta;
+  int* fail_list;        // union kernel: trees of groups whose pending list overflowed (rerun by the bitmap kernel)
+  int* fail_count;
 };
 
 __device__ __forceinline__ u64 ld_row(const u64* p) {
@@ -458,4 +460,252 @@ __global__ void __launch_bounds__(256) group_scatter_kernel(int n, int n_pad, co
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i < n) tord[atomicAdd(&cursor[key[i]], 1)] = i;
   else if (i < n_pad) tord[i] = -1;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Union kernel: the group layout and the shared frontier of sssp_group_kernel, but relaxations are 64-bit L2 atomicMin
+// (eight lanes of a slot hit one 64-byte row: two sectors per edge for eight trees) and P pops are in flight at once.
+// sssp_group_kernel showed what in-order pops cost: two dependent DRAM-latency round trips per pop, ~2,600 cycles, with
+// nothing to overlap them.  Atomics need no ordering between pops, so a step issues the row and record loads of P pops
+// together, then their 4 x P edge atomics, then does the queue bookkeeping -- the structure of sssp_warp_kernel, with
+// the requests of eight trees folded into one.
+//  * no marks in the distance words (they are atomicMin operands); a bit per vertex in shared memory says "in the ring"
+//    (set by the push that wins atomicOr, cleared when the batch holding the vertex is read);
+//  * improvements beyond the threshold go to the pending list unless the vertex is in the ring anyway; duplicates are
+//    possible there, the scan at the bucket transition removes them with the same bit;
+//  * the scan reads a row and takes the smallest distance >= T: below T + delta the vertex enters the ring.
+// The bitmap bounds V by shared memory (4 warps x V/8 bytes per CTA); larger graphs use the other group kernels.
+// -------------------------------------------------------------------------------------------------------------------
+template <int P>
+__global__ void __launch_bounds__(128) sssp_union_kernel(const GroupParams p) {
+  extern __shared__ unsigned s_union_bits[];
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int j = lane >> 3, k = lane & 7;
+  const unsigned lt = sq::lanemask_lt();
+  const int V = p.V;
+  const int gwarp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const unsigned rmask = (unsigned)p.ring_cap - 1u;
+  unsigned* ring = p.ring + (size_t)gwarp * p.ring_cap;
+  unsigned* pend0 = p.pend + (size_t)gwarp * 2 * p.pend_cap;
+  unsigned* bits = s_union_bits + (size_t)(threadIdx.x >> 5) * 2 * p.words;   // "in the ring"
+  unsigned* pbits = bits + p.words;                                            // "listed in the pending list"
+  const double delta = p.delta;
+  const u64 INF = DIST_INF_BITS;
+  const bool leader = k == 0;
+  const int sh = 8 * j;
+
+  int st_pops = 0, st_trans = 0;
+
+  for (;;) {
+    int grp = 0;
+    if (lane == 0) grp = atomicAdd(p.counter, 1);
+    grp = __shfl_sync(FULL, grp, 0);
+    if (grp >= p.n_groups) break;
+    u64* D = p.gdist + (size_t)grp * V * 8;
+    int src = -1;
+    {
+      const int t = __ldg(&p.tord[grp * 8 + k]);
+      if (t >= 0) {
+        const int o = __ldg(&p.origins[t]);
+        if (o >= 0 && o < V) src = __ldg(&p.perm[o]);
+      }
+    }
+    {
+      ulonglong2* d2 = reinterpret_cast<ulonglong2*>(D);
+      const ulonglong2 inf2 = make_ulonglong2(INF, INF);
+      const int n2 = V * 4;
+#pragma unroll 4
+      for (int i = lane; i < n2; i += 32) d2[i] = inf2;
+      for (int i = lane; i < 2 * p.words; i += 32) bits[i] = 0u;
+    }
+    __syncwarp();
+    int rh = 0, rt = 0, np = 0, pcur = 0;
+    bool fail = false;
+    {
+      const bool mine = (j == 0 && src >= 0);
+      if (mine) st_row(D + (size_t)src * 8 + k, 0ull);
+      bool first = mine;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int other = __shfl_sync(FULL, src, q);
+        if (q < k && other == src) first = false;
+      }
+      const unsigned m = __ballot_sync(FULL, first);
+      if (first) {
+        st_u32(&ring[__popc(m & lt)], (unsigned)src);
+        atomicOr(&bits[src >> 5], 1u << (src & 31));
+      }
+      rt = __popc(m);
+    }
+    __syncwarp();
+    double T = delta;
+    u64* Dk = D + k;
+
+    while (!fail) {
+      if (rh == rt) {
+        // ---- bucket transition: four pending entries per step, eight lanes read one row ------------------------------
+        if (np == 0) break;
+        ++st_trans;
+        double T_lo = T;                       // everything below is settled and was relaxed onward
+        double T_new = advance(T, delta);
+        for (;;) {
+          const unsigned* Pc = pend0 + (size_t)pcur * p.pend_cap;
+          unsigned* Pn = pend0 + (size_t)(pcur ^ 1) * p.pend_cap;
+          int nn = 0;
+          rh = 0; rt = 0;
+          u64 gmin = INF;
+          for (int i0 = 0; i0 < np; i0 += 4) {
+            const int idx = i0 + j;
+            const bool valid = idx < np;
+            const unsigned v = valid ? ld_u32(&Pc[idx]) : 0u;
+            const u64 raw = valid ? sq::ld_cg_u64(Dk + ((size_t)v << 3)) : INF;
+            u64 m = (__longlong_as_double((long long)raw) >= T_lo) ? raw : INF;
+#pragma unroll
+            for (int o = 1; o < 8; o <<= 1) {
+              const u64 other = __shfl_xor_sync(FULL, m, o);
+              m = other < m ? other : m;
+            }
+            const bool live = valid && m != INF;
+            bool to_ring = live && __longlong_as_double((long long)m) < T_new;
+            const bool keep = live && !to_ring;
+            if (leader && valid) {
+              const unsigned bit = 1u << (v & 31);
+              if (to_ring) to_ring = (atomicOr(&bits[v >> 5], bit) & bit) == 0u;   // may be in the ring already
+              if (!keep) atomicAnd(&pbits[v >> 5], ~bit);                           // leaves the list
+            }
+            const unsigned mr = __ballot_sync(FULL, to_ring && leader), mk = __ballot_sync(FULL, keep && leader);
+            if (leader) {
+              if (to_ring) st_u32(&ring[(unsigned)(rt + __popc(mr & lt)) & rmask], v);
+              else if (keep) st_u32(&Pn[nn + __popc(mk & lt)], v);
+            }
+            rt += __popc(mr);
+            nn += __popc(mk);
+            if (keep && m < gmin) gmin = m;
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(FULL, gmin, o);
+            gmin = other < gmin ? other : gmin;
+          }
+          __syncwarp();
+          pcur ^= 1;
+          np = nn;
+          if (rt > 0 || nn == 0) break;
+          const double Tg = __longlong_as_double((long long)gmin);   // nothing within reach: jump
+          T_lo = Tg;
+          T_new = advance(Tg, delta);
+        }
+        T = T_new;
+        continue;
+      }
+
+      // ---- one batch of up to 32 pops, P at a time ----------------------------------------------------------------------
+      const int nb = min(32, rt - rh);
+      unsigned ent = 0u;
+      if (lane < nb) {
+        ent = ld_u32(&ring[(unsigned)(rh + lane) & rmask]);
+        atomicAnd(&bits[ent >> 5], ~(1u << (ent & 31)));      // out of the ring from here on: an improvement re-queues it
+      }
+      rh += nb;
+      st_pops += nb;
+      __syncwarp();
+      unsigned* Pc = pend0 + (size_t)pcur * p.pend_cap;
+      for (int b0 = 0; b0 < nb; b0 += P) {
+        u64 du[P];
+        int4 rc[P];
+        bool act[P];
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+          act[q] = b0 + q < nb;
+          const unsigned u = __shfl_sync(FULL, ent, (b0 + q) & 31);
+          du[q] = INF;
+          rc[q] = make_int4(0, 0, 0, 2);
+          if (act[q]) {
+            du[q] = sq::ld_cg_u64(Dk + ((size_t)u << 3));
+            rc[q] = __ldg(reinterpret_cast<const int4*>(p.gell + (size_t)u * 4 + j));
+          }
+        }
+        u64 ndb[P], old[P];
+        bool has[P];
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+          has[q] = act[q] && !(rc[q].w & 2) && du[q] != INF;
+          ndb[q] = (u64)__double_as_longlong(__longlong_as_double((long long)du[q]) + __hiloint2double(rc[q].y, rc[q].x));
+          old[q] = 0ull;
+        }
+#pragma unroll
+        for (int q = 0; q < P; ++q)
+          if (has[q]) old[q] = atomicMin(Dk + ((size_t)(unsigned)rc[q].z << 3), ndb[q]);
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+          const bool imp = has[q] && ndb[q] < old[q];
+          const bool near = imp && __longlong_as_double((long long)ndb[q]) < T;
+          const unsigned b1 = __ballot_sync(FULL, near), b2 = __ballot_sync(FULL, imp);
+          if (b2 == 0u) continue;                                   // warp-uniform
+          const bool s_near = ((b1 >> sh) & 0xffu) != 0u, s_imp = ((b2 >> sh) & 0xffu) != 0u;
+          bool pr = false, pp = false;
+          const unsigned v = (unsigned)rc[q].z;
+          if (leader && s_imp) {
+            const unsigned bit = 1u << (v & 31);
+            if (s_near) pr = (atomicOr(&bits[v >> 5], bit) & bit) == 0u;
+            else if (!(bits[v >> 5] & bit)) pp = (atomicOr(&pbits[v >> 5], bit) & bit) == 0u;
+          }
+          const unsigned mr = __ballot_sync(FULL, pr), mp = __ballot_sync(FULL, pp);
+          if (pr) st_u32(&ring[(unsigned)(rt + __popc(mr & lt)) & rmask], v);
+          if (pp) {
+            const int pos = np + __popc(mp & lt);
+            if (pos < p.pend_cap) st_u32(&Pc[pos], v);
+          }
+          rt += __popc(mr);
+          np += __popc(mp);
+        }
+        // edges beyond the fourth of a vertex (rare on road networks): one edge at a time, lanes 0..7
+#pragma unroll
+        for (int q = 0; q < P; ++q) {
+          const int w0 = __shfl_sync(FULL, rc[q].w, 0), w1 = __shfl_sync(FULL, rc[q].w, 8);
+          const int ovf_n = act[q] ? (w1 >> 6) : 0;
+          if (ovf_n == 0) continue;                                 // warp-uniform
+          const int ovf_b = w0 >> 6;
+          const u64 du0 = __shfl_sync(FULL, du[q], k);              // lanes 0..7 hold the row of u
+          for (int e = 0; e < ovf_n; ++e) {
+            const EdgeRec er = ld_edge(&p.govf[ovf_b + e]);
+            bool imp = false, near = false;
+            if (j == 0 && du0 != INF) {
+              const u64 nb2 = (u64)__double_as_longlong(__longlong_as_double((long long)du0) + er.w);
+              const u64 o2 = atomicMin(Dk + ((size_t)(unsigned)er.v << 3), nb2);
+              imp = nb2 < o2;
+              near = imp && __longlong_as_double((long long)nb2) < T;
+            }
+            const bool a_near = __any_sync(FULL, near), a_imp = __any_sync(FULL, imp);
+            if (!a_imp) continue;
+            const unsigned bit = 1u << (er.v & 31);
+            unsigned was = 0u;
+            if (lane == 0) {
+              if (a_near) was = atomicOr(&bits[er.v >> 5], bit);
+              else was = (bits[er.v >> 5] & bit) ? bit : atomicOr(&pbits[er.v >> 5], bit);
+            }
+            was = __shfl_sync(FULL, was, 0);
+            if (!(was & bit)) {
+              if (a_near) { if (lane == 0) st_u32(&ring[(unsigned)rt & rmask], (unsigned)er.v); ++rt; }
+              else { if (lane == 0 && np < p.pend_cap) st_u32(&Pc[np], (unsigned)er.v); ++np; }
+            }
+          }
+        }
+        if (np > p.pend_cap || rt - rh > p.ring_cap) { fail = true; break; }
+      }
+      __syncwarp();
+    }
+    __syncwarp();
+    if (fail) {
+      // the pending list outgrew its bound (duplicates): hand the group's trees to the fallback kernel
+      const int t = __ldg(&p.tord[grp * 8 + k]);
+      if (j == 0 && t >= 0) p.fail_list[atomicAdd(p.fail_count, 1)] = t;
+    }
+  }
+  if (p.stats && lane == 0) {
+    atomicAdd((u64*)&p.stats[1], (u64)st_pops);
+    atomicAdd((u64*)&p.stats[2], (u64)st_pops * 4ull);
+    atomicAdd((u64*)&p.stats[3], (u64)st_trans);
+  }
 }

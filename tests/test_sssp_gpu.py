@@ -67,7 +67,8 @@ def test_network_mtx_golden(spi):
                                                       (256, 0, 0, 4.0), (64, 0, 0, 0.02),                 # roomy / tight queues
                                                       (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0),    # warp kernel: (ilp, ring)
                                                       (8, 0, 4, 0), (16, 1, 4, 0), (32, 1, 4, 0),         # group kernel: (batch, prefetch)
-                                                      (2, 64, 5, 0), (4, 1024, 5, 0)])                    # grouped warp kernel: (ilp, ring)
+                                                      (2, 64, 5, 0), (4, 1024, 5, 0),                     # grouped warp kernel: (ilp, ring)
+                                                      (4, 0, 6, 0), (8, 0, 6, 0), (16, 0, 6, 0)])         # union kernel: pops in flight
 def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
     from oracle import sssp as osssp
     rng = np.random.default_rng(11 + threads)
@@ -94,6 +95,12 @@ def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
             g.set_algo(4)
             g.set_group_mode(0, smemq)
             g.set_warp_tuning(ilp=threads)
+            g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
+        elif algo == 6:
+            # shared frontier + atomics: parallel edges, self loops, overflow edges, closed links
+            g.set_algo(4)
+            g.set_group_mode(2)
+            g.set_group_tuning(batch=threads)
             g.set_tuning(delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
         else:
             g.set_tuning(threads=threads, smem_queue=smemq, delta_factor=float(rng.choice([0.25, 2.0, 50.0])))
@@ -173,7 +180,7 @@ def test_weight_updates_reach_the_device(spi):
         assert d.tobytes() == do.tobytes() and (p == po).all()
 
 
-@pytest.mark.parametrize("algo", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("algo", [0, 1, 2, 3, 4, 5, 6])
 def test_grid_batch_and_device_api(spi, algo):
     import torch
     from oracle import sssp as osssp
@@ -181,7 +188,7 @@ def test_grid_batch_and_device_api(spi, algo):
     s, e, w = grid_graph(n, seed=1)
     g = spi.from_arrays(s, e, w)
     g.set_algo(min(algo, 4))
-    g.set_group_mode(1 if algo == 4 else 0)
+    g.set_group_mode({4: 1, 6: 2}.get(algo, 0))
     og = osssp.OracleGraph(s, e, w)
     # 1000 origins: above the auto switch-over (six trees per SM), so algo 3 runs the warp kernel here
     origins = np.random.default_rng(2).permutation(n * n)[:1000].astype(np.int32)
@@ -265,7 +272,7 @@ def test_reverse_trees_and_device_weight_refresh(spi):
     g.free()
 
 
-@pytest.mark.parametrize("algo", [3, 4, 5])
+@pytest.mark.parametrize("algo", [3, 4, 5, 6])
 @pytest.mark.parametrize("reverse", [False, True])
 def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo):
     """The compact table the multi-GPU path all-gathers (one byte per vertex) expands to exactly the int32 tree."""
@@ -277,7 +284,7 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo)
     w = np.round(rng.random(E) * 20.0) + 1.0   # many exact ties
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
     g.set_algo(min(algo, 4))
-    g.set_group_mode(1 if algo == 4 else 0, 64 if algo == 5 else 0)   # 5: tiny ring, some trees rerun by the bitmap kernel
+    g.set_group_mode({4: 1, 6: 2}.get(algo, 0), 64 if algo == 5 else 0)   # 5: tiny ring, some trees rerun by the bitmap kernel
     origins = torch.from_numpy(rng.integers(0, V, 40).astype(np.int32)).cuda()
     d = torch.empty((40, V), dtype=torch.float64, device="cuda")
     p32 = torch.empty((40, V), dtype=torch.int32, device="cuda")
@@ -415,7 +422,7 @@ def _congested_weights(s, e, w, seed=2):
     return q / (1900.0 + 0.1) * 3600 * 25 / 25.0 + w
 
 
-@pytest.mark.parametrize("algo,n", [(3, 2368), (4, 2368), (5, 2368), (3, 18944)])
+@pytest.mark.parametrize("algo,n", [(3, 2368), (4, 2368), (5, 2368), (6, 2368), (3, 18944), (6, 18944)])
 def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     """bench.py's HP-2 workload itself: 224x224 grid, bench.origins_for origins, through sp_sssp_batch_device in auto
     mode (2,368 origins: sssp_warp_kernel; 18,944 origins, the benchmarked batch: sssp_group_kernel) and with the group
@@ -426,7 +433,7 @@ def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     s, e, w, V, bench = _config5()
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
     g.set_algo(min(algo, 4))
-    g.set_group_mode(1 if algo == 4 else 0)
+    g.set_group_mode({4: 1, 6: 2}.get(algo, 0))
     origins = bench.origins_for(0, n, V, step=0)
     o_dev = torch.from_numpy(origins).cuda()
     d_dev = torch.empty((n, V), dtype=torch.float64, device="cuda")
@@ -465,7 +472,7 @@ def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     g.free()
 
 
-@pytest.mark.parametrize("algo", [3, 4, 5])
+@pytest.mark.parametrize("algo", [3, 4, 5, 6])
 def test_config5_congested_weight_set(spi, algo):
     """Same graph with the second, congested weight set of SURVEY.md 8(d) (queues ~ Poisson(3)) pushed through
     sp_set_weights_device, 1,024 origins (auto mode: the warp kernel; forced: the group kernel)."""
@@ -475,7 +482,7 @@ def test_config5_congested_weight_set(spi, algo):
     w2 = _congested_weights(s, e, w)
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
     g.set_algo(min(algo, 4))
-    g.set_group_mode(1 if algo == 4 else 0)
+    g.set_group_mode({4: 1, 6: 2}.get(algo, 0))
     g.set_weights_device(torch.from_numpy(w2).cuda())
     origins = bench.origins_for(0, 1024, V, step=3)
     o_dev = torch.from_numpy(origins).cuda()
@@ -489,7 +496,7 @@ def test_config5_congested_weight_set(spi, algo):
     g.free()
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 2])
 def test_group_kernel_on_an_irregular_network_with_closures(spi, mode):
     """The group kernel where its assumptions are weakest: a town-like network (streets removed, one-ways, hubs with
     more than four out-links), 3 % of the links closed at 1e8 (threshold jumps, pending-list rescans), origins

@@ -48,13 +48,17 @@ g.set_algo(4)
 # (mode, warps per SM, a, b, delta factor): mode 0 = grouped warp kernel, a = ILP, b = ring entries per tree;
 #                                           mode 1 = sssp_group_kernel, a = pops per batch, b = prefetch
 configs = json.loads(os.environ.get("CONFIGS", "null")) or [
-    (0, 16, 4, 1024, 4.0, 0), (0, 16, 8, 1024, 4.0, 0), (1, 16, 32, 1, 4.0, 0)]
+    (0, 16, 4, 1024, 4.0, 0), (2, 8, 16, 0, 4.0, 0), (2, 16, 8, 0, 4.0, 0), (2, 12, 8, 0, 4.0, 0), (2, 8, 8, 0, 4.0, 0),
+    (2, 16, 4, 0, 4.0, 0), (2, 4, 16, 0, 4.0, 0), (2, 8, 16, 0, 2.0, 0), (2, 8, 16, 0, 8.0, 0), (2, 16, 8, 0, 8.0, 0)]
 for mode, wps, a, b, df, rm in configs:
     try:
         if mode == 0:
             g.set_group_mode(0, b)
             g.set_warp_tuning(ilp=a)
             g.set_group_tuning(warps_per_sm=wps)
+        elif mode == 2:
+            g.set_group_mode(2)
+            g.set_group_tuning(warps_per_sm=wps, batch=a)
         else:
             g.set_group_mode(1)
             g.set_group_tuning(warps_per_sm=wps, batch=a, prefetch=b)
