@@ -603,15 +603,15 @@ __global__ void __launch_bounds__(128) sssp_union_kernel(const GroupParams p) {
       // ---- one batch of up to 32 pops, P at a time ----------------------------------------------------------------------
       const int nb = min(32, rt - rh);
       unsigned ent = 0u;
-      if (lane < nb) {
-        ent = ld_u32(&ring[(unsigned)(rh + lane) & rmask]);
-        atomicAnd(&bits[ent >> 5], ~(1u << (ent & 31)));      // out of the ring from here on: an improvement re-queues it
-      }
+      if (lane < nb) ent = ld_u32(&ring[(unsigned)(rh + lane) & rmask]);
       rh += nb;
       st_pops += nb;
-      __syncwarp();
       unsigned* Pc = pend0 + (size_t)pcur * p.pend_cap;
       for (int b0 = 0; b0 < nb; b0 += P) {
+        {  // the P vertices of this step leave the ring now: an improvement from here on re-queues them
+          const unsigned e = __shfl_sync(FULL, ent, (b0 + lane) & 31);
+          if (lane < P && b0 + lane < nb) atomicAnd(&bits[e >> 5], ~(1u << (e & 31)));
+        }
         u64 du[P];
         int4 rc[P];
         bool act[P];
