@@ -21,8 +21,19 @@ class Point:
     def coords(self):
         return [(self.x, self.y)]
 
+    def buffer(self, radius):
+        """The disc around the point (the loader splits a link's polyline with `point.buffer(1)`, queue_class.py:84)."""
+        return Disc(self, float(radius))
+
     def __repr__(self):
         return f"POINT ({self.x!r} {self.y!r})"
+
+
+class Disc:
+    __slots__ = ("center", "radius")
+
+    def __init__(self, center, radius):
+        self.center, self.radius = center, radius
 
 
 class LineString:
@@ -54,8 +65,38 @@ class LineString:
                 return Point(x0 + f * (x1 - x0), y0 + f * (y1 - y0))
         return Point(*self.coords[-1])
 
+    def project(self, point):
+        """Arc length of the point of the line closest to `point`."""
+        best, best_d = 0.0, float("inf")
+        for i in range(1, len(self.coords)):
+            (x0, y0), (x1, y1) = self.coords[i - 1], self.coords[i]
+            dx, dy = x1 - x0, y1 - y0
+            seg2 = dx * dx + dy * dy
+            f = 0.0 if seg2 == 0.0 else min(1.0, max(0.0, ((point.x - x0) * dx + (point.y - y0) * dy) / seg2))
+            d = math.hypot(point.x - (x0 + f * dx), point.y - (y0 + f * dy))
+            if d < best_d:
+                best_d, best = d, self._cum[i - 1] + f * (self._cum[i] - self._cum[i - 1])
+        return best
+
+    def cut(self, d0, d1):
+        """The part of the line between arc lengths d0 <= d1 (end points interpolated, inner vertices kept)."""
+        a, b = self.interpolate(d0), self.interpolate(d1)
+        inner = [c for c, s in zip(self.coords, self._cum) if d0 < s < d1]
+        return LineString([(a.x, a.y)] + inner + [(b.x, b.y)])
+
     def __repr__(self):
         return "LINESTRING (" + ", ".join(f"{x!r} {y!r}" for x, y in self.coords) + ")"
+
+
+def split(line, disc):
+    """shapely.ops.split(line, point.buffer(r)) for a disc centred ON the line, as the loader's turn-prohibition code
+    uses it (queue_class.py:84, 91): the pieces before, inside and after the disc, in line order.  The cuts are made
+    at arc length +-r from the centre (shapely intersects with a 64-gon: the same to within a millimetre)."""
+    s = line.project(disc.center)
+    a, b = s - disc.radius, s + disc.radius
+    if not (0.0 < a and b < line.length):
+        raise ValueError("the split disc reaches an end of the line (link shorter than ~10 x the disc radius)")
+    return [line.cut(0.0, a), line.cut(a, b), line.cut(b, line.length)]
 
 
 _NUM = re.compile(r"[-+]?(?:\d+\.?\d*|\.\d+)(?:[eE][-+]?\d+)?")

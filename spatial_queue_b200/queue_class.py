@@ -304,7 +304,7 @@ class Network:
             links_df.loc[links_df["eid"] == closed_eid, "fft"] = 1e8
             links_df.loc[links_df["eid"] == closed_eid, "maxmph"] = 0.00000001
         if len(special_nodes.get("prohibition", {}) or {}) > 0:
-            raise NotImplementedError("turn prohibitions (queue_class.py:69-120) are not supported")
+            nodes_df, links_df = self._split_prohibition_nodes(nodes_df, links_df, special_nodes["prohibition"])
 
         self.g = interface.from_dataframe(links_df, "nid_s", "nid_e", "fft")
 
@@ -325,6 +325,48 @@ class Network:
             known = self.node2link_dict.get(key)
             if known is None or link.fft < self.links[known].fft:    # parallel links: the faster one is routed on
                 self.node2link_dict[key] = link.link_id
+
+    @staticmethod
+    def _split_prohibition_nodes(nodes_df, links_df, prohibition):
+        """Turn prohibitions (model/queue_class.py:69-120): a node with forbidden turns is taken apart.  Every link
+        leaving it starts at a node of its own, placed at 10 % of the link (its geometry keeps what lies beyond a 1 m
+        disc around that point), every link entering it ends at a node of its own at 90 %; each allowed
+        (in-link, out-link) pair gets a zero-length connector link (100 lanes, capacity 100,000, fft 0) between the
+        two.  The old node stays behind without links.  Ids continue the frames' row counts, as in the reference."""
+        links_df = links_df.reset_index(drop=True).copy()
+        new_nodes, new_links = [], []
+        next_node, next_link = nodes_df.shape[0], links_df.shape[0]
+        for node_key, turns in prohibition.items():
+            node = int(node_key)
+            starts, ends = [], []           # (new node id, x, y, link eid) of the out-links / in-links
+            for i in links_df.index[links_df["nid_s"] == node]:
+                geom, eid = links_df.at[i, "geometry"], links_df.at[i, "eid"]
+                pt = geom.interpolate(0.1, normalized=True)
+                links_df.at[i, "nid_s"] = next_node
+                links_df.at[i, "geometry"] = geo.split(geom, pt.buffer(1))[2]
+                starts.append((next_node, pt.x, pt.y, eid))
+                next_node += 1
+            for i in links_df.index[links_df["nid_e"] == node]:
+                geom, eid = links_df.at[i, "geometry"], links_df.at[i, "eid"]
+                pt = geom.interpolate(0.9, normalized=True)
+                links_df.at[i, "nid_e"] = next_node
+                links_df.at[i, "geometry"] = geo.split(geom, pt.buffer(1))[0]
+                ends.append((next_node, pt.x, pt.y, eid))
+                next_node += 1
+            new_nodes += [(n, x, y, "n{}_l{}".format(node, eid)) for n, x, y, eid in starts + ends]
+            banned = {(a, b) for a, b in turns}
+            for n_in, x_in, y_in, e_in in ends:
+                for n_out, x_out, y_out, e_out in starts:
+                    if (e_in, e_out) not in banned:
+                        new_links.append({"eid": next_link, "nid_s": n_in, "nid_e": n_out, "type": np.nan, "lanes": 100,
+                                          "capacity": 100000, "maxmph": 100000, "fft": 0.0, "length": 0.0,
+                                          "geometry": geo.LineString([(x_in, y_in), (x_out, y_out)])})
+                        next_link += 1
+        if new_links:
+            links_df = pd.concat([links_df, pd.DataFrame(new_links)[list(links_df.columns)]], ignore_index=True)
+        if new_nodes:
+            nodes_df = pd.concat([nodes_df, pd.DataFrame(new_nodes, columns=["nid", "x", "y", "osmid"])], ignore_index=True)
+        return nodes_df, links_df
 
     def add_connectivity(self):
         """Per-node turn table (queue_class.py:147-165), wrap rule as written in the reference."""

@@ -103,7 +103,7 @@ def grid(qc, rts, name, n, n_agents, special=None, horizon=100, max_ticks=3000, 
 
 def main():
     qc, rts = rh.import_reference(seed=SEED)
-    which = sys.argv[1:] or ["bolinas", "grid8", "grid7s", "grid5x"]
+    which = sys.argv[1:] or ["bolinas", "grid8", "grid7s", "grid5x", "grid6p"]
     if "bolinas" in which:
         bolinas(qc, rts)
     if "grid8" in which:
@@ -122,6 +122,8 @@ def main():
              exits=[0, 48, 6])
 
 
+    if "grid6p" in which:
+        grid(qc, rts, "grid6p", 6, 900, special=grid6p_special(), horizon=60, exits=[0, 35, 5], max_ticks=2500)
     if "grid5x" in which:
         # a signal whose phases never serve one approach: the vehicles queued there wait for ever and give up after
         # three hours (status shelter_a1, run_traffic_simulation.py:100-104, 113-118), as do the ones stuck behind
@@ -131,6 +133,19 @@ def main():
         sig = {"1": {"phase_1": ["n1_vl"] + served[0:1], "phase_2": ["n1_vl"] + served[1:2]}}   # 2 -> 1 is never served
         grid(qc, rts, "grid5x", n, 500, special={"signal": sig}, horizon=100, exits=[0, 24], max_ticks=11500,
              snapshot_every=900)
+
+
+def grid6p_special(n=6):
+    """Turn prohibitions (queue_class.py:76-131) at two interior nodes of the 6 x 6 grid: the loader splits each node
+    into one node per link end and joins them by zero-length connector links, leaving the forbidden pairs out."""
+    edges, _ = synth.grid_frames(n, seed=1, arterial_every=4)
+    proh = {}
+    for node, skip in ((14, (0, 5, 10)), (21, (3, 6))):
+        ins = [int(x) for x in edges.loc[edges.nid_e == node, "eid"]]
+        outs = [int(x) for x in edges.loc[edges.nid_s == node, "eid"]]
+        pairs = [[a, b] for a in ins for b in outs]
+        proh[str(node)] = [pairs[k] for k in skip]
+    return {"signal": {}, "priority": {}, "prohibition": proh, "closure": []}
 
 
 if __name__ == "__main__":

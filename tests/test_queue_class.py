@@ -39,7 +39,20 @@ def grid7s_special(n=7):
     return {"signal": sig, "priority": pri, "prohibition": {}, "closure": [5, 30]}
 
 
+def grid6p_special(n=6):
+    """tests/golden/make_tick_golden.py:grid6p_special: turn prohibitions at two interior nodes."""
+    edges, _ = synth.grid_frames(n, seed=1, arterial_every=4)
+    proh = {}
+    for node, skip in ((14, (0, 5, 10)), (21, (3, 6))):
+        ins = [int(x) for x in edges.loc[edges.nid_e == node, "eid"]]
+        outs = [int(x) for x in edges.loc[edges.nid_s == node, "eid"]]
+        pairs = [[a, b] for a in ins for b in outs]
+        proh[str(node)] = [pairs[k] for k in skip]
+    return {"signal": {}, "priority": {}, "prohibition": proh, "closure": []}
+
+
 SCENARIOS = {
+    "grid6p": dict(n=6, agents=900, horizon=60, exits=[0, 35, 5], special=grid6p_special()),
     "grid8": dict(n=8, agents=1500, horizon=60, exits=[0, 63], special=EMPTY),
     "grid7s": dict(n=7, agents=1200, horizon=80, exits=[0, 48, 6], special=grid7s_special()),
 }
@@ -70,11 +83,24 @@ def assert_static_equal(flat, gold):
         assert a.tobytes() == b.astype(a.dtype).tobytes(), f"{k} differs from the reference's objects"
 
 
-@pytest.mark.parametrize("name", ["grid8", "grid7s"])
+@pytest.mark.parametrize("name", ["grid8", "grid7s", "grid6p"])
 def test_mirror_loader_matches_reference_objects(name, tmp_path):
+    """grid6p: turn prohibitions (model/queue_class.py:69-120) -- split nodes, trimmed link geometry (turn angles),
+    zero-length connector links, the routing graph over the new ids; agents that start at or head for a node the split
+    left without links shelter at t = 0 like in the reference."""
     z, gold = load_golden(name)
     net, special = build_grid(name, tmp_path)
+    if name == "grid6p":
+        # the reference's first one_step routes everyone: unreachable pairs become shelter_p (queue_class.py:494-499)
+        dests = sorted({a.destin_nid for a in net.agents.values()})
+        assert len(net.links) == len(gold.link_end_node) and len(net.nodes) == 2 * 52
     flat = fl.flatten_network(net, special)
+    if name == "grid6p":
+        keep = [k for k in STATIC_FIELDS if not k.startswith("agent_")]
+        for k in keep:
+            a, b = np.asarray(getattr(flat, k)), np.asarray(getattr(gold, k))
+            assert a.shape == b.shape and a.tobytes() == b.astype(a.dtype).tobytes(), f"{k} differs from the reference's objects"
+        return
     assert_static_equal(flat, gold)
     # string ids of the virtual elements (queue_class.py:210, 213)
     assert net.links["n3_vl"].start_nid == "vn3" and net.links["n3_vl"].end_nid == 3

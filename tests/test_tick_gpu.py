@@ -8,7 +8,7 @@ from tickcheck import load_golden, replay, route_events, state_digest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("name,every", [("grid8", 1), ("grid7s", 1), ("bolinas", 1), ("grid5x", 5)])
+@pytest.mark.parametrize("name,every", [("grid8", 1), ("grid7s", 1), ("bolinas", 1), ("grid5x", 5), ("grid6p", 1)])
 def test_device_replays_reference_golden(name, every):
     from spatial_queue_b200.tick import DeviceSim
     z, flat = load_golden(name)
@@ -68,7 +68,7 @@ def test_device_reports_broken_routes():
         sim.sync()
 
 
-@pytest.mark.parametrize("name", ["grid8", "grid7s", "bolinas", "grid5x"])
+@pytest.mark.parametrize("name", ["grid8", "grid7s", "bolinas", "grid5x", "grid6p"])
 def test_device_router_replays_reference_golden(name):
     """The whole agent loop on the device: no routes and no route events from the golden file are used, only the
     network, the demand and the reference's parameters (reroute every 300 s, staggered by agent id; edge weights

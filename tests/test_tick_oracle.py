@@ -6,7 +6,7 @@ from oracle.tick import OracleSim
 from tickcheck import load_golden, replay
 
 
-@pytest.mark.parametrize("name,every", [("grid8", 1), ("grid7s", 1), ("bolinas", 1), ("grid5x", 5)])
+@pytest.mark.parametrize("name,every", [("grid8", 1), ("grid7s", 1), ("bolinas", 1), ("grid5x", 5), ("grid6p", 1)])
 def test_oracle_replays_reference_golden(name, every):
     """grid5x runs for 11,500 ticks behind a signal approach that is never served: the vehicles stuck there give
     up after three hours on the link (status shelter_a1, run_traffic_simulation.py:100-104)."""
