@@ -56,7 +56,7 @@ def test_config3_butte_standin_with_rules_and_closures_matches_host_path():
     assert 30_000 < len(flat.link_end_node) - N < 32_500 and len(flat.agent_key) == 100_000
     ev = synth.butte_closure_schedule(flat)
     in_window = [e for e in ev if e[0] < TICKS]
-    assert len(in_window) > 100
+    assert len(in_window) > 40
     dev = DeviceSim(flat, seed=3, routes_from_router=True)
     dev.attach_router(synth.routing_graph(flat), flat, reroute_freq=REROUTE, weight_freq=WEIGHT)
     dev.set_reroute_rules(2.0, 10)
