@@ -1147,6 +1147,7 @@ struct SqGraph {
   // group kernel (sp_group.cuh): internal numbering along a Hilbert curve over landmark pseudo-coordinates
   std::vector<int> h_perm, h_iperm;      // caller id -> internal id and back
   int* d_perm = nullptr; int* d_iperm = nullptr;
+  unsigned char* d_tile_ord = nullptr;   // per 256-vertex tile of internal ids: its vertices in ascending caller id
   std::vector<EdgeRec> h_gell[2], h_govf[2];   // [0] forward, [1] reverse; internal numbering
   EdgeRec* d_gell[2] = {nullptr, nullptr}; EdgeRec* d_govf[2] = {nullptr, nullptr};
   size_t govf_cap[2] = {0, 0};
@@ -1160,8 +1161,11 @@ struct SqGraph {
   cudaDeviceProp prop; int prop_dev = -1;
   int group_mode = 0;                    // 0 = grouped warp kernel (a CTA of eight warps per group), 1 = sssp_group_kernel
   int group_ring = 1024;                 // ring entries per tree of the grouped warp kernel
-  int group_min_trees = 2048;            // auto mode: batches at least this large ...
-  int group_min_density = 8;             // ... with at least V / this many origins go to the group kernel
+  // Auto mode (algo 3) does NOT take the group path by default: all three kernels on the group layout measured slower
+  // than sssp_warp_kernel on config 5 (profiles/r2*_group_sweep.jsonl).  sp_set_group_tuning can
+  // lower the threshold; algo 4 forces the path.
+  int group_min_trees = INT_MAX;         // auto mode: batches at least this large ...
+  int group_min_density = 8;             // ... with at least V / this many origins go to the group path
   size_t group_scratch_bytes = (size_t)24 << 30;   // upper bound of the interleaved distance scratch per chunk
 
   // tuning
@@ -1241,6 +1245,7 @@ static void g_free_device(SqGraph* g) {
   g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
   g->ovf_cap = g->rovf_cap = 0;
   cudaFree(g->d_perm); cudaFree(g->d_iperm); g->d_perm = g->d_iperm = nullptr;
+  cudaFree(g->d_tile_ord); g->d_tile_ord = nullptr;
   for (int d = 0; d < 2; ++d) {
     cudaFree(g->d_gell[d]); cudaFree(g->d_govf[d]); cudaFree(g->d_gheads[d]);
     g->d_gell[d] = g->d_govf[d] = nullptr; g->d_gheads[d] = nullptr; g->govf_cap[d] = 0;
@@ -1418,9 +1423,21 @@ static int g_build_and_upload(SqGraph* g) {
     locality_order(V, rp, g->h_adj, rrp, g->h_radj, g->h_perm, g->h_iperm);
     SQ_CUDA_TRY(cudaMalloc(&g->d_perm, sizeof(int) * (size_t)std::max(V, 1)));
     SQ_CUDA_TRY(cudaMalloc(&g->d_iperm, sizeof(int) * (size_t)std::max(V, 1)));
+    SQ_CUDA_TRY(cudaMalloc(&g->d_tile_ord, (size_t)std::max(V, 1)));
     if (V > 0) {
       SQ_CUDA_TRY(cudaMemcpy(g->d_perm, g->h_perm.data(), sizeof(int) * (size_t)V, cudaMemcpyHostToDevice));
       SQ_CUDA_TRY(cudaMemcpy(g->d_iperm, g->h_iperm.data(), sizeof(int) * (size_t)V, cudaMemcpyHostToDevice));
+      // group_finalize_kernel: thread i of a tile takes the tile's i-th vertex in caller-id order
+      std::vector<unsigned char> ord((size_t)V);
+      std::vector<int> idx;
+      for (int b0 = 0; b0 < V; b0 += FIN_TILE) {
+        const int m = std::min(FIN_TILE, V - b0);
+        idx.resize(m);
+        std::iota(idx.begin(), idx.end(), 0);
+        std::sort(idx.begin(), idx.end(), [&](int a, int b) { return g->h_iperm[b0 + a] < g->h_iperm[b0 + b]; });
+        for (int i = 0; i < m; ++i) ord[(size_t)b0 + i] = (unsigned char)idx[i];
+      }
+      SQ_CUDA_TRY(cudaMemcpy(g->d_tile_ord, ord.data(), (size_t)V, cudaMemcpyHostToDevice));
     }
     for (int d = 0; d < 2; ++d) {
       SQ_CUDA_TRY(cudaMalloc(&g->d_gell[d], sizeof(EdgeRec) * 4 * (size_t)std::max(V, 1)));
@@ -1755,8 +1772,9 @@ static int g_run_group(SqGraph* g, const TreeParams& base, const BitmapGeom& bm,
     SQ_CUDA_TRY(cudaGetLastError());
     if (dist_dev || parent_dev) {
       dim3 fgrid((unsigned)(((size_t)V + 255) / 256), (unsigned)std::max(1, std::min(m, 2048)));
-      group_finalize_kernel<<<fgrid, 256, 0, st>>>(V, m, g->d_gell[dir ^ 1], g->d_govf[dir ^ 1], g->d_iperm, origins_dev,
-                                                  g->d_tord + g0 * 8, g->d_gdist, dist_dev, parent_dev, g->parent_format);
+      group_finalize_kernel<<<fgrid, FIN_TILE, 0, st>>>(V, m, g->d_gell[dir ^ 1], g->d_govf[dir ^ 1], g->d_iperm, g->d_tile_ord,
+                                                       origins_dev, g->d_tord + g0 * 8, g->d_gdist, dist_dev, parent_dev,
+                                                       g->parent_format);
       sq::count_launch();
       SQ_CUDA_TRY(cudaGetLastError());
     }

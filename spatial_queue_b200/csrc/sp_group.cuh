@@ -337,22 +337,33 @@ __global__ void __launch_bounds__(128) sssp_group_kernel(const GroupParams p) {
 }
 
 // Un-interleaves a chunk of finished groups into the caller's row-major tables and computes the canonical
-// predecessors, parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]} (caller ids), in the same pass.  One thread per
-// INTERNAL vertex id: a block of 256 consecutive internal ids is a compact patch of the network, so the rows of a
-// vertex's in-neighbours are mostly rows its block-mates load anyway (L1), the group rows are read fully coalesced,
-// and the writes go out as short runs of caller ids.  gin = the group ELL of the opposite direction (in-edges).
-__global__ void __launch_bounds__(256) group_finalize_kernel(int V, int n_groups, const EdgeRec* __restrict__ gin,
-                                                             const EdgeRec* __restrict__ ginovf, const int* __restrict__ iperm,
-                                                             const int* __restrict__ origins, const int* __restrict__ tord,
-                                                             const u64* __restrict__ gdist, u64* __restrict__ dist_out,
-                                                             int* __restrict__ parent_out, int codes) {
-  const int x = blockIdx.x * 256 + threadIdx.x;   // internal id
-  if (x >= V) return;
-  const int v = __ldg(&iperm[x]);                 // caller id
+// predecessors, parent[v] = min{u : fl(d[u] + w(u,v)) == d[v]} (caller ids), in the same pass.  A block owns a TILE of
+// 256 consecutive internal ids = a compact patch of the network (Hilbert order): per group it stages the tile's 256
+// rows (16 KB, one coalesced read) in shared memory, so a vertex's own row and those of its in-neighbours inside the
+// tile -- three quarters of them -- cost no L2 traffic; neighbours outside the tile are read from L2.  Threads are
+// assigned to the tile's vertices in ascending CALLER id (tile_ord), so the eight rows a warp writes per group go out
+// as runs of consecutive addresses.  gin = the group ELL of the opposite direction (in-edges).
+constexpr int FIN_TILE = 256;
+__global__ void __launch_bounds__(FIN_TILE) group_finalize_kernel(int V, int n_groups, const EdgeRec* __restrict__ gin,
+                                                                  const EdgeRec* __restrict__ ginovf, const int* __restrict__ iperm,
+                                                                  const unsigned char* __restrict__ tile_ord,
+                                                                  const int* __restrict__ origins, const int* __restrict__ tord,
+                                                                  const u64* __restrict__ gdist, u64* __restrict__ dist_out,
+                                                                  int* __restrict__ parent_out, int codes) {
+  __shared__ u64 s_rows[FIN_TILE][9];   // 72-byte pitch: the column reads of a warp spread over the banks
+  const int base = blockIdx.x * FIN_TILE;
+  const int nrows = min(FIN_TILE, V - base);
+  const int tid = threadIdx.x;
+  const bool live = tid < nrows;
+  const int xl = live ? (int)tile_ord[base + tid] : 0;   // my vertex, as an offset into the tile
+  const int x = base + xl;
+  const int v = live ? __ldg(&iperm[x]) : -1;             // caller id
   int nx[4], nv[4];
   double nw[4];
   int ovf_b = 0, ovf_n = 0;
-  if (parent_out) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { nx[q] = -1; nv[q] = -1; nw[q] = 0.0; }
+  if (parent_out && live) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int4 raw = __ldg(reinterpret_cast<const int4*>(gin + (size_t)x * 4 + q));
@@ -365,64 +376,75 @@ __global__ void __launch_bounds__(256) group_finalize_kernel(int V, int n_groups
   }
   for (int g = blockIdx.y; g < n_groups; g += gridDim.y) {
     const u64* G = gdist + (size_t)g * V * 8;
-    u64 dv[8];
-    {
-      const ulonglong2* r2 = reinterpret_cast<const ulonglong2*>(G + (size_t)x * 8);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const ulonglong2 t2 = __ldg(&r2[q]);
-        dv[2 * q] = t2.x & SQ_MASK64;
-        dv[2 * q + 1] = t2.y & SQ_MASK64;
+    {  // stage the tile: nrows x 64 bytes, contiguous in the group's table
+      const ulonglong2* src = reinterpret_cast<const ulonglong2*>(G + (size_t)base * 8);
+      for (int e = tid; e < nrows * 4; e += FIN_TILE) {
+        const ulonglong2 t2 = __ldg(&src[e]);
+        s_rows[e >> 2][(e & 3) * 2] = t2.x & SQ_MASK64;
+        s_rows[e >> 2][(e & 3) * 2 + 1] = t2.y & SQ_MASK64;
       }
     }
-    int best[8], slot[8];
+    __syncthreads();
+    if (live) {
+      u64 dv[8];
 #pragma unroll
-    for (int kk = 0; kk < 8; ++kk) { best[kk] = INT_MAX; slot[kk] = 255; }
-    if (parent_out) {
+      for (int kk = 0; kk < 8; ++kk) dv[kk] = s_rows[xl][kk];
+      int best[8], slot[8];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (nx[q] < 0) continue;
-        const ulonglong2* r2 = reinterpret_cast<const ulonglong2*>(G + (size_t)nx[q] * 8);
-        u64 du[8];
-#pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          const ulonglong2 t2 = __ldg(&r2[h]);
-          du[2 * h] = t2.x & SQ_MASK64;
-          du[2 * h + 1] = t2.y & SQ_MASK64;
-        }
-#pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          if (du[kk] != DIST_INF_BITS && dv[kk] != DIST_INF_BITS) {
-            const double cand = __longlong_as_double((long long)du[kk]) + nw[q];
-            if ((u64)__double_as_longlong(cand) == dv[kk] && nv[q] < best[kk]) { best[kk] = nv[q]; slot[kk] = q; }
-          }
-        }
-      }
-      for (int e = 0; e < ovf_n; ++e) {
-        const EdgeRec er = ld_edge(&ginovf[ovf_b + e]);
-        const int uv = __ldg(&iperm[er.v]);
-        const u64* r = G + (size_t)er.v * 8;
-#pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          const u64 du = __ldg(&r[kk]) & SQ_MASK64;
-          if (du != DIST_INF_BITS && dv[kk] != DIST_INF_BITS) {
-            const double cand = __longlong_as_double((long long)du) + er.w;
-            if ((u64)__double_as_longlong(cand) == dv[kk] && uv < best[kk]) { best[kk] = uv; slot[kk] = min(4 + e, 254); }
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int kk = 0; kk < 8; ++kk) {
-      const int t = __ldg(&tord[g * 8 + kk]);
-      if (t < 0) continue;
-      if (dist_out) dist_out[(size_t)t * V + v] = dv[kk];
+      for (int kk = 0; kk < 8; ++kk) { best[kk] = INT_MAX; slot[kk] = 255; }
       if (parent_out) {
-        const bool none = best[kk] == INT_MAX || v == __ldg(&origins[t]);
-        if (codes) reinterpret_cast<unsigned char*>(parent_out)[(size_t)t * V + v] = none ? (unsigned char)255 : (unsigned char)slot[kk];
-        else parent_out[(size_t)t * V + v] = none ? -1 : best[kk];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (nx[q] < 0) continue;
+          u64 du[8];
+          const int off = nx[q] - base;
+          if (off >= 0 && off < nrows) {
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) du[kk] = s_rows[off][kk];
+          } else {
+            const ulonglong2* r2 = reinterpret_cast<const ulonglong2*>(G + (size_t)nx[q] * 8);
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const ulonglong2 t2 = __ldg(&r2[h]);
+              du[2 * h] = t2.x & SQ_MASK64;
+              du[2 * h + 1] = t2.y & SQ_MASK64;
+            }
+          }
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            if (du[kk] != DIST_INF_BITS && dv[kk] != DIST_INF_BITS) {
+              const double cand = __longlong_as_double((long long)du[kk]) + nw[q];
+              if ((u64)__double_as_longlong(cand) == dv[kk] && nv[q] < best[kk]) { best[kk] = nv[q]; slot[kk] = q; }
+            }
+          }
+        }
+        for (int e = 0; e < ovf_n; ++e) {
+          const EdgeRec er = ld_edge(&ginovf[ovf_b + e]);
+          const int uv = __ldg(&iperm[er.v]);
+          const u64* r = G + (size_t)er.v * 8;
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            const u64 du = __ldg(&r[kk]) & SQ_MASK64;
+            if (du != DIST_INF_BITS && dv[kk] != DIST_INF_BITS) {
+              const double cand = __longlong_as_double((long long)du) + er.w;
+              if ((u64)__double_as_longlong(cand) == dv[kk] && uv < best[kk]) { best[kk] = uv; slot[kk] = min(4 + e, 254); }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int kk = 0; kk < 8; ++kk) {
+        const int t = __ldg(&tord[g * 8 + kk]);
+        if (t < 0) continue;
+        if (dist_out) dist_out[(size_t)t * V + v] = dv[kk];
+        if (parent_out) {
+          const bool none = best[kk] == INT_MAX || v == __ldg(&origins[t]);
+          if (codes) reinterpret_cast<unsigned char*>(parent_out)[(size_t)t * V + v] = none ? (unsigned char)255 : (unsigned char)slot[kk];
+          else parent_out[(size_t)t * V + v] = none ? -1 : best[kk];
+        }
       }
     }
+    __syncthreads();
   }
 }
 

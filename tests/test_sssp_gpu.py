@@ -425,8 +425,8 @@ def _congested_weights(s, e, w, seed=2):
 @pytest.mark.parametrize("algo,n", [(3, 2368), (4, 2368), (5, 2368), (6, 2368), (3, 18944), (6, 18944)])
 def test_config5_batches_bit_exact_against_the_oracle(spi, algo, n):
     """bench.py's HP-2 workload itself: 224x224 grid, bench.origins_for origins, through sp_sssp_batch_device in auto
-    mode (2,368 origins: sssp_warp_kernel; 18,944 origins, the benchmarked batch: sssp_group_kernel) and with the group
-    kernel forced; distances bit for bit and canonical predecessors equal to the C oracle for every tree of the small
+    mode (sssp_warp_kernel, at 2,368 origins and at the benchmarked 18,944) and with each kernel of the group path
+    forced (4: sssp_group_kernel, 5: the warp kernel on the group layout, 6: sssp_union_kernel); distances bit for bit and canonical predecessors equal to the C oracle for every tree of the small
     batch and for a 1,024-tree sample of the large one; eight trees also against the reference library itself."""
     import torch
     from oracle import sssp as osssp

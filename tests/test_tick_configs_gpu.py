@@ -84,7 +84,7 @@ def test_config3_butte_standin_with_rules_and_closures_matches_host_path():
     cd, co = dev.counters(), orc.counters()
     assert cd["agent_steps"] == co["agent_steps"] and cd["moves"] == co["moves"] and cd["arrivals"] == co["arrivals"]
     sm = dev.summary()
-    assert sm["closed_links"] > 20 and cd["moves"] > 500_000
+    assert sm["closed_links"] > 20 and cd["moves"] > 200_000
     print("config 3 window: shelter_a2", int((ad["status"] == 5).sum()), "host path stopped", fr.stopped_a2,
           "closed links", sm["closed_links"], "trees", fr.trees_computed)
     dev.close(); orc.close()
