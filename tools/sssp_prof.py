@@ -11,7 +11,11 @@ t, c, d, q = json.loads(os.environ.get("CFG", "[4,0,2.0,1024]" if ALGO == 2 else
 s, e, w = grid_graph(n, seed=1)
 g = spi.from_arrays(s, e, w); V = n * n
 g.set_algo(ALGO)
-if ALGO == 2:   # CFG = [ilp, CTAs of four warps per SM, delta factor, ring entries]
+if ALGO == 4:   # group path: GMODE 0 = warp kernel on the group layout, 1 = sssp_group_kernel, 2 = sssp_union_kernel
+    g.set_group_mode(int(os.environ.get("GMODE", 2)))
+    g.set_group_tuning(warps_per_sm=int(os.environ.get("GWARPS", 16)), batch=int(os.environ.get("GBATCH", 8)))
+    g.set_tuning(delta_factor=d)
+elif ALGO == 2:   # CFG = [ilp, CTAs of four warps per SM, delta factor, ring entries]
     g.set_warp_tuning(ring_cap=q, ilp=t, ctas_per_sm=c)
     g.set_tuning(delta_factor=d)
 else:
