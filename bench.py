@@ -395,7 +395,7 @@ def run_sweep(args, torch, dist, g, V, E, rank, world, peak):
             ms = float(tm.item())
         tps = Btot / (ms / 1e3)
         n_sm = torch.cuda.get_device_properties(0).multi_processor_count
-        kernel = "sssp_warp_kernel" if n >= 6 * n_sm else "sssp_ell_kernel"
+        kernel = "sssp_warp_kernel" if n >= 13 * n_sm else "sssp_ell_kernel"
         points.append({"total_origins": Btot, "origins_per_gpu": n, "ms_per_step": ms, "trees_per_s": tps,
                        "frac_of_one_gpu_roofline": tps * bytes_per_tree / (peak * 1e9) / world, "kernel": kernel})
         del dist_dev, par_dev, gathered

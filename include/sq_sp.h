@@ -141,7 +141,7 @@ int sp_sync(Graph* graph);
  * current), shared-memory queue slots per queue of the bitmap kernel (0 = default). */
 int sp_set_tuning(Graph* graph, int threads, int ctas_per_sm, double delta_factor, int smem_queue);
 
-/* Kernel choice: 3 (default) = auto: the warp kernel for batches of at least six trees per SM (the group path, 4, only
+/* Kernel choice: 3 (default) = auto: the warp kernel for batches of at least 13 trees per SM (the group path, 4, only
  * if sp_set_group_tuning sets a batch-size threshold), the ELL kernel
  * below that (a lone tree finishes ~10x sooner on a whole CTA); if more than 5 % of a batch's trees overflow the
  * warp kernel's ring, the next batches use a 2048-entry ring and, failing that, the ELL kernel; 2 = warp kernel (one tree per warp, four-byte
@@ -166,6 +166,9 @@ int sp_set_group_tuning(Graph* graph, int warps_per_sm, int batch, int prefetch,
  * frontier, 64-bit atomics on the interleaved rows and `batch` (sp_set_group_tuning: 4, 8 or 16) pops in flight; two
  * bits per vertex per warp in shared memory bound it to about 400k vertices (larger graphs run mode 1). */
 int sp_set_group_mode(Graph* graph, int mode, int ring_cap);
+/* Auto mode, batches of at most one tree per SM (the device router's reverse tree per destination): keep each tree's
+ * distance row in shared memory while it is computed (graphs of up to ~25.7k vertices on B200); 1 = on (default), 0 = off. */
+int sp_set_smem_rows(Graph* graph, int on);
 
 /* Warp-kernel knobs: ring capacity in entries (rounded up to a power of two; 0 keeps; default 1024), frontier
  * vertices per step = 8 x ilp (1, 2 or 4; 0 keeps; default 4), CTAs of four warps per SM (0 = default 4, at most

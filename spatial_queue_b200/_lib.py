@@ -65,6 +65,7 @@ def _declare(L):
     L.sp_set_warp_tuning.restype = ci; L.sp_set_warp_tuning.argtypes = [vp, ci, ci, ci]
     L.sp_set_group_tuning.restype = ci; L.sp_set_group_tuning.argtypes = [vp, ci, ci, ci, ci, ci]
     L.sp_set_group_mode.restype = ci; L.sp_set_group_mode.argtypes = [vp, ci, ci]
+    L.sp_set_smem_rows.restype = ci; L.sp_set_smem_rows.argtypes = [vp, ci]
     L.sp_last_stats.restype = ci; L.sp_last_stats.argtypes = [vp, vp]
     L.sp_last_error.restype = C.c_char_p; L.sp_last_error.argtypes = []
     L.sp_kernel_launches.restype = C.c_longlong; L.sp_kernel_launches.argtypes = []

@@ -422,9 +422,15 @@ __device__ __forceinline__ void cta_push2(bool w0, int2 v0, u64 d0, bool w1, int
   if (w1) q.put(base + c0 + __popc(m1 & lt), v1, d1, gcap, fail);
 }
 
-template <int NW>
-__global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreeParams p) {
+// SD: the tree's distance row lives in SHARED memory for the whole tree (V x 8 bytes next to the queues: up to ~25.7k
+// vertices in B200's 227 KB) and is copied to the caller's row at the end.  A lone tree per SM -- the device router's
+// one reverse tree per destination at every weight refresh -- is bound by its ~330 dependent rounds, and half of a
+// round was the two L2 round trips for dist[u] and the atomicMin; with the row in shared memory a
+// round waits for the ELL record only.
+template <int NW, bool SD>
+__global__ void __launch_bounds__(NW * 32, SD ? 1 : 32 / NW) sssp_ell_kernel(const TreeParams p) {
   constexpr int THREADS = NW * 32;
+  extern __shared__ __align__(16) u64 s_dist_row[];
   __shared__ int2 s_qv[4][QS];
   __shared__ u64 s_qd[4][QS];
   __shared__ int s_cnt[4];   // one counter per physical queue
@@ -460,7 +466,9 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
     const int tree = s_tree;
     if (tree >= p.n_trees) break;
 
-    u64* dist = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)blockIdx.x * V;
+    u64* dist_g = p.dist_out ? p.dist_out + (size_t)tree * V : p.dist_scratch + (size_t)blockIdx.x * V;
+    u64* dist = SD ? s_dist_row : dist_g;
+    auto LD = [&](const u64* q) -> u64 { return SD ? *reinterpret_cast<const volatile u64*>(q) : sq::ld_cg_u64(q); };
     const int src = p.origins[tree];
     const bool valid = (src >= 0 && src < V);
 
@@ -524,7 +532,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
               if (i < nf) {
                 v = ld_cg_int2(&fiv[i]);
                 d = sq::ld_cg_u64(&fid[i]);
-                if (sq::ld_cg_u64(&dist[v.x]) == d) {  // else stale: a newer entry exists
+                if (LD(&dist[v.x]) == d) {  // else stale: a newer entry exists
                   if (__longlong_as_double((long long)d) < T2) to_b = true;
                   else { to_f = true; lmin = d < lmin ? d : lmin; }
                 }
@@ -586,7 +594,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
           rec[j].w = 0.0; rec[j].v = -1; rec[j].pad = 0;
           dnow[j] = 0ull;
           if (act[j]) {
-            dnow[j] = sq::ld_cg_u64(&dist[u[j]]);
+            dnow[j] = LD(&dist[u[j]]);
             const int4 raw = __ldg(reinterpret_cast<const int4*>(&p.ell[(size_t)u[j] * 4 + slot]));
             rec[j].w = __hiloint2double(raw.y, raw.x);
             rec[j].v = raw.z;
@@ -665,6 +673,10 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) sssp_ell_kernel(const TreePa
       ++st_rounds;
     }
     __syncthreads();
+    if (SD && (p.dist_out || p.dist_scratch)) {
+      // the finished row goes out in one coalesced pass (the predecessor kernel and the caller read it from there)
+      for (int i = tid; i < V; i += THREADS) dist_g[i] = dist[i];
+    }
 
     if (s_fail) {
       // queue capacity exceeded: hand the tree to the bitmap kernel (its queues cannot overflow)
@@ -1159,6 +1171,7 @@ struct SqGraph {
   int g_warps = 0, g_ring_cap = 0, g_pend_cap = 0, g_words = 0;
   int group_warps_per_sm = 16, group_pb = 16, group_pf = 1;
   cudaDeviceProp prop; int prop_dev = -1;
+  int ell_smem_row = 1;                  // auto mode: lone trees keep their distance row in shared memory when it fits
   int group_mode = 0;                    // 0 = grouped warp kernel (a CTA of eight warps per group), 1 = sssp_group_kernel
   int group_ring = 1024;                 // ring entries per tree of the grouped warp kernel
   // Auto mode (algo 3) does NOT take the group path by default: all three kernels on the group layout measured slower
@@ -1569,14 +1582,43 @@ static int launch_bitmap_kernel(SqGraph* g, TreeParams& p, int grid, size_t smem
   }
 }
 
-static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t st) {
+// Largest V whose distance row fits next to the ELL kernel's static queues in one CTA's shared memory.
+static size_t ell_smem_row_bytes(const cudaDeviceProp& prop) {
+  cudaFuncAttributes fa;
+  if (cudaFuncGetAttributes(&fa, sssp_ell_kernel<32, true>) != cudaSuccess) { cudaGetLastError(); return 0; }
+  const size_t have = prop.sharedMemPerBlockOptin;
+  return have > fa.sharedSizeBytes + 256 ? (have - fa.sharedSizeBytes - 256) & ~(size_t)15 : 0;
+}
+static size_t ell_smem_row_limit(const cudaDeviceProp& prop) { return ell_smem_row_bytes(prop) / sizeof(u64); }
+
+static int launch_ell_kernel(TreeParams& p, int grid, int threads, cudaStream_t st, bool smem_row = false,
+                             const cudaDeviceProp* prop = nullptr) {
+  if (smem_row) {
+    // a lone tree per SM with its distance row in shared memory (1024 threads)
+    const size_t bytes = sizeof(u64) * (size_t)p.V;
+    static bool attr_set[SQ_MAX_DEVICES] = {false};
+    int dev = 0;
+    SQ_CUDA_TRY(cudaGetDevice(&dev));
+    {
+      std::lock_guard<std::mutex> lock(g_attr_mutex);
+      if (dev < 0 || dev >= SQ_MAX_DEVICES || !attr_set[dev]) {
+        SQ_CUDA_TRY(cudaFuncSetAttribute(sssp_ell_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)ell_smem_row_bytes(*prop)));
+        if (dev >= 0 && dev < SQ_MAX_DEVICES) attr_set[dev] = true;
+      }
+    }
+    sssp_ell_kernel<32, true><<<grid, 1024, bytes, st>>>(p);
+    sq::count_launch();
+    SQ_CUDA_TRY(cudaGetLastError());
+    return SQ_OK;
+  }
   switch (threads) {
-    case 32: sssp_ell_kernel<1><<<grid, 32, 0, st>>>(p); break;
-    case 64: sssp_ell_kernel<2><<<grid, 64, 0, st>>>(p); break;
-    case 128: sssp_ell_kernel<4><<<grid, 128, 0, st>>>(p); break;
-    case 256: sssp_ell_kernel<8><<<grid, 256, 0, st>>>(p); break;
-    case 512: sssp_ell_kernel<16><<<grid, 512, 0, st>>>(p); break;
-    case 1024: sssp_ell_kernel<32><<<grid, 1024, 0, st>>>(p); break;
+    case 32: sssp_ell_kernel<1, false><<<grid, 32, 0, st>>>(p); break;
+    case 64: sssp_ell_kernel<2, false><<<grid, 64, 0, st>>>(p); break;
+    case 128: sssp_ell_kernel<4, false><<<grid, 128, 0, st>>>(p); break;
+    case 256: sssp_ell_kernel<8, false><<<grid, 256, 0, st>>>(p); break;
+    case 512: sssp_ell_kernel<16, false><<<grid, 512, 0, st>>>(p); break;
+    case 1024: sssp_ell_kernel<32, false><<<grid, 1024, 0, st>>>(p); break;
     default: return sq::set_error(SQ_ERR_ARG, "ELL kernel: threads must be 32 ... 1024, a power of two (got %d)", threads);
   }
   sq::count_launch();
@@ -1893,9 +1935,11 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
   // ---- warp kernel (algo 2, default) or ELL kernel (algo 0) -------------------------------------------
   int vbits = 1;
   while ((1ll << vbits) < (long long)V) ++vbits;
-  // auto (3): a warp per tree wins on throughput once every SM has several trees per scheduler; below that the
-  // CTA-per-tree ELL kernel finishes a tree ~10x sooner (the router's 8 trees per weight refresh)
-  const bool want_warp = g->algo == 2 || (g->algo == 3 && n >= 6 * n_sm && !g->auto_warp_unfit);
+  // auto (3): a warp per tree wins on throughput once its 16 warp slots per SM are mostly filled; below ~13 trees per SM
+  // the CTA-per-tree ELL kernel is faster (r2 sweep, config 5: 512 trees 286 k/s and full batches 345 k/s on the ELL
+  // kernel; the warp kernel 220 k/s at 1,024 trees, 353 k/s at 2,048, 390 k/s from 2,368 on) and finishes a lone tree
+  // ~10x sooner (the router's 8 trees per weight refresh)
+  const bool want_warp = g->algo == 2 || (g->algo == 3 && n >= 13 * n_sm && !g->auto_warp_unfit);
   const bool use_warp = want_warp && vbits <= 24;   // >= 5 hash bits per queue entry
   // a handful of trees (the device router's one per destination): the GPU is empty, so give each tree a whole
   // SM's worth of threads; a round is then one or two passes over the wavefront instead of five
@@ -1999,7 +2043,9 @@ static int g_run_batch_device(SqGraph* g, const int* origins_dev, int n, u64* di
     sq::count_launch();
     SQ_CUDA_TRY(cudaGetLastError());
   } else {
-    if (int rc = launch_ell_kernel(p, grid, threads, st)) return rc;
+    // a handful of trees on an empty GPU whose vertex count fits: distance rows in shared memory
+    const bool smem_row = g->algo == 3 && g->ell_smem_row && n <= n_sm && threads == 1024 && (size_t)V <= ell_smem_row_limit(prop);
+    if (int rc = launch_ell_kernel(p, grid, threads, st, smem_row, &prop)) return rc;
   }
   // fallback pass over the trees whose queues overflowed (normally none: its CTAs exit at once)
   if (bitmap_fits) {
@@ -2229,6 +2275,12 @@ int sp_set_warp_tuning(Graph* g, int ring_cap, int ilp, int ctas_per_sm) {
   if (ring_cap > 0) g->warp_ring = ring_cap;
   if (ilp > 0) g->warp_ilp = ilp;
   if (ctas_per_sm >= 0) g->warp_ctas_per_sm = ctas_per_sm;
+  return SQ_OK;
+}
+
+int sp_set_smem_rows(Graph* g, int on) {
+  if (!g) return sq::set_error(SQ_ERR_ARG, "sp_set_smem_rows: null graph");
+  g->ell_smem_row = on ? 1 : 0;
   return SQ_OK;
 }
 

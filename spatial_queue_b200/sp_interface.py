@@ -139,6 +139,10 @@ class Graph:
         check(lib().sp_set_group_tuning(self._h, int(warps_per_sm), int(batch), int(prefetch), int(min_trees),
                                         int(min_density)), "sp_set_group_tuning")
 
+    def set_smem_rows(self, on=True):
+        """Lone trees keep their distance row in shared memory when the graph fits (include/sq_sp.h)."""
+        check(lib().sp_set_smem_rows(self._h, 1 if on else 0), "sp_set_smem_rows")
+
     def set_group_mode(self, mode=0, ring_cap=0):
         """0 = grouped warp kernel (default), 1 = sssp_group_kernel; see include/sq_sp.h."""
         check(lib().sp_set_group_mode(self._h, int(mode), int(ring_cap)), "sp_set_group_mode")

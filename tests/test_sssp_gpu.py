@@ -68,7 +68,8 @@ def test_network_mtx_golden(spi):
                                                       (1, 1024, 2, 0), (2, 64, 2, 0), (4, 256, 2, 0),    # warp kernel: (ilp, ring)
                                                       (8, 0, 4, 0), (16, 1, 4, 0), (32, 1, 4, 0),         # group kernel: (batch, prefetch)
                                                       (2, 64, 5, 0), (4, 1024, 5, 0),                     # grouped warp kernel: (ilp, ring)
-                                                      (4, 0, 6, 0), (8, 0, 6, 0), (16, 0, 6, 0)])         # union kernel: pops in flight
+                                                      (4, 0, 6, 0), (8, 0, 6, 0), (16, 0, 6, 0),          # union kernel: pops in flight
+                                                      (256, 0, 3, 0)])    # auto: a handful of trees -> distance rows in shared memory
 def test_random_graphs_bit_exact(spi, directed, threads, smemq, algo, qfac):
     from oracle import sssp as osssp
     rng = np.random.default_rng(11 + threads)
@@ -190,8 +191,8 @@ def test_grid_batch_and_device_api(spi, algo):
     g.set_algo(min(algo, 4))
     g.set_group_mode({4: 1, 6: 2}.get(algo, 0))
     og = osssp.OracleGraph(s, e, w)
-    # 1000 origins: above the auto switch-over (six trees per SM), so algo 3 runs the warp kernel here
-    origins = np.random.default_rng(2).permutation(n * n)[:1000].astype(np.int32)
+    # 2000 origins: above the auto switch-over (13 trees per SM), so algo 3 runs the warp kernel here
+    origins = np.random.default_rng(2).permutation(n * n)[:2000].astype(np.int32)
     o_dev = torch.from_numpy(origins).cuda()
     d_dev = torch.empty((len(origins), n * n), dtype=torch.float64, device="cuda")
     p_dev = torch.empty((len(origins), n * n), dtype=torch.int32, device="cuda")
@@ -311,7 +312,7 @@ def test_one_byte_predecessor_codes_decode_to_the_same_trees(spi, reverse, algo)
 
 
 def test_auto_mode_learns_from_ring_overflows(spi):
-    """Auto kernel choice on a graph whose wavefronts outgrow the warp kernel's ring (a dense random graph, 1000
+    """Auto kernel choice on a graph whose wavefronts outgrow the warp kernel's ring (a dense random graph, 2000
     origins): the first batch hands trees to the fallback kernel, the following ones run with a larger ring or on the
     ELL kernel; every batch is bit-exact."""
     from oracle import sssp as osssp
@@ -323,7 +324,7 @@ def test_auto_mode_learns_from_ring_overflows(spi):
     g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
     g.set_warp_tuning(ring_cap=64)
     og = osssp.OracleGraph(s, e, w, max_vertex_id=V - 1)
-    origins = rng.integers(0, V, 1000).astype(np.int32)
+    origins = rng.integers(0, V, 2000).astype(np.int32)
     do, po = og.sssp_batch(origins)
     overflows = []
     for _ in range(4):
@@ -563,4 +564,35 @@ def test_host_batch_with_one_byte_codes_decodes_to_the_int32_tables(spi, reverse
     assert (g.decode_parents_host(c1, reverse=reverse) == p0).all()
     _, c2 = g.sssp_batch_codes(origins, reverse=reverse)
     assert (c2 == c1).all()
+    g.free()
+
+
+def test_lone_trees_with_shared_memory_rows_equal_global_rows(spi):
+    """Auto mode on a handful of trees (the device router's reverse tree per destination): sssp_ell_kernel keeps the
+    distance row in shared memory when the graph fits (config 4's 25,281 vertices do).  Same tables with the switch off,
+    forward and reverse, closed links included; and a graph one vertex too many for the row falls back by itself."""
+    import torch
+    from oracle import sssp as osssp
+    s, e, w = grid_graph(159, seed=1)
+    V = 159 * 159
+    rng = np.random.default_rng(3)
+    w = w.copy()
+    w[rng.random(len(w)) < 0.01] = 1e8
+    g = spi.from_arrays(s, e, w, max_vertex_id=V - 1)
+    dests = np.array([0, 158, V - 1, V - 159, 79, 79 * 159, V - 80, 80 * 159 - 1], np.int32)
+    for reverse in (False, True):
+        d1, p1 = g.sssp_batch(dests, reverse=reverse)
+        g.set_smem_rows(False)
+        d0, p0 = g.sssp_batch(dests, reverse=reverse)
+        g.set_smem_rows(True)
+        assert d1.tobytes() == d0.tobytes() and (p1 == p0).all()
+        og = osssp.OracleGraph(e, s, w, max_vertex_id=V - 1) if reverse else osssp.OracleGraph(s, e, w, max_vertex_id=V - 1)
+        do, po = og.sssp_batch(dests)
+        assert d1.tobytes() == do.tobytes() and (p1 == po).all()
+    g.free()
+    s, e, w = grid_graph(162, seed=1)          # 26,244 vertices: the row does not fit any more
+    g = spi.from_arrays(s, e, w)
+    d, p = g.sssp_batch(dests)
+    do, po = osssp.OracleGraph(s, e, w).sssp_batch(dests)
+    assert d.tobytes() == do.tobytes() and (p == po).all()
     g.free()
