@@ -18,6 +18,9 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 TICKS=700 timeout 600 python tools/tick_prof.py > $O/tick_prof_plain.log 2>&1 && \
 TICKS=700 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 1200 -c 900 --csv \
   --log-file $O/tick_launches.csv python tools/tick_prof.py > $O/ncu_tick_launches.log 2>&1
+CASE=c3 TICKS=3400 timeout 600 python tools/tick_prof.py > $O/tick_c3_prof_plain.log 2>&1 && \
+CASE=c3 TICKS=3400 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 9000 -c 1200 --csv \
+  --log-file $O/tick_c3_launches.csv python tools/tick_prof.py > $O/ncu_tick_c3_launches.log 2>&1
 # full captures
 BATCH=2368 timeout 300 python tools/sssp_prof.py > $O/sssp_prof_plain.log 2>&1 && \
 BATCH=2368 timeout 900 ncu --set full --clock-control none --import-source on -k regex:sssp_warp_kernel -s 1 -c 1 \
