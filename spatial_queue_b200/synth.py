@@ -325,7 +325,7 @@ def town_frames(n, seed=1, **shape):
 
 
 def town_scenario(n, n_agents, horizon=600, seed=1, n_exits=8, signals=0.04, priority=0.03, router=None,
-                  device_routes=False, exits_on_rim=False, **shape):
+                  device_routes=False, exits_on_rim=False, exits_in_core=False, **shape):
     """Irregular network + signal and priority nodes + demand from every node that can reach its exit.  Signal nodes
     alternate between the roughly north-south and the roughly east-west approaches (the source link is always
     green), priority nodes rank all their approaches in a random order."""
@@ -352,13 +352,19 @@ def town_scenario(n, n_agents, horizon=600, seed=1, n_exits=8, signals=0.04, pri
     rank[o] = np.arange(len(il)) - f.node_in_ptr[node_of[o]]
     f.node_in_prio = np.where(f.node_type[node_of] == 2, rank, -1).astype(np.int32)
 
+    candidates = np.arange(N)
+    if exits_in_core:
+        # exits the network can actually reach: nodes of the largest strongly connected component (a removed street can
+        # leave a rim node with a handful of upstream nodes; every agent bound for it would then start at one node)
+        from scipy.sparse import coo_matrix
+        from scipy.sparse.csgraph import connected_components
+        _, lab = connected_components(coo_matrix((np.ones(len(s)), (s, e)), shape=(N, N)), directed=True, connection="strong")
+        candidates = np.flatnonzero(lab == np.bincount(lab).argmax())
     if exits_on_rim:
-        # an evacuation: the exits are nodes on the rim of the network that most of it can reach
-        ii, jj = np.divmod(np.arange(N), n)
-        rim = np.flatnonzero(((ii == 0) | (ii == n - 1) | (jj == 0) | (jj == n - 1)) & (indeg >= 2))
-        exits = rng.choice(rim, n_exits, replace=False).astype(np.int64)
-    else:
-        exits = rng.choice(N, n_exits, replace=False).astype(np.int64)
+        # an evacuation: the exits are nodes on the rim of the network
+        ii, jj = np.divmod(candidates, n)
+        candidates = candidates[((ii == 0) | (ii == n - 1) | (jj == 0) | (jj == n - 1)) & (indeg[candidates] >= 2)]
+    exits = rng.choice(candidates, n_exits, replace=False).astype(np.int64)
     next_link = next_link_tables(f, exits, router)
     dslot = rng.integers(0, n_exits, n_agents)
     origin = np.empty(n_agents, np.int64)
@@ -387,14 +393,14 @@ def berkeley_standin(router=None, device_routes=False, n_agents=50_000):
     ~15k nodes -- the jittered lattice with 36 % of its streets removed, 8 % one-way, diagonals, hubs, 1-4 lanes --
     and 50,000 agents leaving over twenty minutes."""
     return town_scenario(122, n_agents, horizon=1200, seed=21, n_exits=12, router=router, device_routes=device_routes,
-                         drop=0.36, oneway=0.08, diag=0.06, hubs=4, hub_links=8)
+                         exits_in_core=True, drop=0.36, oneway=0.08, diag=0.06, hubs=4, hub_links=8)
 
 
 def butte_standin(router=None, device_routes=True, n_agents=100_000):
     """BASELINE config 3 (model/dta_meso_butte.py: 18,001 ticks, link ids up to 30,175 at :99; inputs not shipped):
     ~31k links on ~12k nodes, 100,000 evacuees leaving over two hours for six exits on the rim."""
     return town_scenario(110, n_agents, horizon=7200, seed=31, n_exits=6, router=router, device_routes=device_routes,
-                         exits_on_rim=True, drop=0.36, oneway=0.08, diag=0.06, hubs=3, hub_links=8)
+                         exits_on_rim=True, exits_in_core=True, drop=0.36, oneway=0.08, diag=0.06, hubs=3, hub_links=8)
 
 
 def butte_closure_schedule(f, seed=7, last_fire_tick=340 * 60, fire_share=0.005, p_close=0.15, reopen_after=3600):
