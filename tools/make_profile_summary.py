@@ -86,7 +86,7 @@ def full(rep, out):
 with open(os.path.join(dst, f"{tag}_launches.txt"), "w") as out:
     out.write("Per-kernel share of the step, from `ncu --metrics gpu__time_duration.sum --clock-control none` (tools/gpu_round.sh).\n"
               "Times under ncu are serialised and cold-cache: read the shares, not the absolutes.\n\n")
-    for f in ("sssp_launches.csv", "tick_launches.csv", "tick_c3_launches.csv"):
+    for f in ("sssp_launches.csv", "tick_launches.csv", "tick_c2_launches.csv", "tick_c3_launches.csv"):
         if os.path.exists(os.path.join(src, f)):
             launches(os.path.join(src, f), out)
 for f in sorted(os.listdir(src)):
