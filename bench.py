@@ -48,6 +48,29 @@ def measured_traffic(kind):
         return None
 
 
+def bind_to_gpu_numa_node(torch, local):
+    """N > 1: run this rank on the cores of its GPU's NUMA node, so that the page-locked host buffers of the e2e calls
+    (cudaHostAlloc places them where the allocating thread runs) sit behind the GPU's own root complex instead of all
+    eight ranks writing through one socket.  Returns a note for the JSON line."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return f"gpu {local}: no NUMA node reported"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"gpu {local}: NUMA node {node} has no allowed cores"
+        os.sched_setaffinity(0, cpus)
+        return f"gpu {local} -> NUMA node {node} ({len(cpus)} cores)"
+    except Exception as ex:
+        return f"not bound ({type(ex).__name__}: {ex})"
+
+
 def sssp_workload_name(n, E, V):
     """The same string in both arms (the driver compares config.workload of `ours` and `reference`)."""
     return f"config 5: batched SSSP reroute sweep, {n}x{n} grid ({E} links, {V} nodes), full trees + canonical predecessors"
@@ -442,6 +465,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback "
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa_note = bind_to_gpu_numa_node(torch, local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from spatial_queue_b200 import _lib, sp_interface as spi
@@ -660,6 +684,7 @@ def main():
                            "gather_verified": gather_ok,
                            "e2e_call": "sp_sssp_batch_codes: host origins in, one-byte predecessor codes (50 KB per tree) in "
                                        "page-locked host memory out; e2e_full = f64 distances + int32 predecessors",
+                           "host_numa": numa_note,
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
