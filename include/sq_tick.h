@@ -170,6 +170,11 @@ int sq_get_summary(SqSim* sim, int64_t* out16);
  * reference records as (in_link, None), are total_vehicles_left[in_link] minus the row sum. */
 int sq_enable_pair_moves(SqSim* sim);
 int sq_get_pair_moves(SqSim* sim, int64_t* out);
+/* Measurement aid, no reference counterpart: record %globaltimer (ns) at entry and exit of every warp of the two phase
+ * kernels for ticks [t0, t0 + n_ticks).  sq_get_timeline returns the window and the row stride (warps), then -- when
+ * out is not null -- n_ticks x 2 (link phase, node phase) x stride pairs (entry, exit); unused slots are (0, 0). */
+int sq_enable_timeline(SqSim* sim, int32_t t0, int32_t n_ticks);
+int sq_get_timeline(SqSim* sim, int32_t* n_ticks, int32_t* stride, uint64_t* out);
 /* Per link: vehicles that sheltered on it (sum over a node's in-links = node.shelter_counts); per agent: the tick
  * at which it arrived or sheltered (-1 otherwise). */
 int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick);

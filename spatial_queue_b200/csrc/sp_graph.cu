@@ -1060,11 +1060,13 @@ struct WeightSlots {
 __global__ void __launch_bounds__(256) scatter_weights_kernel(int n, int V, const double* __restrict__ w, WeightSlots ws,
                                                               EdgeRec* adj, EdgeRec* radj, EdgeRec* ell, EdgeRec* ovf,
                                                               EdgeRec* rell, EdgeRec* rovf, double* fs_w, double* rs_w,
-                                                              EdgeRec* gell, EdgeRec* govf, EdgeRec* grell, EdgeRec* grovf) {
+                                                              EdgeRec* gell, EdgeRec* govf, EdgeRec* grell, EdgeRec* grovf,
+                                                              double* __restrict__ wlog) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
   const double x = w[i];
   if (x != x) return;
+  wlog[i] = x;   // the edge log in insertion order; the host copy catches up on demand (g_pull_host_log)
   const int a = ws.adj[i];
   if (a < 0) return;
   adj[a].w = x;
@@ -1128,6 +1130,12 @@ struct SqGraph {
   int* d_fs_v = nullptr;       // slot-major forward ELL (predecessors of trees on the reversed graph)
   double* d_fs_w = nullptr;
   int* d_wslots = nullptr;     // 4 x n_log: where the weight of edge i lives (scatter_weights_kernel)
+  // sp_set_weights_device leaves the newest weights on the device only (no host round trip inside a simulation's
+  // refresh): d_wlog is the edge log's weight column while dev_leads; every host reader / editor of the log pulls first
+  double* d_wlog = nullptr;
+  size_t wlog_cap = 0;
+  bool dev_leads = false;
+  cudaStream_t lead_stream = nullptr;
   size_t wslots_n = 0;
   int2* d_q2scratch = nullptr;
   int* d_q2v = nullptr;
@@ -1237,7 +1245,23 @@ __global__ void __launch_bounds__(128) route_write_kernel(const int* __restrict_
   for (int i = len - 1; i >= 0; --i) { out[i] = v; if (i) v = parent[row + v]; }
 }
 
+// The device holds newer weights than the host log (sp_set_weights_device): bring the log and the host CSR up to date.
+static int g_pull_host_log(SqGraph* g) {
+  if (!g->dev_leads) return SQ_OK;
+  g->dev_leads = false;
+  const size_t n = g->ew.size();
+  if (n == 0) return SQ_OK;
+  SQ_CUDA_TRY(cudaStreamSynchronize(g->lead_stream));
+  SQ_CUDA_TRY(cudaMemcpy(g->ew.data(), g->d_wlog, sizeof(double) * n, cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < n && i < g->edge_slot.size(); ++i) {
+    const int a = g->edge_slot[i];
+    if (a >= 0) { g->h_adj[a].w = g->ew[i]; g->h_radj[g->edge_rslot[i]].w = g->ew[i]; }
+  }
+  return SQ_OK;
+}
+
 static void g_add_edge(SqGraph* g, int v1, int v2, double w) {
+  g_pull_host_log(g);
   if (!g->directed && v1 > v2) std::swap(v1, v2);
   const int id = (int)g->es.size();
   g->es.push_back(v1);
@@ -1254,6 +1278,7 @@ static void g_free_device(SqGraph* g) {
   cudaFree(g->d_rs_v); cudaFree(g->d_rs_w); g->d_rs_v = nullptr; g->d_rs_w = nullptr;
   cudaFree(g->d_fs_v); cudaFree(g->d_fs_w); g->d_fs_v = nullptr; g->d_fs_w = nullptr;
   cudaFree(g->d_wslots); g->d_wslots = nullptr; g->wslots_n = 0;
+  cudaFree(g->d_wlog); g->d_wlog = nullptr; g->wlog_cap = 0; g->dev_leads = false;
   g->d_row_ptr = g->d_rrow_ptr = nullptr; g->d_adj = g->d_radj = nullptr;
   g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
   g->ovf_cap = g->rovf_cap = 0;
@@ -2172,6 +2197,7 @@ bool writegraph(Graph* g, char* filename) {
     std::cout << "Write matrix market file: Output file not found\n";
     return false;
   }
+  g_pull_host_log(g);
   file << "%%MatrixMarket matrix coordinate real general\n%\n";
   file << g->nvertices << " " << g->nvertices << " " << g->key2edge.size() << "\n";
   for (const auto& kv : g->key2edge)
@@ -2187,6 +2213,7 @@ void update_edge(Graph* g, int v1, int v2, double w) {
     sq::set_error(SQ_ERR_ARG, "update_edge: no edge (%d,%d); ignored", v1, v2);
     return;
   }
+  g_pull_host_log(g);
   g->ew[it->second] = w;
   g->w_dirty = true;
 }
@@ -2196,6 +2223,7 @@ int sp_remove_edge(Graph* g, int v1, int v2) {
   if (!g->directed && v1 > v2) std::swap(v1, v2);
   auto it = g->key2edge.find(std::make_pair(v1, v2));
   if (it == g->key2edge.end()) return sq::set_error(SQ_ERR_ARG, "remove_edge: no edge (%d,%d)", v1, v2);
+  if (int rc = g_pull_host_log(g)) return rc;
   g->alive[it->second] = 0;
   g->key2edge.erase(it);
   g->topo_dirty = true;
@@ -2206,6 +2234,7 @@ int sp_set_weights(Graph* g, const double* w, int nedges) {
   if (!g || !w) return sq::set_error(SQ_ERR_ARG, "sp_set_weights: null argument");
   if (nedges != (int)g->ew.size())
     return sq::set_error(SQ_ERR_ARG, "sp_set_weights: %d weights for %d edges", nedges, (int)g->ew.size());
+  if (int rc = g_pull_host_log(g)) return rc;   // keeps the host CSR consistent; every weight is replaced below
   std::copy(w, w + nedges, g->ew.begin());
   g->w_dirty = true;
   return SQ_OK;
@@ -2347,22 +2376,24 @@ int sp_set_weights_device(Graph* g, const double* weights_dev, int nedges, void*
   cudaStream_t st = (cudaStream_t)stream;
   const size_t n = (size_t)nedges;
   WeightSlots ws{g->d_wslots, g->d_wslots + n, g->d_wslots + 2 * n, g->d_wslots + 3 * n, g->d_wslots + 4 * n, g->d_wslots + 5 * n};
+  if (!g->dev_leads) {   // first device-side refresh since the host last led: seed the device log with the host's
+    if (g->wlog_cap < n) {
+      cudaFree(g->d_wlog); g->d_wlog = nullptr;
+      SQ_CUDA_TRY(cudaMalloc(&g->d_wlog, sizeof(double) * n));
+      g->wlog_cap = n;
+    }
+    SQ_CUDA_TRY(cudaMemcpyAsync(g->d_wlog, g->ew.data(), sizeof(double) * n, cudaMemcpyHostToDevice, st));
+  }
   scatter_weights_kernel<<<(nedges + 255) / 256, 256, 0, st>>>(nedges, g->V, weights_dev, ws, g->d_adj, g->d_radj, g->d_ell,
                                                              g->d_ovf, g->d_rell, g->d_rovf, g->d_fs_w, g->d_rs_w,
-                                                             g->d_gell[0], g->d_govf[0], g->d_gell[1], g->d_govf[1]);
+                                                             g->d_gell[0], g->d_govf[0], g->d_gell[1], g->d_govf[1], g->d_wlog);
   sq::count_launch();
   SQ_CUDA_TRY(cudaGetLastError());
-  // keep the host log in step (it is what update_edge / writegraph / the next structural rebuild start from)
-  g->w_stage.resize(n);
-  SQ_CUDA_TRY(cudaMemcpyAsync(g->w_stage.data(), weights_dev, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
-  SQ_CUDA_TRY(cudaStreamSynchronize(st));
-  for (size_t i = 0; i < n; ++i) {
-    const double x = g->w_stage[i];
-    if (x != x) continue;
-    g->ew[i] = x;
-    const int a = g->edge_slot[i];
-    if (a >= 0) { g->h_adj[a].w = x; g->h_radj[g->edge_rslot[i]].w = x; }
-  }
+  // The host log (what update_edge / writegraph / the next structural rebuild start from) is not touched here: a
+  // device-to-host copy and a stream synchronisation per refresh leave the GPU idle while the host catches up, every
+  // weight_freq ticks of a simulation.  The log catches up when somebody on the host looks (g_pull_host_log).
+  g->dev_leads = true;
+  g->lead_stream = st;
   return SQ_OK;
 }
 

@@ -126,7 +126,20 @@ struct TickState {
   u64* counters;   // [0] ticks [1] agent_steps [2] moves [3] active nodes [4] arrivals [5] loaded [6] loaded, frozen
                    // [7] sheltered on a link [8] the same, frozen
   int* err;        // [0] code (0 = ok) [1] agent [2] node [3] link
+  // measurement aid (sq_enable_timeline), nullptr = off: %globaltimer at entry and exit of every warp of the two
+  // phase kernels for ticks [tl_t0, tl_t0 + tl_ticks); entry [(tick - tl_t0) * 2 + phase][warp]
+  ulonglong2* timeline; int tl_t0, tl_ticks, tl_stride;
 };
+
+__device__ __forceinline__ u64 global_ns() { u64 v; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v)); return v; }
+// Slot of this warp in the timeline, or nullptr (off, outside the window, not lane 0).
+__device__ __forceinline__ ulonglong2* timeline_slot(const TickState& s, int t, int phase) {
+  if (!s.timeline || (threadIdx.x & 31u)) return nullptr;
+  const int rel = t - s.tl_t0;
+  const int w = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (rel < 0 || rel >= s.tl_ticks || w >= s.tl_stride) return nullptr;
+  return s.timeline + ((size_t)(rel * 2 + phase) * s.tl_stride + w);
+}
 
 __device__ __forceinline__ u64 fmix64(u64 x) {
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
@@ -205,12 +218,15 @@ __device__ void reroute_slot(const TickState& s, int i);
 // (reroute: next link, epoch, route kind; load / give-up: enter time, status), both with word-sized stores, and a
 // reroute reads nothing the link half writes except the status, where either value gives the same decision.
 __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_blocks) {
+  const int t = *s.tick_link;
+  ulonglong2* const tls = timeline_slot(s, t, 0);
+  const u64 tl0 = tls ? global_ns() : 0;
   if ((int)blockIdx.x >= link_blocks) {
     reroute_slot(s, ((int)blockIdx.x - link_blocks) * (int)blockDim.x + (int)threadIdx.x);
+    if (tls) *tls = make_ulonglong2(tl0, global_ns());
     return;
   }
   const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  const int t = *s.tick_link;
   if (l == 0) {
     *s.tick_node = t;
     // vehicles on links after the previous tick = loaded - arrived up to then; counters[6] is the loaded
@@ -324,6 +340,7 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       if (sh) atomicAdd(&s.counters[7], (u64)sh);
     }
   }
+  if (tls) *tls = make_ulonglong2(tl0, global_ns());
 }
 
 // ---- phase 2: node model, one thread per node ---------------------------------------------------------------
@@ -627,6 +644,8 @@ __device__ __forceinline__ int pick_secondary(const TickState& s, int n, int ib,
 __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   const int t = *s.tick_node;
+  ulonglong2* const tls = timeline_slot(s, t, 1);
+  const u64 tl0 = tls ? global_ns() : 0;
   if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; s.counters[8] = s.counters[7]; }
   int moves = 0, arrivals = 0, active = 0;
   if (n < s.N) {
@@ -753,6 +772,7 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
       if (a) atomicAdd(&s.counters[4], (u64)a);
     }
   }
+  if (tls) *tls = make_ulonglong2(tl0, global_ns());
 }
 
 // ---- host-ordered stops (sq_stop_agents): a driver rule took vehicles off the road ----------------------------
@@ -1405,6 +1425,7 @@ void sq_destroy(SqSim* sim) {
   if (sim->graph) cudaGraphExecDestroy(sim->graph);
   for (void* p : sim->allocs) cudaFree(p);
   cudaFree(sim->d_pool);
+  cudaFree(sim->st.timeline);
   cudaFree(sim->d_ev_link); cudaFree(sim->d_ev_closed); cudaFree(sim->d_summary);
   if (sim->stream && sim->own_stream) cudaStreamDestroy(sim->stream);
   if (sim->cap_stream) cudaStreamDestroy(sim->cap_stream);
@@ -1579,6 +1600,30 @@ int sq_get_pair_moves(SqSim* sim, int64_t* out) {
   if (int rc = sq_sync(sim)) return rc;
   for (size_t i = 0; i < sim->n_turn; ++i) out[i] = (int64_t)h[i];
   return SQ_OK;
+}
+
+int sq_enable_timeline(SqSim* sim, int32_t t0, int32_t n_ticks) {
+  if (!sim || n_ticks <= 0) return sq::set_error(SQ_ERR_ARG, "sq_enable_timeline: null sim or empty window");
+  SQ_CUDA_TRY(cudaStreamSynchronize(sim->stream));
+  TickState& s = sim->st;
+  const int stride = std::max((sim->L + 31) / 32 + (sim->A + 31) / 32 / std::max(s.freq, 1) + 64, (sim->N + 31) / 32);
+  const size_t bytes = sizeof(ulonglong2) * (size_t)n_ticks * 2 * (size_t)stride;
+  if (s.timeline) { cudaFree(s.timeline); s.timeline = nullptr; }
+  SQ_CUDA_TRY(cudaMalloc(&s.timeline, bytes));
+  SQ_CUDA_TRY(cudaMemset(s.timeline, 0, bytes));
+  s.tl_t0 = t0; s.tl_ticks = n_ticks; s.tl_stride = stride;
+  if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel parameters changed
+  return SQ_OK;
+}
+
+int sq_get_timeline(SqSim* sim, int32_t* n_ticks, int32_t* stride, uint64_t* out) {
+  if (!sim || !sim->st.timeline) return sq::set_error(SQ_ERR_ARG, "sq_get_timeline: call sq_enable_timeline first");
+  if (n_ticks) *n_ticks = sim->st.tl_ticks;
+  if (stride) *stride = sim->st.tl_stride;
+  if (!out) return SQ_OK;
+  const size_t bytes = sizeof(ulonglong2) * (size_t)sim->st.tl_ticks * 2 * (size_t)sim->st.tl_stride;
+  SQ_CUDA_TRY(cudaMemcpyAsync(out, sim->st.timeline, bytes, cudaMemcpyDeviceToHost, sim->stream));
+  return sq_sync(sim);
 }
 
 int sq_set_shelter_after(SqSim* sim, int32_t seconds) {

@@ -243,6 +243,19 @@ class DeviceSim(_SimBase):
         """Start counting moves per (in_link, out_link) pair (include/sq_tick.h sq_enable_pair_moves)."""
         self._check(self._L.sq_enable_pair_moves(self._h), "enable_pair_moves")
 
+    def enable_timeline(self, t0, n_ticks):
+        """Measurement aid (include/sq_tick.h sq_enable_timeline): warp entry / exit times of both phase kernels."""
+        self._check(self._L.sq_enable_timeline(self._h, int(t0), int(n_ticks)), "enable_timeline")
+
+    def timeline(self):
+        """-> u64[n_ticks, 2 (link, node), warps, 2 (entry, exit)] in ns of %globaltimer; unused slots are 0."""
+        import ctypes as C
+        n, st = C.c_int32(0), C.c_int32(0)
+        self._check(self._L.sq_get_timeline(self._h, C.addressof(n), C.addressof(st), None), "get_timeline")
+        out = np.zeros((n.value, 2, st.value, 2), np.uint64)
+        self._check(self._L.sq_get_timeline(self._h, None, None, out.ctypes.data), "get_timeline")
+        return out
+
     def set_shelter_after(self, seconds):
         self._check(self._L.sq_set_shelter_after(self._h, int(seconds)), "set_shelter_after")
 

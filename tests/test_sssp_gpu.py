@@ -270,6 +270,21 @@ def test_reverse_trees_and_device_weight_refresh(spi):
     last = np.nonzero((s == s[0]) & (e == e[0]))[0][-1]
     w2[last] = 3.25
     check(w2)
+    # two device refreshes in a row (the host log is brought up to date lazily), then a structural edit: the rebuild
+    # starts from the newest weights
+    for k in range(2):
+        upd = rng.random(E) < 0.3
+        w2[upd] = rng.random(int(upd.sum())) * 60.0 + 0.2
+        g.set_weights_device(torch.from_numpy(np.where(upd, w2, np.nan)).cuda())
+    check(w2)
+    a, b = int(s[5]), int(e[5])
+    g.remove_edge(a, b)
+    keep = ~((s == a) & (e == b))
+    keep[np.nonzero(~keep)[0][:-1]] = True      # the last edge logged under the key is the one removed
+    g.sssp_batch_device(o_dev, d_dev, p_dev, reverse=True)
+    torch.cuda.synchronize()
+    do, po = osssp.OracleGraph(e[keep], s[keep], w2[keep], max_vertex_id=V - 1).sssp_batch(dests)
+    assert d_dev.cpu().numpy().tobytes() == do.tobytes()
     g.free()
 
 
