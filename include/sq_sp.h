@@ -106,6 +106,15 @@ void sp_free_host(void* ptr);
 int sp_sssp_batch_device(Graph* graph, const int* origins_dev, int n, double* dist_dev,
                          int* parent_dev, void* stream);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * sp_sssp_batch_device (bit-identical distances and canonical predecessors; dist_dev is required, parent_dev may be
+ * null) computed by the bitmap tree kernel with its scratch in a file-scope device array of 8 MiB + 256 bytes that every
+ * GPU loading the library holds until exit.  Calls no cudaMalloc / cudaFree / allocating library routine.  Limits: at
+ * most 65,536 vertices (SQ_ERR_LIMIT beyond); the graph must already be on the device (sp_sync after the last edit,
+ * else SQ_ERR_STATE).  Every call shares the one array: calls that overlap on a GPU (two streams, two threads) race. */
+int sp_sssp_batch_device_noalloc(Graph* graph, const int* origins_dev, int n, double* dist_dev, int* parent_dev,
+                                 void* stream);
 /* sp_sssp_batch_device with a direction flag: reverse != 0 runs the trees on the reversed graph, i.e.
  * dist[i][v] = shortest distance from v TO origins[i] and parent[i][v] = the next vertex on that path (canonical:
  * smallest id among exact ties).  One reverse tree per destination routes every agent heading there

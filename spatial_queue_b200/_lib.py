@@ -51,6 +51,7 @@ def _declare(L):
     L.sp_route_batch.restype = ci; L.sp_route_batch.argtypes = [vp, vp, vp, ci, vp, vp, vp]
     L.sp_route_pool.restype = vp; L.sp_route_pool.argtypes = [vp]
     L.sp_sssp_batch_device.restype = ci; L.sp_sssp_batch_device.argtypes = [vp, vp, ci, vp, vp, vp]
+    L.sp_sssp_batch_device_noalloc.restype = ci; L.sp_sssp_batch_device_noalloc.argtypes = [vp, vp, ci, vp, vp, vp]
     L.sp_sssp_batch_device_ex.restype = ci; L.sp_sssp_batch_device_ex.argtypes = [vp, vp, ci, vp, vp, vp, ci]
     L.sp_set_weights_device.restype = ci; L.sp_set_weights_device.argtypes = [vp, vp, ci, vp]
     L.sp_set_weights.restype = ci; L.sp_set_weights.argtypes = [vp, vp, ci]

@@ -2402,6 +2402,80 @@ int sp_sssp_batch_device(Graph* g, const int* origins_dev, int n, double* dist_d
   return g_run_batch_device(g, origins_dev, n, reinterpret_cast<u64*>(dist_dev), parent_dev, (cudaStream_t)stream);
 }
 
+// ---- allocation-free variant (no counterpart in the reference) -----
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops): the bitmap tree kernel with its
+// scratch -- the tree scheduler's counter and the global overflow parts of the four queues of every CTA -- in a
+// file-scope device array instead of per-graph allocations.  Every GPU that loads the library holds the array until
+// exit; every call shares it, so calls that overlap on one GPU race.
+#define SQ_NOALLOC_MAX_VERTICES 65536
+#define SQ_NOALLOC_HEADER_BYTES 256                 /* [0] tree counter, cleared by every call */
+#define SQ_NOALLOC_QUEUE_BYTES (8u << 20)           /* [CTAs][4][V] ints: 8 CTAs at the largest V, more on smaller graphs */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[SQ_NOALLOC_HEADER_BYTES + SQ_NOALLOC_QUEUE_BYTES];
+static unsigned char* g_noalloc_addr[SQ_MAX_DEVICES];   // the array's device address on each device (host code cannot
+                                                        // use the symbol's name as a pointer)
+
+// Set-up, once per device, with that device current: the device address of the scratch array.
+static int noalloc_scratch_address(unsigned char** out) {
+  int dev = -1;
+  SQ_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= SQ_MAX_DEVICES) return sq::set_error(SQ_ERR_LIMIT, "sp_sssp_batch_device_noalloc: device %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_attr_mutex);
+  if (!g_noalloc_addr[dev]) {
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+      cudaGetLastError();
+      return sq::set_error(SQ_ERR_CUDA, "sp_sssp_batch_device_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                           cudaGetErrorString(e));
+    }
+    g_noalloc_addr[dev] = static_cast<unsigned char*>(ptr);
+  }
+  *out = g_noalloc_addr[dev];
+  return SQ_OK;
+}
+
+int sp_sssp_batch_device_noalloc(Graph* g, const int* origins_dev, int n, double* dist_dev, int* parent_dev, void* stream) {
+  if (!g || !dist_dev || (!origins_dev && n > 0))
+    return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch_device_noalloc: null argument (the distance table is required)");
+  if (n <= 0) return SQ_OK;
+  if (g->topo_dirty || g->w_dirty || !g->d_row_ptr)
+    return sq::set_error(sq::SQ_ERR_STATE, "sp_sssp_batch_device_noalloc: the graph has edits that are not on the device yet; "
+                                       "call sp_sync first (it allocates, this call must not)");
+  const int V = g->V;
+  if (V <= 0) return sq::set_error(SQ_ERR_ARG, "graph has no vertices");
+  if (V > SQ_NOALLOC_MAX_VERTICES)
+    return sq::set_error(SQ_ERR_LIMIT, "sp_sssp_batch_device_noalloc: %d vertices, the static scratch is sized for at most %d",
+                         V, SQ_NOALLOC_MAX_VERTICES);
+  unsigned char* scratch = nullptr;
+  if (int rc = noalloc_scratch_address(&scratch)) return rc;
+  int dev = 0, n_sm = 0;
+  SQ_CUDA_TRY(cudaGetDevice(&dev));
+  SQ_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  cudaStream_t st = (cudaStream_t)stream;
+
+  const int words = (V + 31) / 32;
+  const size_t bits_bytes = (size_t)3 * words * sizeof(unsigned);
+  int nq = std::min(2048, std::max(32, V));
+  const size_t smem = bits_bytes + (size_t)4 * nq * sizeof(int);      // <= 24 KB + 32 KB at the largest V
+  const int threads = 256;
+  const size_t per_cta = sizeof(int) * 4 * (size_t)V;
+  const int grid = (int)std::min<size_t>({(size_t)n, (size_t)SQ_NOALLOC_QUEUE_BYTES / per_cta, (size_t)n_sm * 4});
+
+  TreeParams p;
+  memset(&p, 0, sizeof(p));
+  p.V = V; p.n_trees = n;
+  p.row_ptr = g->d_row_ptr; p.adj = g->d_adj; p.rrow_ptr = g->d_rrow_ptr; p.radj = g->d_radj;
+  p.origins = origins_dev;
+  p.dist_out = reinterpret_cast<u64*>(dist_dev);
+  p.parent_out = parent_dev;
+  p.tree_counter = reinterpret_cast<int*>(scratch);
+  p.qscratch = reinterpret_cast<int*>(scratch + SQ_NOALLOC_HEADER_BYTES);
+  p.delta = g->delta; p.nq = nq; p.words = words;
+  // the array keeps the last call's contents: the counter must start at zero, the queue parts are written before read
+  SQ_CUDA_TRY(cudaMemsetAsync(scratch, 0, SQ_NOALLOC_HEADER_BYTES, st));
+  return launch_bitmap_kernel(g, p, grid, smem, threads, st);
+}
+
 static bool is_pinned_host(const void* ptr) {
   if (!ptr) return true;
   cudaPointerAttributes at;

@@ -231,6 +231,16 @@ class Graph:
                                             C.c_void_p(parent_dev.data_ptr()) if parent_dev is not None else None,
                                             sp, 1 if reverse else 0), "sp_sssp_batch_device")
 
+    def sssp_batch_device_noalloc(self, origins_dev, dist_dev, parent_dev=None, stream=None):
+        """sssp_batch_device for callers that must not allocate (include/sq_sp.h sp_sssp_batch_device_noalloc): static
+        scratch, at most 65,536 vertices, graph already synced; calls that overlap on one GPU race."""
+        import torch
+        sp = C.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
+        check(lib().sp_sssp_batch_device_noalloc(self._h, C.c_void_p(origins_dev.data_ptr()), int(origins_dev.numel()),
+                                                 C.c_void_p(dist_dev.data_ptr()),
+                                                 C.c_void_p(parent_dev.data_ptr()) if parent_dev is not None else None, sp),
+              "sp_sssp_batch_device_noalloc")
+
     def last_stats(self):
         out = (C.c_longlong * 5)()
         lib().sp_last_stats(self._h, out)
