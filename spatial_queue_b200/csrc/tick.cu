@@ -30,6 +30,7 @@
 #include <cstdint>
 #include <cstdlib>
 #include <numeric>
+#include <utility>
 #include <vector>
 
 #include "../../include/sq_sp.h"
@@ -64,8 +65,22 @@ struct __align__(32) WinRec {
   int lanes, rcol, pad;
 };
 
+// Static words of a node, one 64-byte record read before the dynamic chain starts: its first eight in-links and, per
+// in-link slot i, who the opposite approach is when i is the primary link (:267-293) -- the other slots ordered by
+// |turn angle onto the reverse of link i|, so that the choice is "first of the list that has a queue" instead of a walk
+// over the angle table.
+//   sec[i]: bits 0..2 entries, bits 3..23 the slots (3 bits each); NR_NONE: link i has no reverse link (no opposite
+//   approach); NR_SLOW: equal angles / duplicate priority ranks, the order of the walk matters -> pick_secondary.
+//   sec[0] & NR_NODE_SLOW: more than eight in-links, the record is not used.
+struct __align__(64) NodeRec {
+  int in[8];
+  unsigned sec[8];
+};
+constexpr unsigned NR_NONE = 1u << 30, NR_SLOW = 1u << 31, NR_NODE_SLOW = 1u << 29;
+
 struct TickState {
   int N, L, A;
+  const NodeRec* n_rec;
   u64 seed;
   // links, static
   const int* l_start; const int* l_end; const int* l_lanes; const int* l_rev; const WinRec* l_win;
@@ -129,7 +144,16 @@ struct TickState {
   // measurement aid (sq_enable_timeline), nullptr = off: %globaltimer at entry and exit of every warp of the two
   // phase kernels for ticks [tl_t0, tl_t0 + tl_ticks); entry [(tick - tl_t0) * 2 + phase][warp]
   ulonglong2* timeline; int tl_t0, tl_ticks, tl_stride;
+  int pdl_early;   // 1: let the next kernel's CTAs be placed as soon as this kernel's dependency is met (see pdl_wait)
 };
+
+// Programmatic dependent launch (sm_90+): the three per-tick kernels are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so the next kernel's CTAs are placed on the SMs while this one
+// still runs.  pdl_wait() returns once the previous kernel has completed and its writes are visible -- nothing written
+// by an earlier kernel may be read before it; pdl_release() lets the following kernel start its own prologue.  It is
+// issued after the wait, so at most one kernel runs ahead.  Launched without the attribute both are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ u64 global_ns() { u64 v; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v)); return v; }
 // Slot of this warp in the timeline, or nullptr (off, outside the window, not lane 0).
@@ -218,6 +242,8 @@ __device__ void reroute_slot(const TickState& s, int i);
 // (reroute: next link, epoch, route kind; load / give-up: enter time, status), both with word-sized stores, and a
 // reroute reads nothing the link half writes except the status, where either value gives the same decision.
 __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_blocks) {
+  pdl_wait();
+  if (s.pdl_early) pdl_release();
   const int t = *s.tick_link;
   ulonglong2* const tls = timeline_slot(s, t, 0);
   const u64 tl0 = tls ? global_ns() : 0;
@@ -505,20 +531,26 @@ __device__ __forceinline__ void win_load(const TickState& s, Win& w, int il) {
 // GATHER vehicles at a time, level by level, so the sequential part runs on local data.  The four levels are
 // separate functions so that the node kernel can interleave the gathers of two in-links (issue the loads of one
 // link's level, then consume the other's).
-struct VSet {
-  Veh v[GATHER];
-  int st[GATHER], ep[GATHER], dl[GATHER], en[GATHER];
+template <int G>
+struct VSetT {
+  Veh v[G];
+  int st[G], ep[G], dl[G], en[G];
 };
+typedef VSetT<GATHER> VSet;
+constexpr int GATHER_WIDE = 8;   // vehicles gathered together beyond the first set of a window (long windows: source
+                                 // links release up to 100 vehicles a tick, each set costs four dependent round trips)
 
-__device__ __forceinline__ void lvl_ring(const TickState& s, const Win& w, int i0, VSet& g) {
+template <int G>
+__device__ __forceinline__ void lvl_ring(const TickState& s, const Win& w, int i0, VSetT<G>& g) {
   const int cnt = w.k - i0;
 #pragma unroll
-  for (int j = 0; j < GATHER; ++j) g.v[j].agent = j < cnt ? s.ring[w.base + ((w.h + (unsigned)(i0 + j)) & w.mask)].x : -1;
+  for (int j = 0; j < G; ++j) g.v[j].agent = j < cnt ? s.ring[w.base + ((w.h + (unsigned)(i0 + j)) & w.mask)].x : -1;
 }
 
-__device__ __forceinline__ void lvl_agent(const TickState& s, VSet& g) {
+template <int G>
+__device__ __forceinline__ void lvl_agent(const TickState& s, VSetT<G>& g) {
 #pragma unroll
-  for (int j = 0; j < GATHER; ++j) {
+  for (int j = 0; j < G; ++j) {
     Veh& v = g.v[j];
     v.ol = -1; v.recw = 0; v.destin = -1; v.rlen = 0; g.ep[j] = 0; g.dl[j] = 0;
     if (v.agent >= 0) {
@@ -531,20 +563,46 @@ __device__ __forceinline__ void lvl_agent(const TickState& s, VSet& g) {
   }
 }
 
-__device__ __forceinline__ void lvl_hop(const TickState& s, int node, VSet& g) {
+template <int G>
+__device__ __forceinline__ void lvl_hop(const TickState& s, int node, VSetT<G>& g) {
 #pragma unroll
-  for (int j = 0; j < GATHER; ++j) {
+  for (int j = 0; j < G; ++j) {
     g.st[j] = node; g.v[j].lc = 0; g.en[j] = 0;
     if (g.v[j].ol >= 0) { const int4 hop = s.l_hop[g.v[j].ol]; g.st[j] = hop.x; g.en[j] = hop.y; g.v[j].lc = hop.z; }
   }
 }
 
-__device__ __forceinline__ void lvl_tbl(const TickState& s, VSet& g) {
+template <int G>
+__device__ __forceinline__ void lvl_tbl(const TickState& s, VSetT<G>& g) {
 #pragma unroll
-  for (int j = 0; j < GATHER; ++j) {
+  for (int j = 0; j < G; ++j) {
     g.v[j].nxt = -1;
     if (g.v[j].ol >= 0 && g.v[j].rlen < 0) g.v[j].nxt = s.next_tbl[tbl_index(s, g.ep[j], g.dl[j], g.en[j])];
   }
+}
+
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+// The words outcache_fill will read for out-link `ol`, requested as soon as the link is known (two levels of the gather
+// before the admit loop needs them).  All of them are written by this node's thread only, or -- head -- are safe to
+// read early (outcache_fill), so a line that sits in L1 since the prefetch is as good as a fresh one.
+__device__ __forceinline__ void prefetch_out_link(const TickState& s, int ol) {
+  prefetch_l1(&s.in_c[ol]); prefetch_l1(&s.storage_c[ol]); prefetch_l1(&s.tail[ol]); prefetch_l1(&s.len_in[ol]);
+  prefetch_l1(&s.head[ol]); prefetch_l1(&s.l_ring_mask[ol]); prefetch_l1(&s.l_ring_base[ol]); prefetch_l1(&s.l_fft[ol]);
+}
+
+template <int G>
+__device__ __forceinline__ void lvl_prefetch_out(const TickState& s, const VSetT<G>& g) {
+#pragma unroll
+  for (int j = 0; j < G; ++j)
+    if (g.v[j].ol >= 0) prefetch_out_link(s, g.v[j].ol);
+}
+
+__device__ __forceinline__ int sel8(const int4& a, const int4& b, int i) {
+  int r = a.x;
+  r = i == 1 ? a.y : r; r = i == 2 ? a.z : r; r = i == 3 ? a.w : r;
+  r = i == 4 ? b.x : r; r = i == 5 ? b.y : r; r = i == 6 ? b.z : r; r = i == 7 ? b.w : r;
+  return r;
 }
 
 // What the admit loop accumulates for one in-link.
@@ -559,10 +617,13 @@ struct LinkAcc {
 // applies the "no more left turns from the opposite approach" skip of :289-292.  For the primary link the same
 // records answer non_conflict_vehicles' question "does any of them turn left" (:248-263): acc.any_left is set
 // from the next links the vehicles had before anything moved.
-__device__ __forceinline__ void admit_set(const TickState& s, AdmitCtx& c, OutCache& oc, Win& w, bool secondary, const VSet& g,
-                                          int i0, LinkAcc& acc) {
-  const int cnt = min(GATHER, w.k - i0);
-  for (int j = 0; j < cnt; ++j) {
+template <int G>
+__device__ __forceinline__ void admit_set(const TickState& s, AdmitCtx& c, OutCache& oc, Win& w, bool secondary,
+                                          const VSetT<G>& g, int i0, LinkAcc& acc) {
+  const int cnt = min(G, w.k - i0);
+#pragma unroll
+  for (int j = 0; j < G; ++j) {
+    if (j >= cnt) break;
     const int i = i0 + j;
     const Veh& v = g.v[j];
     bool stay;
@@ -580,10 +641,11 @@ __device__ __forceinline__ void admit_set(const TickState& s, AdmitCtx& c, OutCa
 
 // The rest of a window beyond its first (pre-gathered) set, then the queue bookkeeping of the link.
 __device__ void admit_finish(const TickState& s, AdmitCtx& c, OutCache& oc, Win& w, bool secondary, LinkAcc& acc) {
-  for (int i0 = GATHER; i0 < w.k; i0 += GATHER) {
-    VSet g;
+  for (int i0 = GATHER; i0 < w.k; i0 += GATHER_WIDE) {
+    VSetT<GATHER_WIDE> g;
     lvl_ring(s, w, i0, g);
     lvl_agent(s, g);
+    lvl_prefetch_out(s, g);
     lvl_hop(s, c.node, g);
     lvl_tbl(s, g);
     admit_set(s, c, oc, w, secondary, g, i0, acc);
@@ -643,18 +705,25 @@ __device__ __forceinline__ int pick_secondary(const TickState& s, int n, int ib,
 
 __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  // static words of the node, read while the link phase is still running
+  int ib = 0, indeg = 0, type = 0;
+  long long key = 0;
+  int4 nin0 = make_int4(-1, -1, -1, -1), nin1 = nin0, nsec0 = make_int4(0, 0, 0, 0), nsec1 = nsec0;
+  if (n < s.N) {
+    ib = s.in_ptr[n]; indeg = s.in_ptr[n + 1] - ib; key = s.n_key[n]; type = s.n_type[n];
+    const int4* q = reinterpret_cast<const int4*>(&s.n_rec[n]);
+    nin0 = __ldg(q); nin1 = __ldg(q + 1); nsec0 = __ldg(q + 2); nsec1 = __ldg(q + 3);
+  }
+  pdl_wait();
+  if (s.pdl_early) pdl_release();
   const int t = *s.tick_node;
   ulonglong2* const tls = timeline_slot(s, t, 1);
   const u64 tl0 = tls ? global_ns() : 0;
   if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; s.counters[8] = s.counters[7]; }
   int moves = 0, arrivals = 0, active = 0;
   if (n < s.N) {
-    const int ib = s.in_ptr[n];
-    const int indeg = s.in_ptr[n + 1] - ib;
     // candidate in-links: non-empty queue, incoming_links order (:230); the link phase keeps the mask
     u64 cand = s.n_cand[n];
-    const long long key = s.n_key[n];     // issued with the mask: coalesced, and off the active nodes' chain
-    const int type = s.n_type[n];
     if (cand) {
       active = 1;
       int primary = -1;  // local index of the primary in-link
@@ -713,7 +782,8 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
 #pragma unroll
         for (int i = 0; i < MAXO; ++i) oc.link[i] = -1;
         oc.dirty = 0u;
-        const int lp = s.in_links[ib + primary];
+        const bool rec_ok = !((unsigned)nsec0.x & NR_NODE_SLOW);
+        const int lp = rec_ok ? sel8(nin0, nin1, primary) : s.in_links[ib + primary];
         // The primary link's vehicles go first (run_node_model walks the go-list in order); the same pass tells
         // whether any of them turns left (:248-263), which decides if the opposite approach moves at all.
         // Nothing the choice of that approach reads (candidate set, angle table, the other links' queues), and
@@ -723,16 +793,33 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
         // thread keeps both chains of dependent loads in flight, and the admits themselves stay in the
         // reference's order.
         Win wp, ws;
-        win_load(s, wp, lp);
         const u64 rest = cand & ~(1ull << primary);
         VSet gp, gs;
-        lvl_ring(s, wp, 0, gp);
         int secondary = -1;
-        if (rest && wp.rcol >= 0) secondary = pick_secondary(s, n, ib, indeg, type, rest, first, wp.rcol);
-        win_load(s, ws, secondary >= 0 ? s.in_links[ib + secondary] : -1);
+        const unsigned sw = rec_ok ? (unsigned)sel8(nsec0, nsec1, primary) : NR_SLOW;
+        if (!(sw & (NR_SLOW | NR_NODE_SLOW))) {
+          // the opposite approach from the node's static record: both windows are loaded together
+          if (rest && !(sw & NR_NONE)) {
+            const int cnt = (int)(sw & 7u);
+            for (int a = 0; a < cnt; ++a) {
+              const int j = (int)((sw >> (3 + 3 * a)) & 7u);
+              if ((rest >> j) & 1ull) { secondary = j; break; }
+            }
+          }
+          win_load(s, wp, lp);
+          win_load(s, ws, secondary >= 0 ? sel8(nin0, nin1, secondary) : -1);
+          lvl_ring(s, wp, 0, gp);
+        } else {
+          win_load(s, wp, lp);
+          lvl_ring(s, wp, 0, gp);
+          if (rest && wp.rcol >= 0) secondary = pick_secondary(s, n, ib, indeg, type, rest, first, wp.rcol);
+          win_load(s, ws, secondary >= 0 ? s.in_links[ib + secondary] : -1);
+        }
         lvl_ring(s, ws, 0, gs);
         lvl_agent(s, gp);
         lvl_agent(s, gs);
+        lvl_prefetch_out(s, gp);
+        lvl_prefetch_out(s, gs);
         lvl_hop(s, n, gp);
         lvl_hop(s, n, gs);
         lvl_tbl(s, gp);
@@ -903,6 +990,8 @@ __global__ void __launch_bounds__(128) k_reroute_all(const TickState s) {
 // An agent due in both slots is handled by its closure-slot thread, in the reference's order.
 __global__ void __launch_bounds__(128) k_reroute_rules(const TickState s) {
   const int i = blockIdx.x * 128 + threadIdx.x;
+  pdl_wait();
+  if (s.pdl_early) pdl_release();
   const int t = *s.tick_link;
   if (t <= 0) return;
   if (s.cfreq > 0) {
@@ -1029,6 +1118,7 @@ struct SqSim {
   cudaStream_t stream = nullptr;
   cudaStream_t cap_stream = nullptr;
   bool own_stream = true;
+  bool pdl = true;       // programmatic dependent launch between the per-tick kernels (SQ_TICK_PDL=0 turns it off)
   int next_t = INT_MIN;  // tick the device counters are armed for
   long long sheltered = 0;
   // device router
@@ -1188,6 +1278,41 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     }
     if ((rc = dev_upload(sim, &s.l_win, win))) return rc;
   }
+  {
+    std::vector<NodeRec> nrec((size_t)N);
+    for (int n = 0; n < N; ++n) {
+      NodeRec& r = nrec[n];
+      const int ib = d->node_in_ptr[n], indeg = d->node_in_ptr[n + 1] - ib;
+      const int outdeg = d->node_out_ptr[n + 1] - d->node_out_ptr[n];
+      for (int i = 0; i < 8; ++i) { r.in[i] = i < indeg ? d->node_in_links[ib + i] : -1; r.sec[i] = NR_NONE; }
+      if (indeg > 8) { r.sec[0] |= NR_NODE_SLOW; continue; }
+      bool dup_rank = false;   // pick_secondary's priority walk skips links that share a rank: keep that path
+      if (d->node_type[n] == 2)
+        for (int a = 0; a < indeg; ++a)
+          for (int b = a + 1; b < indeg; ++b)
+            if (d->node_in_prio[ib + a] >= 0 && d->node_in_prio[ib + a] == d->node_in_prio[ib + b]) dup_rank = true;
+      const double* tb = d->turn_angle + d->node_turn_ptr[n];
+      for (int i = 0; i < indeg; ++i) {
+        const int rev = d->link_reverse[r.in[i]];
+        if (rev < 0) continue;                                    // NR_NONE
+        const int rcol = (int)out_local[rev];
+        int order[8], cnt = 0;
+        bool slow = dup_rank || rcol >= outdeg;
+        for (int j = 0; j < indeg; ++j) if (j != i) order[cnt++] = j;
+        auto ang = [&](int j) { return std::fabs(tb[(size_t)j * outdeg + rcol]); };
+        for (int a = 0; a < cnt && !slow; ++a) {
+          if (!(ang(order[a]) == ang(order[a]))) slow = true;     // NaN
+          for (int b = a + 1; b < cnt && !slow; ++b) if (ang(order[a]) == ang(order[b])) slow = true;
+        }
+        if (slow) { r.sec[i] = NR_SLOW; continue; }
+        std::sort(order, order + cnt, [&](int a, int b) { return ang(a) < ang(b); });
+        unsigned w = (unsigned)cnt;
+        for (int a = 0; a < cnt; ++a) w |= (unsigned)order[a] << (3 + 3 * a);
+        r.sec[i] = w;
+      }
+    }
+    if ((rc = dev_upload(sim, &s.n_rec, nrec))) return rc;
+  }
   if ((rc = dev_upload_rw(sim, &s.ring, ring))) return rc;
   {
     std::vector<unsigned> z(L, 0u);
@@ -1276,6 +1401,19 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
   return SQ_OK;
 }
 
+// Launch with the programmatic-serialisation attribute (see pdl_wait): in a captured graph it becomes a programmatic
+// dependency edge on the previous kernel node.
+template <typename... P, typename... A>
+static void launch_pdl(bool pdl, void (*kern)(P...), unsigned grid, unsigned block, cudaStream_t st, A&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kern, std::forward<A>(args)...);
+}
+
 static int launch_tick(SqSim* sim, cudaStream_t st) {
   const int L = sim->L, N = sim->N;
   const int lb = 128;   // measured: 31.5 / 31.5 / 32.1 us per tick with 64 / 128 / 256 threads
@@ -1284,13 +1422,13 @@ static int launch_tick(SqSim* sim, cudaStream_t st) {
   if (sim->st.a_rdist) {
     // Butte's rules: the reroutes run as their own launch before the link phase
     const int work = std::max(sim->max_bucket, sim->st.max_cbucket);
-    if (work > 0) k_reroute_rules<<<(work + 127) / 128, 128, 0, st>>>(sim->st);
+    if (work > 0) launch_pdl(sim->pdl, k_reroute_rules, (unsigned)((work + 127) / 128), 128u, st, sim->st);
     reroute_blocks = 0;
   }
-  k_link_phase<<<link_blocks + reroute_blocks, lb, 0, st>>>(sim->st, link_blocks);
+  launch_pdl(sim->pdl, k_link_phase, (unsigned)(link_blocks + reroute_blocks), (unsigned)lb, st, sim->st, link_blocks);
   // one warp per CTA: the warps are independent chains, the finer grain spreads them evenly over the SMs (measured:
   // 31.7 / 32.1 / 32.5 us per tick with 32 / 64 / 128 threads)
-  k_node_phase<<<(N + 31) / 32, 32, 0, st>>>(sim->st);
+  launch_pdl(sim->pdl, k_node_phase, (unsigned)((N + 31) / 32), 32u, st, sim->st);
   return SQ_OK;
 }
 
@@ -1416,6 +1554,9 @@ extern "C" {
 SqSim* sq_create(const SqNetDesc* desc) {
   if (!desc) { sq::set_error(SQ_ERR_ARG, "sq_create: null description"); return nullptr; }
   SqSim* sim = new SqSim();
+  if (const char* e = getenv("SQ_TICK_PDL")) sim->pdl = atoi(e) != 0;
+  sim->st.pdl_early = 0;
+  if (const char* e = getenv("SQ_TICK_PDL")) sim->st.pdl_early = atoi(e) == 2;
   if (sim_build(sim, desc) != SQ_OK || build_graph(sim) != SQ_OK) { sq_destroy(sim); return nullptr; }
   return sim;
 }
