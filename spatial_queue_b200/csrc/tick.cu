@@ -144,6 +144,9 @@ struct TickState {
   // measurement aid (sq_enable_timeline), nullptr = off: %globaltimer at entry and exit of every warp of the two
   // phase kernels for ticks [tl_t0, tl_t0 + tl_ticks); entry [(tick - tl_t0) * 2 + phase][warp]
   ulonglong2* timeline; int tl_t0, tl_ticks, tl_stride;
+#ifdef SQ_TICK_PHASES
+  u64* phases;     // experiment build only: [tl_ticks][tl_stride][16] checkpoints inside k_node_phase
+#endif
   int pdl_early;   // 1: let the next kernel's CTAs be placed as soon as this kernel's dependency is met (see pdl_wait)
 };
 
@@ -267,20 +270,40 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       sheltered += strip_stopped(s, l);
       s.l_tomb[l] = 0;
     }
+    // Level 1: every word that does not depend on another load, issued together.  A thread is a chain of dependent
+    // L2 round trips (~0.4 us each); read where they are used, these made seven of them.
+    const bool virt = s.l_virtual[l] != 0;
     unsigned tl = s.tail[l];
     unsigned qt = s.qtail[l];
+    unsigned h = s.head[l];
     const long long base = s.l_ring_base[l];
     const unsigned mask = s.l_ring_mask[l];
     long long li = s.len_in[l];
-    if (s.congest_after > 0 && !s.l_virtual[l]) {
+    long long lout = s.len_out[l];
+    const int dwell = s.l_dwell[l];
+    const unsigned vcnt = (unsigned)s.l_vcount[l];
+    const int in_local = s.l_in_local[l];
+    const int end_node = s.l_end[l];
+    const double storage = s.l_storage[l];
+    const double cap = s.l_cap_s[l];
+    const bool closed = s.l_closed[l] != 0;
+    // Level 2: the ring entries the three scans below start from (oldest vehicle, first running vehicle, next
+    // departure), read together; a scan that goes further loads as it goes.
+    const unsigned h0 = h, qt0 = qt, tl0v = tl;
+    int2 e_h = make_int2(-1, INT_MAX), e_q = e_h, e_t = e_h;
+    const bool want_h = !virt && h != tl && (s.shelter_after > 0);
+    const bool want_q = qt != tl;
+    const bool want_t = virt && tl < vcnt;
+    if (want_h) e_h = s.ring[base + (h & mask)];
+    if (want_q) e_q = s.ring[base + (qt & mask)];
+    if (want_t) e_t = s.ring[base + tl];
+    if (s.congest_after > 0 && !virt) {
       // agent loop of the driver (run_traffic_simulation.py:80-82, 100-102): link.congested = vehicles that have
       // been on this link for more than congest_after seconds, recounted every tick.  Ring order is entry order, so
       // these vehicles are a prefix [head, p); p only moves forward, and the ready tick in the ring entry brackets
       // the enter time (ready - dwell <= enter <= ready - 1), so the agent record is read at the boundary only.
-      const unsigned h = s.head[l];
       unsigned p = s.cong_pos[l];
       if ((int)(p - h) < 0) p = h;
-      const int dwell = s.l_dwell[l];
       const long long limit = (long long)t - s.congest_after;   // congested <=> enter < limit
       while (p != tl) {
         const int2 e = s.ring[base + (p & mask)];
@@ -294,16 +317,14 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       s.cong_pos[l] = p;
       s.l_congested[l] = (long long)(p - h);
     }
-    if (s.shelter_after > 0 && !s.l_virtual[l]) {
+    if (s.shelter_after > 0 && !virt) {
       // agent loop of the driver (run_traffic_simulation.py:100-104, 113-118): a vehicle that has spent more
       // than shelter_after seconds on this link gives up (status shelter_a1) and is taken off the link before
       // the link model runs.  Ring order is entry order, so these vehicles are a prefix of the ring.
-      unsigned h = s.head[l];
-      const int dwell = s.l_dwell[l];
       long long lo = 0;
       int gave_up = 0;
       while (h != tl) {
-        const int2 e = s.ring[base + (h & mask)];
+        const int2 e = h == h0 ? e_h : s.ring[base + (h & mask)];
         if (e.y != INT_MAX && (long long)t - e.y + dwell <= s.shelter_after) break;   // cannot be old enough yet
         const int4 rec = s.ag[e.x].rec;
         if (t - rec.z <= s.shelter_after) break;
@@ -314,17 +335,17 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
       }
       if (gave_up) {
         s.head[l] = h;
-        s.len_out[l] += lo;
+        lout += lo;
+        s.len_out[l] = lout;
         s.l_shelter[l] += gave_up;
         if ((int)(qt - h) < 0) { qt = h; s.qtail[l] = qt; }   // they were still in the run part
         sheltered += gave_up;
       }
     }
-    if (s.l_virtual[l]) {
+    if (virt) {
       // load_vehicle (:587-596): the next entries of the prefilled departure sequence whose departure == t
-      const unsigned cnt = (unsigned)s.l_vcount[l];
-      while (tl < cnt) {
-        const int2 e = s.ring[base + tl];
+      while (tl < vcnt) {
+        const int2 e = tl == tl0v ? e_t : s.ring[base + tl];
         if (e.y - 1 > t) break;
         const int w = s.ag[e.x].rec.w;
         s.ag[e.x].rec.z = e.y - 1;                        // current_link_enter_time = departure tick
@@ -336,22 +357,25 @@ __global__ void __launch_bounds__(256) k_link_phase(const TickState s, int link_
     }
     // run -> queue promotion (:446-449): advance the boundary over entries whose ready tick has come
     if (qt != tl) {
-      const unsigned qt0 = qt;
-      while (qt != tl && s.ring[base + (qt & mask)].y <= t) ++qt;
-      if (qt != qt0) s.qtail[l] = qt;
+      const unsigned qs = qt;
+      while (qt != tl) {
+        const int2 e = (qt == qt0 && want_q) ? e_q : s.ring[base + (qt & mask)];
+        if (e.y > t) break;
+        ++qt;
+      }
+      if (qt != qs) s.qtail[l] = qt;
     }
     // candidate bit of the end node: k_node_phase reads one word per node instead of walking its in-links' queue
     // bounds (three dependent loads at the head of every node's chain); fire-and-forget REDs (updating only on change, via a per-link byte, measured slower)
     {
-      const u64 bit = 1ull << s.l_in_local[l];
-      u64* w = &s.n_cand[s.l_end[l]];
-      if (qt != s.head[l]) atomicOr(w, bit); else atomicAnd(w, ~bit);
+      const u64 bit = 1ull << in_local;
+      u64* w = &s.n_cand[end_node];
+      if (qt != h) atomicOr(w, bit); else atomicAnd(w, ~bit);
     }
     // capacities (:453-455)
-    s.storage_c[l] = s.l_storage[l] - (double)(li - s.len_out[l]);
-    const double c = s.l_cap_s[l];
-    s.out_c[l] = c;
-    s.in_c[l] = s.l_closed[l] ? 0.0 : c;
+    s.storage_c[l] = storage - (double)(li - lout);
+    s.out_c[l] = cap;
+    s.in_c[l] = closed ? 0.0 : cap;
   }
   const unsigned any = __ballot_sync(0xffffffffu, (loaded | sheltered) > 0);
   if (any) {
@@ -581,29 +605,29 @@ __device__ __forceinline__ void lvl_tbl(const TickState& s, VSetT<G>& g) {
   }
 }
 
-__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
-
-// The words outcache_fill will read for out-link `ol`, requested as soon as the link is known (two levels of the gather
-// before the admit loop needs them).  All of them are written by this node's thread only, or -- head -- are safe to
-// read early (outcache_fill), so a line that sits in L1 since the prefetch is as good as a fresh one.
-__device__ __forceinline__ void prefetch_out_link(const TickState& s, int ol) {
-  prefetch_l1(&s.in_c[ol]); prefetch_l1(&s.storage_c[ol]); prefetch_l1(&s.tail[ol]); prefetch_l1(&s.len_in[ol]);
-  prefetch_l1(&s.head[ol]); prefetch_l1(&s.l_ring_mask[ol]); prefetch_l1(&s.l_ring_base[ol]); prefetch_l1(&s.l_fft[ol]);
-}
-
-template <int G>
-__device__ __forceinline__ void lvl_prefetch_out(const TickState& s, const VSetT<G>& g) {
-#pragma unroll
-  for (int j = 0; j < G; ++j)
-    if (g.v[j].ol >= 0) prefetch_out_link(s, g.v[j].ol);
-}
-
 __device__ __forceinline__ int sel8(const int4& a, const int4& b, int i) {
   int r = a.x;
   r = i == 1 ? a.y : r; r = i == 2 ? a.z : r; r = i == 3 ? a.w : r;
   r = i == 4 ? b.x : r; r = i == 5 ? b.y : r; r = i == 6 ? b.z : r; r = i == 7 ? b.w : r;
   return r;
 }
+
+// Experiment build (SQ_NVCC_EXTRA=-DSQ_TICK_PHASES, tools/tick_phases.py): %globaltimer at checkpoints of k_node_phase,
+// written by the first active lane of the warp.
+#ifdef SQ_TICK_PHASES
+#define PHASE(k) phase_mark(s, t, (k))
+__device__ __forceinline__ void phase_mark(const TickState& s, int t, int k) {
+  if (!s.phases) return;
+  const unsigned m = __activemask();
+  if ((threadIdx.x & 31u) != (unsigned)(__ffs(m) - 1)) return;
+  const int rel = t - s.tl_t0;
+  const int w = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (rel < 0 || rel >= s.tl_ticks || w >= s.tl_stride) return;
+  s.phases[((size_t)rel * s.tl_stride + w) * 16 + k] = global_ns();
+}
+#else
+#define PHASE(k)
+#endif
 
 // What the admit loop accumulates for one in-link.
 struct LinkAcc {
@@ -645,7 +669,6 @@ __device__ void admit_finish(const TickState& s, AdmitCtx& c, OutCache& oc, Win&
     VSetT<GATHER_WIDE> g;
     lvl_ring(s, w, i0, g);
     lvl_agent(s, g);
-    lvl_prefetch_out(s, g);
     lvl_hop(s, c.node, g);
     lvl_tbl(s, g);
     admit_set(s, c, oc, w, secondary, g, i0, acc);
@@ -719,12 +742,14 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
   const int t = *s.tick_node;
   ulonglong2* const tls = timeline_slot(s, t, 1);
   const u64 tl0 = tls ? global_ns() : 0;
+  PHASE(0);
   if (n == 0) { *s.tick_link = t + 1; s.counters[6] = s.counters[5]; s.counters[8] = s.counters[7]; }
   int moves = 0, arrivals = 0, active = 0;
   if (n < s.N) {
     // candidate in-links: non-empty queue, incoming_links order (:230); the link phase keeps the mask
     u64 cand = s.n_cand[n];
     if (cand) {
+      PHASE(1);
       active = 1;
       int primary = -1;  // local index of the primary in-link
       // `order` semantics: after the shuffle replacement the list is [c_r, rest in original order].
@@ -776,6 +801,7 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
         }
       }
       if (primary >= 0) {
+        PHASE(2);
         AdmitCtx c;
         c.t = t; c.node = n; c.toss = 0; c.moves = 0; c.arrivals = 0; c.key = key;
         OutCache oc;
@@ -816,28 +842,35 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
           win_load(s, ws, secondary >= 0 ? s.in_links[ib + secondary] : -1);
         }
         lvl_ring(s, ws, 0, gs);
+        PHASE(3);
         lvl_agent(s, gp);
         lvl_agent(s, gs);
-        lvl_prefetch_out(s, gp);
-        lvl_prefetch_out(s, gs);
+        PHASE(4);
         lvl_hop(s, n, gp);
         lvl_hop(s, n, gs);
+        PHASE(5);
         lvl_tbl(s, gp);
         lvl_tbl(s, gs);
+        PHASE(6);
         LinkAcc ap;
         long long pair0 = 0;
         int outdeg = 0;
         if (s.pair_moves) { pair0 = s.turn_ptr[n]; outdeg = s.out_ptr[n + 1] - s.out_ptr[n]; }
         c.pair_row = pair0 + (long long)primary * outdeg;
         admit_set(s, c, oc, wp, false, gp, 0, ap);
+        PHASE(7);
         admit_finish(s, c, oc, wp, false, ap);
+        PHASE(8);
         if (!ap.any_left && ws.il >= 0) {                                         // opposite approach (:267-293)
           LinkAcc as;
           c.pair_row = pair0 + (long long)secondary * outdeg;
           admit_set(s, c, oc, ws, true, gs, 0, as);
+          PHASE(9);
           admit_finish(s, c, oc, ws, true, as);
+          PHASE(10);
         }
         outcache_flush(s, oc);
+        PHASE(11);
         if (c.moves) atomicAdd(reinterpret_cast<u64*>(&s.node_move[n]), (u64)c.moves);   // result unused: a fire-and-forget RED
         moves = c.moves; arrivals = c.arrivals;
       }
@@ -859,6 +892,7 @@ __global__ void __launch_bounds__(32) k_node_phase(const TickState s) {
       if (a) atomicAdd(&s.counters[4], (u64)a);
     }
   }
+  PHASE(12);
   if (tls) *tls = make_ulonglong2(tl0, global_ns());
 }
 
@@ -1753,6 +1787,11 @@ int sq_enable_timeline(SqSim* sim, int32_t t0, int32_t n_ticks) {
   SQ_CUDA_TRY(cudaMalloc(&s.timeline, bytes));
   SQ_CUDA_TRY(cudaMemset(s.timeline, 0, bytes));
   s.tl_t0 = t0; s.tl_ticks = n_ticks; s.tl_stride = stride;
+#ifdef SQ_TICK_PHASES
+  if (s.phases) { cudaFree(s.phases); s.phases = nullptr; }
+  SQ_CUDA_TRY(cudaMalloc(&s.phases, sizeof(u64) * 16 * (size_t)n_ticks * (size_t)stride));
+  SQ_CUDA_TRY(cudaMemset(s.phases, 0, sizeof(u64) * 16 * (size_t)n_ticks * (size_t)stride));
+#endif
   if (sim->graph) { cudaGraphExecDestroy(sim->graph); sim->graph = nullptr; }  // kernel parameters changed
   return SQ_OK;
 }
@@ -1766,6 +1805,15 @@ int sq_get_timeline(SqSim* sim, int32_t* n_ticks, int32_t* stride, uint64_t* out
   SQ_CUDA_TRY(cudaMemcpyAsync(out, sim->st.timeline, bytes, cudaMemcpyDeviceToHost, sim->stream));
   return sq_sync(sim);
 }
+
+#ifdef SQ_TICK_PHASES
+int sq_get_phases(SqSim* sim, uint64_t* out) {   // experiment build only: [tl_ticks][tl_stride][16]
+  if (!sim || !sim->st.phases || !out) return sq::set_error(SQ_ERR_ARG, "sq_get_phases: not enabled");
+  SQ_CUDA_TRY(cudaMemcpyAsync(out, sim->st.phases, sizeof(u64) * 16 * (size_t)sim->st.tl_ticks * (size_t)sim->st.tl_stride,
+                              cudaMemcpyDeviceToHost, sim->stream));
+  return sq_sync(sim);
+}
+#endif
 
 int sq_set_shelter_after(SqSim* sim, int32_t seconds) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_set_shelter_after: null sim");
