@@ -561,8 +561,14 @@ struct VSetT {
   int st[G], ep[G], dl[G], en[G];
 };
 typedef VSetT<GATHER> VSet;
-constexpr int GATHER_WIDE = 8;   // vehicles gathered together beyond the first set of a window (long windows: source
-                                 // links release up to 100 vehicles a tick, each set costs four dependent round trips)
+#ifndef SQ_GATHER_WIDE
+#define SQ_GATHER_WIDE 4
+#endif
+// Vehicles gathered together beyond the first set of a window (long windows: source links release up to 100 vehicles a
+// tick).  Measured on config 4 (profiles/r2q_tick_timeline.jsonl): 8 instead of 4 halves the dependent round trips of a
+// long window but runs slower in the congested hours (node phase 23.8 vs 22.0 us at tick 7000): the unrolled admit loop
+// is what a long window costs, not the gather.
+constexpr int GATHER_WIDE = SQ_GATHER_WIDE;
 
 template <int G>
 __device__ __forceinline__ void lvl_ring(const TickState& s, const Win& w, int i0, VSetT<G>& g) {
