@@ -27,5 +27,8 @@ BATCH=2368 timeout 900 ncu --set full --clock-control none --import-source on -k
   -o $O/sssp_warp_full -f python tools/sssp_prof.py > $O/ncu_sssp_full.log 2>&1
 TICKS=2600 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_node_phase -s 2500 -c 1 \
   -o $O/tick_node_full -f python tools/tick_prof.py > $O/ncu_tick_full.log 2>&1
+for T0 in 3000 7000; do T0=$T0 timeout 300 python tools/tick_timeline.py > $O/timeline_c4_$T0.json 2> $O/timeline_c4_$T0.err; done
+CASE=c2 T0=800 timeout 300 python tools/tick_timeline.py > $O/timeline_c2.json 2> $O/timeline_c2.err
+CASE=c3 T0=3000 timeout 300 python tools/tick_timeline.py > $O/timeline_c3.json 2> $O/timeline_c3.err
 ls -la $O
 tail -3 $O/pytest_gpu.log; tail -2 $O/smoke.log; head -c 3000 $O/bench.json
