@@ -604,30 +604,36 @@ def main():
     if compact:
         g.set_parent_format(0)
     # ---- e2e through the host-buffer C ABI: host origins in, host next-hop tables out ---------------------------------
-    # `e2e` = sp_sssp_batch_codes: the whole batch, predecessors as one-byte in-edge codes in page-locked host memory
-    # (50 KB per tree; a consumer holding the graph follows the codes directly, sp_decode_parents_host gives vertex ids).
+    # `e2e` = sp_sssp_batch_codes4: the whole batch, predecessors as four-bit in-edge codes in page-locked host memory
+    # (25 KB per tree; a consumer holding the graph follows the codes directly, sp_decode_parents_host4 gives vertex ids).
+    # `e2e_codes8` = sp_sssp_batch_codes, the one-byte form (50 KB per tree; any in-degree up to 254).
     # `e2e_full` = sp_sssp_batch: f64 distances + int32 predecessors (602 KB per tree: PCIe-bound), 4,096 trees.
-    e2e = e2e_full = None
+    e2e = e2e_full = e2e_codes8 = None
     if rank == 0 or world > 1:
         oh = origins_for(rank, B, V, step=7)
-        ch = spi.pinned_empty((B, V), np.uint8)
-        g.sssp_batch_codes(oh[:2368], out=(None, ch[:2368]))
-        g.sssp_batch_codes(oh, out=(None, ch))
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
         reps = 2
-        for _ in range(reps):
-            g.sssp_batch_codes(oh, out=(None, ch))
-        wall = time.perf_counter() - t0
-        if world > 1:
-            tw = torch.tensor([wall], device="cuda")
-            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
-            wall = float(tw.item())
-        e2e = {"value": world * B * reps / wall, "unit": "trees/s", "h2d_bytes_per_step": int(oh.nbytes),
-               "d2h_bytes_per_step": int(ch.nbytes), "trees_per_call": B,
-               "call": "sp_sssp_batch_codes (host origins in, one-byte predecessor codes in page-locked host memory out)"}
-        del ch
+
+        def timed_codes(call, width, what):
+            ch = spi.pinned_empty((B, width), np.uint8)
+            call(oh[:2368], out=(None, ch[:2368]))
+            call(oh, out=(None, ch))
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                call(oh, out=(None, ch))
+            wall = time.perf_counter() - t0
+            if world > 1:
+                tw = torch.tensor([wall], device="cuda")
+                dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+                wall = float(tw.item())
+            return {"value": world * B * reps / wall, "unit": "trees/s", "h2d_bytes_per_step": int(oh.nbytes),
+                    "d2h_bytes_per_step": int(ch.nbytes), "trees_per_call": B, "call": what}
+
+        e2e = timed_codes(g.sssp_batch_codes4, (V + 1) // 2,
+                          "sp_sssp_batch_codes4 (host origins in, four-bit predecessor codes in page-locked host memory out)")
+        e2e_codes8 = timed_codes(g.sssp_batch_codes, V,
+                                 "sp_sssp_batch_codes (host origins in, one-byte predecessor codes in page-locked host memory out)")
         eb = min(B, 4096)
         dh, ph = spi.pinned_empty((eb, V), np.float64), spi.pinned_empty((eb, V), np.int32)
         g.sssp_batch(oh[:256], out=(dh[:256], ph[:256]))
@@ -682,8 +688,9 @@ def main():
                            "gather": (f"one-byte next-hop tables in {n_chunks} chunks ({gather_kind}), overlapped with the next "
                                       f"chunk's trees") if gather_kind else None,
                            "gather_verified": gather_ok,
-                           "e2e_call": "sp_sssp_batch_codes: host origins in, one-byte predecessor codes (50 KB per tree) in "
-                                       "page-locked host memory out; e2e_full = f64 distances + int32 predecessors",
+                           "e2e_call": "sp_sssp_batch_codes4: host origins in, four-bit predecessor codes (25 KB per tree) in "
+                                       "page-locked host memory out; e2e_codes8 = one-byte codes; e2e_full = f64 distances + "
+                                       "int32 predecessors",
                            "host_numa": numa_note,
                            "l2": f"outputs of one step ({(12 * B * V) >> 20} MiB) exceed L2; no flush needed",
                            "metric_of": "BASELINE.json: agent-steps/s per sim tick (object 'tick') + reroute SSSP trees/s (top level)"},
@@ -692,7 +699,7 @@ def main():
                              "traffic_source": tr["source"] if tr else None,
                              "kernel": "tree kernel + predecessor / un-interleave pass, both inside kernel_ms", "kernel_ms": kernel_ms,
                              "bytes_per_tree": bytes_per_tree, "peak_source": peak_src},
-                "e2e": e2e, "e2e_full": e2e_full, "e2e_routes": e2e_routes, "gpu_launches": int(launches), "clocks": clocks}
+                "e2e": e2e, "e2e_codes8": e2e_codes8, "e2e_full": e2e_full, "e2e_routes": e2e_routes, "gpu_launches": int(launches), "clocks": clocks}
 
     # ---- HP-1 + CPU baselines: single GPU, rank 0 ----------------------------------------------------------------
     if rank == 0 and world == 1:

@@ -81,6 +81,12 @@ int sp_sssp_batch_ex(Graph* graph, const int* origins, int n, double* dist_out, 
  * of 602 KB, so the call is bound by the tree kernel, not by the link. */
 int sp_sssp_batch_codes(Graph* graph, const int* origins, int n, double* dist_out, unsigned char* codes_out, int reverse);
 int sp_decode_parents_host(Graph* graph, const unsigned char* codes, int n, int* parent_out, int reverse);
+/* The same with two vertices per byte: codes_out[n][(V + 1) / 2], low nibble = even vertex, 15 = none.  For graphs whose
+ * largest in-degree (out-degree for reverse trees) is at most 15 -- road networks -- else SQ_ERR_LIMIT.  25 KB per tree on
+ * config 5: with eight GPUs behind one host the byte form is bound by what the host can take in (83 GB/s on the
+ * measured box), this form is not. */
+int sp_sssp_batch_codes4(Graph* graph, const int* origins, int n, double* dist_out, unsigned char* codes_out, int reverse);
+int sp_decode_parents_host4(Graph* graph, const unsigned char* codes, int n, int* parent_out, int reverse);
 
 /* Agent.get_path for a batch of agents (queue_class.py:491-512 / model/queue_class.py:491-512: g.dijkstra(origin,
  * destin), sp.distance(destin), sp.route(destin)): for every pair k the distance origins[k] -> dests[k] (DBL_MAX

@@ -48,6 +48,8 @@ def _declare(L):
     L.sp_sssp_batch_ex.restype = ci; L.sp_sssp_batch_ex.argtypes = [vp, vp, ci, vp, vp, ci]
     L.sp_sssp_batch_codes.restype = ci; L.sp_sssp_batch_codes.argtypes = [vp, vp, ci, vp, vp, ci]
     L.sp_decode_parents_host.restype = ci; L.sp_decode_parents_host.argtypes = [vp, vp, ci, vp, ci]
+    L.sp_sssp_batch_codes4.restype = ci; L.sp_sssp_batch_codes4.argtypes = [vp, vp, ci, vp, vp, ci]
+    L.sp_decode_parents_host4.restype = ci; L.sp_decode_parents_host4.argtypes = [vp, vp, ci, vp, ci]
     L.sp_route_batch.restype = ci; L.sp_route_batch.argtypes = [vp, vp, vp, ci, vp, vp, vp]
     L.sp_route_pool.restype = vp; L.sp_route_pool.argtypes = [vp]
     L.sp_sssp_batch_device.restype = ci; L.sp_sssp_batch_device.argtypes = [vp, vp, ci, vp, vp, vp]

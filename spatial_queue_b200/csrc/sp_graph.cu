@@ -1050,6 +1050,20 @@ __global__ void __launch_bounds__(256) decode_parents_kernel(int V, int n_trees,
   }
 }
 
+// One-byte codes -> two vertices per byte (low nibble = even vertex), 255 -> 15.  The caller has checked that every
+// code is below 15 (largest in-degree <= 15).  One thread per output byte.
+__global__ void __launch_bounds__(256) pack_codes4_kernel(int V, int n_trees, const unsigned char* __restrict__ codes,
+                                                          unsigned char* __restrict__ packed) {
+  const size_t vh = ((size_t)V + 1) / 2;
+  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= vh * (size_t)n_trees) return;
+  const size_t tree = i / vh, b = i - tree * vh;
+  const unsigned char* row = codes + tree * (size_t)V;
+  const unsigned lo = row[2 * b];
+  const unsigned hi = 2 * b + 1 < (size_t)V ? row[2 * b + 1] : 255u;
+  packed[i] = (unsigned char)((lo >= 15u ? 15u : lo) | ((hi >= 15u ? 15u : hi) << 4));
+}
+
 // Device-side weight refresh: weights[i] belongs to edge i of the insertion log; NaN keeps the current weight.
 // Every copy of the weight (CSR/CSC records, ELL + overflow records, slot-major arrays) is rewritten in place.
 struct WeightSlots {
@@ -1132,6 +1146,8 @@ struct SqGraph {
   int* d_wslots = nullptr;     // 4 x n_log: where the weight of edge i lives (scatter_weights_kernel)
   // sp_set_weights_device leaves the newest weights on the device only (no host round trip inside a simulation's
   // refresh): d_wlog is the edge log's weight column while dev_leads; every host reader / editor of the log pulls first
+  unsigned char* d_pack_buf = nullptr;   // sp_sssp_batch_codes4: two chunks of packed codes
+  size_t pack_buf_bytes = 0;
   double* d_wlog = nullptr;
   size_t wlog_cap = 0;
   bool dev_leads = false;
@@ -1278,6 +1294,7 @@ static void g_free_device(SqGraph* g) {
   cudaFree(g->d_rs_v); cudaFree(g->d_rs_w); g->d_rs_v = nullptr; g->d_rs_w = nullptr;
   cudaFree(g->d_fs_v); cudaFree(g->d_fs_w); g->d_fs_v = nullptr; g->d_fs_w = nullptr;
   cudaFree(g->d_wslots); g->d_wslots = nullptr; g->wslots_n = 0;
+  cudaFree(g->d_pack_buf); g->d_pack_buf = nullptr; g->pack_buf_bytes = 0;
   cudaFree(g->d_wlog); g->d_wlog = nullptr; g->wlog_cap = 0; g->dev_leads = false;
   g->d_row_ptr = g->d_rrow_ptr = nullptr; g->d_adj = g->d_radj = nullptr;
   g->d_ell = g->d_rell = g->d_ovf = g->d_rovf = nullptr;
@@ -2532,6 +2549,14 @@ static int g_batch_host(SqGraph* g, const int* origins, int n, double* dist_out,
   }
   SQ_CUDA_TRY(cudaMemcpy(g->d_origins, origins, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
   const size_t psize = codes ? 1 : sizeof(int);
+  const size_t vh = (V + 1) / 2;   // bytes of a tree's packed codes (codes == 2)
+  if (codes == 2) {
+    size_t worst = 0;
+    const std::vector<int>& rp = reverse ? g->h_rp : g->h_rrp;
+    for (size_t v = 0; v < V; ++v) worst = std::max(worst, (size_t)(rp[v + 1] - rp[v]));
+    if (worst > 15)
+      return sq::set_error(SQ_ERR_LIMIT, "four-bit predecessor codes need in-degree <= 15 (found %zu); use sp_sssp_batch_codes", worst);
+  }
   const size_t per_tree = V * ((dist_out ? sizeof(u64) : 0) + (parent_out ? psize : 0));
   size_t chunk = std::max<size_t>(1, std::min<size_t>((size_t)n, ((size_t)1 << 29) / std::max<size_t>(per_tree, 1)));
   // at least four chunks on large batches (the copy of one hides behind the trees of the next), but never so small that
@@ -2549,6 +2574,11 @@ static int g_batch_host(SqGraph* g, const int* origins, int n, double* dist_out,
     SQ_CUDA_TRY(cudaMalloc(&g->d_parent_buf, sizeof(int) * pelems));
     g->parent_buf_elems = pelems;
   }
+  if (codes == 2 && g->pack_buf_bytes < 2 * chunk * vh) {
+    cudaFree(g->d_pack_buf); g->d_pack_buf = nullptr;
+    SQ_CUDA_TRY(cudaMalloc(&g->d_pack_buf, 2 * chunk * vh));
+    g->pack_buf_bytes = 2 * chunk * vh;
+  }
   if (int rc = g_ensure_streams(g)) return rc;
   const bool pinned = is_pinned_host(dist_out) && is_pinned_host(parent_out);
   int k = 0;
@@ -2563,12 +2593,23 @@ static int g_batch_host(SqGraph* g, const int* origins, int n, double* dist_out,
     const int rc_run = g_run_batch_device(g, g->d_origins + off, m, dbuf, reinterpret_cast<int*>(pbuf), g->s_compute, reverse != 0);
     g->parent_format = fmt;
     if (rc_run) return rc_run;
+    unsigned char* qbuf = nullptr;
+    if (codes == 2) {
+      qbuf = g->d_pack_buf + (size_t)b * chunk * vh;
+      const size_t total = vh * (size_t)m;
+      pack_codes4_kernel<<<(unsigned)((total + 255) / 256), 256, 0, g->s_compute>>>((int)V, m, pbuf, qbuf);
+      sq::count_launch();
+      SQ_CUDA_TRY(cudaGetLastError());
+    }
     SQ_CUDA_TRY(cudaEventRecord(g->ev_done[b], g->s_compute));
     SQ_CUDA_TRY(cudaStreamWaitEvent(g->s_copy, g->ev_done[b], 0));
     if (!pinned) SQ_CUDA_TRY(cudaStreamSynchronize(g->s_compute));  // pageable copies block the host anyway
     if (dist_out)
       SQ_CUDA_TRY(cudaMemcpyAsync(dist_out + off * V, dbuf, sizeof(u64) * (size_t)m * V, cudaMemcpyDeviceToHost, g->s_copy));
-    if (parent_out)
+    if (parent_out && codes == 2)
+      SQ_CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<unsigned char*>(parent_out) + off * vh, qbuf, (size_t)m * vh,
+                                  cudaMemcpyDeviceToHost, g->s_copy));
+    else if (parent_out)
       SQ_CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<unsigned char*>(parent_out) + off * V * psize, pbuf, psize * (size_t)m * V,
                                   cudaMemcpyDeviceToHost, g->s_copy));
     SQ_CUDA_TRY(cudaEventRecord(g->ev_copied[b], g->s_copy));
@@ -2586,6 +2627,29 @@ int sp_sssp_batch_ex(Graph* g, const int* origins, int n, double* dist_out, int*
 int sp_sssp_batch_codes(Graph* g, const int* origins, int n, double* dist_out, unsigned char* codes_out, int reverse) {
   if (!codes_out) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch_codes: null codes_out");
   return g_batch_host(g, origins, n, dist_out, codes_out, reverse, 1);
+}
+
+int sp_sssp_batch_codes4(Graph* g, const int* origins, int n, double* dist_out, unsigned char* codes_out, int reverse) {
+  if (!codes_out) return sq::set_error(SQ_ERR_ARG, "sp_sssp_batch_codes4: null codes_out");
+  return g_batch_host(g, origins, n, dist_out, codes_out, reverse, 2);
+}
+
+// Four-bit codes -> vertex ids on the host: codes[n][(V + 1) / 2], low nibble = even vertex, 15 = none.
+int sp_decode_parents_host4(Graph* g, const unsigned char* codes, int n, int* parent_out, int reverse) {
+  if (!g || !codes || !parent_out) return sq::set_error(SQ_ERR_ARG, "sp_decode_parents_host4: null argument");
+  if (int rc = g_build_and_upload(g)) return rc;
+  const std::vector<int>& rp = reverse ? g->h_rp : g->h_rrp;
+  const std::vector<EdgeRec>& adj = reverse ? g->h_adj : g->h_radj;
+  const size_t V = (size_t)g->V, vh = (V + 1) / 2;
+  for (int i = 0; i < n; ++i) {
+    const unsigned char* c = codes + (size_t)i * vh;
+    int* p = parent_out + (size_t)i * V;
+    for (size_t v = 0; v < V; ++v) {
+      const int code = (c[v >> 1] >> ((v & 1) * 4)) & 15;
+      p[v] = (code == 15 || rp[v] + code >= rp[v + 1]) ? -1 : adj[(size_t)rp[v] + code].v;
+    }
+  }
+  return SQ_OK;
 }
 
 // One-byte in-edge codes -> vertex ids on the host (what sp_decode_parents_device does on the GPU): code c of vertex v

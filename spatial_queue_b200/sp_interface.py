@@ -183,6 +183,28 @@ class Graph:
                                         c.ctypes.data, 1 if reverse else 0), "sp_sssp_batch_codes")
         return d, c
 
+    def sssp_batch_codes4(self, origins, want_dist=False, out=None, reverse=False):
+        """sssp_batch_codes with two vertices per byte (sp_sssp_batch_codes4): codes u8[n, (V + 1) // 2], low nibble = even
+        vertex, 15 = none; graphs with in-degree <= 15 only."""
+        o = np.ascontiguousarray(origins, dtype=np.int32)
+        V = self.nvertices
+        if out is not None:
+            d, c = out
+        else:
+            d = pinned_empty((len(o), V), np.float64) if want_dist else None
+            c = pinned_empty((len(o), (V + 1) // 2), np.uint8)
+        check(lib().sp_sssp_batch_codes4(self._h, o.ctypes.data, len(o), d.ctypes.data if d is not None else None,
+                                         c.ctypes.data, 1 if reverse else 0), "sp_sssp_batch_codes4")
+        return d, c
+
+    def decode_parents_host4(self, codes, reverse=False):
+        """codes u8[n, (V + 1) // 2] -> parent i32[n, V] on the host (sp_decode_parents_host4)."""
+        c = np.ascontiguousarray(codes, dtype=np.uint8)
+        p = np.empty((c.shape[0], self.nvertices), np.int32)
+        check(lib().sp_decode_parents_host4(self._h, c.ctypes.data, int(c.shape[0]), p.ctypes.data, 1 if reverse else 0),
+              "sp_decode_parents_host4")
+        return p
+
     def decode_parents_host(self, codes, reverse=False):
         """codes u8[n,V] -> parent i32[n,V] on the host (sp_decode_parents_host)."""
         c = np.ascontiguousarray(codes, dtype=np.uint8)

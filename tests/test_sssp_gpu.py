@@ -582,6 +582,33 @@ def test_host_batch_with_one_byte_codes_decodes_to_the_int32_tables(spi, reverse
     g.free()
 
 
+@pytest.mark.parametrize("reverse", [False, True])
+def test_host_batch_with_four_bit_codes(spi, reverse):
+    """sp_sssp_batch_codes4 (two vertices per byte) + sp_decode_parents_host4 == sp_sssp_batch's int32 table on a road-like
+    graph (odd vertex count, several chunks, invalid origins); a graph with an in-degree above 15 is refused."""
+    s, e, w = grid_graph(53, seed=11)
+    V = 53 * 53
+    g = spi.from_arrays(s, e, np.round(w) + 1.0, max_vertex_id=V - 1)      # many exact ties
+    rng = np.random.default_rng(43)
+    origins = np.concatenate([rng.integers(0, V, 5000), [-1, V + 3]]).astype(np.int32)
+    d0, p0 = g.sssp_batch(origins, reverse=reverse)
+    d1, c4 = g.sssp_batch_codes4(origins, want_dist=True, reverse=reverse)
+    assert c4.shape == (len(origins), (V + 1) // 2)
+    assert d1.tobytes() == d0.tobytes()
+    assert (g.decode_parents_host4(c4, reverse=reverse) == p0).all()
+    _, c1 = g.sssp_batch_codes(origins, reverse=reverse)
+    lo = np.minimum(c1[:, 0::2], 15)
+    hi = np.minimum(np.concatenate([c1[:, 1::2], np.full((len(origins), (V + 1) // 2 - V // 2), 255, np.uint8)], axis=1), 15)
+    assert (c4 == (lo | (hi << 4))).all()
+    g.free()
+    hub_s = np.arange(1, 18, dtype=np.int32)
+    g = spi.from_arrays(np.concatenate([hub_s, [0]]).astype(np.int32), np.concatenate([np.zeros(17, np.int32), [1]]).astype(np.int32),
+                        np.ones(18), max_vertex_id=17)
+    with pytest.raises(Exception, match="in-degree <= 15"):
+        g.sssp_batch_codes4(np.array([1], np.int32), reverse=False)
+    g.free()
+
+
 def test_lone_trees_with_shared_memory_rows_equal_global_rows(spi):
     """Auto mode on a handful of trees (the device router's reverse tree per destination): sssp_ell_kernel keeps the
     distance row in shared memory when the graph fits (config 4's 25,281 vertices do).  Same tables with the switch off,
