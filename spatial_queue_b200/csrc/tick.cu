@@ -1028,29 +1028,69 @@ __global__ void __launch_bounds__(128) k_reroute_all(const TickState s) {
 //   regular stagger slot  t % freq  == key % freq   -> get_path (+ the detour test in reroute_agent);
 //   closure stagger slot  t % cfreq == key % cfreq  -> get_path again if the agent's next link is closed.
 // An agent due in both slots is handled by its closure-slot thread, in the reference's order.
+// A thread serves (at most) one agent of the closure slot and one of the regular slot; they are different agents, so
+// the words the two decisions start from are read together, level by level (bucket bounds -> agent ids -> records ->
+// link words), and reroute_agent_with() gets what it needs in registers: ten dependent round trips became six.
+__device__ __forceinline__ void reroute_agent_with(const TickState& s, int a, int t, const int4& rec, int dslot, int node, int e) {
+  const int st = rec.w & 0xff;
+  if (st != SQ_UNLOADED && st != SQ_ENROUTE) return;
+  const size_t idx = tbl_index(s, e, dslot, node);
+  const double d = s.dist_tbl[idx];
+  const int nl = s.next_tbl[idx];
+  double prev = 0.0;
+  if (s.a_rdist) prev = s.a_rdist[a];
+  if (d > 1e8) return;
+  s.ag[a].epoch = e;
+  s.ag[a].route_len = -1;
+  s.ag[a].rec.x = nl;
+  if (s.a_rdist) {
+    // previous_distance = agent.route_distance; get_path; shelter_a2 if the trip more than doubled
+    // (model/dta_meso_butte.py:195-198, 201-204)
+    s.a_rdist[a] = d;
+    if (s.detour_factor > 0.0 && st == SQ_ENROUTE && d > prev * s.detour_factor) {
+      s.ag[a].rec.w = (rec.w & ~0xff) | SQ_SHELTER_A2;
+      s.a_arrive[a] = t;
+      atomicAdd(&s.l_tomb[rec.y], 1);      // the link phase of this tick takes the vehicle off the link
+    }
+  }
+}
+
 __global__ void __launch_bounds__(128) k_reroute_rules(const TickState s) {
   const int i = blockIdx.x * 128 + threadIdx.x;
   pdl_wait();
   if (s.pdl_early) pdl_release();
   const int t = *s.tick_link;
+  const int e = *s.cur_epoch;
   if (t <= 0) return;
-  if (s.cfreq > 0) {
-    const int b2 = t % s.cfreq;
-    const int k2 = s.cbucket_ptr[b2] + i;
-    if (k2 < s.cbucket_ptr[b2 + 1]) {
-      const int a = s.cbucket_agents[k2];
-      if (s.a_rslot[a] == t % s.freq) reroute_agent(s, a, t);
-      const int4 rec = s.ag[a].rec;
-      const int st = rec.w & 0xff;
-      if ((st == SQ_UNLOADED || st == SQ_ENROUTE) && rec.x >= 0 && s.l_closed[rec.x]) reroute_agent(s, a, t);
-    }
-  }
+  // level 2: bucket bounds
   const int b = t % s.freq;
+  const int b2 = s.cfreq > 0 ? t % s.cfreq : 0;
   const int k = s.bucket_ptr[b] + i;
-  if (k < s.bucket_ptr[b + 1]) {
-    const int a = s.bucket_agents[k];
-    if (!(s.cfreq > 0 && s.a_cslot[a] == t % s.cfreq)) reroute_agent(s, a, t);
+  const bool have = k < s.bucket_ptr[b + 1];
+  int k2 = 0;
+  bool have2 = false;
+  if (s.cfreq > 0) { k2 = s.cbucket_ptr[b2] + i; have2 = k2 < s.cbucket_ptr[b2 + 1]; }
+  // level 3: agent ids
+  const int a = have ? s.bucket_agents[k] : 0;
+  const int a2 = have2 ? s.cbucket_agents[k2] : 0;
+  // level 4: records
+  int4 rec = make_int4(-1, 0, 0, SQ_ARRIVE), rec2 = rec;
+  int ds = 0, ds2 = 0, cslot = -1, rslot2 = -1;
+  if (have) { rec = s.ag[a].rec; ds = s.ag[a].dslot; if (s.cfreq > 0) cslot = s.a_cslot[a]; }
+  if (have2) { rec2 = s.ag[a2].rec; ds2 = s.ag[a2].dslot; rslot2 = s.a_rslot[a2]; }
+  // level 5: link words
+  const int node = have ? s.l_end[rec.y] : 0;
+  const int node2 = have2 ? s.l_end[rec2.y] : 0;
+  if (have2) {
+    if (rslot2 == b) {
+      // due in both slots: the regular reroute first, then the closure test on the link it chose
+      reroute_agent_with(s, a2, t, rec2, ds2, node2, e);
+      rec2 = s.ag[a2].rec;
+    }
+    const int st2 = rec2.w & 0xff;
+    if ((st2 == SQ_UNLOADED || st2 == SQ_ENROUTE) && rec2.x >= 0 && s.l_closed[rec2.x]) reroute_agent_with(s, a2, t, rec2, ds2, node2, e);
   }
+  if (have && !(s.cfreq > 0 && cslot == b2)) reroute_agent_with(s, a, t, rec, ds, node, e);
 }
 
 // Before table slot `slot` is overwritten: agents that still follow it (their reroutes kept failing) get
