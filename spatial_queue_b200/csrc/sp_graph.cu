@@ -1151,7 +1151,7 @@ struct SqGraph {
   double* d_wlog = nullptr;
   size_t wlog_cap = 0;
   bool dev_leads = false;
-  cudaStream_t lead_stream = nullptr;
+  cudaEvent_t ev_wlog = nullptr;   // recorded behind the last device-side refresh (outlives the caller's stream)
   size_t wslots_n = 0;
   int2* d_q2scratch = nullptr;
   int* d_q2v = nullptr;
@@ -1264,11 +1264,11 @@ __global__ void __launch_bounds__(128) route_write_kernel(const int* __restrict_
 // The device holds newer weights than the host log (sp_set_weights_device): bring the log and the host CSR up to date.
 static int g_pull_host_log(SqGraph* g) {
   if (!g->dev_leads) return SQ_OK;
-  g->dev_leads = false;
   const size_t n = g->ew.size();
-  if (n == 0) return SQ_OK;
-  SQ_CUDA_TRY(cudaStreamSynchronize(g->lead_stream));
+  if (n == 0) { g->dev_leads = false; return SQ_OK; }
+  SQ_CUDA_TRY(cudaEventSynchronize(g->ev_wlog));
   SQ_CUDA_TRY(cudaMemcpy(g->ew.data(), g->d_wlog, sizeof(double) * n, cudaMemcpyDeviceToHost));
+  g->dev_leads = false;
   for (size_t i = 0; i < n && i < g->edge_slot.size(); ++i) {
     const int a = g->edge_slot[i];
     if (a >= 0) { g->h_adj[a].w = g->ew[i]; g->h_radj[g->edge_rslot[i]].w = g->ew[i]; }
@@ -2277,6 +2277,7 @@ int sp_nedges_logged(Graph* g) { return g ? (int)g->es.size() : 0; }
 void sp_free_graph(Graph* g) {
   if (!g) return;
   g_free_device(g);
+  if (g->ev_wlog) cudaEventDestroy(g->ev_wlog);
   cudaFree(g->d_counter); cudaFree(g->d_stats); cudaFree(g->d_dist_scratch); cudaFree(g->d_qscratch);
   cudaFree(g->d_origins); cudaFree(g->d_dist_buf); cudaFree(g->d_parent_buf);
   cudaFree(g->d_q2scratch); cudaFree(g->d_q2v); cudaFree(g->d_dist_tmp); cudaFree(g->d_fail); cudaFree(g->d_wfar);
@@ -2409,8 +2410,9 @@ int sp_set_weights_device(Graph* g, const double* weights_dev, int nedges, void*
   // The host log (what update_edge / writegraph / the next structural rebuild start from) is not touched here: a
   // device-to-host copy and a stream synchronisation per refresh leave the GPU idle while the host catches up, every
   // weight_freq ticks of a simulation.  The log catches up when somebody on the host looks (g_pull_host_log).
+  if (!g->ev_wlog) SQ_CUDA_TRY(cudaEventCreateWithFlags(&g->ev_wlog, cudaEventDisableTiming));
+  SQ_CUDA_TRY(cudaEventRecord(g->ev_wlog, st));
   g->dev_leads = true;
-  g->lead_stream = st;
   return SQ_OK;
 }
 

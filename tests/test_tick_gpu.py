@@ -224,6 +224,36 @@ def test_town_device_router_on_free_flow_weights_equals_fixed_routes():
     dev.close(); orc.close()
 
 
+def test_routing_graph_outlives_the_simulation_with_its_refreshed_weights():
+    """The router leaves the newest edge weights on the device (no host round trip inside a refresh); the host's edge log
+    catches up when somebody looks -- here after the simulation and its stream are gone: update_edge must start from the
+    weights of the last refresh, not from the ones the graph was created with."""
+    from oracle import sssp as osssp
+    from spatial_queue_b200 import synth
+    from spatial_queue_b200.tick import DeviceSim
+    routed = _town(device_routes=True)
+    g = synth.routing_graph(routed)
+    dev = DeviceSim(routed, seed=4, routes_from_router=True)
+    dev.attach_router(g, routed, reroute_freq=60, weight_freq=100)
+    dev.run(0, 300); dev.sync()                       # refreshes at 0, 100, 200
+    N = len(routed.node_key)
+    w300 = np.asarray(dev.link_weights())[N:]         # what the refresh of tick 300 computes (state after tick 299)
+    assert not np.isnan(w300).any()
+    dev.run(300, 50); dev.sync()                      # refresh at 300, then ticks that change the queues again
+    s, e = np.asarray(routed.edge_start), np.asarray(routed.edge_end)
+    w_ref = np.asarray(routed.edge_fft, np.float64)
+    assert (w300 != w_ref).any(), "the run never changed a weight: the test would prove nothing"
+    origins = np.array([0, N // 3, N - 1], np.int32)
+    dev.close()                                       # the stream the refreshes ran on is gone
+    g.update_edge(int(s[0]), int(e[0]), 123.5)        # first host edit after the device-side refreshes
+    d_new, _ = g.sssp_batch(origins)
+    w_now = w300.copy()
+    w_now[0] = 123.5
+    d_orc = osssp.OracleGraph(s, e, w_now, max_vertex_id=N - 1).sssp_batch(origins)[0]
+    assert d_new.tobytes() == d_orc.tobytes()
+    g.free()
+
+
 def test_stop_agents_matches_oracle():
     """sq_stop_agents (a driver rule shelters enroute agents between ticks: they leave their link's queue / run list
     at once, model/dta_meso_butte.py:256-263) against the oracle's list filtering: random agents anywhere in the
