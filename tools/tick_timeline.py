@@ -21,6 +21,8 @@ name = os.environ.get("CASE", "c4")
 case = {c["key"]: c for c in bench.tick_cases(args)}[{"c4": "tick", "c2": "tick_c2", "c3": "tick_c3"}[name]]
 flat = case["flat"]()
 sim = bench.make_tick_sim(flat, case, torch.cuda.current_stream().cuda_stream)
+if os.environ.get("DELTA") and getattr(sim, "_router_graph", None) is not None:
+    sim._router_graph.set_tuning(delta_factor=float(os.environ["DELTA"]))      # bucket width of the router's trees
 sim.run(0, T0)
 sim.sync()
 sim.enable_timeline(T0, W)
