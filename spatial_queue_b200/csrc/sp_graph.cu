@@ -574,7 +574,11 @@ __global__ void __launch_bounds__(NW * 32, SD ? 1 : 32 / NW) sssp_ell_kernel(con
       const HQ2 qin = Q(cur), qn = Q(nxt), qb = Q(bkt);
       const HQ2 qf = FARQ(fcur);
       const double T2 = advance(T, p.delta);
-      for (int base = warp * 16; base < n; base += NW * 16) {
+      // SD (a lone tree on an SM: most of the 32 warps have nothing to do in a round): eight vertices per warp instead
+      // of sixteen, so that a wavefront of ~150 vertices is spread over twice as many warps and the round's critical
+      // path -- one warp's instruction stream -- is half as long (J = 1: the j = 1 halves below compile away).
+      constexpr int J = SD ? 1 : 2;
+      for (int base = warp * 8 * J; base < n; base += NW * 8 * J) {
         int u[2], from[2];
         u64 dub[2];
         bool act[2];
@@ -582,7 +586,7 @@ __global__ void __launch_bounds__(NW * 32, SD ? 1 : 32 / NW) sssp_ell_kernel(con
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           const int idx = base + j * 8 + grp;
-          act[j] = idx < n;
+          act[j] = j < J && idx < n;
           int2 ent = make_int2(0, -1);
           dub[j] = 0ull;
           if (act[j]) qin.get(idx, ent, dub[j]);
