@@ -626,9 +626,24 @@ __global__ void __launch_bounds__(NW * 32, SD ? 1 : 32 / NW) sssp_ell_kernel(con
           st_relax += has[j];
         }
         const int2 e0 = make_int2(rec[0].v, u[0]), e1 = make_int2(rec[1].v, u[1]);
-        cta_push2(imp[0] && nd[0] < T, e0, ndb[0], imp[1] && nd[1] < T, e1, ndb[1], qn, &s_cnt[nxt], gcap, &s_fail);
-        cta_push2(imp[0] && nd[0] >= T && nd[0] < T2, e0, ndb[0], imp[1] && nd[1] >= T && nd[1] < T2, e1, ndb[1], qb,
-                  &s_cnt[bkt], gcap, &s_fail);
+        if (SD) {
+          // one vertex per lane group: both queues' appends in one go, their two counters bumped by two lanes at once
+          const bool pn = imp[0] && nd[0] < T, pb = imp[0] && nd[0] >= T && nd[0] < T2;
+          const unsigned mn = __ballot_sync(0xffffffffu, pn), mb = __ballot_sync(0xffffffffu, pb);
+          if (mn | mb) {
+            int base = 0;
+            if (lane == 0 && mn) base = atomicAdd(&s_cnt[nxt], __popc(mn));
+            if (lane == 1 && mb) base = atomicAdd(&s_cnt[bkt], __popc(mb));
+            const int bn = __shfl_sync(0xffffffffu, base, 0), bb = __shfl_sync(0xffffffffu, base, 1);
+            const unsigned lt = sq::lanemask_lt();
+            if (pn) qn.put(bn + __popc(mn & lt), e0, ndb[0], gcap, &s_fail);
+            if (pb) qb.put(bb + __popc(mb & lt), e0, ndb[0], gcap, &s_fail);
+          }
+        } else {
+          cta_push2(imp[0] && nd[0] < T, e0, ndb[0], imp[1] && nd[1] < T, e1, ndb[1], qn, &s_cnt[nxt], gcap, &s_fail);
+          cta_push2(imp[0] && nd[0] >= T && nd[0] < T2, e0, ndb[0], imp[1] && nd[1] >= T && nd[1] < T2, e1, ndb[1], qb,
+                    &s_cnt[bkt], gcap, &s_fail);
+        }
         if (__any_sync(0xffffffffu, (imp[0] && nd[0] >= T2) || (imp[1] && nd[1] >= T2))) {
           const bool f0 = imp[0] && nd[0] >= T2, f1 = imp[1] && nd[1] >= T2;
           const unsigned m0 = __ballot_sync(0xffffffffu, f0), m1 = __ballot_sync(0xffffffffu, f1);
