@@ -522,7 +522,14 @@ __device__ __forceinline__ bool admit_one(const TickState& s, AdmitCtx& c, OutCa
   return false;
 }
 
-constexpr int GATHER = 4;   // vehicles whose records are gathered together (independent loads in flight)
+#ifndef SQ_GATHER
+#define SQ_GATHER 2
+#endif
+// Vehicles whose records are gathered together (independent loads in flight).  Measured on config 4 (node phase at ticks
+// 3000 / 7000, us; first set x later sets): 4x4 12.8 / 22.0, 3x3 13.2 / 21.8, 2x4 13.1 / 22.4, 2x2 11.7 / 21.2, 2x1
+// 11.7 / 24.0, 1x1 13.9 / 25.2.  Most windows hold one or two vehicles (whole lanes); the unrolled admit loop runs as
+// many iterations as the longest window of the warp has vehicles in the set, and its code size goes with the set.
+constexpr int GATHER = SQ_GATHER;
 
 // The window of an in-link the node model works on this tick: its first k queued vehicles.
 struct Win {
@@ -562,12 +569,11 @@ struct VSetT {
 };
 typedef VSetT<GATHER> VSet;
 #ifndef SQ_GATHER_WIDE
-#define SQ_GATHER_WIDE 4
+#define SQ_GATHER_WIDE 2
 #endif
 // Vehicles gathered together beyond the first set of a window (long windows: source links release up to 100 vehicles a
-// tick).  Measured on config 4 (profiles/r2q_tick_timeline.jsonl): 8 instead of 4 halves the dependent round trips of a
-// long window but runs slower in the congested hours (node phase 23.8 vs 22.0 us at tick 7000): the unrolled admit loop
-// is what a long window costs, not the gather.
+// tick).  8 instead of 4 halves the dependent round trips of a long window but runs slower in the congested hours (node
+// phase 23.8 vs 22.0 us at tick 7000): the unrolled admit loop is what a long window costs, not the gather.
 constexpr int GATHER_WIDE = SQ_GATHER_WIDE;
 
 template <int G>
