@@ -175,6 +175,13 @@ int sq_get_pair_moves(SqSim* sim, int64_t* out);
  * out is not null -- n_ticks x 2 (link phase, node phase) x stride pairs (entry, exit); unused slots are (0, 0). */
 int sq_enable_timeline(SqSim* sim, int32_t t0, int32_t n_ticks);
 int sq_get_timeline(SqSim* sim, int32_t* n_ticks, int32_t* stride, uint64_t* out);
+/* Test hook, host only (no GPU needed), no reference counterpart: the static node records the node kernel reads before
+ * its dependent chain -- per node 16 ints: the first eight in-links (-1 beyond the in-degree), then per in-link slot i the
+ * packed order in which the other slots are tried as the opposite approach when i is the primary link (bits 0..2 count,
+ * 3 bits per entry from bit 3; bit 30 = link i has no reverse link, bit 31 = ties / duplicate ranks: the kernel walks
+ * the angle table as queue_class.py:267-293 does; bit 29 of slot 0 = more than eight in-links).
+ * tests/test_node_records.py checks the lists against that walk for every candidate set. */
+int sq_build_node_records(const SqNetDesc* desc, int32_t* out);
 /* Per link: vehicles that sheltered on it (sum over a node's in-links = node.shelter_counts); per agent: the tick
  * at which it arrived or sheltered (-1 otherwise). */
 int sq_get_shelter_state(SqSim* sim, int32_t* link_shelter, int32_t* agent_stop_tick);

@@ -102,6 +102,7 @@ def _declare(L):
     L.sq_get_pair_moves.restype = ci; L.sq_get_pair_moves.argtypes = [vp, vp]
     L.sq_enable_timeline.restype = ci; L.sq_enable_timeline.argtypes = [vp, i32, i32]
     L.sq_get_timeline.restype = ci; L.sq_get_timeline.argtypes = [vp, vp, vp, vp]
+    L.sq_build_node_records.restype = ci; L.sq_build_node_records.argtypes = [vp, vp]
     L.sq_get_counters.restype = ci; L.sq_get_counters.argtypes = [vp, vp]
     L.sq_last_error.restype = C.c_char_p; L.sq_last_error.argtypes = []
     L.sq_kernel_launches.restype = C.c_longlong; L.sq_kernel_launches.argtypes = []

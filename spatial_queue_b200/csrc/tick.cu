@@ -1245,6 +1245,44 @@ static int dev_upload_ptr(SqSim* sim, const T** dst, const T* src, size_t n) {
   return dev_upload(sim, dst, v);
 }
 
+// The static node records (NodeRec): host-only, also exported for the CPU test that checks the opposite-approach lists
+// against the walk of pick_secondary for every candidate set (sq_build_node_records).
+static void build_node_records(const SqNetDesc* d, const std::vector<unsigned char>& out_local, std::vector<NodeRec>& nrec) {
+  const int N = d->n_nodes;
+  nrec.assign((size_t)N, NodeRec());
+  for (int n = 0; n < N; ++n) {
+    NodeRec& r = nrec[n];
+    const int ib = d->node_in_ptr[n], indeg = d->node_in_ptr[n + 1] - ib;
+    const int outdeg = d->node_out_ptr[n + 1] - d->node_out_ptr[n];
+    for (int i = 0; i < 8; ++i) { r.in[i] = i < indeg ? d->node_in_links[ib + i] : -1; r.sec[i] = NR_NONE; }
+    if (indeg > 8) { r.sec[0] |= NR_NODE_SLOW; continue; }
+    bool dup_rank = false;   // pick_secondary's priority walk skips links that share a rank: keep that path
+    if (d->node_type[n] == 2)
+      for (int a = 0; a < indeg; ++a)
+        for (int b = a + 1; b < indeg; ++b)
+          if (d->node_in_prio[ib + a] >= 0 && d->node_in_prio[ib + a] == d->node_in_prio[ib + b]) dup_rank = true;
+    const double* tb = d->turn_angle + d->node_turn_ptr[n];
+    for (int i = 0; i < indeg; ++i) {
+      const int rev = d->link_reverse[r.in[i]];
+      if (rev < 0) continue;                                    // NR_NONE
+      const int rcol = (int)out_local[rev];
+      int order[8], cnt = 0;
+      bool slow = dup_rank || rcol >= outdeg;
+      for (int j = 0; j < indeg; ++j) if (j != i) order[cnt++] = j;
+      auto ang = [&](int j) { return std::fabs(tb[(size_t)j * outdeg + rcol]); };
+      for (int a = 0; a < cnt && !slow; ++a) {
+        if (!(ang(order[a]) == ang(order[a]))) slow = true;     // NaN
+        for (int b = a + 1; b < cnt && !slow; ++b) if (ang(order[a]) == ang(order[b])) slow = true;
+      }
+      if (slow) { r.sec[i] = NR_SLOW; continue; }
+      std::sort(order, order + cnt, [&](int a, int b) { return ang(a) < ang(b); });
+      unsigned w = (unsigned)cnt;
+      for (int a = 0; a < cnt; ++a) w |= (unsigned)order[a] << (3 + 3 * a);
+      r.sec[i] = w;
+    }
+  }
+}
+
 static int sim_build(SqSim* sim, const SqNetDesc* d) {
   if (int rc = sq::require_device()) return rc;
   const int N = d->n_nodes, L = d->n_links, A = d->n_agents;
@@ -1365,38 +1403,8 @@ static int sim_build(SqSim* sim, const SqNetDesc* d) {
     if ((rc = dev_upload(sim, &s.l_win, win))) return rc;
   }
   {
-    std::vector<NodeRec> nrec((size_t)N);
-    for (int n = 0; n < N; ++n) {
-      NodeRec& r = nrec[n];
-      const int ib = d->node_in_ptr[n], indeg = d->node_in_ptr[n + 1] - ib;
-      const int outdeg = d->node_out_ptr[n + 1] - d->node_out_ptr[n];
-      for (int i = 0; i < 8; ++i) { r.in[i] = i < indeg ? d->node_in_links[ib + i] : -1; r.sec[i] = NR_NONE; }
-      if (indeg > 8) { r.sec[0] |= NR_NODE_SLOW; continue; }
-      bool dup_rank = false;   // pick_secondary's priority walk skips links that share a rank: keep that path
-      if (d->node_type[n] == 2)
-        for (int a = 0; a < indeg; ++a)
-          for (int b = a + 1; b < indeg; ++b)
-            if (d->node_in_prio[ib + a] >= 0 && d->node_in_prio[ib + a] == d->node_in_prio[ib + b]) dup_rank = true;
-      const double* tb = d->turn_angle + d->node_turn_ptr[n];
-      for (int i = 0; i < indeg; ++i) {
-        const int rev = d->link_reverse[r.in[i]];
-        if (rev < 0) continue;                                    // NR_NONE
-        const int rcol = (int)out_local[rev];
-        int order[8], cnt = 0;
-        bool slow = dup_rank || rcol >= outdeg;
-        for (int j = 0; j < indeg; ++j) if (j != i) order[cnt++] = j;
-        auto ang = [&](int j) { return std::fabs(tb[(size_t)j * outdeg + rcol]); };
-        for (int a = 0; a < cnt && !slow; ++a) {
-          if (!(ang(order[a]) == ang(order[a]))) slow = true;     // NaN
-          for (int b = a + 1; b < cnt && !slow; ++b) if (ang(order[a]) == ang(order[b])) slow = true;
-        }
-        if (slow) { r.sec[i] = NR_SLOW; continue; }
-        std::sort(order, order + cnt, [&](int a, int b) { return ang(a) < ang(b); });
-        unsigned w = (unsigned)cnt;
-        for (int a = 0; a < cnt; ++a) w |= (unsigned)order[a] << (3 + 3 * a);
-        r.sec[i] = w;
-      }
-    }
+    std::vector<NodeRec> nrec;
+    build_node_records(d, out_local, nrec);
     if ((rc = dev_upload(sim, &s.n_rec, nrec))) return rc;
   }
   if ((rc = dev_upload_rw(sim, &s.ring, ring))) return rc;
@@ -1866,6 +1874,19 @@ int sq_get_phases(SqSim* sim, uint64_t* out) {   // experiment build only: [tl_t
   return sq_sync(sim);
 }
 #endif
+
+int sq_build_node_records(const SqNetDesc* d, int32_t* out) {
+  if (!d || !out) return sq::set_error(SQ_ERR_ARG, "sq_build_node_records: null argument");
+  const int N = d->n_nodes, L = d->n_links;
+  std::vector<unsigned char> out_local((size_t)std::max(L, 1), 0);
+  for (int n = 0; n < N; ++n)
+    for (int j = d->node_out_ptr[n]; j < d->node_out_ptr[n + 1]; ++j) out_local[d->node_out_links[j]] = (unsigned char)(j - d->node_out_ptr[n]);
+  std::vector<NodeRec> nrec;
+  build_node_records(d, out_local, nrec);
+  for (int n = 0; n < N; ++n)
+    for (int i = 0; i < 8; ++i) { out[(size_t)n * 16 + i] = nrec[n].in[i]; out[(size_t)n * 16 + 8 + i] = (int32_t)nrec[n].sec[i]; }
+  return SQ_OK;
+}
 
 int sq_set_shelter_after(SqSim* sim, int32_t seconds) {
   if (!sim) return sq::set_error(SQ_ERR_ARG, "sq_set_shelter_after: null sim");
